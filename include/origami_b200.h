@@ -1,0 +1,178 @@
+/*
+ * origami_b200 -- C ABI of the B200 (sm_100a) page-geometry kernels.
+ *
+ * Drop-in boundary for the hot path of poke1024/origami.  The
+ * reference has no FFI for this path: it calls OpenCV / SciPy / scikit-image from Python.
+ * Each entry point below names the reference call site (paths relative to the reference
+ * root) whose arithmetic it reproduces bit for bit.  INTEGRATION.md shows the ctypes
+ * binding a maintainer adds on the reference side.
+ *
+ * Conventions
+ *  - every pointer is a DEVICE pointer unless the parameter is documented as host;
+ *  - the caller owns and allocates every buffer; the library never allocates device
+ *    memory, never frees and never keeps a pointer after the call returns;
+ *  - `stream` is a cudaStream_t passed as void* (NULL = the legacy default stream);
+ *    calls only enqueue work, they do not synchronise;
+ *  - return value: 0 = ok, < 0 = argument error (OG_E_*), > 0 = a cudaError_t value;
+ *    og_last_error() returns a thread-local message for the last non-zero return;
+ *  - images are row-major 8-bit gray with a row pitch in BYTES; maps and grids are
+ *    contiguous fp32 with the last axis (x, y), exactly the layout of dewarp.zip's
+ *    data.npy (reference docs/formats.md:298-306).
+ */
+#ifndef ORIGAMI_B200_H
+#define ORIGAMI_B200_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define OG_OK 0
+#define OG_E_ARG (-1)      /* null pointer, non-positive size, bad enum            */
+#define OG_E_RANGE (-2)    /* dimension beyond what OpenCV itself accepts (>=32767) */
+#define OG_E_ALIGN (-3)    /* pointer / pitch alignment the kernel cannot serve     */
+#define OG_E_WINDOW (-4)   /* Sauvola window even, 1, or larger than supported      */
+
+#define OG_INTER_NEAREST 0 /* == cv2.INTER_NEAREST */
+#define OG_INTER_LINEAR 1  /* == cv2.INTER_LINEAR  */
+
+#define OG_BIN_NONE 0
+#define OG_BIN_OTSU 1
+#define OG_BIN_SAUVOLA 2
+
+/* One text line in DEWARPED page space.  Mirrors the fields of the reference's Line
+ * (origami/core/block.py:35-55; lines.zip: docs/formats.md:223-246) plus the result of
+ * Line._position (block.py:195-221), which the host evaluates because it is scalar work.
+ * All vectors are (x, y).  112 bytes, 8-byte aligned. */
+typedef struct og_line {
+	double p[2];      /* bottom-left corner of the line box (un-clipped)                 */
+	double right[2];  /* baseline vector (un-clipped)                                    */
+	double up[2];     /* ascender vector, points to smaller y                            */
+	double cp[2];     /* origin after table-column clipping (== p without a column)      */
+	double cright[2]; /* baseline vector after clipping      (== right without a column) */
+	double xres;      /* samples per warped pixel along the line, after column rescale   */
+	double yres;      /* samples per warped pixel across the line                        */
+	int32_t xsteps;   /* > 0: fixed sample count; 0: derive from the rough 2x2 extent    */
+	int32_t ysteps;   /* > 0: fixed (target_height); 0: derive                           */
+	int32_t flags;    /* reserved, 0                                                     */
+	int32_t pad_;
+} og_line;
+
+/* Message for the last non-zero return on this thread (never NULL). */
+const char *og_last_error(void);
+
+/* Library / build identification, e.g. "origami_b200 0.1 sm_100a". */
+const char *og_version(void);
+
+/* A2  Grid.points("full")  -- origami/core/dewarp.py:514-526 (2x cv2.resize INTER_LINEAR of
+ * the x and y planes, np.dstack).  grid (gh, gw, 2) fp32 -> map_out (gh*cell, gw*cell, 2)
+ * fp32, bit-identical to OpenCV's generic (cv2.setUseOptimized(False)) code path. */
+int og_expand_map(const float *grid, int gh, int gw, int cell, float *map_out, void *stream);
+
+/* A2+A3+A4  Dewarper.dewarped / Dewarper.dewarp_image -- origami/core/dewarp.py:608-627
+ * (cv2.remap of the page through Grid.points("full")), fused with the map expansion.
+ * src (H, W) u8 -> dst (gh*cell, gw*cell) u8.  The sampling coordinates are the dense map
+ * times (scale_x, scale_y) in fp32 (1.0f, 1.0f for Dewarper.dewarped; w1/w0, h1/h0 rounded
+ * to fp32 for dewarp_image).  map_out, if not NULL, receives the UNSCALED dense map
+ * (same bits as og_expand_map); dst may be NULL when only the map is wanted.
+ * interp: OG_INTER_LINEAR (OpenCV's 1/32-px fixed-point bilinear, BORDER_CONSTANT 0) or
+ * OG_INTER_NEAREST. */
+int og_remap_page(const uint8_t *src, int H, int W, int64_t src_pitch,
+	const float *grid, int gh, int gw, int cell,
+	uint8_t *dst, int64_t dst_pitch, float *map_out,
+	float scale_x, float scale_y, int interp, void *stream);
+
+/* A5  Grid.inverse_yx -- origami/core/dewarp.py:561-567 (SciPy RegularGridInterpolator,
+ * linear, extrapolating) evaluated at n points.  pts_yx (n, 2) f64 dewarped (y, x) ->
+ * out_xy (n, 2) f64 warped (x, y).  The dense map is not read: its nodes are recomputed
+ * from the sparse grid with the A2 arithmetic, then blended in float64 in SciPy's order. */
+int og_inverse_yx(const float *grid, int gh, int gw, int cell,
+	const double *pts_yx, int64_t n, double *out_xy, void *stream);
+
+/* A8 (step counts) + A21  Line.warped_grid step derivation -- origami/core/block.py:226-236.
+ * For every line: steps_out[i] = (xsteps, ysteps); pix_offsets_out[i] = sum over j<i of
+ * xsteps*ysteps (n+1 entries, element offsets of each strip in a packed buffer);
+ * chunk_offsets_out (n+1 entries) = prefix sum of the work items the extraction kernels
+ * split each line into.  One launch, no host synchronisation. */
+int og_line_steps(const float *grid, int gh, int gw, int cell,
+	const og_line *lines, int n,
+	int32_t *steps_out, int64_t *pix_offsets_out, int32_t *chunk_offsets_out, void *stream);
+
+/* A8  Line.warped_grid -- origami/core/block.py:223-248.  Writes the fp32 (ysteps, xsteps, 2)
+ * warped sampling grid of every line, packed at 2*pix_offsets[i] floats.  capacity is in
+ * grid points (pixels); lines that would not fit are skipped (check pix_offsets[n]). */
+int og_warped_grids(const float *grid, int gh, int gw, int cell,
+	const og_line *lines, int n,
+	const int32_t *steps, const int64_t *pix_offsets, const int32_t *chunk_offsets,
+	float *grids_out, int64_t capacity, void *stream);
+
+/* A9+A10+A21  Line.dewarped_image / Line.image -- origami/core/block.py:129-143, 250-259,
+ * batched over all lines of a page in one launch (replaces LineExtractor's ThreadPool,
+ * origami/batch/core/lines.py:148-149).  src is the WARPED page.  Strip i is written as
+ * (ysteps, xsteps) u8, row 0 = top of the text (the reference's pixels[::-1]), at byte
+ * offset pix_offsets[i] of strips_out.  bbox_out, if not NULL, receives per line
+ * (floor min x, floor min y, ceil max x, ceil max y) of its fp32 warped grid as int32
+ * (origami/core/mask.py:10-12 convention).  capacity in bytes of strips_out. */
+int og_extract_lines(const uint8_t *src, int H, int W, int64_t src_pitch,
+	const float *grid, int gh, int gw, int cell,
+	const og_line *lines, int n,
+	const int32_t *steps, const int64_t *pix_offsets, const int32_t *chunk_offsets,
+	uint8_t *strips_out, int64_t capacity, int32_t *bbox_out, void *stream);
+
+/* A12  binarizers on packed strips -- origami/core/binarize.py:11-43 as applied per line by
+ * Line.image (block.py:140-141).  gray and out hold n strips packed at pix_offsets; they
+ * must not alias for OG_BIN_SAUVOLA (window odd, 3..127; k = 0.2, r = 127.5 as in the
+ * reference).  thresholds_out (n int32, OTSU only, may be NULL) receives each threshold. */
+int og_binarize_strips(const uint8_t *gray, const int32_t *steps, const int64_t *pix_offsets,
+	const int32_t *chunk_offsets, int n, int mode, int window, uint8_t *out,
+	int32_t *thresholds_out, void *stream);
+
+/* A12  page-scale Sauvola -- skimage.filters.threshold_sauvola (0.16.2) + `> t` as used by
+ * Page.binarized (origami/core/page.py:101-104) and Regions.binarized
+ * (origami/batch/detect/layout.py:157-169).  out = 255 where src > t else 0. */
+int og_sauvola(const uint8_t *src, int h, int w, int64_t src_pitch, int window,
+	double k, double r, uint8_t *dst, int64_t dst_pitch, void *stream);
+
+/* A12  page-scale Otsu -- skimage.filters.threshold_otsu (0.16.2) via origami/core/
+ * binarize.py:18-26.  hist_scratch: 256 uint32 (zeroed by the call). */
+int og_otsu(const uint8_t *src, int h, int w, int64_t src_pitch,
+	uint8_t *dst, int64_t dst_pitch, uint32_t *hist_scratch, int32_t *threshold_out,
+	void *stream);
+
+/* A15  ConfidenceSampler.__call__ -- origami/batch/detect/lines.py:34-54.  For every line:
+ * warped grid at (xres, yres) from the descriptors, scaled to the label map by
+ * fp32(lw/W), fp32(lh/H), NEAREST lookup (OOB -> label 0), histogram.  counts_out
+ * (n, n_classes) int64, zeroed by the call; labels >= n_classes are counted in
+ * overflow_out[i] (n int64, may be NULL; np.bincount would have grown the array). */
+int og_sample_labels(const uint8_t *labels, int lh, int lw, int64_t labels_pitch,
+	int H, int W,
+	const float *grid, int gh, int gw, int cell,
+	const og_line *lines, int n,
+	const int32_t *steps, const int32_t *chunk_offsets,
+	int n_classes, int64_t *counts_out, int64_t *overflow_out, void *stream);
+
+/* A18+A19  label argmax and class masks -- origami/core/predict.py:281-285,
+ * origami/core/contours.py:488.  probs (M, h, w, C) fp32 -> labels (h, w) u8 =
+ * argmax_c of the in-order fp32 sum over models (first maximum wins); masks_out, if not
+ * NULL, (n_mask, h, w) u8 with masks_out[k] = (labels == mask_values[k]) (mask_values is a
+ * HOST array of n_mask bytes). */
+int og_argmax_labels(const float *probs, int M, int C, int h, int w,
+	uint8_t *labels_out, uint8_t *masks_out, const uint8_t *mask_values, int n_mask,
+	void *stream);
+
+/* A19 alone: masks from an existing label map. */
+int og_class_masks(const uint8_t *labels, int h, int w, int64_t pitch,
+	uint8_t *masks_out, const uint8_t *mask_values, int n_mask, void *stream);
+
+/* A11  warpAffine stage of Line._extract_deskewed -- origami/core/block.py:155-172
+ * (--do-not-dewarp path; the cairo polygon cut-out that follows is not reproduced).
+ * M is a HOST 2x3 float64 forward matrix as returned by cv2.getAffineTransform. */
+int og_warp_affine(const uint8_t *src, int H, int W, int64_t src_pitch,
+	const double *M, uint8_t *dst, int width, int height, int64_t dst_pitch,
+	int border_value, void *stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif

@@ -1,0 +1,525 @@
+"""
+ORACLE (test infrastructure, not product code) -- bit-exact NumPy restatement of the
+arithmetic on Origami's page-geometry hot path.
+
+Only tests/, __graft_entry__.smoke() and bench.py's cpu_baseline / --impl reference
+legs may import this module.  Nothing under origami_b200/ does.
+
+Every function restates one row of SURVEY.md section 8(a) and cites the reference
+call site (paths relative to /root/reference) whose behaviour it reproduces.  The
+arithmetic that lives in third-party libraries the reference calls is restated from
+the published algorithm:
+
+  * OpenCV (reference pins opencv-python==4.2.0.32, docker/pip_requirements.txt;
+    this image has 4.13.0): cv2.resize INTER_LINEAR generic path
+    (modules/imgproc/src/resize.cpp: HResizeLinear / VResizeLinear), cv2.remap
+    INTER_LINEAR / INTER_NEAREST on 8-bit images (modules/imgproc/src/imgwarp.cpp:
+    RemapInvoker, remapBilinear, remapNearest), cv2.warpAffine.
+  * SciPy RegularGridInterpolator, method="linear" (reference pins scipy==1.3.1; this
+    image has 1.18.1): scipy/interpolate/_rgi.py _evaluate_linear.
+  * scikit-image 0.16.2 threshold_sauvola / threshold_otsu (skimage/filters/
+    thresholding.py); scikit-image is NOT installed here, so these two restatements
+    are "parity unpinned" against skimage itself (they are pinned against a second,
+    independent integral-image formulation in tests/test_oracle.py).
+
+Pinning: tests/test_oracle.py checks every function here against cv2 (generic path,
+cv2.setUseOptimized(False)), scipy and numpy run in-process, and against the golden
+vectors in tests/golden/ that oracle/make_golden.py produced by importing the
+UNMODIFIED reference modules from /root/reference.
+"""
+
+import math
+
+import numpy as np
+
+F32 = np.float32
+F64 = np.float64
+
+INTER_NEAREST = 0  # same integer values as cv2.INTER_NEAREST / cv2.INTER_LINEAR
+INTER_LINEAR = 1
+
+
+# --------------------------------------------------------------------------------------
+# A2  Grid.points("full")        origami/core/dewarp.py:514-526
+# --------------------------------------------------------------------------------------
+
+def _resize_axis(n_src, s):
+	"""Per destination index: source index and fp32 fraction, cv2.resize INTER_LINEAR.
+
+	resize.cpp: fx = (float)((dx+0.5)*scale_x - 0.5) with scale_x = 1./(dsize/ssize)
+	evaluated in double; sx = cvFloor(fx); fx -= sx (float).
+	"""
+	d = np.arange(n_src * s, dtype=F64)
+	f = ((d + 0.5) * (1.0 / float(s)) - 0.5).astype(F32)
+	i = np.floor(f).astype(np.int32)
+	fr = (f - i.astype(F32)).astype(F32)
+	return i, fr
+
+
+def expand_plane(S, s):
+	"""cv2.resize(S, (gw*s, gh*s), INTER_LINEAR) of one fp32 plane, generic code path.
+
+	Horizontal pass first (x index clamped AND fraction reset at both borders), then
+	vertical pass (row indices clamped, fraction NOT reset); every blend is
+	fl(fl(a*(1-f)) + fl(b*f)) in fp32 without fused multiply-add.
+	"""
+	S = np.ascontiguousarray(S, dtype=F32)
+	gh, gw = S.shape
+	ix, fx = _resize_axis(gw, s)
+	lo = ix < 0
+	ix[lo] = 0
+	fx[lo] = 0
+	hi = ix >= gw - 1
+	ix[hi] = gw - 1
+	fx[hi] = 0
+	ix1 = np.minimum(ix + 1, gw - 1)
+	a0 = (F32(1) - fx).astype(F32)
+	H = (S[:, ix] * a0).astype(F32) + (S[:, ix1] * fx).astype(F32)
+
+	iy, fy = _resize_axis(gh, s)
+	r0 = np.clip(iy, 0, gh - 1)
+	r1 = np.clip(iy + 1, 0, gh - 1)
+	b0 = (F32(1) - fy).astype(F32)[:, None]
+	b1 = fy[:, None]
+	return ((H[r0] * b0).astype(F32) + (H[r1] * b1).astype(F32)).astype(F32)
+
+
+def expand_map(grid, s):
+	"""Grid.points("full"): (gh, gw, 2) fp32 -> (gh*s, gw*s, 2) fp32, [..., 0] = x.
+
+	origami/core/dewarp.py:518-524 resizes the x plane and the y plane separately and
+	stacks them with np.dstack.
+	"""
+	grid = np.asarray(grid, dtype=F32)
+	return np.dstack([expand_plane(grid[:, :, 0], s), expand_plane(grid[:, :, 1], s)])
+
+
+# --------------------------------------------------------------------------------------
+# A3 / A4  cv2.remap on 8-bit images   origami/core/dewarp.py:608-627, core/block.py:256
+# --------------------------------------------------------------------------------------
+
+def _sat_short(v):
+	return np.clip(v, -32768, 32767)
+
+
+def _tap(src, iy, ix, border):
+	H, W = src.shape
+	inside = (ix >= 0) & (ix < W) & (iy >= 0) & (iy < H)
+	v = src[np.clip(iy, 0, H - 1), np.clip(ix, 0, W - 1)].astype(np.int64)
+	return np.where(inside, v, border)
+
+
+def remap_linear(src, map_xy, border=0):
+	"""cv2.remap(src u8, map fp32 (h,w,2), None, INTER_LINEAR), BORDER_CONSTANT.
+
+	imgwarp.cpp RemapInvoker: sx = cvRound(x*32) (fp32 product, round-half-even),
+	ix = saturate_cast<short>(sx >> 5), fx = sx & 31; remapBilinear with the 15-bit
+	BilinearTab_i weights, which for a 32x32 table are exactly (32-fx)(32-fy)*32 etc.,
+	so out = (sum + 2^14) >> 15 == (sum/32 + 512) >> 10.  Taps outside the image
+	contribute the border value.
+	"""
+	src = np.asarray(src, dtype=np.uint8)
+	m = np.asarray(map_xy, dtype=F32)
+	sx = np.rint(m[..., 0] * F32(32)).astype(np.int64)
+	sy = np.rint(m[..., 1] * F32(32)).astype(np.int64)
+	ix = _sat_short(sx >> 5)
+	iy = _sat_short(sy >> 5)
+	fx = sx & 31
+	fy = sy & 31
+	p00 = _tap(src, iy, ix, border)
+	p01 = _tap(src, iy, ix + 1, border)
+	p10 = _tap(src, iy + 1, ix, border)
+	p11 = _tap(src, iy + 1, ix + 1, border)
+	acc = ((32 - fx) * (32 - fy) * p00 + fx * (32 - fy) * p01
+		+ (32 - fx) * fy * p10 + fx * fy * p11)
+	return ((acc + 512) >> 10).astype(np.uint8)
+
+
+def remap_nearest(src, map_xy, border=0):
+	"""cv2.remap(..., INTER_NEAREST): p[rint(y), rint(x)], round-half-even, OOB -> border.
+
+	imgwarp.cpp RemapInvoker nearest branch: XY = saturate_cast<short>(float).
+	"""
+	src = np.asarray(src, dtype=np.uint8)
+	m = np.asarray(map_xy, dtype=F32)
+	ix = _sat_short(np.rint(m[..., 0]).astype(np.int64))
+	iy = _sat_short(np.rint(m[..., 1]).astype(np.int64))
+	return _tap(src, iy, ix, border).astype(np.uint8)
+
+
+def scale_map(map_xy, w0, h0, w1, h1):
+	"""In-place-style scaling of an fp32 map by Python-float ratios.
+
+	Dewarper.dewarp_image (origami/core/dewarp.py:622-623) and scale_grid
+	(origami/batch/detect/lines.py:18-22): `grid[:, :, 0] *= w1 / w0` on an fp32 array
+	multiplies in fp32 by the ratio rounded to fp32 (NumPy >= 2 weak-scalar rule).
+	Returns a copy (the reference mutates the lru_cache'd map; that bug is not kept).
+	"""
+	m = np.array(map_xy, dtype=F32, copy=True)
+	m[..., 0] *= F32(w1 / w0)
+	m[..., 1] *= F32(h1 / h0)
+	return m
+
+
+def dewarp_page(src, grid, s):
+	"""Dewarper.dewarped (origami/core/dewarp.py:608-614)."""
+	return remap_linear(src, expand_map(grid, s))
+
+
+def dewarp_image(im, page_size, grid, s, interpolation=INTER_LINEAR):
+	"""Dewarper.dewarp_image (origami/core/dewarp.py:616-627); page_size = (w0, h0)."""
+	w0, h0 = page_size
+	h1, w1 = im.shape
+	m = scale_map(expand_map(grid, s), w0, h0, w1, h1)
+	if interpolation == INTER_NEAREST:
+		return remap_nearest(im, m)
+	return remap_linear(im, m)
+
+
+# --------------------------------------------------------------------------------------
+# A5  Grid.inverse_yx            origami/core/dewarp.py:561-567
+# --------------------------------------------------------------------------------------
+
+def inverse_yx(dense, pts_yx):
+	"""RegularGridInterpolator((arange(Hd), arange(Wd)), dense, "linear",
+	bounds_error=False, fill_value=None)(pts) -- linear extrapolation outside.
+
+	scipy/interpolate/_rgi.py: find_indices gives i = clip(searchsorted-1, 0, n-2) and
+	the normalised distance y - i (cell width 1); _evaluate_linear accumulates, in
+	float64 and in this order, v00*((1-a)(1-b)) + v01*((1-a)b) + v10*(a(1-b)) + v11*(ab),
+	starting from 0.0, with the fp32 nodes promoted to float64.
+
+	The cell of an exactly integral coordinate k is k-1 with a = 1 in SciPy and k with
+	a = 0 here; both give the same float64 result because the vanishing terms are exact
+	zeros.
+	"""
+	dense = np.asarray(dense)
+	Hd, Wd = dense.shape[:2]
+	p = np.asarray(pts_yx, dtype=F64)
+	y = p[..., 0]
+	x = p[..., 1]
+	i0 = np.clip(np.floor(y), 0, Hd - 2).astype(np.int64)
+	i1 = np.clip(np.floor(x), 0, Wd - 2).astype(np.int64)
+	a = y - i0
+	b = x - i1
+	wa = 1 - a
+	wb = 1 - b
+	out = np.zeros(p.shape[:-1] + (dense.shape[2],), dtype=F64)
+	for (di, dj, w) in ((0, 0, wa * wb), (0, 1, wa * b), (1, 0, a * wb), (1, 1, a * b)):
+		out = out + dense[i0 + di, i1 + dj].astype(F64) * w[..., None]
+	return out
+
+
+# --------------------------------------------------------------------------------------
+# A7 / A8  Line._position, Line.warped_grid     origami/core/block.py:195-248
+# --------------------------------------------------------------------------------------
+
+def line_position(p, right, up, xres=1, column=None):
+	"""Line._position (origami/core/block.py:195-221) without shapely.
+
+	The reference intersects the baseline with the two vertical lines x = x0, x = x1 via
+	shapely (absent here: parity of the intersection point's last bits is unpinned).
+	Restated as the parametric intersection in float64; a miss keeps the endpoint, as
+	`intersect_segments(..., default=...)` does.
+	"""
+	p0 = np.asarray(p, dtype=F64)
+	right = np.asarray(right, dtype=F64)
+	up = np.asarray(up, dtype=F64)
+	if column is not None:
+		p1 = p0 + right
+		px0, px1 = min(p0[0], p1[0]), max(p0[0], p1[0])
+		x0, x1 = column
+		if x0 is None:
+			x0 = px0
+		if x1 is None:
+			x1 = px1
+
+		def hit(xv, default):
+			dx = p1[0] - p0[0]
+			if dx == 0:
+				return default
+			t = (xv - p0[0]) / dx
+			if t < 0 or t > 1:
+				return default
+			return np.array([xv, p0[1] + t * (p1[1] - p0[1])], dtype=F64)
+
+		q0 = hit(x0, p0)
+		q1 = hit(x1, p1)
+		right = q1 - q0
+		p0 = q0
+		xres = xres * ((x1 - x0) / (px1 - px0))
+	return p0, right, up, xres
+
+
+def _linspace2(stop, num):
+	"""np.linspace([0, 0], stop, num) restated (numpy/_core/function_base.py).
+
+	step = stop/div; if ANY component's step is zero every component uses (i/div)*stop,
+	else i*step; the last sample is forced to `stop`.
+	"""
+	stop = np.asarray(stop, dtype=F64)
+	i = np.arange(num, dtype=F64)[:, None]
+	div = num - 1
+	if div > 0:
+		step = stop / div
+		if (step == 0).any():
+			y = (i / div) * stop
+		else:
+			y = i * step
+	else:
+		y = i * stop
+	y = y + 0.0
+	if num > 1:
+		y[-1] = stop
+	return y
+
+
+def _rough_extent(dense, p, right, up):
+	"""Line.warped_grid(xsteps=2, ysteps=2) on the un-clipped line (block.py:226-228)."""
+	g = lattice_to_warped(dense, np.asarray(p, F64), np.asarray(right, F64), np.asarray(up, F64), 2, 2)
+	wx = np.max(np.abs(g[:, 0, 0] - g[:, 1, 0]))  # fp32
+	wy = np.max(np.abs(g[0, :, 1] - g[1, :, 1]))  # fp32
+	return wx, wy
+
+
+def lattice_to_warped(dense, p0, right, up, xsteps, ysteps):
+	"""The body of Line.warped_grid after the step counts are known (block.py:238-248)."""
+	ys = _linspace2(up, ysteps)
+	xs = _linspace2(right, xsteps)
+	dg = (ys + p0)[:, None] + xs[None, :]
+	dg = np.flip(dg, axis=-1)
+	out = inverse_yx(dense, dg.reshape(-1, 2))
+	return out.reshape(ysteps, xsteps, 2).astype(F32)
+
+
+def line_steps(dense, p, right, up, xsteps=None, ysteps=None, xres=1, yres=1, column=None):
+	"""Step counts of Line.warped_grid (block.py:226-236).
+
+	The rough 2x2 grid is taken WITHOUT the column (the recursive call passes none) and is
+	already fp32, so the extent is an fp32 difference; `xsteps * xres` with a Python float
+	stays fp32 under NumPy >= 2 (xres rounded to fp32 first).
+	"""
+	_, _, _, xres_c = line_position(p, right, up, xres, column)
+	if xsteps is None or ysteps is None:
+		wx, wy = _rough_extent(dense, p, right, up)
+	if xsteps is None:
+		xsteps = max(2, int(np.ceil(wx * F32(xres_c))))
+	if ysteps is None:
+		ysteps = max(2, int(np.ceil(wy * F32(yres))))
+	return xsteps, ysteps
+
+
+def warped_grid(dense, p, right, up, xsteps=None, ysteps=None, xres=1, yres=1, column=None):
+	"""Line.warped_grid (origami/core/block.py:223-248) -> (ysteps, xsteps, 2) fp32."""
+	xsteps, ysteps = line_steps(dense, p, right, up, xsteps, ysteps, xres, yres, column)
+	p0, right_c, up_c, _ = line_position(p, right, up, xres, column)
+	return lattice_to_warped(dense, p0, right_c, up_c, xsteps, ysteps)
+
+
+def dewarped_line_image(warped_page, dense, p, right, up, target_height=48, column=None):
+	"""Line.dewarped_image (origami/core/block.py:250-259): remap + vertical flip."""
+	g = warped_grid(dense, p, right, up, ysteps=target_height, column=column)
+	return remap_linear(warped_page, g)[::-1, :]
+
+
+def warped_path(dense, p, right, up, resolution=1):
+	"""Line.warped_path (origami/core/block.py:261-267)."""
+	g = warped_grid(dense, p, right, up, ysteps=2, xres=resolution)
+	height = np.median(np.linalg.norm(g[1] - g[0], axis=-1))
+	return np.mean(g, axis=0), abs(height)
+
+
+def grid_bbox(g):
+	"""A21: integer source-space box of an fp32 warped grid, Mask.__init__ convention
+	(origami/core/mask.py:10-12): floor(min), ceil(max) as int32 -> (x0, y0, x1, y1)."""
+	return (int(math.floor(g[..., 0].min())), int(math.floor(g[..., 1].min())),
+		int(math.ceil(g[..., 0].max())), int(math.ceil(g[..., 1].max())))
+
+
+# --------------------------------------------------------------------------------------
+# A15  ConfidenceSampler.__call__     origami/batch/detect/lines.py:34-54
+# --------------------------------------------------------------------------------------
+
+def sample_label_counts(labels, page_shape, dense, p, right, up, n_classes, res=0.5):
+	"""Half-resolution warped grid, scaled to the label map, NEAREST remap, bincount."""
+	g = warped_grid(dense, p, right, up, xres=res, yres=res)
+	h0, w0 = page_shape
+	h1, w1 = labels.shape
+	g = scale_map(g, w0, h0, w1, h1)
+	lab = remap_nearest(labels, g)
+	return np.bincount(lab.flatten(), minlength=n_classes)
+
+
+# --------------------------------------------------------------------------------------
+# A12  binarizers                      origami/core/binarize.py:11-43
+# --------------------------------------------------------------------------------------
+
+def _reflect_index(i, n):
+	"""np.pad(mode="reflect") index map (no edge repeat), any overhang."""
+	if n == 1:
+		return np.zeros_like(i)
+	period = 2 * (n - 1)
+	i = np.mod(i, period)
+	return np.where(i >= n, period - i, i)
+
+
+def window_sums(pixels, w):
+	"""Exact integer sums of p and p^2 over the centred w x w window, reflect-padded.
+
+	skimage 0.16.2 _mean_std pads by (w//2+1, w//2) with mode="reflect", builds float64
+	integral images and correlates with a (w+1)^2 corner kernel, which is the centred
+	window sum; for 8-bit input every intermediate is an integer < 2^53, so it is exact.
+	"""
+	p = np.asarray(pixels).astype(np.int64)
+	h, wd = p.shape
+	r = w // 2
+	yy = _reflect_index(np.arange(-r, h + r), h)
+	xx = _reflect_index(np.arange(-r, wd + r), wd)
+	pad = p[yy][:, xx]
+
+	def box(a):
+		c = np.cumsum(a, axis=0)
+		c = np.vstack([np.zeros((1, a.shape[1]), np.int64), c])
+		v = c[w:] - c[:-w]
+		c = np.cumsum(v, axis=1)
+		c = np.hstack([np.zeros((v.shape[0], 1), np.int64), c])
+		return c[:, w:] - c[:, :-w]
+
+	return box(pad), box(pad * pad)
+
+
+def threshold_sauvola(pixels, window_size=15, k=0.2, r=None):
+	"""skimage.filters.threshold_sauvola 0.16.2 for 8-bit input (float64).
+
+	m = S1/w^2, g2 = S2/w^2, s = sqrt(clip(g2 - m*m, 0)), t = m*(1 + k*((s/r) - 1)),
+	r = 127.5 for uint8 (0.5*(imax-imin) of the dtype limits).
+	"""
+	if window_size == 1 or window_size % 2 == 0:
+		raise ValueError("Window size w = %s must be odd and greater than 1." % window_size)
+	if r is None:
+		r = 0.5 * (255 - 0)
+	s1, s2 = window_sums(pixels, window_size)
+	n = float(window_size ** 2)
+	m = s1.astype(F64) / n
+	g2 = s2.astype(F64) / n
+	s = np.sqrt(np.clip(g2 - m * m, 0, None))
+	return m * (1 + k * ((s / r) - 1))
+
+
+def threshold_otsu(pixels):
+	"""skimage.filters.threshold_otsu 0.16.2 for 8-bit input.
+
+	Histogram over [min, max] with integer bin centres; float64 cumulative sums; first
+	argmax of w1*w2*(m1-m2)^2.  A single-valued image raises ValueError, which
+	origami/core/binarize.py:20-23 turns into the threshold 128.
+	"""
+	p = np.asarray(pixels)
+	lo, hi = int(p.min()), int(p.max())
+	if lo == hi:
+		raise ValueError("single colour")
+	hist = np.bincount(p.ravel(), minlength=hi + 1)[lo:].astype(F64)
+	centers = np.arange(lo, hi + 1)
+	w1 = np.cumsum(hist)
+	w2 = np.cumsum(hist[::-1])[::-1]
+	m1 = np.cumsum(hist * centers) / w1
+	m2 = (np.cumsum((hist * centers)[::-1]) / w2[::-1])[::-1]
+	var12 = w1[:-1] * w2[1:] * (m1[:-1] - m2[1:]) ** 2
+	return int(centers[:-1][np.argmax(var12)])
+
+
+def binarize(pixels, spec):
+	"""binarize_with_threshold (origami/core/binarize.py:11-15): (pixels > t) * 255.
+
+	spec: None | ("otsu",) | ("sauvola", window_size)
+	"""
+	pixels = np.asarray(pixels, dtype=np.uint8)
+	if spec is None:
+		return pixels
+	if spec[0] == "otsu":
+		try:
+			t = threshold_otsu(pixels)
+		except ValueError:
+			t = 128
+	elif spec[0] == "sauvola":
+		t = threshold_sauvola(pixels, spec[1])
+	else:
+		raise ValueError(spec)
+	return (pixels > t).astype(np.uint8) * 255
+
+
+# --------------------------------------------------------------------------------------
+# A18 / A19  label argmax and class masks   origami/core/predict.py:281-285, contours.py:488
+# --------------------------------------------------------------------------------------
+
+def argmax_labels(pr_masks):
+	"""np.argmax(np.sum(pr_masks, axis=0), axis=-1).astype(uint8): fp32 sum over models in
+	order, first maximum wins."""
+	pr = np.asarray(pr_masks, dtype=F32)
+	acc = pr[0].copy()
+	for m in range(1, pr.shape[0]):
+		acc = (acc + pr[m]).astype(F32)
+	return np.argmax(acc, axis=-1).astype(np.uint8)
+
+
+def class_masks(labels, values):
+	"""pixels == c.value for every class value (origami/core/contours.py:488)."""
+	return np.stack([(labels == v) for v in values]).astype(np.uint8)
+
+
+# --------------------------------------------------------------------------------------
+# A11  Line._extract_deskewed warpAffine stage   origami/core/block.py:155-172
+# --------------------------------------------------------------------------------------
+
+def affine_from_points(src_tri, dst_tri):
+	"""cv2.getAffineTransform on fp32-rounded points, solved in float64 (LU in OpenCV;
+	the tests compare the matrix with cv2's to 1e-9 and use cv2's matrix for pixel parity)."""
+	src = np.asarray(src_tri, dtype=F32).astype(F64)
+	dst = np.asarray(dst_tri, dtype=F32).astype(F64)
+	A = np.zeros((6, 6))
+	b = np.zeros(6)
+	for i in range(3):
+		A[i, 0:2] = src[i]
+		A[i, 2] = 1
+		A[i + 3, 3:5] = src[i]
+		A[i + 3, 5] = 1
+		b[i] = dst[i, 0]
+		b[i + 3] = dst[i, 1]
+	return np.linalg.solve(A, b).reshape(2, 3)
+
+
+def warp_affine_linear(src, M, width, height, border=0):
+	"""cv2.warpAffine(src u8, M, (width, height), INTER_LINEAR|INTER_AREA, BORDER_CONSTANT).
+
+	imgwarp.cpp warpAffine: M inverted in double; per column adelta = rint(iM00*x*1024),
+	bdelta = rint(iM10*x*1024); per row X0 = rint((iM01*y + iM02)*1024) + 16 (half of
+	1024/32), likewise Y0; X = (X0 + adelta) >> 5 gives ix = X >> 5, fx = X & 31; then the
+	same integer bilinear blend as remap.
+	"""
+	src = np.asarray(src, dtype=np.uint8)
+	M = np.asarray(M, dtype=F64)
+	D = M[0, 0] * M[1, 1] - M[0, 1] * M[1, 0]
+	D = 1.0 / D if D != 0 else 0.0
+	A11 = M[1, 1] * D
+	A22 = M[0, 0] * D
+	i00, i01, i10, i11 = A11, M[0, 1] * (-D), M[1, 0] * (-D), A22
+	b1 = -i00 * M[0, 2] - i01 * M[1, 2]
+	b2 = -i10 * M[0, 2] - i11 * M[1, 2]
+	xs = np.arange(width, dtype=F64)
+	ys = np.arange(height, dtype=F64)
+	adelta = np.rint(i00 * xs * 1024).astype(np.int64)
+	bdelta = np.rint(i10 * xs * 1024).astype(np.int64)
+	X0 = np.rint((i01 * ys + b1) * 1024).astype(np.int64) + 16
+	Y0 = np.rint((i11 * ys + b2) * 1024).astype(np.int64) + 16
+	X = (X0[:, None] + adelta[None, :]) >> 5
+	Y = (Y0[:, None] + bdelta[None, :]) >> 5
+	ix = _sat_short(X >> 5)
+	iy = _sat_short(Y >> 5)
+	fx = X & 31
+	fy = Y & 31
+	p00 = _tap(src, iy, ix, border)
+	p01 = _tap(src, iy, ix + 1, border)
+	p10 = _tap(src, iy + 1, ix, border)
+	p11 = _tap(src, iy + 1, ix + 1, border)
+	acc = ((32 - fx) * (32 - fy) * p00 + fx * (32 - fy) * p01
+		+ (32 - fx) * fy * p10 + fx * fy * p11)
+	return ((acc + 512) >> 10).astype(np.uint8)

@@ -1,0 +1,346 @@
+// Binarizers (A12): Otsu and Sauvola thresholds, on whole pages and on packed line strips.
+//
+// Reference: origami/core/binarize.py:11-43 (binarize_with_threshold: (pixels > t) * 255),
+// called per line by Line.image (origami/core/block.py:140-141), on the page by
+// Page.binarized (origami/core/page.py:101-104) and Regions.binarized
+// (origami/batch/detect/layout.py:157-169).  The thresholds are scikit-image 0.16.2's
+// threshold_otsu / threshold_sauvola; both are restated with exact integer window sums /
+// histograms followed by the same float64 operations in the same order.
+#include "og_common.cuh"
+
+namespace {
+
+constexpr int BTHREADS = 256;
+constexpr int ST_W = 64;  // Sauvola output tile (== line chunk width)
+constexpr int ST_H = 32;
+constexpr int MAX_WINDOW = 127;
+
+// np.pad(mode="reflect") index (no edge repeat), any overhang
+__device__ __forceinline__ int reflect_index(int i, int n) {
+	if (n == 1) return 0;
+	const int period = 2 * (n - 1);
+	i %= period;
+	if (i < 0) i += period;
+	return i >= n ? period - i : i;
+}
+
+// ---------------------------------------------------------------------------------------
+// Otsu threshold from an exact 256-bin histogram (skimage 0.16.2 threshold_otsu on uint8:
+// bins = the integers [min, max], float64 cumulative sums, first argmax of
+// w1 * w2 * (m1 - m2)^2; a single-valued image is the ValueError -> 128 case of
+// origami/core/binarize.py:20-23).  One warp; each lane owns 8 consecutive bins.
+// ---------------------------------------------------------------------------------------
+__device__ int otsu_from_hist_warp(const unsigned int *hist) {
+	const int lane = threadIdx.x & 31;
+	unsigned long long cnt = 0, sum = 0;
+	int lo = 256, hi = -1;
+	for (int k = 0; k < 8; ++k) {
+		const int b = lane * 8 + k;
+		const unsigned int h = hist[b];
+		cnt += h;
+		sum += (unsigned long long)h * b;
+		if (h) {
+			lo = min(lo, b);
+			hi = max(hi, b);
+		}
+	}
+	unsigned long long icnt = cnt, isum = sum;
+#pragma unroll
+	for (int o = 1; o < 32; o <<= 1) {
+		unsigned long long tc = __shfl_up_sync(0xffffffffu, icnt, o);
+		unsigned long long ts = __shfl_up_sync(0xffffffffu, isum, o);
+		if (lane >= o) {
+			icnt += tc;
+			isum += ts;
+		}
+	}
+	const unsigned long long total_cnt = __shfl_sync(0xffffffffu, icnt, 31);
+	const unsigned long long total_sum = __shfl_sync(0xffffffffu, isum, 31);
+#pragma unroll
+	for (int o = 16; o > 0; o >>= 1) {
+		lo = min(lo, __shfl_xor_sync(0xffffffffu, lo, o));
+		hi = max(hi, __shfl_xor_sync(0xffffffffu, hi, o));
+	}
+	if (hi <= lo) return 128;  // empty or single colour
+	// candidate thresholds i in [lo, hi - 1]: class 1 = bins <= i, class 2 = bins > i
+	unsigned long long c1 = icnt - cnt, s1 = isum - sum;  // exclusive prefix
+	double best = -1.0;
+	int best_i = 0x7fffffff;
+	for (int k = 0; k < 8; ++k) {
+		const int b = lane * 8 + k;
+		const unsigned int h = hist[b];
+		c1 += h;
+		s1 += (unsigned long long)h * b;
+		if (b >= lo && b < hi) {
+			const unsigned long long c2 = total_cnt - c1, s2 = total_sum - s1;
+			const double w1 = (double)c1, w2 = (double)c2;
+			const double m1 = __ddiv_rn((double)s1, w1), m2 = __ddiv_rn((double)s2, w2);
+			const double d = __dsub_rn(m1, m2);
+			const double v = __dmul_rn(__dmul_rn(w1, w2), __dmul_rn(d, d));
+			if (v > best) {
+				best = v;
+				best_i = b;
+			}
+		}
+	}
+#pragma unroll
+	for (int o = 16; o > 0; o >>= 1) {
+		const double ob = __shfl_xor_sync(0xffffffffu, best, o);
+		const int oi = __shfl_xor_sync(0xffffffffu, best_i, o);
+		if (ob > best || (ob == best && oi < best_i)) {
+			best = ob;
+			best_i = oi;
+		}
+	}
+	return best_i;
+}
+
+// ---------------------------------------------------------------------------------------
+// strips, Otsu: one CTA per line -- histogram in shared memory, threshold, apply
+// ---------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(BTHREADS) og_otsu_strips_kernel(
+	const uint8_t *__restrict__ gray, const int32_t *__restrict__ steps, const int64_t *__restrict__ pix_offsets,
+	int n, uint8_t *__restrict__ out, int32_t *__restrict__ thresholds) {
+	__shared__ unsigned int hist[256];
+	__shared__ int s_t;
+	for (int li = blockIdx.x; li < n; li += gridDim.x) {
+		const int64_t off = pix_offsets[li];
+		const int64_t npix = (int64_t)steps[2 * li] * steps[2 * li + 1];
+		for (int k = threadIdx.x; k < 256; k += BTHREADS) hist[k] = 0;
+		__syncthreads();
+		for (int64_t i = threadIdx.x; i < npix; i += BTHREADS) atomicAdd(&hist[gray[off + i]], 1u);
+		__syncthreads();
+		if (threadIdx.x < 32) {
+			const int t = otsu_from_hist_warp(hist);
+			if (threadIdx.x == 0) {
+				s_t = t;
+				if (thresholds != nullptr) thresholds[li] = t;
+			}
+		}
+		__syncthreads();
+		const int t = s_t;
+		for (int64_t i = threadIdx.x; i < npix; i += BTHREADS) out[off + i] = gray[off + i] > t ? 255 : 0;
+		__syncthreads();
+	}
+}
+
+// ---------------------------------------------------------------------------------------
+// page, Otsu: global histogram (scratch), then threshold + apply
+// ---------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(BTHREADS) og_hist_kernel(
+	const uint8_t *__restrict__ src, int h, int w, int64_t pitch, unsigned int *__restrict__ hist_out) {
+	__shared__ unsigned int hist[256];
+	for (int k = threadIdx.x; k < 256; k += BTHREADS) hist[k] = 0;
+	__syncthreads();
+	const int64_t total = (int64_t)h * w;
+	for (int64_t i = (int64_t)blockIdx.x * BTHREADS + threadIdx.x; i < total; i += (int64_t)gridDim.x * BTHREADS) {
+		const int y = (int)(i / w), x = (int)(i - (int64_t)y * w);
+		atomicAdd(&hist[src[(int64_t)y * pitch + x]], 1u);
+	}
+	__syncthreads();
+	for (int k = threadIdx.x; k < 256; k += BTHREADS)
+		if (hist[k]) atomicAdd(hist_out + k, hist[k]);
+}
+
+__global__ void __launch_bounds__(BTHREADS) og_otsu_apply_kernel(
+	const uint8_t *__restrict__ src, int h, int w, int64_t src_pitch, uint8_t *__restrict__ dst, int64_t dst_pitch,
+	const unsigned int *__restrict__ hist_in, int32_t *__restrict__ threshold_out) {
+	__shared__ unsigned int hist[256];
+	__shared__ int s_t;
+	for (int k = threadIdx.x; k < 256; k += BTHREADS) hist[k] = hist_in[k];
+	__syncthreads();
+	if (threadIdx.x < 32) {
+		const int t = otsu_from_hist_warp(hist);
+		if (threadIdx.x == 0) {
+			s_t = t;
+			if (blockIdx.x == 0 && threshold_out != nullptr) *threshold_out = t;
+		}
+	}
+	__syncthreads();
+	const int t = s_t;
+	const int64_t total = (int64_t)h * w;
+	for (int64_t i = (int64_t)blockIdx.x * BTHREADS + threadIdx.x; i < total; i += (int64_t)gridDim.x * BTHREADS) {
+		const int y = (int)(i / w), x = (int)(i - (int64_t)y * w);
+		dst[(int64_t)y * dst_pitch + x] = src[(int64_t)y * src_pitch + x] > t ? 255 : 0;
+	}
+}
+
+// ---------------------------------------------------------------------------------------
+// Sauvola on one ST_H x ST_W output tile of an image (skimage 0.16.2 threshold_sauvola:
+// reflect-padded centred window, m = S1/w^2, s = sqrt(max(S2/w^2 - m*m, 0)),
+// t = m * (1 + k * ((s / r) - 1)) in float64).  Window sums are exact integers.
+// ---------------------------------------------------------------------------------------
+__device__ void sauvola_tile(const uint8_t *__restrict__ img, int h, int w, int64_t pitch,
+	uint8_t *__restrict__ out, int64_t out_pitch, int ty0, int tx0, int win, double kk, double rr,
+	unsigned char *smem) {
+	const int rad = win / 2;
+	const int PW = ST_W + 2 * rad, PH = ST_H + 2 * rad;
+	uint8_t *tile = smem;                                          // PH x PW
+	unsigned int *v1 = reinterpret_cast<unsigned int *>(smem + ((PH * PW + 15) & ~15));  // ST_H x PW
+	unsigned int *v2 = v1 + ST_H * PW;
+	const int tid = threadIdx.x;
+	__syncthreads();
+	for (int k = tid; k < PH * PW; k += BTHREADS) {
+		const int py = k / PW, px = k - py * PW;
+		const int y = reflect_index(ty0 - rad + py, h), x = reflect_index(tx0 - rad + px, w);
+		tile[k] = __ldg(img + (int64_t)y * pitch + x);
+	}
+	__syncthreads();
+	// vertical running sums, one padded column per thread
+	for (int px = tid; px < PW; px += BTHREADS) {
+		unsigned int s1 = 0, s2 = 0;
+		for (int py = 0; py < win; ++py) {
+			const unsigned int v = tile[py * PW + px];
+			s1 += v;
+			s2 += v * v;
+		}
+		v1[px] = s1;
+		v2[px] = s2;
+		for (int y = 1; y < ST_H; ++y) {
+			const unsigned int a = tile[(y - 1) * PW + px], b = tile[(y + win - 1) * PW + px];
+			s1 += b - a;
+			s2 += b * b - a * a;
+			v1[y * PW + px] = s1;
+			v2[y * PW + px] = s2;
+		}
+	}
+	__syncthreads();
+	// horizontal running sums: thread = (row, 8-column segment)
+	constexpr int SEG = ST_W * ST_H / BTHREADS;  // 8
+	const int row = tid / (ST_W / SEG), seg = tid % (ST_W / SEG);
+	const int y = ty0 + row;
+	if (y < h) {
+		const unsigned int *r1 = v1 + row * PW, *r2 = v2 + row * PW;
+		const int xb = seg * SEG;
+		unsigned int s1 = 0, s2 = 0;
+		for (int j = 0; j < win; ++j) {
+			s1 += r1[xb + j];
+			s2 += r2[xb + j];
+		}
+		const double n = (double)(win * win);
+		for (int j = 0; j < SEG; ++j) {
+			const int x = tx0 + xb + j;
+			if (j > 0) {
+				s1 += r1[xb + j + win - 1] - r1[xb + j - 1];
+				s2 += r2[xb + j + win - 1] - r2[xb + j - 1];
+			}
+			if (x < w) {
+				const double m = __ddiv_rn((double)s1, n);
+				const double g2 = __ddiv_rn((double)s2, n);
+				double var = __dsub_rn(g2, __dmul_rn(m, m));
+				var = var > 0.0 ? var : 0.0;
+				const double s = __dsqrt_rn(var);
+				const double t = __dmul_rn(m, __dadd_rn(1.0, __dmul_rn(kk, __dsub_rn(__ddiv_rn(s, rr), 1.0))));
+				const int pv = tile[(row + rad) * PW + xb + j + rad];
+				out[(int64_t)y * out_pitch + x] = ((double)pv > t) ? 255 : 0;
+			}
+		}
+	}
+}
+
+__host__ __device__ inline size_t sauvola_smem_bytes(int win) {
+	const int rad = win / 2;
+	const int PW = ST_W + 2 * rad, PH = ST_H + 2 * rad;
+	return (size_t)((PH * PW + 15) & ~15) + (size_t)2 * ST_H * PW * sizeof(unsigned int);
+}
+
+__global__ void __launch_bounds__(BTHREADS) og_sauvola_page_kernel(
+	const uint8_t *__restrict__ src, int h, int w, int64_t src_pitch, uint8_t *__restrict__ dst, int64_t dst_pitch,
+	int win, double kk, double rr) {
+	extern __shared__ __align__(16) unsigned char smem_raw[];
+	const int tiles_x = (w + ST_W - 1) / ST_W, tiles_y = (h + ST_H - 1) / ST_H;
+	const int64_t total = (int64_t)tiles_x * tiles_y;
+	for (int64_t t = blockIdx.x; t < total; t += gridDim.x) {
+		const int ty = (int)(t / tiles_x), tx = (int)(t - (int64_t)ty * tiles_x);
+		sauvola_tile(src, h, w, src_pitch, dst, dst_pitch, ty * ST_H, tx * ST_W, win, kk, rr, smem_raw);
+	}
+}
+
+__device__ __forceinline__ int find_line_b(const int32_t *__restrict__ chunk_offsets, int n, int item) {
+	int lo = 0, hi = n;
+	while (hi - lo > 1) {
+		int mid = (lo + hi) >> 1;
+		if (__ldg(chunk_offsets + mid) <= item) lo = mid; else hi = mid;
+	}
+	return lo;
+}
+
+__global__ void __launch_bounds__(BTHREADS) og_sauvola_strips_kernel(
+	const uint8_t *__restrict__ gray, const int32_t *__restrict__ steps, const int64_t *__restrict__ pix_offsets,
+	const int32_t *__restrict__ chunk_offsets, int n, uint8_t *__restrict__ out, int win, double kk, double rr) {
+	extern __shared__ __align__(16) unsigned char smem_raw[];
+	const int total = __ldg(chunk_offsets + n);
+	for (int item = blockIdx.x; item < total; item += gridDim.x) {
+		const int li = find_line_b(chunk_offsets, n, item);
+		const int chunk = item - __ldg(chunk_offsets + li);
+		const int w = steps[2 * li], h = steps[2 * li + 1];
+		const int64_t off = pix_offsets[li];
+		for (int ty0 = 0; ty0 < h; ty0 += ST_H)
+			sauvola_tile(gray + off, h, w, w, out + off, w, ty0, chunk * ST_W, win, kk, rr, smem_raw);
+	}
+}
+
+int check_window(int window) {
+	OG_REQUIRE(window >= 3 && (window & 1) == 1, OG_E_WINDOW,
+		"Window size w = %d must be odd and greater than 1.", window);
+	OG_REQUIRE(window <= MAX_WINDOW, OG_E_WINDOW, "window %d larger than the supported maximum %d", window, MAX_WINDOW);
+	return OG_OK;
+}
+
+}  // namespace
+
+extern "C" int og_binarize_strips(const uint8_t *gray, const int32_t *steps, const int64_t *pix_offsets,
+	const int32_t *chunk_offsets, int n, int mode, int window, uint8_t *out,
+	int32_t *thresholds_out, void *stream) {
+	OG_REQUIRE(n >= 0, OG_E_ARG, "n < 0");
+	OG_REQUIRE(mode == OG_BIN_OTSU || mode == OG_BIN_SAUVOLA, OG_E_ARG, "mode %d unsupported", mode);
+	if (n == 0) return OG_OK;
+	OG_REQUIRE(gray != nullptr && out != nullptr && steps != nullptr && pix_offsets != nullptr && chunk_offsets != nullptr,
+		OG_E_ARG, "NULL pointer");
+	cudaStream_t st = (cudaStream_t)stream;
+	if (mode == OG_BIN_OTSU) {
+		og_otsu_strips_kernel<<<min(n, OG_NUM_SMS * 8), BTHREADS, 0, st>>>(gray, steps, pix_offsets, n, out, thresholds_out);
+		return og_check_launch("og_otsu_strips_kernel");
+	}
+	int rc = check_window(window);
+	if (rc) return rc;
+	OG_REQUIRE(gray != out, OG_E_ARG, "Sauvola cannot run in place");
+	const size_t smem = sauvola_smem_bytes(window);
+	cudaError_t e = cudaFuncSetAttribute(og_sauvola_strips_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+	if (e != cudaSuccess) return og_set_error((int)e, "cudaFuncSetAttribute: %s", cudaGetErrorString(e));
+	og_sauvola_strips_kernel<<<OG_NUM_SMS * 4, BTHREADS, smem, st>>>(gray, steps, pix_offsets, chunk_offsets, n, out,
+		window, 0.2, 127.5);
+	return og_check_launch("og_sauvola_strips_kernel");
+}
+
+extern "C" int og_sauvola(const uint8_t *src, int h, int w, int64_t src_pitch, int window,
+	double k, double r, uint8_t *dst, int64_t dst_pitch, void *stream) {
+	OG_REQUIRE(src != nullptr && dst != nullptr, OG_E_ARG, "NULL pointer");
+	OG_REQUIRE(h > 0 && w > 0 && src_pitch >= w && dst_pitch >= w, OG_E_ARG, "image %d x %d / pitch invalid", w, h);
+	OG_REQUIRE(src != dst, OG_E_ARG, "Sauvola cannot run in place");
+	int rc = check_window(window);
+	if (rc) return rc;
+	const size_t smem = sauvola_smem_bytes(window);
+	cudaError_t e = cudaFuncSetAttribute(og_sauvola_page_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+	if (e != cudaSuccess) return og_set_error((int)e, "cudaFuncSetAttribute: %s", cudaGetErrorString(e));
+	const int64_t tiles = (int64_t)((w + ST_W - 1) / ST_W) * ((h + ST_H - 1) / ST_H);
+	const int blocks = (int)(tiles < (int64_t)OG_NUM_SMS * 8 ? tiles : (int64_t)OG_NUM_SMS * 8);
+	og_sauvola_page_kernel<<<blocks, BTHREADS, smem, (cudaStream_t)stream>>>(src, h, w, src_pitch, dst, dst_pitch, window, k, r);
+	return og_check_launch("og_sauvola_page_kernel");
+}
+
+extern "C" int og_otsu(const uint8_t *src, int h, int w, int64_t src_pitch,
+	uint8_t *dst, int64_t dst_pitch, uint32_t *hist_scratch, int32_t *threshold_out, void *stream) {
+	OG_REQUIRE(src != nullptr && dst != nullptr && hist_scratch != nullptr, OG_E_ARG, "NULL pointer");
+	OG_REQUIRE(h > 0 && w > 0 && src_pitch >= w && dst_pitch >= w, OG_E_ARG, "image %d x %d / pitch invalid", w, h);
+	OG_REQUIRE((int64_t)h * w < ((int64_t)1 << 32), OG_E_RANGE, "image larger than 2^32 pixels");
+	cudaStream_t st = (cudaStream_t)stream;
+	cudaError_t e = cudaMemsetAsync(hist_scratch, 0, 256 * sizeof(uint32_t), st);
+	if (e != cudaSuccess) return og_set_error((int)e, "cudaMemsetAsync: %s", cudaGetErrorString(e));
+	const int blocks = OG_NUM_SMS * 8;
+	og_hist_kernel<<<blocks, BTHREADS, 0, st>>>(src, h, w, src_pitch, hist_scratch);
+	int rc = og_check_launch("og_hist_kernel");
+	if (rc) return rc;
+	og_otsu_apply_kernel<<<blocks, BTHREADS, 0, st>>>(src, h, w, src_pitch, dst, dst_pitch, hist_scratch, threshold_out);
+	return og_check_launch("og_otsu_apply_kernel");
+}

@@ -1,0 +1,193 @@
+// Page kernels: dense map expansion (A2) fused with the page remap (A3/A4).
+//
+// Reference: Grid.points("full") origami/core/dewarp.py:514-526 and Dewarper.dewarped /
+// dewarp_image origami/core/dewarp.py:608-627.  HBM-bound: 9 B written + ~1 B read per
+// dewarped pixel; no tensor cores.
+//
+// Layout: one CTA = 64 x 4 threads covers a 256 x 32 pixel tile of the dewarped page.  A
+// thread owns 4 consecutive pixels of a row (one uchar4 image store, two float4 map stores:
+// a warp writes 128 B / 1 KiB contiguous per row) and walks 8 consecutive rows, so the
+// x-axis interpolation state and the horizontally interpolated sparse rows stay in
+// registers; they are refreshed only when the row crosses into the next sparse cell, which
+// is uniform across the CTA.
+#include "og_common.cuh"
+
+namespace {
+
+constexpr int TPX = 4;    // pixels per thread along x
+constexpr int TBX = 64;   // threads along x
+constexpr int TBY = 4;    // thread rows
+constexpr int TROWS = 8;  // rows walked per thread
+constexpr int TILE_W = TPX * TBX;
+constexpr int TILE_H = TBY * TROWS;
+
+struct PageParams {
+	const uint8_t *src;
+	int H, W;
+	int64_t src_pitch;
+	const float2 *grid;
+	int gh, gw, cell;
+	uint8_t *dst;
+	int64_t dst_pitch;
+	float *map_out;
+	float scale_x, scale_y;
+};
+
+template <bool LINEAR>
+__global__ void __launch_bounds__(TBX *TBY) og_page_kernel(PageParams p) {
+	const int Wd = p.gw * p.cell, Hd = p.gh * p.cell;
+	const int x0 = (blockIdx.x * TBX + threadIdx.x) * TPX;
+	const int ybeg = blockIdx.y * TILE_H + threadIdx.y * TROWS;
+	if (x0 >= Wd || ybeg >= Hd) return;
+	const double inv_cell = 1.0 / (double)p.cell;
+	const int npx = min(TPX, Wd - x0);
+
+	int sx[TPX], sx1[TPX];
+	float a0[TPX], a1[TPX];
+#pragma unroll
+	for (int k = 0; k < TPX; ++k) {
+		og_axis ax = og_resize_axis_x(min(x0 + k, Wd - 1), inv_cell, p.gw);
+		sx[k] = ax.i;
+		sx1[k] = min(ax.i + 1, p.gw - 1);
+		a1[k] = ax.f;
+		a0[k] = __fsub_rn(1.f, ax.f);
+	}
+
+	const bool vec_map = p.map_out != nullptr && npx == TPX && (Wd & 1) == 0 &&
+		((reinterpret_cast<uintptr_t>(p.map_out) & 15) == 0);
+	const bool vec_img = p.dst != nullptr && npx == TPX && (p.dst_pitch & 3) == 0 &&
+		((reinterpret_cast<uintptr_t>(p.dst) & 3) == 0);
+
+	int cur_r0 = -1, cur_r1 = -1;
+	float2 h0[TPX], h1[TPX];
+
+	const int yend = min(ybeg + TROWS, Hd);
+	for (int y = ybeg; y < yend; ++y) {
+		og_axis ay = og_resize_axis(y, inv_cell);
+		const int r0 = min(max(ay.i, 0), p.gh - 1);
+		const int r1 = min(max(ay.i + 1, 0), p.gh - 1);
+		const float b1 = ay.f, b0 = __fsub_rn(1.f, ay.f);
+		if (r0 != cur_r0 || r1 != cur_r1) {
+			cur_r0 = r0;
+			cur_r1 = r1;
+			const float2 *g0 = p.grid + (size_t)r0 * p.gw;
+			const float2 *g1 = p.grid + (size_t)r1 * p.gw;
+#pragma unroll
+			for (int k = 0; k < TPX; ++k) {
+				float2 s00 = __ldg(g0 + sx[k]), s01 = __ldg(g0 + sx1[k]);
+				float2 s10 = __ldg(g1 + sx[k]), s11 = __ldg(g1 + sx1[k]);
+				h0[k].x = og_lerp_cv(s00.x, s01.x, a0[k], a1[k]);
+				h0[k].y = og_lerp_cv(s00.y, s01.y, a0[k], a1[k]);
+				h1[k].x = og_lerp_cv(s10.x, s11.x, a0[k], a1[k]);
+				h1[k].y = og_lerp_cv(s10.y, s11.y, a0[k], a1[k]);
+			}
+		}
+		float2 d[TPX];
+#pragma unroll
+		for (int k = 0; k < TPX; ++k) {
+			d[k].x = og_lerp_cv(h0[k].x, h1[k].x, b0, b1);
+			d[k].y = og_lerp_cv(h0[k].y, h1[k].y, b0, b1);
+		}
+		if (p.map_out != nullptr) {
+			float *row = p.map_out + ((size_t)y * Wd + x0) * 2;
+			if (vec_map) {
+				__stcs(reinterpret_cast<float4 *>(row), make_float4(d[0].x, d[0].y, d[1].x, d[1].y));
+				__stcs(reinterpret_cast<float4 *>(row) + 1, make_float4(d[2].x, d[2].y, d[3].x, d[3].y));
+			} else {
+#pragma unroll
+				for (int k = 0; k < TPX; ++k)
+					if (k < npx) __stcs(reinterpret_cast<float2 *>(row) + k, d[k]);
+			}
+		}
+		if (p.dst != nullptr) {
+			int v[TPX];
+#pragma unroll
+			for (int k = 0; k < TPX; ++k) {
+				float mx = __fmul_rn(d[k].x, p.scale_x);
+				float my = __fmul_rn(d[k].y, p.scale_y);
+				v[k] = LINEAR ? og_sample_linear(p.src, p.H, p.W, p.src_pitch, mx, my, 0)
+							  : og_sample_nearest(p.src, p.H, p.W, p.src_pitch, mx, my, 0);
+			}
+			uint8_t *orow = p.dst + (int64_t)y * p.dst_pitch + x0;
+			if (vec_img) {
+				uint32_t pk = (uint32_t)v[0] | ((uint32_t)v[1] << 8) | ((uint32_t)v[2] << 16) |
+					((uint32_t)v[3] << 24);
+				__stcs(reinterpret_cast<uint32_t *>(orow), pk);
+			} else {
+#pragma unroll
+				for (int k = 0; k < TPX; ++k)
+					if (k < npx) orow[k] = (uint8_t)v[k];
+			}
+		}
+	}
+}
+
+int launch_page(const PageParams &p, int interp, cudaStream_t st) {
+	const int Wd = p.gw * p.cell, Hd = p.gh * p.cell;
+	dim3 block(TBX, TBY);
+	dim3 grid((Wd + TILE_W - 1) / TILE_W, (Hd + TILE_H - 1) / TILE_H);
+	if (interp == OG_INTER_LINEAR)
+		og_page_kernel<true><<<grid, block, 0, st>>>(p);
+	else
+		og_page_kernel<false><<<grid, block, 0, st>>>(p);
+	return og_check_launch("og_page_kernel");
+}
+
+int check_grid(const float *grid, int gh, int gw, int cell) {
+	OG_REQUIRE(grid != nullptr, OG_E_ARG, "grid is NULL");
+	OG_REQUIRE(gh >= 2 && gw >= 2 && cell >= 1, OG_E_ARG, "grid shape (%d, %d) cell %d invalid", gh, gw, cell);
+	OG_REQUIRE((reinterpret_cast<uintptr_t>(grid) & 7) == 0, OG_E_ALIGN, "grid must be 8-byte aligned");
+	// cv2.remap asserts dst.cols < SHRT_MAX && dst.rows < SHRT_MAX
+	OG_REQUIRE((int64_t)gh * cell < 32767 && (int64_t)gw * cell < 32767, OG_E_RANGE,
+		"dewarped size %lld x %lld exceeds OpenCV's 32767 limit", (long long)gw * cell, (long long)gh * cell);
+	return OG_OK;
+}
+
+}  // namespace
+
+extern "C" int og_expand_map(const float *grid, int gh, int gw, int cell, float *map_out, void *stream) {
+	int rc = check_grid(grid, gh, gw, cell);
+	if (rc) return rc;
+	OG_REQUIRE(map_out != nullptr, OG_E_ARG, "map_out is NULL");
+	OG_REQUIRE((reinterpret_cast<uintptr_t>(map_out) & 7) == 0, OG_E_ALIGN, "map_out must be 8-byte aligned");
+	PageParams p{};
+	p.grid = reinterpret_cast<const float2 *>(grid);
+	p.gh = gh;
+	p.gw = gw;
+	p.cell = cell;
+	p.map_out = map_out;
+	p.scale_x = p.scale_y = 1.f;
+	return launch_page(p, OG_INTER_LINEAR, (cudaStream_t)stream);
+}
+
+extern "C" int og_remap_page(const uint8_t *src, int H, int W, int64_t src_pitch,
+	const float *grid, int gh, int gw, int cell,
+	uint8_t *dst, int64_t dst_pitch, float *map_out,
+	float scale_x, float scale_y, int interp, void *stream) {
+	int rc = check_grid(grid, gh, gw, cell);
+	if (rc) return rc;
+	OG_REQUIRE(dst != nullptr || map_out != nullptr, OG_E_ARG, "both dst and map_out are NULL");
+	OG_REQUIRE(interp == OG_INTER_LINEAR || interp == OG_INTER_NEAREST, OG_E_ARG, "interp %d unsupported", interp);
+	if (dst != nullptr) {
+		OG_REQUIRE(src != nullptr && H > 0 && W > 0, OG_E_ARG, "src is NULL or empty (%d x %d)", W, H);
+		OG_REQUIRE(H < 32767 && W < 32767, OG_E_RANGE, "source %d x %d exceeds OpenCV's 32767 limit", W, H);
+		OG_REQUIRE(src_pitch >= W && dst_pitch >= (int64_t)gw * cell, OG_E_ARG, "pitch smaller than row");
+	}
+	if (map_out != nullptr)
+		OG_REQUIRE((reinterpret_cast<uintptr_t>(map_out) & 7) == 0, OG_E_ALIGN, "map_out must be 8-byte aligned");
+	PageParams p{};
+	p.src = src;
+	p.H = H;
+	p.W = W;
+	p.src_pitch = src_pitch;
+	p.grid = reinterpret_cast<const float2 *>(grid);
+	p.gh = gh;
+	p.gw = gw;
+	p.cell = cell;
+	p.dst = dst;
+	p.dst_pitch = dst_pitch;
+	p.map_out = map_out;
+	p.scale_x = scale_x;
+	p.scale_y = scale_y;
+	return launch_page(p, interp, (cudaStream_t)stream);
+}

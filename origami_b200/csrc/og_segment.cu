@@ -1,0 +1,190 @@
+// Segmentation post-process (A18/A19) and the deskew affine warp (A11).
+//
+// Reference: label argmax origami/core/predict.py:281-285
+// (np.argmax(np.sum(pr_masks, axis=0), -1).astype(uint8)), class masks
+// origami/core/contours.py:488 (pixels == c.value), Line._extract_deskewed
+// origami/core/block.py:155-172 (cv2.warpAffine, BORDER_CONSTANT).
+// HBM-bound streaming kernels: 4*M*C bytes read and 1 + n_mask bytes written per pixel.
+#include "og_common.cuh"
+
+namespace {
+
+constexpr int MAX_MASKS = 16;
+
+struct MaskValues {
+	uint8_t v[MAX_MASKS];
+};
+
+// C == 4: a thread owns 4 consecutive pixels -> float4 loads, uchar4 stores
+__global__ void __launch_bounds__(256) og_argmax4_kernel(
+	const float4 *__restrict__ probs, int M, int64_t npix,
+	uint8_t *__restrict__ labels, uint8_t *__restrict__ masks, MaskValues mv, int n_mask) {
+	const int64_t q = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+	const int64_t i0 = q * 4;
+	if (i0 >= npix) return;
+	const int cnt = (int)min((int64_t)4, npix - i0);
+	uint32_t lab[4] = {0, 0, 0, 0};
+#pragma unroll
+	for (int k = 0; k < 4; ++k) {
+		if (k < cnt) {
+			float4 acc = __ldcs(probs + i0 + k);
+			for (int m = 1; m < M; ++m) {
+				const float4 v = __ldcs(probs + (int64_t)m * npix + i0 + k);
+				acc.x = __fadd_rn(acc.x, v.x);
+				acc.y = __fadd_rn(acc.y, v.y);
+				acc.z = __fadd_rn(acc.z, v.z);
+				acc.w = __fadd_rn(acc.w, v.w);
+			}
+			float best = acc.x;
+			uint32_t bi = 0;
+			if (acc.y > best) { best = acc.y; bi = 1; }
+			if (acc.z > best) { best = acc.z; bi = 2; }
+			if (acc.w > best) { best = acc.w; bi = 3; }
+			lab[k] = bi;
+		}
+	}
+	const bool vec = cnt == 4 && ((reinterpret_cast<uintptr_t>(labels) & 3) == 0);
+	if (vec) {
+		reinterpret_cast<uint32_t *>(labels)[q] = lab[0] | (lab[1] << 8) | (lab[2] << 16) | (lab[3] << 24);
+	} else {
+		for (int k = 0; k < cnt; ++k) labels[i0 + k] = (uint8_t)lab[k];
+	}
+	if (masks != nullptr) {
+		const bool vecm = cnt == 4 && ((reinterpret_cast<uintptr_t>(masks) & 3) == 0) && ((npix & 3) == 0);
+		for (int j = 0; j < n_mask; ++j) {
+			const uint32_t val = mv.v[j];
+			uint8_t *mrow = masks + (int64_t)j * npix;
+			if (vecm) {
+				reinterpret_cast<uint32_t *>(mrow)[q] = (uint32_t)(lab[0] == val) | ((uint32_t)(lab[1] == val) << 8) |
+					((uint32_t)(lab[2] == val) << 16) | ((uint32_t)(lab[3] == val) << 24);
+			} else {
+				for (int k = 0; k < cnt; ++k) mrow[i0 + k] = lab[k] == val;
+			}
+		}
+	}
+}
+
+// any C: one pixel per thread
+__global__ void __launch_bounds__(256) og_argmax_kernel(
+	const float *__restrict__ probs, int M, int C, int64_t npix,
+	uint8_t *__restrict__ labels, uint8_t *__restrict__ masks, MaskValues mv, int n_mask) {
+	const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+	if (i >= npix) return;
+	float best = 0.f;
+	int bi = 0;
+	for (int c = 0; c < C; ++c) {
+		float acc = probs[i * C + c];
+		for (int m = 1; m < M; ++m) acc = __fadd_rn(acc, probs[((int64_t)m * npix + i) * C + c]);
+		if (c == 0 || acc > best) {
+			best = acc;
+			bi = c;
+		}
+	}
+	labels[i] = (uint8_t)bi;
+	if (masks != nullptr)
+		for (int j = 0; j < n_mask; ++j) masks[(int64_t)j * npix + i] = (bi == mv.v[j]);
+}
+
+__global__ void __launch_bounds__(256) og_masks_kernel(
+	const uint8_t *__restrict__ labels, int h, int w, int64_t pitch,
+	uint8_t *__restrict__ masks, MaskValues mv, int n_mask) {
+	const int64_t npix = (int64_t)h * w;
+	const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+	if (i >= npix) return;
+	const int y = (int)(i / w), x = (int)(i - (int64_t)y * w);
+	const int v = labels[(int64_t)y * pitch + x];
+	for (int j = 0; j < n_mask; ++j) masks[(int64_t)j * npix + i] = (v == mv.v[j]);
+}
+
+struct AffineParams {
+	double m00, m01, b1, m10, m11, b2;  // inverse map
+};
+
+__global__ void __launch_bounds__(256) og_warp_affine_kernel(
+	const uint8_t *__restrict__ src, int H, int W, int64_t src_pitch, AffineParams a,
+	uint8_t *__restrict__ dst, int width, int height, int64_t dst_pitch, int border) {
+	const int x = blockIdx.x * blockDim.x + threadIdx.x;
+	const int y = blockIdx.y;
+	if (x >= width || y >= height) return;
+	// imgwarp.cpp warpAffine: AB_BITS = 10, round_delta = AB_SCALE / INTER_TAB_SIZE / 2 = 16
+	const int adelta = __double2int_rn(__dmul_rn(__dmul_rn(a.m00, (double)x), 1024.0));
+	const int bdelta = __double2int_rn(__dmul_rn(__dmul_rn(a.m10, (double)x), 1024.0));
+	const int X0 = __double2int_rn(__dmul_rn(__dadd_rn(__dmul_rn(a.m01, (double)y), a.b1), 1024.0)) + 16;
+	const int Y0 = __double2int_rn(__dmul_rn(__dadd_rn(__dmul_rn(a.m11, (double)y), a.b2), 1024.0)) + 16;
+	const int X = (X0 + adelta) >> 5, Y = (Y0 + bdelta) >> 5;
+	og_fix q;
+	q.ix = og_sat_short(X >> 5);
+	q.iy = og_sat_short(Y >> 5);
+	q.fx = X & 31;
+	q.fy = Y & 31;
+	const int p00 = og_tap(src, H, W, src_pitch, q.iy, q.ix, border);
+	const int p01 = og_tap(src, H, W, src_pitch, q.iy, q.ix + 1, border);
+	const int p10 = og_tap(src, H, W, src_pitch, q.iy + 1, q.ix, border);
+	const int p11 = og_tap(src, H, W, src_pitch, q.iy + 1, q.ix + 1, border);
+	dst[(int64_t)y * dst_pitch + x] = (uint8_t)og_blend(q, p00, p01, p10, p11);
+}
+
+int fill_masks(MaskValues &mv, const uint8_t *mask_values, int n_mask) {
+	OG_REQUIRE(n_mask >= 0 && n_mask <= MAX_MASKS, OG_E_ARG, "n_mask %d outside [0, %d]", n_mask, MAX_MASKS);
+	OG_REQUIRE(n_mask == 0 || mask_values != nullptr, OG_E_ARG, "mask_values is NULL");
+	for (int j = 0; j < n_mask; ++j) mv.v[j] = mask_values[j];
+	return OG_OK;
+}
+
+}  // namespace
+
+extern "C" int og_argmax_labels(const float *probs, int M, int C, int h, int w,
+	uint8_t *labels_out, uint8_t *masks_out, const uint8_t *mask_values, int n_mask, void *stream) {
+	OG_REQUIRE(probs != nullptr && labels_out != nullptr, OG_E_ARG, "NULL pointer");
+	OG_REQUIRE(M >= 1 && C >= 1 && C <= 256 && h > 0 && w > 0, OG_E_ARG, "shape (%d, %d, %d, %d) invalid", M, h, w, C);
+	MaskValues mv{};
+	int rc = fill_masks(mv, mask_values, masks_out ? n_mask : 0);
+	if (rc) return rc;
+	const int64_t npix = (int64_t)h * w;
+	cudaStream_t st = (cudaStream_t)stream;
+	if (C == 4 && (reinterpret_cast<uintptr_t>(probs) & 15) == 0) {
+		const int64_t quads = (npix + 3) / 4;
+		og_argmax4_kernel<<<(unsigned)((quads + 255) / 256), 256, 0, st>>>(
+			reinterpret_cast<const float4 *>(probs), M, npix, labels_out, masks_out, mv, n_mask);
+	} else {
+		og_argmax_kernel<<<(unsigned)((npix + 255) / 256), 256, 0, st>>>(probs, M, C, npix, labels_out, masks_out, mv, n_mask);
+	}
+	return og_check_launch("og_argmax_kernel");
+}
+
+extern "C" int og_class_masks(const uint8_t *labels, int h, int w, int64_t pitch,
+	uint8_t *masks_out, const uint8_t *mask_values, int n_mask, void *stream) {
+	OG_REQUIRE(labels != nullptr && masks_out != nullptr, OG_E_ARG, "NULL pointer");
+	OG_REQUIRE(h > 0 && w > 0 && pitch >= w, OG_E_ARG, "image %d x %d / pitch invalid", w, h);
+	MaskValues mv{};
+	int rc = fill_masks(mv, mask_values, n_mask);
+	if (rc) return rc;
+	if (n_mask == 0) return OG_OK;
+	const int64_t npix = (int64_t)h * w;
+	og_masks_kernel<<<(unsigned)((npix + 255) / 256), 256, 0, (cudaStream_t)stream>>>(labels, h, w, pitch, masks_out, mv, n_mask);
+	return og_check_launch("og_masks_kernel");
+}
+
+extern "C" int og_warp_affine(const uint8_t *src, int H, int W, int64_t src_pitch,
+	const double *M, uint8_t *dst, int width, int height, int64_t dst_pitch, int border_value, void *stream) {
+	OG_REQUIRE(src != nullptr && dst != nullptr && M != nullptr, OG_E_ARG, "NULL pointer");
+	OG_REQUIRE(H > 0 && W > 0 && width > 0 && height > 0 && src_pitch >= W && dst_pitch >= width, OG_E_ARG, "size / pitch invalid");
+	OG_REQUIRE(H < 32767 && W < 32767 && width < 32767 && height < 32767, OG_E_RANGE, "size exceeds OpenCV's 32767 limit");
+	// invert the forward matrix exactly as imgwarp.cpp does (double precision)
+	volatile double m0 = M[0], m1 = M[1], m2 = M[2], m3 = M[3], m4 = M[4], m5 = M[5];
+	double D = m0 * m4 - m1 * m3;
+	D = D != 0 ? 1. / D : 0;
+	const double A11 = m4 * D, A22 = m0 * D;
+	AffineParams a;
+	a.m00 = A11;
+	a.m01 = m1 * (-D);
+	a.m10 = m3 * (-D);
+	a.m11 = A22;
+	volatile double t0 = -a.m00 * m2, t1 = a.m01 * m5, t2 = -a.m10 * m2, t3 = a.m11 * m5;
+	a.b1 = t0 - t1;
+	a.b2 = t2 - t3;
+	dim3 block(256), grid((width + 255) / 256, height);
+	og_warp_affine_kernel<<<grid, block, 0, (cudaStream_t)stream>>>(src, H, W, src_pitch, a, dst, width, height, dst_pitch,
+		border_value & 255);
+	return og_check_launch("og_warp_affine_kernel");
+}

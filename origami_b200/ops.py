@@ -1,0 +1,253 @@
+"""
+Thin torch-tensor front end of the C ABI: allocates outputs with torch, passes
+`tensor.data_ptr()` and the current CUDA stream to liborigami_b200.so.  torch is used for
+device memory and streams only; every computation happens in the hand-written kernels.
+"""
+
+import numpy as np
+import torch
+
+from . import _lib
+from ._lib import LINE_DTYPE, OG_BIN_NONE, OG_BIN_OTSU, OG_BIN_SAUVOLA, OG_INTER_LINEAR, OG_INTER_NEAREST
+
+PITCH_ALIGN = 128
+
+
+def _require_cuda():
+	if not torch.cuda.is_available():
+		raise _lib.OrigamiB200Error("origami_b200 needs a CUDA device (there is no CPU fallback)")
+
+
+def _stream():
+	return torch.cuda.current_stream().cuda_stream
+
+
+def _ptr(t):
+	return 0 if t is None else t.data_ptr()
+
+
+def _check_u8_image(t, name):
+	if t.dtype != torch.uint8 or t.dim() != 2 or not t.is_cuda or t.stride(1) != 1:
+		raise ValueError("%s must be a 2-D uint8 CUDA tensor with unit column stride" % name)
+
+
+def alloc_image(h, w, device=None):
+	"""(h, w) uint8 view into a buffer whose row pitch is a multiple of 128 bytes, so the
+	kernels can use aligned vector stores for any width."""
+	_require_cuda()
+	pitch = (w + PITCH_ALIGN - 1) // PITCH_ALIGN * PITCH_ALIGN
+	buf = torch.empty((h, pitch), dtype=torch.uint8, device=device or "cuda")
+	return buf[:, :w]
+
+
+def to_device_image(a, device=None):
+	"""Host uint8 (h, w) ndarray -> pitched device image."""
+	a = np.ascontiguousarray(a, dtype=np.uint8)
+	out = alloc_image(a.shape[0], a.shape[1], device)
+	out.copy_(torch.from_numpy(a))
+	return out
+
+
+def _check_grid(grid):
+	if grid.dtype != torch.float32 or grid.dim() != 3 or grid.shape[2] != 2 or not grid.is_cuda or not grid.is_contiguous():
+		raise ValueError("grid must be a contiguous float32 CUDA tensor of shape (gh, gw, 2)")
+	return int(grid.shape[0]), int(grid.shape[1])
+
+
+def expand_map(grid, cell, out=None):
+	"""Grid.points("full") (reference origami/core/dewarp.py:514-526)."""
+	_require_cuda()
+	gh, gw = _check_grid(grid)
+	if out is None:
+		out = torch.empty((gh * cell, gw * cell, 2), dtype=torch.float32, device=grid.device)
+	_lib.call("og_expand_map", grid.data_ptr(), gh, gw, cell, out.data_ptr(), _stream())
+	return out
+
+
+def remap_page(src, grid, cell, dst=None, map_out=None, scale=(1.0, 1.0), interpolation=OG_INTER_LINEAR,
+		want_image=True):
+	"""Dewarper.dewarped / dewarp_image (reference origami/core/dewarp.py:608-627) fused with
+	the map expansion.  Returns (dst, map_out)."""
+	_require_cuda()
+	gh, gw = _check_grid(grid)
+	H = W = 0
+	if want_image:
+		_check_u8_image(src, "src")
+		H, W = int(src.shape[0]), int(src.shape[1])
+		if dst is None:
+			dst = alloc_image(gh * cell, gw * cell, grid.device)
+		_check_u8_image(dst, "dst")
+	_lib.call("og_remap_page", _ptr(src) if want_image else 0, H, W, src.stride(0) if want_image else 0,
+		grid.data_ptr(), gh, gw, cell,
+		_ptr(dst) if want_image else 0, dst.stride(0) if want_image else 0, _ptr(map_out),
+		float(np.float32(scale[0])), float(np.float32(scale[1])), int(interpolation), _stream())
+	return dst, map_out
+
+
+def inverse_yx(grid, cell, pts_yx):
+	"""Grid.inverse_yx (reference origami/core/dewarp.py:561-567) on an (n, 2) float64 tensor."""
+	_require_cuda()
+	gh, gw = _check_grid(grid)
+	pts = pts_yx.contiguous()
+	if pts.dtype != torch.float64 or pts.dim() != 2 or pts.shape[1] != 2:
+		raise ValueError("pts_yx must be float64 (n, 2)")
+	out = torch.empty_like(pts)
+	_lib.call("og_inverse_yx", grid.data_ptr(), gh, gw, cell, pts.data_ptr(), pts.shape[0], out.data_ptr(), _stream())
+	return out
+
+
+def pack_lines(records):
+	"""records: iterable of dicts with p, right, up and optional cp, cright, xres, yres, xsteps,
+	ysteps -> structured ndarray of og_line."""
+	records = list(records)
+	a = np.zeros(len(records), dtype=LINE_DTYPE)
+	for i, r in enumerate(records):
+		a["p"][i] = r["p"]
+		a["right"][i] = r["right"]
+		a["up"][i] = r["up"]
+		a["cp"][i] = r.get("cp", r["p"])
+		a["cright"][i] = r.get("cright", r["right"])
+		a["xres"][i] = r.get("xres", 1.0)
+		a["yres"][i] = r.get("yres", 1.0)
+		a["xsteps"][i] = r.get("xsteps") or 0
+		a["ysteps"][i] = r.get("ysteps") or 0
+	return a
+
+
+def lines_to_device(lines_np, device=None):
+	_require_cuda()
+	raw = torch.from_numpy(lines_np.view(np.uint8).reshape(-1).copy())
+	return raw.to(device or "cuda", non_blocking=True)
+
+
+class LinePlan:
+	"""Device-side step counts and offsets of a batch of lines (output of og_line_steps)."""
+
+	def __init__(self, lines_dev, n, steps, pix_offsets, chunk_offsets):
+		self.lines = lines_dev
+		self.n = n
+		self.steps = steps
+		self.pix_offsets = pix_offsets
+		self.chunk_offsets = chunk_offsets
+
+
+def line_steps(grid, cell, lines_dev, n):
+	"""Step counts of Line.warped_grid (reference origami/core/block.py:226-236) + offsets."""
+	_require_cuda()
+	gh, gw = _check_grid(grid)
+	dev = grid.device
+	steps = torch.empty((max(n, 1), 2), dtype=torch.int32, device=dev)
+	pix = torch.empty((n + 1,), dtype=torch.int64, device=dev)
+	chunks = torch.empty((n + 1,), dtype=torch.int32, device=dev)
+	_lib.call("og_line_steps", grid.data_ptr(), gh, gw, cell, lines_dev.data_ptr(), n,
+		steps.data_ptr(), pix.data_ptr(), chunks.data_ptr(), _stream())
+	return LinePlan(lines_dev, n, steps, pix, chunks)
+
+
+def warped_grids(grid, cell, plan, out):
+	"""Line.warped_grid for every line; out: float32 buffer of 2*capacity elements."""
+	gh, gw = _check_grid(grid)
+	_lib.call("og_warped_grids", grid.data_ptr(), gh, gw, cell, plan.lines.data_ptr(), plan.n,
+		plan.steps.data_ptr(), plan.pix_offsets.data_ptr(), plan.chunk_offsets.data_ptr(),
+		out.data_ptr(), out.numel() // 2, _stream())
+	return out
+
+
+def extract_lines(src, grid, cell, plan, out, bbox=None):
+	"""Line.dewarped_image for every line into the packed uint8 buffer `out`."""
+	gh, gw = _check_grid(grid)
+	_check_u8_image(src, "src")
+	_lib.call("og_extract_lines", src.data_ptr(), int(src.shape[0]), int(src.shape[1]), src.stride(0),
+		grid.data_ptr(), gh, gw, cell, plan.lines.data_ptr(), plan.n,
+		plan.steps.data_ptr(), plan.pix_offsets.data_ptr(), plan.chunk_offsets.data_ptr(),
+		out.data_ptr(), out.numel(), _ptr(bbox), _stream())
+	return out
+
+
+def binarize_strips(gray, plan, mode, window=15, out=None, thresholds=None):
+	if out is None:
+		out = torch.empty_like(gray)
+	_lib.call("og_binarize_strips", gray.data_ptr(), plan.steps.data_ptr(), plan.pix_offsets.data_ptr(),
+		plan.chunk_offsets.data_ptr(), plan.n, int(mode), int(window), out.data_ptr(), _ptr(thresholds), _stream())
+	return out
+
+
+def sauvola(src, window=15, k=0.2, r=127.5, dst=None):
+	"""(src > threshold_sauvola(src, window)) * 255 on a device image."""
+	_require_cuda()
+	_check_u8_image(src, "src")
+	h, w = int(src.shape[0]), int(src.shape[1])
+	if dst is None:
+		dst = alloc_image(h, w, src.device)
+	_lib.call("og_sauvola", src.data_ptr(), h, w, src.stride(0), int(window), float(k), float(r),
+		dst.data_ptr(), dst.stride(0), _stream())
+	return dst
+
+
+def otsu(src, dst=None, hist_scratch=None, threshold=None):
+	"""(src > threshold_otsu(src)) * 255 on a device image; returns (dst, threshold tensor)."""
+	_require_cuda()
+	_check_u8_image(src, "src")
+	h, w = int(src.shape[0]), int(src.shape[1])
+	if dst is None:
+		dst = alloc_image(h, w, src.device)
+	if hist_scratch is None:
+		hist_scratch = torch.empty((256,), dtype=torch.int32, device=src.device)
+	if threshold is None:
+		threshold = torch.empty((1,), dtype=torch.int32, device=src.device)
+	_lib.call("og_otsu", src.data_ptr(), h, w, src.stride(0), dst.data_ptr(), dst.stride(0),
+		hist_scratch.data_ptr(), threshold.data_ptr(), _stream())
+	return dst, threshold
+
+
+def sample_labels(labels, page_shape, grid, cell, plan, n_classes):
+	"""ConfidenceSampler counts (reference origami/batch/detect/lines.py:34-54)."""
+	gh, gw = _check_grid(grid)
+	_check_u8_image(labels, "labels")
+	counts = torch.empty((max(plan.n, 1), n_classes), dtype=torch.int64, device=grid.device)
+	overflow = torch.empty((max(plan.n, 1),), dtype=torch.int64, device=grid.device)
+	_lib.call("og_sample_labels", labels.data_ptr(), int(labels.shape[0]), int(labels.shape[1]), labels.stride(0),
+		int(page_shape[0]), int(page_shape[1]), grid.data_ptr(), gh, gw, cell, plan.lines.data_ptr(), plan.n,
+		plan.steps.data_ptr(), plan.chunk_offsets.data_ptr(), n_classes, counts.data_ptr(), overflow.data_ptr(), _stream())
+	return counts[:plan.n], overflow[:plan.n]
+
+
+def argmax_labels(probs, mask_values=None):
+	"""probs (M, h, w, C) float32 -> (labels (h, w) uint8, masks (n_mask, h, w) uint8 | None)."""
+	_require_cuda()
+	if probs.dtype != torch.float32 or probs.dim() != 4 or not probs.is_cuda or not probs.is_contiguous():
+		raise ValueError("probs must be a contiguous float32 CUDA tensor (M, h, w, C)")
+	M, h, w, C = (int(v) for v in probs.shape)
+	labels = torch.empty((h, w), dtype=torch.uint8, device=probs.device)
+	masks = None
+	mv = None
+	n_mask = 0
+	if mask_values is not None and len(mask_values) > 0:
+		mv = np.ascontiguousarray(mask_values, dtype=np.uint8)
+		n_mask = int(mv.shape[0])
+		masks = torch.empty((n_mask, h, w), dtype=torch.uint8, device=probs.device)
+	_lib.call("og_argmax_labels", probs.data_ptr(), M, C, h, w, labels.data_ptr(), _ptr(masks),
+		mv.ctypes.data if mv is not None else 0, n_mask, _stream())
+	return labels, masks
+
+
+def class_masks(labels, mask_values):
+	_require_cuda()
+	_check_u8_image(labels, "labels")
+	mv = np.ascontiguousarray(mask_values, dtype=np.uint8)
+	h, w = int(labels.shape[0]), int(labels.shape[1])
+	masks = torch.empty((int(mv.shape[0]), h, w), dtype=torch.uint8, device=labels.device)
+	_lib.call("og_class_masks", labels.data_ptr(), h, w, labels.stride(0), masks.data_ptr(), mv.ctypes.data,
+		int(mv.shape[0]), _stream())
+	return masks
+
+
+def warp_affine(src, M, width, height, border_value=0):
+	"""cv2.warpAffine(src, M, (width, height), INTER_LINEAR, BORDER_CONSTANT, border_value)."""
+	_require_cuda()
+	_check_u8_image(src, "src")
+	Mh = np.ascontiguousarray(M, dtype=np.float64).reshape(6)
+	dst = alloc_image(height, width, src.device)
+	_lib.call("og_warp_affine", src.data_ptr(), int(src.shape[0]), int(src.shape[1]), src.stride(0),
+		Mh.ctypes.data, dst.data_ptr(), width, height, dst.stride(0), int(border_value), _stream())
+	return dst
