@@ -1,0 +1,432 @@
+#!/usr/bin/env python3
+"""
+bench.py -- page-geometry hot path of Origami on B200: dense map expansion + bilinear page
+remap + line-strip extraction (+ Otsu binarization of the strips) on synthetic 600-dpi
+4800x7200 broadsheet pages (BASELINE.json configs[1]; ~2000 lines/page as in configs[3]).
+
+    python bench.py --gpus 1 --steps K --warmup W            # this repository's CUDA path
+    python bench.py --impl reference --steps K --warmup W    # the reference's CPU path
+
+A step = one page through the whole path.  Pages are independent, so with N ranks every
+rank processes its own pages (weak scaling, no data-path collective); `value` is the
+whole-job megapixels/s of dewarped page area: N * Hd*Wd * K / max-over-ranks(time).
+
+Prints ONE JSON line on rank 0.
+"""
+
+import argparse
+import json
+import os
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+if ROOT not in sys.path:
+	sys.path.insert(0, ROOT)
+
+PAGE_W, PAGE_H, CELL = 4800, 7200, 25
+N_LINES = 2000
+LINE_HEIGHT = 48
+METRIC = "megapixels/sec dewarp remap+line extraction"
+UNIT = "megapixels/s"
+FALLBACK_HBM_GBS = 6650.0
+
+
+def parse_args():
+	ap = argparse.ArgumentParser()
+	ap.add_argument("--gpus", type=int, default=1)
+	ap.add_argument("--steps", type=int, default=200)
+	ap.add_argument("--warmup", type=int, default=10)
+	ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+	ap.add_argument("--page-sets", type=int, default=3, help="distinct resident pages rotated through")
+	ap.add_argument("--lines", type=int, default=N_LINES)
+	ap.add_argument("--binarize", default="otsu", choices=["none", "otsu", "sauvola"])
+	ap.add_argument("--e2e-steps", type=int, default=4)
+	ap.add_argument("--no-cpu-baseline", action="store_true")
+	ap.add_argument("--no-e2e", action="store_true")
+	return ap.parse_args()
+
+
+def workload_config(args, extra=None):
+	cfg = {
+		"workload": "configs[1]: single 600-dpi 4800x7200 broadsheet page: dense map expansion + bilinear remap + "
+			"extraction of %d text lines to %d-px strips" % (args.lines, LINE_HEIGHT),
+		"page": [PAGE_W, PAGE_H], "cell": CELL, "lines_per_page": args.lines, "line_height": LINE_HEIGHT,
+		"binarize": args.binarize, "emit_dense_map": True,
+		"cache": "inputs larger than L2: every step writes a 281 MB dense map + 35 MB page and rotates over "
+			"%d resident pages" % args.page_sets,
+		"sharding": "pages by index, no collective",
+	}
+	if extra:
+		cfg.update(extra)
+	return cfg
+
+
+def make_inputs(args, page_index):
+	from origami_b200 import synth
+	page = synth.make_page(PAGE_W, PAGE_H, seed=page_index, kind="text", dpi=600)
+	grid = synth.make_grid(PAGE_W, PAGE_H, CELL, seed=page_index)
+	gh, gw = grid.shape[:2]
+	lines = synth.make_lines(gw * CELL, gh * CELL, args.lines, seed=page_index, dpi=600)
+	return page, grid, lines
+
+
+def measured_peak():
+	p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+	try:
+		with open(p) as f:
+			return float(json.load(f)["hbm_gbs"]), "measured (MEASURED_PEAKS.json)"
+	except Exception:
+		return FALLBACK_HBM_GBS, "fallback (B200_PROFILING.md)"
+
+
+def recorded_traffic():
+	"""Per-launch DRAM bytes from the committed ncu capture (profiles/traffic.json), if any."""
+	try:
+		with open(os.path.join(ROOT, "profiles", "traffic.json")) as f:
+			return json.load(f)
+	except Exception:
+		return {}
+
+
+# ---------------------------------------------------------------------------------------
+# clocks
+# ---------------------------------------------------------------------------------------
+class ClockSampler(threading.Thread):
+	def __init__(self, index, period=0.005):
+		super().__init__(daemon=True)
+		self.index, self.period = index, period
+		self.samples, self.reasons = [], set()
+		self.max_mhz = None
+		self._stop_evt = threading.Event()
+		self.ok = False
+		try:
+			import pynvml
+			pynvml.nvmlInit()
+			self.nv = pynvml
+			self.h = pynvml.nvmlDeviceGetHandleByIndex(index)
+			self.max_mhz = pynvml.nvmlDeviceGetMaxClockInfo(self.h, pynvml.NVML_CLOCK_SM)
+			self.ok = True
+		except Exception:
+			self.ok = False
+
+	def run(self):
+		if not self.ok:
+			return
+		nv = self.nv
+		names = {
+			getattr(nv, "nvmlClocksEventReasonSwPowerCap", 0x4): "sw_power_cap",
+			getattr(nv, "nvmlClocksThrottleReasonHwSlowdown", 0x8): "hw_slowdown",
+			getattr(nv, "nvmlClocksThrottleReasonSwThermalSlowdown", 0x20): "sw_thermal_slowdown",
+			getattr(nv, "nvmlClocksThrottleReasonHwThermalSlowdown", 0x40): "hw_thermal_slowdown",
+			getattr(nv, "nvmlClocksThrottleReasonHwPowerBrakeSlowdown", 0x80): "hw_power_brake",
+		}
+		while not self._stop_evt.is_set():
+			try:
+				self.samples.append(nv.nvmlDeviceGetClockInfo(self.h, nv.NVML_CLOCK_SM))
+				try:
+					r = nv.nvmlDeviceGetCurrentClocksEventReasons(self.h)
+				except Exception:
+					r = nv.nvmlDeviceGetCurrentClocksThrottleReasons(self.h)
+				for bit, name in names.items():
+					if r & bit:
+						self.reasons.add(name)
+			except Exception:
+				pass
+			time.sleep(self.period)
+
+	def stop(self):
+		self._stop_evt.set()
+		self.join(timeout=2)
+		if not self.samples:
+			return {"sm_mhz": None, "sm_max_mhz": self.max_mhz, "reasons": sorted(self.reasons), "samples": 0}
+		return {"sm_mhz": float(np.median(self.samples)), "sm_max_mhz": self.max_mhz,
+			"reasons": sorted(self.reasons), "samples": len(self.samples)}
+
+
+# ---------------------------------------------------------------------------------------
+# CPU reference path (oracle/reference_path.py) -- cpu_baseline leg and --impl reference
+# ---------------------------------------------------------------------------------------
+def cpu_reference_step(page, grid, lines, n_sample, binarize):
+	"""One page through the reference's CPU path on a bounded sample of its lines.  Returns
+	(seconds for the full page extrapolated, seconds measured)."""
+	from oracle import reference_path
+	import PIL.Image
+	t0 = time.perf_counter()
+	g = reference_path.RefGrid(grid, CELL)
+	pil = PIL.Image.fromarray(page)
+	reference_path.dewarped(pil, g)
+	t1 = time.perf_counter()
+	sel = lines[:n_sample]
+	spec = None if binarize == "none" else (("otsu",) if binarize == "otsu" else ("sauvola", 15))
+	reference_path.extract_lines(pil, g, sel, LINE_HEIGHT, spec)
+	t2 = time.perf_counter()
+	t_page, t_lines = t1 - t0, t2 - t1
+	return t_page + t_lines * (len(lines) / max(len(sel), 1)), t2 - t0, t_page, t_lines
+
+
+def cpu_baseline(args, page, grid, lines, n_sample=96, reps=2):
+	import cv2
+	gh, gw = grid.shape[:2]
+	mp = gh * CELL * gw * CELL / 1e6
+	est = []
+	for _ in range(reps):
+		e, _, tp, tl = cpu_reference_step(page, grid, lines, n_sample, args.binarize)
+		est.append((e, tp, tl))
+	e, tp, tl = min(est)
+	return {
+		"value": mp / e, "unit": UNIT, "cores": max(cv2.getNumThreads(), 8), "kind": "port",
+		"sample": "1 page 4800x7200 expand+remap in full (%.3f s) + %d of %d lines through the 8-thread pool (%.3f s), "
+			"line time scaled to %d lines; best of %d; host has %d logical cores, cv2 threads %d" % (
+			tp, n_sample, len(lines), tl, len(lines), reps, os.cpu_count(), cv2.getNumThreads()),
+	}
+
+
+def run_reference(args):
+	rank = int(os.environ.get("RANK", "0"))
+	if rank != 0:
+		return
+	import cv2
+	page, grid, lines = make_inputs(args, 0)
+	gh, gw = grid.shape[:2]
+	mp = gh * CELL * gw * CELL / 1e6
+	# size the line sample so that warmup + steps stay within ~150 s
+	_, t_meas, t_page, t_lines = cpu_reference_step(page, grid, lines, 16, args.binarize)
+	per_line = t_lines / 16
+	budget = 150.0 / max(args.steps + args.warmup, 1)
+	n_sample = int(max(8, min(len(lines), (budget - t_page) / max(per_line, 1e-6))))
+	for _ in range(args.warmup):
+		cpu_reference_step(page, grid, lines, n_sample, args.binarize)
+	t0 = time.perf_counter()
+	total_est = 0.0
+	for _ in range(args.steps):
+		e, _, _, _ = cpu_reference_step(page, grid, lines, n_sample, args.binarize)
+		total_est += e
+	wall = time.perf_counter() - t0
+	value = mp * args.steps / total_est
+	cores = max(cv2.getNumThreads(), 8)
+	sample = ("each step: 1 page 4800x7200 expand+remap in full + %d of %d lines through the reference's 8-thread pool, "
+		"line time scaled to %d lines (measured wall %.1f s for %d steps)" % (n_sample, len(lines), len(lines), wall, args.steps))
+	print(json.dumps({
+		"impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus,
+		"steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * total_est / max(args.steps, 1),
+		"higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "u8", "data": "synthetic",
+		"config": workload_config(args),
+		"cpu_baseline": {"value": value, "unit": UNIT, "cores": cores, "kind": "port", "sample": sample},
+		"e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+		"gpu_launches": 0,
+	}))
+
+
+# ---------------------------------------------------------------------------------------
+# this repository's CUDA path
+# ---------------------------------------------------------------------------------------
+class PageSet:
+	"""Device-resident inputs and outputs of one page."""
+
+	def __init__(self, args, page, grid, lines, device):
+		import torch
+		from origami_b200 import ops
+		self.gh, self.gw = int(grid.shape[0]), int(grid.shape[1])
+		self.Hd, self.Wd = self.gh * CELL, self.gw * CELL
+		self.H, self.W = page.shape
+		self.src = ops.to_device_image(page, device)
+		self.grid = torch.from_numpy(grid).to(device)
+		recs = [dict(p=l["p"], right=l["right"], up=l["up"], ysteps=LINE_HEIGHT) for l in lines]
+		self.lines_np = ops.pack_lines(recs)
+		self.lines = ops.lines_to_device(self.lines_np, device)
+		self.n = len(recs)
+		self.dst = ops.alloc_image(self.Hd, self.Wd, device)
+		self.map = torch.empty((self.Hd, self.Wd, 2), dtype=torch.float32, device=device)
+		# generous strip capacity: |right| * 1.1 + 16 columns per line
+		cap = int(sum(LINE_HEIGHT * (np.hypot(*l["right"]) * 1.1 + 16) for l in lines))
+		self.gray = torch.empty((cap,), dtype=torch.uint8, device=device)
+		self.bin = torch.empty((cap,), dtype=torch.uint8, device=device)
+		self.bbox = torch.empty((self.n, 4), dtype=torch.int32, device=device)
+		self.steps = torch.empty((self.n, 2), dtype=torch.int32, device=device)
+		self.pix = torch.empty((self.n + 1,), dtype=torch.int64, device=device)
+		self.chunks = torch.empty((self.n + 1,), dtype=torch.int32, device=device)
+		self.plan = ops.LinePlan(self.lines, self.n, self.steps, self.pix, self.chunks)
+
+
+KERNELS = ["og_page_kernel", "og_line_steps_kernel", "og_lines_kernel", "og_binarize"]
+
+
+def run_step(ps, args, events=None):
+	"""One page through the path: 4 C-ABI calls (5 kernel launches; 4 without binarization)."""
+	import torch
+	from origami_b200 import _lib, ops
+	st = torch.cuda.current_stream().cuda_stream
+
+	def mark(k):
+		if events is not None:
+			e = torch.cuda.Event(enable_timing=True)
+			e.record()
+			events.append((k, e))
+
+	mark("start")
+	_lib.call("og_remap_page", ps.src.data_ptr(), ps.H, ps.W, ps.src.stride(0), ps.grid.data_ptr(), ps.gh, ps.gw, CELL,
+		ps.dst.data_ptr(), ps.dst.stride(0), ps.map.data_ptr(), 1.0, 1.0, ops.OG_INTER_LINEAR, st)
+	mark("og_page_kernel")
+	_lib.call("og_line_steps", ps.grid.data_ptr(), ps.gh, ps.gw, CELL, ps.lines.data_ptr(), ps.n,
+		ps.steps.data_ptr(), ps.pix.data_ptr(), ps.chunks.data_ptr(), st)
+	mark("og_line_steps_kernel")
+	_lib.call("og_extract_lines", ps.src.data_ptr(), ps.H, ps.W, ps.src.stride(0), ps.grid.data_ptr(), ps.gh, ps.gw, CELL,
+		ps.lines.data_ptr(), ps.n, ps.steps.data_ptr(), ps.pix.data_ptr(), ps.chunks.data_ptr(),
+		ps.gray.data_ptr(), ps.gray.numel(), ps.bbox.data_ptr(), st)
+	mark("og_lines_kernel")
+	launches = 4
+	if args.binarize != "none":
+		mode = ops.OG_BIN_OTSU if args.binarize == "otsu" else ops.OG_BIN_SAUVOLA
+		_lib.call("og_binarize_strips", ps.gray.data_ptr(), ps.steps.data_ptr(), ps.pix.data_ptr(), ps.chunks.data_ptr(),
+			ps.n, mode, 15, ps.bin.data_ptr(), 0, st)
+		mark("og_binarize")
+		launches += 1
+	return launches
+
+
+def run_e2e(args, inputs, device, n_steps):
+	"""The same work through the public API with HOST buffers: Page(ndarray, Grid).dewarped and
+	LineExtractor(...)(lines); host<->device copies are inside the timed region."""
+	import torch
+	from origami_b200.core.dewarp import Grid
+	from origami_b200.core.page import Page
+	from origami_b200.core.block import Block, Line, Stage
+	from origami_b200.batch.core.lines import LineExtractor
+
+	def one(page, grid_hv, lines):
+		grid = Grid(grid_hv, CELL)
+		pg = Page(page, grid)
+		dewarped = pg.dewarped
+		block = Block(pg, None, Stage.RELIABLE)
+		ldict = dict((("regions", "TEXT", str(i // 50), str(i % 50)), Line(block, l["p"], l["right"], l["up"], confidence=1))
+			for i, l in enumerate(lines))
+		ex = LineExtractor(dict(columns={}), LINE_HEIGHT,
+			dict(binarize="" if args.binarize == "none" else args.binarize, do_not_dewarp=False, do_not_deskew=False))
+		strips = ex.extract_arrays(ldict)
+		return dewarped, strips
+
+	page, grid_hv, lines = inputs[0]
+	dw, strips = one(page, grid_hv, lines)  # warm-up
+	strip_bytes = int(sum(s.size for _, s in strips))
+	torch.cuda.synchronize()
+	t0 = time.perf_counter()
+	for i in range(n_steps):
+		page, grid_hv, lines = inputs[i % len(inputs)]
+		one(page, grid_hv, lines)
+	torch.cuda.synchronize()
+	dt = time.perf_counter() - t0
+	gh, gw = grid_hv.shape[:2]
+	h2d = page.size + grid_hv.nbytes + len(lines) * 112
+	d2h = gh * CELL * gw * CELL + strip_bytes + (len(lines) + 1) * 8 + len(lines) * 8
+	return dt / n_steps, h2d, d2h
+
+
+def run_ours(args):
+	import torch
+	from origami_b200 import _lib, shard
+	if not torch.cuda.is_available():
+		raise SystemExit("bench.py needs a CUDA device: the CUDA path has no CPU fallback")
+	_lib.load()
+	rank, local_rank, world = shard.init()
+	torch.cuda.set_device(local_rank)
+	device = torch.device("cuda", local_rank)
+
+	# every rank owns the pages rank, rank+N, ... of a conceptually endless page stream
+	inputs = [make_inputs(args, rank + k * world) for k in range(args.page_sets)]
+	sets = [PageSet(args, p, g, l, device) for (p, g, l) in inputs]
+	ps0 = sets[0]
+	mp_page = ps0.Hd * ps0.Wd / 1e6
+
+	for i in range(max(args.warmup, 3)):
+		launches = run_step(sets[i % len(sets)], args)
+	torch.cuda.synchronize()
+	total_strip_px = int(ps0.pix[-1].item())
+	if total_strip_px > ps0.gray.numel():
+		raise SystemExit("strip capacity too small")
+
+	sampler = ClockSampler(local_rank) if rank == 0 else None
+	events = []
+	shard.barrier()
+	torch.cuda.synchronize()
+	if sampler:
+		sampler.start()
+	start = torch.cuda.Event(enable_timing=True)
+	end = torch.cuda.Event(enable_timing=True)
+	start.record()
+	n_launch = 0
+	for i in range(args.steps):
+		n_launch += run_step(sets[i % len(sets)], args, events)
+	end.record()
+	torch.cuda.synchronize()
+	clocks = sampler.stop() if sampler else None
+	shard.barrier()
+	ms_local = start.elapsed_time(end)
+	ms = shard.max_over_ranks(ms_local, device)
+
+	# per-kernel device time inside the timed region
+	per_kernel = {}
+	for (k0, e0), (k1, e1) in zip(events[:-1], events[1:]):
+		if k1 == "start":
+			continue
+		per_kernel.setdefault(k1, []).append(e0.elapsed_time(e1))
+	kernel_ms = dict((k, float(np.mean(v))) for k, v in per_kernel.items())
+
+	e2e = None
+	cpu = None
+	if not args.no_e2e:
+		s_e2e, h2d, d2h = run_e2e(args, inputs, device, args.e2e_steps)
+		s_e2e = shard.max_over_ranks(s_e2e, device)
+		e2e = {"value": world * mp_page / s_e2e, "unit": UNIT, "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(d2h),
+			"ms_per_step": 1e3 * s_e2e, "api": "Page(ndarray, Grid).dewarped + LineExtractor.extract_arrays(lines)"}
+	if rank == 0 and world == 1 and not args.no_cpu_baseline:
+		cpu = cpu_baseline(args, *inputs[0])
+
+	if rank == 0:
+		peak, peak_src = measured_peak()
+		strip_px = total_strip_px
+		src_rows = float(np.mean([np.ceil(np.hypot(*l["up"])) + 2 for l in inputs[0][2]]))
+		alg_bytes = {
+			"og_page_kernel": 9 * ps0.Hd * ps0.Wd + ps0.H * ps0.W,
+			"og_lines_kernel": strip_px + strip_px / LINE_HEIGHT * src_rows,
+			"og_binarize": 2 * strip_px,
+			"og_line_steps_kernel": ps0.n * (112 + 8 + 8 + 4),
+		}
+		traffic = recorded_traffic()
+		rl_all = {}
+		for k, t in kernel_ms.items():
+			a = alg_bytes.get(k, 0) / (t * 1e-3) / 1e9
+			rl_all[k] = {"ms": t, "algorithmic_bytes": int(alg_bytes.get(k, 0)), "achieved": a, "frac": a / peak,
+				"share_of_step": t / max(sum(kernel_ms.values()), 1e-9), "traffic": traffic.get(k)}
+		dom = max(kernel_ms, key=kernel_ms.get)  # dominant = largest share of the step's device time
+		roof = {"bound": "hbm", "kernel": dom, "achieved": rl_all[dom]["achieved"], "peak": peak, "unit": "GB/s",
+			"frac": rl_all[dom]["frac"], "traffic": traffic.get(dom), "peak_source": peak_src,
+			"algorithmic_bytes": rl_all[dom]["algorithmic_bytes"], "ms": rl_all[dom]["ms"],
+			"share_of_step": rl_all[dom]["share_of_step"],
+			"note": "every kernel of the step is listed in roofline_kernels"}
+		out = {
+			"metric": METRIC, "value": world * mp_page * args.steps / (ms * 1e-3), "unit": UNIT, "n_gpus": world,
+			"steps": args.steps, "warmup": max(args.warmup, 3), "ms_per_step": ms / args.steps,
+			"higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "u8", "data": "synthetic",
+			"config": workload_config(args, {"strip_pixels_per_page": strip_px,
+				"strip_megapixels_per_s": world * strip_px * args.steps / (ms * 1e-3) / 1e6}),
+			"clocks": clocks, "e2e": e2e, "gpu_launches": n_launch,
+			"roofline": roof, "roofline_kernels": rl_all, "cpu_baseline": cpu, "impl": "ours",
+		}
+		print(json.dumps(out))
+	shard.finalize()
+
+
+def main():
+	args = parse_args()
+	if args.impl == "reference":
+		run_reference(args)
+	else:
+		run_ours(args)
+
+
+if __name__ == "__main__":
+	main()

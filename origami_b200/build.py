@@ -21,7 +21,7 @@ NVCC_FLAGS = [
 	"-O3", "-lineinfo", "-std=c++17",
 	"--fmad=false",  # parity: no implicit FMA contraction anywhere (explicit *_rn are used on top)
 	"-Xcompiler", "-fPIC", "-Xcompiler", "-O2",
-	"-shared", "-cudart", "shared",
+	"-shared",
 ]
 
 

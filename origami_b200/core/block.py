@@ -1,0 +1,288 @@
+"""
+Line and Block with the interface of the reference's origami/core/block.py on the
+page-geometry path: Line.warped_grid / dewarped_image / deskewed_image / image /
+warped_path (block.py:129-267).  Geometry that the reference delegates to shapely
+(polygons, text areas) is carried as opaque data; the sampling runs on the GPU.
+
+`lines_to_records` / `extract_strips` are the batched forms used by LineExtractor: all
+lines of a page go through ONE kernel launch instead of a Python thread pool.
+"""
+
+import enum
+import math
+from functools import cached_property
+
+import numpy as np
+import PIL.Image
+import torch
+
+from .. import ops
+from .dewarp import INTER_LINEAR
+
+
+class Stage(enum.Enum):
+	"""origami/batch/core/io.py:29-38"""
+	WARPED = 0
+	DEWARPED = 1
+	AGGREGATE = 2
+	RELIABLE = 3
+	ANY = -1
+
+	@property
+	def is_dewarped(self):
+		return self.value >= Stage.DEWARPED.value
+
+
+class Block:
+	"""origami/core/block.py:373-392 (the part the line path touches)."""
+
+	def __init__(self, page, polygon, stage):
+		self._image_space_polygon = polygon
+		self._page = page
+		self._stage = stage
+
+	@property
+	def page(self):
+		return self._page
+
+	@property
+	def page_pixels(self):
+		return self.page.pixels(self._stage.is_dewarped)
+
+	@property
+	def stage(self):
+		return self._stage
+
+	@property
+	def image_space_polygon(self):
+		return self._image_space_polygon
+
+	@cached_property
+	def background(self):
+		"""0.8-quantile of the block's pixels (block.py:415-420); without a polygon
+		rasteriser the block's bounding box stands in for the polygon mask."""
+		pixels = self.page_pixels
+		poly = self._image_space_polygon
+		if poly is not None and hasattr(poly, "bounds"):
+			x0, y0, x1, y1 = poly.bounds
+			x0, y0 = max(int(math.floor(x0)), 0), max(int(math.floor(y0)), 0)
+			pixels = pixels[y0:int(math.ceil(y1)), x0:int(math.ceil(x1))]
+		return np.quantile(pixels, 0.8)
+
+
+def position(p, right, up, xres, column):
+	"""Line._position (block.py:195-221): clip the baseline to a table column [x0, x1].
+
+	The reference intersects shapely LineStrings; this is the same intersection of the
+	baseline with the vertical lines x = x0 and x = x1 in float64 (a miss keeps the end
+	point, as intersect_segments' default does)."""
+	p0 = np.asarray(p, dtype=np.float64)
+	right = np.asarray(right, dtype=np.float64)
+	up = np.asarray(up, dtype=np.float64)
+	if column is not None:
+		p1 = p0 + right
+		px0, px1 = min(p0[0], p1[0]), max(p0[0], p1[0])
+		x0, x1 = column
+		if x0 is None:
+			x0 = px0
+		if x1 is None:
+			x1 = px1
+
+		def hit(xv, default):
+			dx = p1[0] - p0[0]
+			if dx == 0:
+				return default
+			t = (xv - p0[0]) / dx
+			if t < 0 or t > 1:
+				return default
+			return np.array([xv, p0[1] + t * (p1[1] - p0[1])], dtype=np.float64)
+
+		q0 = hit(x0, p0)
+		q1 = hit(x1, p1)
+		right = q1 - q0
+		p0 = q0
+		xres = xres * ((x1 - x0) / (px1 - px0))
+	return p0, right, up, xres
+
+
+class Line:
+	def __init__(
+		self, block, p, right, up,
+		tesseract_data=None,
+		wkt=None, text_area=None, confidence=1):
+
+		self._tesseract_data = tesseract_data
+		self._block = block
+
+		self._p = np.array(p, dtype=np.float64)
+		self._right = np.array(right, dtype=np.float64)
+		self._up = np.array(up, dtype=np.float64)
+
+		self._wkt = wkt
+		self._confidence = confidence
+
+	@property
+	def block(self):
+		return self._block
+
+	@property
+	def confidence(self):
+		return self._confidence
+
+	@property
+	def info(self):
+		td = self._tesseract_data or dict()
+		return dict(
+			p=self._p.tolist(),
+			right=self._right.tolist(),
+			up=self._up.tolist(),
+			wkt=self._wkt,
+			confidence=self._confidence,
+			tesseract_data=dict((k, td.get(k)) for k in ("baseline", "descent", "ascent", "height")))
+
+	@cached_property
+	def length(self):
+		return np.linalg.norm(self._right)
+
+	@cached_property
+	def height(self):
+		return np.linalg.norm(self._up)
+
+	def _position(self, xres, column):
+		return position(self._p, self._right, self._up, xres, column)
+
+	def record(self, xsteps=None, ysteps=None, xres=1, yres=1, column=None):
+		"""The og_line descriptor of this line for the given sampling request."""
+		p0, right, up, xres = self._position(xres, column)
+		return dict(p=self._p, right=self._right, up=self._up, cp=p0, cright=right,
+			xres=float(xres), yres=float(yres), xsteps=xsteps, ysteps=ysteps)
+
+	def _grid(self):
+		return self.block.page.dewarper.grid
+
+	def warped_grid(self, xsteps=None, ysteps=None, xres=1, yres=1, column=None):
+		grid = self._grid()
+		grids, _ = warped_grids(grid, [self.record(xsteps, ysteps, xres, yres, column)])
+		# grid is [y, x, p] and p is [x, y].
+		return grids[0]
+
+	def dewarped_image(self, target_height=48, column=None, interpolation=INTER_LINEAR):
+		assert self.block.stage.is_dewarped
+		if interpolation != INTER_LINEAR:
+			raise ValueError("only INTER_LINEAR strips are implemented")
+		dewarper = self.block.page.dewarper
+		strips, _ = extract_strips(dewarper, [self.record(ysteps=target_height, column=column)])
+		return PIL.Image.fromarray(strips[0])
+
+	def _extract_deskewed(self, pixels, target_height=48, background=255, interpolation=None):
+		"""cv2.getAffineTransform + cv2.warpAffine stage of block.py:155-172 (INTER_AREA and
+		INTER_LINEAR give identical bytes for warpAffine).  The cairo polygon cut-out that
+		follows in the reference (block.py:174-186) needs a rasteriser and is not applied."""
+		p, right, up = self._p, self._right, self._up
+		width = int(math.ceil(np.linalg.norm(right)))
+		M = affine_transform(
+			np.array([p, p + right, p + up]).astype(np.float32),
+			np.array([(0, target_height - 1), (width, target_height - 1), (0, 0)]).astype(np.float32))
+		src = ops.to_device_image(np.asarray(pixels, dtype=np.uint8))
+		return ops.warp_affine(src, M, width, target_height, int(background)).cpu().numpy()
+
+	def deskewed_image(self, target_height=48, interpolation=None):
+		return PIL.Image.fromarray(self._extract_deskewed(
+			self._block.page_pixels, target_height, self._block.background, interpolation))
+
+	@property
+	def warped_image(self):
+		raise NotImplementedError("raw polygon crops need the reference's cairo Mask (out of scope)")
+
+	def image(
+		self, target_height=48, column=None,
+		dewarped=True, deskewed=True, binarizer=None):
+
+		if dewarped:
+			im = self.dewarped_image(target_height, column=column)
+		elif deskewed:
+			im = self.deskewed_image(target_height)
+		else:
+			im = self.warped_image
+
+		if binarizer:
+			im = binarizer(im)
+
+		return im
+
+	def warped_path(self, resolution=1):
+		assert self.block.stage.is_dewarped
+		warped_grid = self.warped_grid(ysteps=2, xres=resolution)
+		height = np.median(np.linalg.norm(warped_grid[1] - warped_grid[0], axis=-1))
+		return np.mean(warped_grid, axis=0), abs(height)
+
+
+def affine_transform(src_tri, dst_tri):
+	"""cv2.getAffineTransform: the 6x6 system solved in float64 on fp32-rounded points."""
+	src = np.asarray(src_tri, dtype=np.float32).astype(np.float64)
+	dst = np.asarray(dst_tri, dtype=np.float32).astype(np.float64)
+	A = np.zeros((6, 6))
+	b = np.zeros(6)
+	for i in range(3):
+		A[i, 0:2] = src[i]
+		A[i, 2] = 1
+		A[i + 3, 3:5] = src[i]
+		A[i + 3, 5] = 1
+		b[i] = dst[i, 0]
+		b[i + 3] = dst[i, 1]
+	return np.linalg.solve(A, b).reshape(2, 3)
+
+
+# ---------------------------------------------------------------------------------------
+# batched forms
+# ---------------------------------------------------------------------------------------
+
+def _plan(grid, records):
+	la = ops.pack_lines(records)
+	dev = grid._device
+	ld = ops.lines_to_device(la, dev) if len(records) else torch.zeros((8,), dtype=torch.uint8, device=dev)
+	plan = ops.line_steps(grid.device_grid, grid.resolution, ld, len(records))
+	host = torch.empty((len(records) + 1,), dtype=torch.int64).pin_memory()
+	host.copy_(plan.pix_offsets, non_blocking=True)
+	steps = plan.steps.cpu().numpy()[:len(records)]
+	torch.cuda.current_stream().synchronize()
+	offs = host.numpy()
+	if len(records) and (steps <= 0).any():
+		bad = int(np.argmax((steps <= 0).any(axis=1)))
+		raise ValueError("line %d has a degenerate or non-finite extent" % bad)
+	return plan, steps, offs
+
+
+def warped_grids(grid, records):
+	"""Line.warped_grid for a list of og_line records -> ([ (ysteps, xsteps, 2) fp32 ], steps)."""
+	plan, steps, offs = _plan(grid, records)
+	out = torch.empty((max(int(offs[-1]), 1) * 2,), dtype=torch.float32, device=grid._device)
+	ops.warped_grids(grid.device_grid, grid.resolution, plan, out)
+	flat = out.cpu().numpy()
+	res = [flat[2 * offs[i]:2 * offs[i + 1]].reshape(steps[i][1], steps[i][0], 2) for i in range(len(records))]
+	return res, steps
+
+
+def extract_strips(dewarper, records, binarize=None, want_bbox=False):
+	"""Line.image(dewarped=True) for a list of records in one launch.
+
+	binarize: None | ("otsu",) | ("sauvola", window).  Returns ([ (ysteps, xsteps) uint8 ], bbox | None).
+	"""
+	grid = dewarper.grid
+	plan, steps, offs = _plan(grid, records)
+	dev = grid._device
+	total = max(int(offs[-1]), 1)
+	gray = torch.empty((total,), dtype=torch.uint8, device=dev)
+	bbox = torch.empty((max(len(records), 1), 4), dtype=torch.int32, device=dev) if want_bbox else None
+	ops.extract_lines(dewarper.device_image, grid.device_grid, grid.resolution, plan, gray, bbox)
+	if binarize is not None:
+		mode = ops.OG_BIN_OTSU if binarize[0] == "otsu" else ops.OG_BIN_SAUVOLA
+		window = binarize[1] if len(binarize) > 1 else 15
+		gray = ops.binarize_strips(gray, plan, mode, window)
+	host = torch.empty((total,), dtype=torch.uint8).pin_memory()
+	host.copy_(gray, non_blocking=True)
+	bb = bbox.cpu().numpy()[:len(records)] if want_bbox else None
+	torch.cuda.current_stream().synchronize()
+	flat = host.numpy()
+	strips = [flat[offs[i]:offs[i + 1]].reshape(steps[i][1], steps[i][0]) for i in range(len(records))]
+	return strips, bb

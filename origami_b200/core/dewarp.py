@@ -1,0 +1,164 @@
+"""
+Grid and Dewarper with the interface of the reference's origami/core/dewarp.py:496-627,
+backed by the sm_100a kernels.  Same names, argument order, defaults and return types
+(NumPy arrays / PIL images at the API edge); the sparse grid lives on the GPU and nothing
+is computed on the CPU.
+
+Differences that are deliberate:
+  * Dewarper.dewarp_image does not scale the cached dense map in place (the reference does,
+    origami/core/dewarp.py:621-623, which corrupts later Grid.points("full") users); the
+    scale is folded into the kernel instead.
+  * Grid.create (GridFactory, SURVEY.md section 8(f) "next") is not part of this path.
+"""
+
+import io
+import json
+import zipfile
+from functools import cached_property
+
+import numpy as np
+import PIL.Image
+import torch
+
+from .. import ops
+from .math import Geometry
+
+INTER_NEAREST = ops.OG_INTER_NEAREST  # == cv2.INTER_NEAREST
+INTER_LINEAR = ops.OG_INTER_LINEAR  # == cv2.INTER_LINEAR
+
+
+def _device(device=None):
+	if device is not None:
+		return torch.device(device)
+	if not torch.cuda.is_available():
+		raise ops._lib.OrigamiB200Error("origami_b200 needs a CUDA device (there is no CPU fallback)")
+	return torch.device("cuda", torch.cuda.current_device())
+
+
+class Grid:
+	"""Sparse dewarping grid: (gh, gw, 2) fp32 lattice on the dewarped page holding warped-page
+	(x, y) positions (reference docs/formats.md:298-306)."""
+
+	def __init__(self, hv, res, device=None):
+		hv = np.ascontiguousarray(hv, dtype=np.float32)
+		if hv.ndim != 3 or hv.shape[2] != 2:
+			raise ValueError("grid must have shape (gh, gw, 2)")
+		self._grid_hv = hv
+		self._grid_res = int(res)
+		self._device = _device(device)
+		self._points_cache = dict()
+
+	# -- container (reference :501-511, :528-553)
+	@property
+	def geometry(self):
+		h, w = self._grid_hv.shape[:2]
+		r = self._grid_res
+		return Geometry(w * r, h * r)
+
+	@property
+	def resolution(self):
+		return self._grid_res
+
+	@property
+	def shape(self):
+		return self._grid_hv.shape
+
+	@cached_property
+	def device_grid(self):
+		return torch.from_numpy(self._grid_hv).to(self._device)
+
+	@cached_property
+	def warping(self):
+		pts = self.points("sample")
+		dy = (pts[1:, :, 0] - pts[:-1, :, 1]).flatten()
+		dx = (pts[:, 1:, 1] - pts[:, :-1, 0]).flatten()
+		return max(np.std(dx), np.std(dy))
+
+	@staticmethod
+	def open(path, device=None):
+		with zipfile.ZipFile(path, "r") as zf:
+			info = json.loads(zf.read("meta.json").decode("utf8"))
+			data = io.BytesIO(zf.read("data.npy"))
+			grid = np.load(data, allow_pickle=False)
+		grid = grid.reshape(info["shape"])
+		return Grid(grid, info["cell"], device=device)
+
+	def save(self, path, compression=zipfile.ZIP_DEFLATED):
+		data = io.BytesIO()
+		np.save(data, self._grid_hv.astype(np.float32), allow_pickle=False)
+		info = dict(version=1, cell=self._grid_res, shape=self._grid_hv.shape)
+		with zipfile.ZipFile(path, "w", compression) as zf:
+			zf.writestr("data.npy", data.getvalue())
+			zf.writestr("meta.json", json.dumps(info))
+
+	# -- A2
+	def device_points(self):
+		"""Dense map as a CUDA tensor (Hd, Wd, 2) fp32 (not cached)."""
+		return ops.expand_map(self.device_grid, self._grid_res)
+
+	def points(self, resolution="full", interpolation=INTER_LINEAR):
+		if resolution == "sample":
+			return self._grid_hv
+		elif resolution == "full":
+			if interpolation != INTER_LINEAR:
+				raise ValueError("only INTER_LINEAR map expansion is implemented")
+			key = (resolution, interpolation)
+			if key not in self._points_cache:  # the reference lru_caches 8 of these
+				self._points_cache[key] = self.device_points().cpu().numpy()
+			return self._points_cache[key]
+		else:
+			raise ValueError(resolution)
+
+	# -- A5
+	@cached_property
+	def inverse_yx(self):
+		def f(pts_yx):
+			pts = np.asarray(pts_yx, dtype=np.float64)
+			flat = np.ascontiguousarray(pts.reshape(-1, 2))
+			out = ops.inverse_yx(self.device_grid, self._grid_res, torch.from_numpy(flat).to(self._device))
+			return out.cpu().numpy().reshape(pts.shape[:-1] + (2,))
+
+		return f
+
+	@cached_property
+	def inverse(self):
+		interp = self.inverse_yx
+
+		def f(pts):
+			return interp(np.flip(pts, axis=-1))
+
+		return f
+
+
+class Dewarper:
+	def __init__(self, im, grid):
+		self._im = im
+		self._grid = grid
+
+	@property
+	def grid(self):
+		return self._grid
+
+	@cached_property
+	def device_image(self):
+		"""The warped page as a pitched CUDA uint8 image (uploaded once)."""
+		return ops.to_device_image(np.asarray(self._im, dtype=np.uint8), self._grid._device)
+
+	def device_dewarped(self, map_out=None):
+		dst, _ = ops.remap_page(self.device_image, self._grid.device_grid, self._grid.resolution, map_out=map_out)
+		return dst
+
+	@cached_property
+	def dewarped(self):
+		return PIL.Image.fromarray(self.device_dewarped().cpu().numpy())
+
+	def dewarp_image(self, im, interpolation=INTER_LINEAR):
+		w0, h0 = self._im.size
+		w1, h1 = im.size
+		pixels = np.array(im)
+		if pixels.ndim != 2 or pixels.dtype != np.uint8:
+			raise ValueError("dewarp_image expects an 8-bit single-channel image")
+		src = ops.to_device_image(pixels, self._grid._device)
+		dst, _ = ops.remap_page(src, self._grid.device_grid, self._grid.resolution,
+			scale=(w1 / w0, h1 / h0), interpolation=interpolation)
+		return PIL.Image.fromarray(dst.cpu().numpy())

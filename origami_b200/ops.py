@@ -40,11 +40,28 @@ def alloc_image(h, w, device=None):
 	return buf[:, :w]
 
 
+_PINNED = {}
+
+
+def pinned_staging(nbytes):
+	"""A reusable page-locked host buffer of at least nbytes (host<->device copies go through
+	pinned memory so they run at PCIe speed and can be asynchronous)."""
+	buf = _PINNED.get("u8")
+	if buf is None or buf.numel() < nbytes:
+		buf = torch.empty((max(nbytes, 1 << 20),), dtype=torch.uint8).pin_memory()
+		_PINNED["u8"] = buf
+	return buf[:nbytes]
+
+
 def to_device_image(a, device=None):
-	"""Host uint8 (h, w) ndarray -> pitched device image."""
+	"""Host uint8 (h, w) ndarray -> pitched device image (through pinned staging memory)."""
 	a = np.ascontiguousarray(a, dtype=np.uint8)
-	out = alloc_image(a.shape[0], a.shape[1], device)
-	out.copy_(torch.from_numpy(a))
+	h, w = a.shape
+	out = alloc_image(h, w, device)
+	stage = pinned_staging(h * w).view(h, w)
+	stage.copy_(torch.from_numpy(a))
+	out.copy_(stage, non_blocking=True)
+	torch.cuda.current_stream().synchronize()  # the staging buffer is reused by the next call
 	return out
 
 
