@@ -120,6 +120,43 @@ __device__ __forceinline__ int og_sample_linear(
 	return og_blend(q, p00, p01, p10, p11);
 }
 
+// 4 taps of one pixel with a fast interior path: when all taps lie inside the image one
+// address is formed in 32-bit arithmetic (H * pitch < 2^31 is checked on the host); border
+// pixels take the per-tap test that yields OpenCV's BORDER_CONSTANT value per tap.
+__device__ __forceinline__ int og_sample_linear_fast(
+	const uint8_t *__restrict__ src, int H, int W, int pitch, float mx, float my) {
+	const int sx = __float2int_rn(__fmul_rn(mx, 32.f));
+	const int sy = __float2int_rn(__fmul_rn(my, 32.f));
+	const int ix = sx >> 5, iy = sy >> 5;
+	og_fix q;
+	q.fx = sx & 31;
+	q.fy = sy & 31;
+	int p00, p01, p10, p11;
+	if ((unsigned)ix < (unsigned)(W - 1) && (unsigned)iy < (unsigned)(H - 1)) {
+		const uint8_t *s = src + (iy * pitch + ix);
+		p00 = __ldg(s);
+		p01 = __ldg(s + 1);
+		p10 = __ldg(s + pitch);
+		p11 = __ldg(s + pitch + 1);
+	} else {
+		q.ix = og_sat_short(ix);
+		q.iy = og_sat_short(iy);
+		p00 = og_tap(src, H, W, pitch, q.iy, q.ix, 0);
+		p01 = og_tap(src, H, W, pitch, q.iy, q.ix + 1, 0);
+		p10 = og_tap(src, H, W, pitch, q.iy + 1, q.ix, 0);
+		p11 = og_tap(src, H, W, pitch, q.iy + 1, q.ix + 1, 0);
+	}
+	return og_blend(q, p00, p01, p10, p11);
+}
+
+__device__ __forceinline__ int og_sample_nearest_fast(
+	const uint8_t *__restrict__ src, int H, int W, int pitch, float mx, float my) {
+	const int ix = og_sat_short(__float2int_rn(mx));
+	const int iy = og_sat_short(__float2int_rn(my));
+	if ((unsigned)ix < (unsigned)W && (unsigned)iy < (unsigned)H) return (int)__ldg(src + (iy * pitch + ix));
+	return 0;
+}
+
 // A4: cv2.remap INTER_NEAREST: saturate_cast<short>(float) = round half to even.
 __device__ __forceinline__ int og_sample_nearest(
 	const uint8_t *__restrict__ src, int H, int W, int64_t pitch, float x, float y, int border) {

@@ -6,29 +6,86 @@
 // lines.py:131-149, ConfidenceSampler origami/batch/detect/lines.py:34-54.
 //
 // The reference materialises the 281 MB dense map and feeds it to SciPy's interpolator for
-// every line.  Here a work item is (line, 64-column chunk): the CTA recomputes, with the
-// exact cv2.resize arithmetic, only the dense-map nodes under that chunk into shared memory
-// (as float64, so each fp32->fp64 conversion happens once per node instead of four times
-// per sample), then every thread walks a column of the strip doing SciPy's float64 blend,
-// the fp32 cast, OpenCV's 1/32-px quantisation and the integer bilinear blend.  Work items
-// come from a device-side prefix sum, so a whole page is ONE launch with no host round trip.
+// every line.  Here a work item is (line, 64-column chunk).  A persistent CTA of 8 worker
+// warps + 1 planner warp loops over items:
+//   planner  -- while the workers process item k, computes the descriptor of item k+1
+//               (line lookup, np.linspace parameters, per-row lattice offsets, the region of
+//               dense-map nodes under the chunk) into a double-buffered shared structure;
+//   workers  -- recompute, with the exact cv2.resize arithmetic, only the dense-map nodes
+//               under the chunk into shared memory (as float64, so each fp32->fp64
+//               conversion happens once per node instead of four times per sample), then
+//               every thread walks a column of the strip: SciPy's float64 blend, the fp32
+//               cast, OpenCV's 1/32-px quantisation and the integer bilinear blend.
+// Work items come from a device-side prefix sum, so a whole page is ONE launch with no host
+// round trip.  The bound of this kernel is the FP64 pipe + instruction issue, not HBM: the
+// float64 blend that bit-parity with SciPy requires costs ~30 DP-pipe instructions per
+// sample.
 #include "og_common.cuh"
 
 namespace {
 
-constexpr int CW = 64;          // strip columns per work item
-constexpr int LTHREADS = 256;   // threads per CTA
-constexpr int RSPLIT = LTHREADS / CW;
+constexpr int CW = 64;                  // strip columns per work item
+constexpr int WORKERS = 256;            // worker threads per CTA
+constexpr int LTHREADS = WORKERS + 32;  // + one planner warp
+constexpr int RSPLIT = WORKERS / CW;    // rows are dealt round-robin to 4 thread groups
 constexpr int SMEM_BUDGET = 100 * 1024;
+constexpr int MAX_ROWS = 128;           // rows with a precomputed lattice offset
 constexpr int MAX_CLASSES = 256;
 
+__device__ __forceinline__ void bar_sync(int id, int nthreads) {
+	asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(nthreads) : "memory");
+}
+
 // ---------------------------------------------------------------------------------------
-// step counts + prefix sums: one CTA
+// step counts: 4 lanes per line (one per corner of the rough 2x2 grid), then one scan CTA
 // ---------------------------------------------------------------------------------------
-__device__ __forceinline__ float2 rough_point(const float2 *grid, int gh, int gw, int cell,
-	double inv_cell, double px, double py) {
-	og_d2 o = og_inverse_point(grid, gh, gw, cell, inv_cell, py, px);
-	return make_float2(__double2float_rn(o.x), __double2float_rn(o.y));
+__global__ void __launch_bounds__(256) og_line_steps_kernel(
+	const float2 *__restrict__ grid, int gh, int gw, int cell,
+	const og_line *__restrict__ lines, int n, int32_t *__restrict__ steps_out) {
+	const int t = blockIdx.x * blockDim.x + threadIdx.x;
+	const int i = min(t >> 2, n - 1), corner = t & 3;
+	const double inv_cell = 1.0 / (double)cell;
+	const og_line *ln = lines + i;
+	int xs = ln->xsteps, ys = ln->ysteps;
+	const bool derive = xs <= 0 || ys <= 0;
+	// Line.warped_grid(xsteps=2, ysteps=2) on the un-clipped line (block.py:226-228):
+	// samples p, p + right, (up + p), (up + p) + right
+	double qx = ln->p[0], qy = ln->p[1];
+	if (corner & 2) {
+		qx = __dadd_rn(ln->up[0], qx);
+		qy = __dadd_rn(ln->up[1], qy);
+	}
+	if (corner & 1) {
+		qx = __dadd_rn(qx, ln->right[0]);
+		qy = __dadd_rn(qy, ln->right[1]);
+	}
+	float gx = 0.f, gy = 0.f;
+	if (derive) {
+		og_d2 o = og_inverse_point(grid, gh, gw, cell, inv_cell, qy, qx);
+		gx = __double2float_rn(o.x);
+		gy = __double2float_rn(o.y);
+	}
+	const int base = (threadIdx.x & 31) & ~3;
+	const float g00x = __shfl_sync(0xffffffffu, gx, base), g00y = __shfl_sync(0xffffffffu, gy, base);
+	const float g01x = __shfl_sync(0xffffffffu, gx, base + 1), g01y = __shfl_sync(0xffffffffu, gy, base + 1);
+	const float g10x = __shfl_sync(0xffffffffu, gx, base + 2), g10y = __shfl_sync(0xffffffffu, gy, base + 2);
+	const float g11x = __shfl_sync(0xffffffffu, gx, base + 3), g11y = __shfl_sync(0xffffffffu, gy, base + 3);
+	if ((t >> 2) < n && corner == 0) {
+		if (xs <= 0) {
+			// np.max(np.abs(rough[:, 0, 0] - rough[:, 1, 0])) * xres, all fp32
+			const float wx = fmaxf(fabsf(__fsub_rn(g00x, g01x)), fabsf(__fsub_rn(g10x, g11x)));
+			const float v = ceilf(__fmul_rn(wx, (float)ln->xres));
+			xs = (wx == wx && v >= 0.f && v < 1.0e6f) ? max(2, (int)v) : 0;
+		}
+		if (ys <= 0) {
+			const float wy = fmaxf(fabsf(__fsub_rn(g00y, g10y)), fabsf(__fsub_rn(g01y, g11y)));
+			const float v = ceilf(__fmul_rn(wy, (float)ln->yres));
+			ys = (wy == wy && v >= 0.f && v < 1.0e6f) ? max(2, (int)v) : 0;
+		}
+		if ((long long)xs * ys >= (1ll << 31)) xs = ys = 0;
+		steps_out[2 * i] = xs;
+		steps_out[2 * i + 1] = ys;
+	}
 }
 
 template <typename T>
@@ -60,45 +117,18 @@ __device__ __forceinline__ T block_exclusive_scan(T v, T *warp_sums, T &total) {
 	return res;
 }
 
-__global__ void __launch_bounds__(1024) og_line_steps_kernel(
-	const float2 *__restrict__ grid, int gh, int gw, int cell,
-	const og_line *__restrict__ lines, int n,
-	int32_t *__restrict__ steps_out, int64_t *__restrict__ pix_offsets, int32_t *__restrict__ chunk_offsets) {
+__global__ void __launch_bounds__(1024) og_line_scan_kernel(
+	const int32_t *__restrict__ steps, int n, int64_t *__restrict__ pix_offsets, int32_t *__restrict__ chunk_offsets) {
 	__shared__ long long ws64[33];
 	__shared__ int ws32[33];
-	const double inv_cell = 1.0 / (double)cell;
 	long long carry_pix = 0;
 	int carry_chunks = 0;
 	for (int base = 0; base < n; base += blockDim.x) {
 		const int i = base + threadIdx.x;
 		int xs = 0, ys = 0;
 		if (i < n) {
-			const og_line ln = lines[i];
-			xs = ln.xsteps;
-			ys = ln.ysteps;
-			if (xs <= 0 || ys <= 0) {
-				// Line.warped_grid(xsteps=2, ysteps=2) on the un-clipped line (block.py:226-228):
-				// samples p, p+right, (up+p), (up+p)+right
-				const double qx = __dadd_rn(ln.up[0], ln.p[0]), qy = __dadd_rn(ln.up[1], ln.p[1]);
-				float2 g00 = rough_point(grid, gh, gw, cell, inv_cell, ln.p[0], ln.p[1]);
-				float2 g01 = rough_point(grid, gh, gw, cell, inv_cell, __dadd_rn(ln.p[0], ln.right[0]), __dadd_rn(ln.p[1], ln.right[1]));
-				float2 g10 = rough_point(grid, gh, gw, cell, inv_cell, qx, qy);
-				float2 g11 = rough_point(grid, gh, gw, cell, inv_cell, __dadd_rn(qx, ln.right[0]), __dadd_rn(qy, ln.right[1]));
-				if (xs <= 0) {
-					float wx = fmaxf(fabsf(__fsub_rn(g00.x, g01.x)), fabsf(__fsub_rn(g10.x, g11.x)));
-					float v = ceilf(__fmul_rn(wx, (float)ln.xres));
-					xs = (v >= 0.f && v < 1.0e6f) ? max(2, (int)v) : 0;
-					if (!(wx == wx)) xs = 0;
-				}
-				if (ys <= 0) {
-					float wy = fmaxf(fabsf(__fsub_rn(g00.y, g10.y)), fabsf(__fsub_rn(g01.y, g11.y)));
-					float v = ceilf(__fmul_rn(wy, (float)ln.yres));
-					ys = (v >= 0.f && v < 1.0e6f) ? max(2, (int)v) : 0;
-					if (!(wy == wy)) ys = 0;
-				}
-			}
-			steps_out[2 * i] = xs;
-			steps_out[2 * i + 1] = ys;
+			xs = steps[2 * i];
+			ys = steps[2 * i + 1];
 		}
 		long long npix = (long long)xs * (long long)ys;
 		int nchunks = (xs > 0 && ys > 0) ? (xs + CW - 1) / CW : 0;
@@ -134,10 +164,10 @@ struct LineParams {
 	const int32_t *chunk_offsets;
 	// MODE_GRID
 	float *grids_out;
-	// MODE_STRIP
+	// MODE_STRIP (src = warped page) / MODE_LABELS (src = label map)
 	const uint8_t *src;
 	int H, W;
-	int64_t src_pitch;
+	int src_pitch;
 	uint8_t *strips_out;
 	int32_t *bbox_out;
 	int64_t capacity;
@@ -153,6 +183,17 @@ struct RowEntry {
 	float b0, b1;
 };
 
+struct ItemCtx {
+	int valid;
+	int li, c0, ncols, xsteps, ysteps;
+	int staged, R0, C0, NR, NC, SR0, NSR;
+	int rows_tabled;
+	long long pix0;
+	og_lin lx, ly;
+	double cpx, cpy;
+	double2 rowbase[MAX_ROWS];  // (ys[r] + p0), block.py:241
+};
+
 __device__ __forceinline__ int find_line(const int32_t *__restrict__ chunk_offsets, int n, int item) {
 	int lo = 0, hi = n;  // invariant: chunk_offsets[lo] <= item < chunk_offsets[hi]
 	while (hi - lo > 1) {
@@ -162,127 +203,193 @@ __device__ __forceinline__ int find_line(const int32_t *__restrict__ chunk_offse
 	return lo;
 }
 
+// executed by the whole planner warp
 template <int MODE>
-__global__ void __launch_bounds__(LTHREADS) og_lines_kernel(LineParams p) {
-	extern __shared__ __align__(16) unsigned char smem_raw[];
-	__shared__ unsigned int hist[MODE == MODE_LABELS ? MAX_CLASSES + 1 : 1];
-	__shared__ int s_bbox[4];
-
+__device__ void plan_item(const LineParams &p, int item, ItemCtx *c) {
+	const int lane = threadIdx.x & 31;
 	const int Hd = p.gh * p.cell, Wd = p.gw * p.cell;
 	const double inv_cell = 1.0 / (double)p.cell;
+	const int li = find_line(p.chunk_offsets, p.n, item);
+	const int chunk = item - __ldg(p.chunk_offsets + li);
+	const int xsteps = __ldg(p.steps + 2 * li), ysteps = __ldg(p.steps + 2 * li + 1);
+	const long long pix0 = (MODE != MODE_LABELS) ? __ldg(p.pix_offsets + li) : 0;
+	const bool valid = MODE == MODE_LABELS || pix0 + (long long)xsteps * ysteps <= p.capacity;
+	const og_line *ln = p.lines + li;
+	const double cpx = ln->cp[0], cpy = ln->cp[1];
+	const int c0 = chunk * CW;
+	const int ncols = min(CW, xsteps - c0);
+	const og_lin lx = og_linspace_setup(ln->cright[0], ln->cright[1], xsteps);
+	const og_lin ly = og_linspace_setup(ln->up[0], ln->up[1], ysteps);
+
+	// region of dense-map nodes under this chunk: the lattice is affine, so its extremes
+	// are at the four corners (one margin cell absorbs rounding)
+	double ymin = 1e300, ymax = -1e300, xmin = 1e300, xmax = -1e300;
+#pragma unroll
+	for (int k = 0; k < 4; ++k) {
+		og_d2 yr = og_linspace_at(ly, (k & 1) ? ysteps - 1 : 0);
+		og_d2 xc = og_linspace_at(lx, (k & 2) ? c0 + ncols - 1 : c0);
+		const double px = __dadd_rn(__dadd_rn(yr.x, cpx), xc.x);
+		const double py = __dadd_rn(__dadd_rn(yr.y, cpy), xc.y);
+		ymin = fmin(ymin, py); ymax = fmax(ymax, py);
+		xmin = fmin(xmin, px); xmax = fmax(xmax, px);
+	}
+	bool staged = (ymin == ymin) && (xmin == xmin) && fabs(ymin) < 1e9 && fabs(ymax) < 1e9 &&
+		fabs(xmin) < 1e9 && fabs(xmax) < 1e9;
+	int R0 = 0, C0 = 0, NR = 0, NC = 0, SR0 = 0, NSR = 0;
+	if (staged) {
+		R0 = min(max((int)floor(ymin) - 1, 0), Hd - 2);
+		const int R1 = min(max((int)floor(ymax) + 1, 0), Hd - 2) + 1;
+		C0 = min(max((int)floor(xmin) - 1, 0), Wd - 2);
+		const int C1 = min(max((int)floor(xmax) + 1, 0), Wd - 2) + 1;
+		NR = R1 - R0 + 1;
+		NC = C1 - C0 + 1;
+		og_axis a0 = og_resize_axis(R0, inv_cell), a1 = og_resize_axis(R1, inv_cell);
+		SR0 = min(max(a0.i, 0), p.gh - 1);
+		const int SR1 = min(max(a1.i + 1, 0), p.gh - 1);
+		NSR = SR1 - SR0 + 1;
+		const size_t need = (size_t)NR * NC * sizeof(double2) + (size_t)NSR * NC * sizeof(float2) +
+			(size_t)NR * sizeof(RowEntry);
+		staged = need <= (size_t)SMEM_BUDGET;
+	}
+	const int tabled = ysteps <= MAX_ROWS;
+	if (tabled) {
+		for (int r = lane; r < ysteps; r += 32) {
+			og_d2 yr = og_linspace_at(ly, r);
+			c->rowbase[r] = make_double2(__dadd_rn(yr.x, cpx), __dadd_rn(yr.y, cpy));
+		}
+	}
+	if (lane == 0) {
+		c->valid = valid;
+		c->li = li; c->c0 = c0; c->ncols = ncols; c->xsteps = xsteps; c->ysteps = ysteps;
+		c->staged = staged; c->R0 = R0; c->C0 = C0; c->NR = NR; c->NC = NC; c->SR0 = SR0; c->NSR = NSR;
+		c->rows_tabled = tabled;
+		c->pix0 = pix0;
+		c->lx = lx; c->ly = ly;
+		c->cpx = cpx; c->cpy = cpy;
+	}
+	__syncwarp();
+}
+
+template <int MODE, bool BBOX>
+__global__ void __launch_bounds__(LTHREADS, 2) og_lines_kernel(const __grid_constant__ LineParams p) {
+	extern __shared__ __align__(16) unsigned char smem_raw[];
+	__shared__ ItemCtx s_ctx[2];
+	__shared__ unsigned int s_hist[MODE == MODE_LABELS ? MAX_CLASSES + 1 : 1];
+	__shared__ int s_bbox[4];
+
 	const int total_items = __ldg(p.chunk_offsets + p.n);
 	const int tid = threadIdx.x;
+	const bool planner = tid >= WORKERS;
+	const int first = blockIdx.x;
+	if (first >= total_items) return;
 
-	for (int item = blockIdx.x; item < total_items; item += gridDim.x) {
-		const int li = find_line(p.chunk_offsets, p.n, item);
-		const int chunk = item - __ldg(p.chunk_offsets + li);
-		const int xsteps = __ldg(p.steps + 2 * li), ysteps = __ldg(p.steps + 2 * li + 1);
-		const int64_t pix0 = (MODE != MODE_LABELS) ? __ldg(p.pix_offsets + li) : 0;
-		if (MODE != MODE_LABELS && pix0 + (int64_t)xsteps * ysteps > p.capacity) continue;
-		const og_line ln = p.lines[li];
-		const int c0 = chunk * CW;
-		const int ncols = min(CW, xsteps - c0);
-		const og_lin lx = og_linspace_setup(ln.cright[0], ln.cright[1], xsteps);
-		const og_lin ly = og_linspace_setup(ln.up[0], ln.up[1], ysteps);
+	if (planner) plan_item<MODE>(p, first, &s_ctx[0]);
+	bar_sync(0, LTHREADS);
 
-		// ---- region of dense-map nodes under this chunk (corners of the affine lattice)
-		double ymin = 1e300, ymax = -1e300, xmin = 1e300, xmax = -1e300;
-#pragma unroll
-		for (int k = 0; k < 4; ++k) {
-			og_d2 yr = og_linspace_at(ly, (k & 1) ? ysteps - 1 : 0);
-			og_d2 xc = og_linspace_at(lx, (k & 2) ? c0 + ncols - 1 : c0);
-			double px = __dadd_rn(__dadd_rn(yr.x, ln.cp[0]), xc.x);
-			double py = __dadd_rn(__dadd_rn(yr.y, ln.cp[1]), xc.y);
-			ymin = fmin(ymin, py); ymax = fmax(ymax, py);
-			xmin = fmin(xmin, px); xmax = fmax(xmax, px);
+	int k = 0;
+	for (int item = first; item < total_items; item += gridDim.x, ++k) {
+		if (planner) {
+			const int next = item + gridDim.x;
+			if (next < total_items) plan_item<MODE>(p, next, &s_ctx[(k + 1) & 1]);
+			bar_sync(0, LTHREADS);
+			continue;
 		}
-		bool staged = (ymin == ymin) && (xmin == xmin) && fabs(ymin) < 1e9 && fabs(ymax) < 1e9 &&
-			fabs(xmin) < 1e9 && fabs(xmax) < 1e9;
-		int R0 = 0, C0 = 0, NR = 0, NC = 0, SR0 = 0, NSR = 0;
-		if (staged) {
-			R0 = min(max((int)floor(ymin) - 1, 0), Hd - 2);
-			int R1 = min(max((int)floor(ymax) + 1, 0), Hd - 2) + 1;
-			C0 = min(max((int)floor(xmin) - 1, 0), Wd - 2);
-			int C1 = min(max((int)floor(xmax) + 1, 0), Wd - 2) + 1;
-			NR = R1 - R0 + 1;
-			NC = C1 - C0 + 1;
-			og_axis a0 = og_resize_axis(R0, inv_cell), a1 = og_resize_axis(R1, inv_cell);
-			SR0 = min(max(a0.i, 0), p.gh - 1);
-			int SR1 = min(max(a1.i + 1, 0), p.gh - 1);
-			NSR = SR1 - SR0 + 1;
-			size_t need = (size_t)NR * NC * sizeof(double2) + (size_t)NSR * NC * sizeof(float2) +
-				(size_t)NR * sizeof(RowEntry);
-			staged = need <= (size_t)SMEM_BUDGET;
+		const ItemCtx &c = s_ctx[k & 1];
+		if (!c.valid) {
+			bar_sync(0, LTHREADS);
+			continue;
 		}
+		const int Hd = p.gh * p.cell, Wd = p.gw * p.cell;
+		const double inv_cell = 1.0 / (double)p.cell;
+		const int NR = c.NR, NC = c.NC, NSR = c.NSR, R0 = c.R0, C0 = c.C0;
+		const bool staged = c.staged != 0;
 		double2 *nodes = reinterpret_cast<double2 *>(smem_raw);
 		float2 *hs = reinterpret_cast<float2 *>(smem_raw + (size_t)NR * NC * sizeof(double2));
 		RowEntry *rows = reinterpret_cast<RowEntry *>(smem_raw + (size_t)NR * NC * sizeof(double2) +
 			(size_t)NSR * NC * sizeof(float2));
 
-		__syncthreads();  // previous item's shared data is dead
-		if (MODE == MODE_LABELS) {
-			for (int k = tid; k <= MAX_CLASSES; k += LTHREADS) hist[k] = 0;
-		}
-		if (MODE == MODE_STRIP && tid < 4) s_bbox[tid] = (tid < 2) ? INT_MAX : INT_MIN;
+		if (MODE == MODE_LABELS)
+			for (int q = tid; q <= MAX_CLASSES; q += WORKERS) s_hist[q] = 0;
+		if (BBOX && tid < 4) s_bbox[tid] = (tid < 2) ? INT_MAX : INT_MIN;
 		if (staged) {
 			// horizontal pass over the sparse rows of the band (HResizeLinear)
-			for (int j = tid; j < NC; j += LTHREADS) {
+			for (int j = tid; j < NC; j += WORKERS) {
 				og_axis ax = og_resize_axis_x(C0 + j, inv_cell, p.gw);
 				const int c1 = min(ax.i + 1, p.gw - 1);
 				const float w0 = __fsub_rn(1.f, ax.f), w1 = ax.f;
 				for (int r = 0; r < NSR; ++r) {
-					const float2 *g = p.grid + (size_t)(SR0 + r) * p.gw;
+					const float2 *g = p.grid + (c.SR0 + r) * p.gw;
 					float2 s0 = __ldg(g + ax.i), s1 = __ldg(g + c1);
 					hs[r * NC + j] = make_float2(og_lerp_cv(s0.x, s1.x, w0, w1), og_lerp_cv(s0.y, s1.y, w0, w1));
 				}
 			}
-			for (int i = tid; i < NR; i += LTHREADS) {
+			for (int i = tid; i < NR; i += WORKERS) {
 				og_axis ay = og_resize_axis(R0 + i, inv_cell);
 				RowEntry e;
-				e.r0 = min(max(ay.i, 0), p.gh - 1) - SR0;
-				e.r1 = min(max(ay.i + 1, 0), p.gh - 1) - SR0;
+				e.r0 = (min(max(ay.i, 0), p.gh - 1) - c.SR0) * NC;
+				e.r1 = (min(max(ay.i + 1, 0), p.gh - 1) - c.SR0) * NC;
 				e.b1 = ay.f;
 				e.b0 = __fsub_rn(1.f, ay.f);
 				rows[i] = e;
 			}
-			__syncthreads();
-			// vertical pass (VResizeLinear) -> float64 nodes
-			for (int k = tid; k < NR * NC; k += LTHREADS) {
-				const int i = k / NC, j = k - i * NC;
+			bar_sync(1, WORKERS);
+			// vertical pass (VResizeLinear) -> float64 nodes; (i, j) advance without division
+			int i = tid / NC, j = tid - i * NC;
+			const int di = WORKERS / NC, dj = WORKERS - di * NC;
+			for (int q = tid; q < NR * NC; q += WORKERS) {
 				const RowEntry e = rows[i];
-				const float2 u = hs[e.r0 * NC + j], v = hs[e.r1 * NC + j];
-				nodes[k] = make_double2((double)og_lerp_cv(u.x, v.x, e.b0, e.b1),
+				const float2 u = hs[e.r0 + j], v = hs[e.r1 + j];
+				nodes[q] = make_double2((double)og_lerp_cv(u.x, v.x, e.b0, e.b1),
 					(double)og_lerp_cv(u.y, v.y, e.b0, e.b1));
+				i += di;
+				j += dj;
+				if (j >= NC) {
+					j -= NC;
+					++i;
+				}
 			}
 		}
-		__syncthreads();
+		bar_sync(1, WORKERS);
 
-		// ---- sample phase: thread = (column, row quarter)
-		const int col = tid % CW, rq = tid / CW;
-		const int rows_per = (ysteps + RSPLIT - 1) / RSPLIT;
-		const int rbeg = rq * rows_per, rend = min(ysteps, rbeg + rows_per);
+		// ---- sample phase: thread = (column, row group)
+		const int col = tid & (CW - 1), rq = tid / CW;
+		const int xsteps = c.xsteps, ysteps = c.ysteps;
 		float bx0 = 3.0e38f, by0 = 3.0e38f, bx1 = -3.0e38f, by1 = -3.0e38f;
-		if (col < ncols) {
-			const int c = c0 + col;
-			const og_d2 xc = og_linspace_at(lx, c);
-			for (int r = rbeg; r < rend; ++r) {
-				const og_d2 yr = og_linspace_at(ly, r);
+		if (col < c.ncols) {
+			const int cc = c.c0 + col;
+			const og_d2 xc = og_linspace_at(c.lx, cc);
+			const int NRm = NR - 1, NCm = NC - 1, Hm = Hd - 2, Wm = Wd - 2;
+			const bool tabled = c.rows_tabled != 0;
+			uint8_t *strip = (MODE == MODE_STRIP) ? p.strips_out + c.pix0 + cc : nullptr;
+			float2 *gout = (MODE == MODE_GRID) ? reinterpret_cast<float2 *>(p.grids_out) + c.pix0 + cc : nullptr;
+			const uint8_t *__restrict__ src = p.src;
+			const int H = p.H, W = p.W, spitch = p.src_pitch;
+#pragma unroll 2
+			for (int r = rq; r < ysteps; r += RSPLIT) {
+				double2 rb;
+				if (tabled) {
+					rb = c.rowbase[r];
+				} else {
+					og_d2 yr = og_linspace_at(c.ly, r);
+					rb = make_double2(__dadd_rn(yr.x, c.cpx), __dadd_rn(yr.y, c.cpy));
+				}
 				// dewarped_grid = (ys + p0)[:, None] + xs[None, :]   (block.py:241)
-				const double px = __dadd_rn(__dadd_rn(yr.x, ln.cp[0]), xc.x);
-				const double py = __dadd_rn(__dadd_rn(yr.y, ln.cp[1]), xc.y);
+				const double px = __dadd_rn(rb.x, xc.x);
+				const double py = __dadd_rn(rb.y, xc.y);
 				og_d2 w;
 				bool done = false;
 				if (staged) {
-					double fy = fmin(fmax(floor(py), 0.0), (double)(Hd - 2));
-					double fx = fmin(fmax(floor(px), 0.0), (double)(Wd - 2));
-					const int ri = (int)fy - R0, ci = (int)fx - C0;
-					if (ri >= 0 && ri < NR - 1 && ci >= 0 && ci < NC - 1) {
-						const double a = __dsub_rn(py, fy), b = __dsub_rn(px, fx);
+					// i = clip(floor(y), 0, n - 2) (SciPy find_indices); |y| < 1e9 here
+					const int i0 = min(max(__double2int_rd(py), 0), Hm);
+					const int i1 = min(max(__double2int_rd(px), 0), Wm);
+					const int ri = i0 - R0, ci = i1 - C0;
+					if ((unsigned)ri < (unsigned)NRm && (unsigned)ci < (unsigned)NCm) {
+						const double a = __dsub_rn(py, (double)i0), b = __dsub_rn(px, (double)i1);
 						const double wa = __dsub_rn(1.0, a), wb = __dsub_rn(1.0, b);
 						const double w00 = __dmul_rn(wa, wb), w01 = __dmul_rn(wa, b);
 						const double w10 = __dmul_rn(a, wb), w11 = __dmul_rn(a, b);
-						const double2 v00 = nodes[ri * NC + ci], v01 = nodes[ri * NC + ci + 1];
-						const double2 v10 = nodes[(ri + 1) * NC + ci], v11 = nodes[(ri + 1) * NC + ci + 1];
+						const double2 *nd = nodes + (ri * NC + ci);
+						const double2 v00 = nd[0], v01 = nd[1], v10 = nd[NC], v11 = nd[NC + 1];
 						w.x = __dadd_rn(__dadd_rn(__dadd_rn(__dmul_rn(v00.x, w00), __dmul_rn(v01.x, w01)),
 							__dmul_rn(v10.x, w10)), __dmul_rn(v11.x, w11));
 						w.y = __dadd_rn(__dadd_rn(__dadd_rn(__dmul_rn(v00.y, w00), __dmul_rn(v01.y, w01)),
@@ -293,23 +400,23 @@ __global__ void __launch_bounds__(LTHREADS) og_lines_kernel(LineParams p) {
 				if (!done) w = og_inverse_point(p.grid, p.gh, p.gw, p.cell, inv_cell, py, px);
 				const float gx = __double2float_rn(w.x), gy = __double2float_rn(w.y);
 				if (MODE == MODE_GRID) {
-					float2 *o = reinterpret_cast<float2 *>(p.grids_out) + pix0 + (int64_t)r * xsteps + c;
-					*o = make_float2(gx, gy);
+					gout[r * xsteps] = make_float2(gx, gy);
 				} else if (MODE == MODE_STRIP) {
-					const int v = og_sample_linear(p.src, p.H, p.W, p.src_pitch, gx, gy, 0);
 					// pixels[::-1, :]  (block.py:257)
-					p.strips_out[pix0 + (int64_t)(ysteps - 1 - r) * xsteps + c] = (uint8_t)v;
-					bx0 = fminf(bx0, gx); bx1 = fmaxf(bx1, gx);
-					by0 = fminf(by0, gy); by1 = fmaxf(by1, gy);
+					strip[(ysteps - 1 - r) * xsteps] = (uint8_t)og_sample_linear_fast(src, H, W, spitch, gx, gy);
+					if (BBOX) {
+						bx0 = fminf(bx0, gx); bx1 = fmaxf(bx1, gx);
+						by0 = fminf(by0, gy); by1 = fmaxf(by1, gy);
+					}
 				} else {
 					// scale_grid (batch/detect/lines.py:18-22) then cv2.remap INTER_NEAREST
 					const float sx = __fmul_rn(gx, p.scale_x), sy = __fmul_rn(gy, p.scale_y);
-					const int lab = og_sample_nearest(p.src, p.H, p.W, p.src_pitch, sx, sy, 0);
-					atomicAdd(&hist[min(lab, p.n_classes)], 1u);
+					const int lab = og_sample_nearest_fast(src, H, W, spitch, sx, sy);
+					atomicAdd(&s_hist[min(lab, p.n_classes)], 1u);
 				}
 			}
 		}
-		if (MODE == MODE_STRIP && p.bbox_out != nullptr) {
+		if (BBOX) {
 #pragma unroll
 			for (int o = 16; o > 0; o >>= 1) {
 				bx0 = fminf(bx0, __shfl_xor_sync(0xffffffffu, bx0, o));
@@ -323,19 +430,20 @@ __global__ void __launch_bounds__(LTHREADS) og_lines_kernel(LineParams p) {
 				atomicMax(&s_bbox[2], (int)ceilf(bx1));
 				atomicMax(&s_bbox[3], (int)ceilf(by1));
 			}
-			__syncthreads();
+			bar_sync(1, WORKERS);
 			if (tid < 4 && s_bbox[0] <= s_bbox[2]) {
-				if (tid < 2) atomicMin(p.bbox_out + 4 * li + tid, s_bbox[tid]);
-				else atomicMax(p.bbox_out + 4 * li + tid, s_bbox[tid]);
+				if (tid < 2) atomicMin(p.bbox_out + 4 * c.li + tid, s_bbox[tid]);
+				else atomicMax(p.bbox_out + 4 * c.li + tid, s_bbox[tid]);
 			}
 		}
 		if (MODE == MODE_LABELS) {
-			__syncthreads();
-			for (int k = tid; k < p.n_classes; k += LTHREADS)
-				if (hist[k]) atomicAdd(p.counts_out + (size_t)li * p.n_classes + k, (unsigned long long)hist[k]);
-			if (tid == 0 && hist[p.n_classes] && p.overflow_out != nullptr)
-				atomicAdd(p.overflow_out + li, (unsigned long long)hist[p.n_classes]);
+			bar_sync(1, WORKERS);
+			for (int q = tid; q < p.n_classes; q += WORKERS)
+				if (s_hist[q]) atomicAdd(p.counts_out + (size_t)c.li * p.n_classes + q, (unsigned long long)s_hist[q]);
+			if (tid == 0 && s_hist[p.n_classes] && p.overflow_out != nullptr)
+				atomicAdd(p.overflow_out + c.li, (unsigned long long)s_hist[p.n_classes]);
 		}
+		bar_sync(0, LTHREADS);
 	}
 }
 
@@ -376,12 +484,12 @@ int check_lines(const og_line *lines, int n, const int32_t *steps, const int32_t
 	return OG_OK;
 }
 
-template <int MODE>
+template <int MODE, bool BBOX>
 int launch_lines(const LineParams &p, cudaStream_t st) {
-	cudaError_t e = cudaFuncSetAttribute(og_lines_kernel<MODE>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_BUDGET);
+	cudaError_t e = cudaFuncSetAttribute(og_lines_kernel<MODE, BBOX>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_BUDGET);
 	if (e != cudaSuccess) return og_set_error((int)e, "cudaFuncSetAttribute: %s", cudaGetErrorString(e));
-	// persistent grid: two CTAs per SM fit the 100 KB staging budget
-	og_lines_kernel<MODE><<<OG_NUM_SMS * 2, LTHREADS, SMEM_BUDGET, st>>>(p);
+	// persistent grid: two CTAs per SM fit the staging budget
+	og_lines_kernel<MODE, BBOX><<<OG_NUM_SMS * 2, LTHREADS, SMEM_BUDGET, st>>>(p);
 	return og_check_launch("og_lines_kernel");
 }
 
@@ -409,9 +517,16 @@ extern "C" int og_line_steps(const float *grid, int gh, int gw, int cell,
 	OG_REQUIRE(n == 0 || lines != nullptr, OG_E_ARG, "lines is NULL");
 	OG_REQUIRE(pix_offsets_out != nullptr && chunk_offsets_out != nullptr && (n == 0 || steps_out != nullptr),
 		OG_E_ARG, "output pointer is NULL");
-	og_line_steps_kernel<<<1, 1024, 0, (cudaStream_t)stream>>>(reinterpret_cast<const float2 *>(grid), gh, gw, cell,
-		lines, n, steps_out, pix_offsets_out, chunk_offsets_out);
-	return og_check_launch("og_line_steps_kernel");
+	cudaStream_t st = (cudaStream_t)stream;
+	if (n > 0) {
+		const int threads = 256, per_block = threads / 4;
+		og_line_steps_kernel<<<(n + per_block - 1) / per_block, threads, 0, st>>>(
+			reinterpret_cast<const float2 *>(grid), gh, gw, cell, lines, n, steps_out);
+		rc = og_check_launch("og_line_steps_kernel");
+		if (rc) return rc;
+	}
+	og_line_scan_kernel<<<1, 1024, 0, st>>>(steps_out, n, pix_offsets_out, chunk_offsets_out);
+	return og_check_launch("og_line_scan_kernel");
 }
 
 extern "C" int og_warped_grids(const float *grid, int gh, int gw, int cell,
@@ -432,7 +547,7 @@ extern "C" int og_warped_grids(const float *grid, int gh, int gw, int cell,
 	p.steps = steps; p.pix_offsets = pix_offsets; p.chunk_offsets = chunk_offsets;
 	p.grids_out = grids_out;
 	p.capacity = capacity;
-	return launch_lines<MODE_GRID>(p, (cudaStream_t)stream);
+	return launch_lines<MODE_GRID, false>(p, (cudaStream_t)stream);
 }
 
 extern "C" int og_extract_lines(const uint8_t *src, int H, int W, int64_t src_pitch,
@@ -447,23 +562,25 @@ extern "C" int og_extract_lines(const uint8_t *src, int H, int W, int64_t src_pi
 	if (n == 0) return OG_OK;
 	OG_REQUIRE(src != nullptr && H > 0 && W > 0 && src_pitch >= W, OG_E_ARG, "src invalid");
 	OG_REQUIRE(H < 32767 && W < 32767, OG_E_RANGE, "source %d x %d exceeds OpenCV's 32767 limit", W, H);
+	OG_REQUIRE((int64_t)H * src_pitch < ((int64_t)1 << 31), OG_E_RANGE, "source image larger than 2 GiB");
 	OG_REQUIRE(pix_offsets != nullptr && strips_out != nullptr, OG_E_ARG, "pix_offsets / strips_out is NULL");
 	cudaStream_t st = (cudaStream_t)stream;
-	if (bbox_out != nullptr) {
-		og_bbox_init_kernel<<<(n + 255) / 256, 256, 0, st>>>(bbox_out, n);
-		rc = og_check_launch("og_bbox_init_kernel");
-		if (rc) return rc;
-	}
 	LineParams p{};
 	p.grid = reinterpret_cast<const float2 *>(grid);
 	p.gh = gh; p.gw = gw; p.cell = cell;
 	p.lines = lines; p.n = n;
 	p.steps = steps; p.pix_offsets = pix_offsets; p.chunk_offsets = chunk_offsets;
-	p.src = src; p.H = H; p.W = W; p.src_pitch = src_pitch;
+	p.src = src; p.H = H; p.W = W; p.src_pitch = (int)src_pitch;
 	p.strips_out = strips_out;
 	p.bbox_out = bbox_out;
 	p.capacity = capacity;
-	return launch_lines<MODE_STRIP>(p, st);
+	if (bbox_out != nullptr) {
+		og_bbox_init_kernel<<<(n + 255) / 256, 256, 0, st>>>(bbox_out, n);
+		rc = og_check_launch("og_bbox_init_kernel");
+		if (rc) return rc;
+		return launch_lines<MODE_STRIP, true>(p, st);
+	}
+	return launch_lines<MODE_STRIP, false>(p, st);
 }
 
 extern "C" int og_sample_labels(const uint8_t *labels, int lh, int lw, int64_t labels_pitch,
@@ -480,6 +597,7 @@ extern "C" int og_sample_labels(const uint8_t *labels, int lh, int lw, int64_t l
 	if (n == 0) return OG_OK;
 	OG_REQUIRE(labels != nullptr && lh > 0 && lw > 0 && labels_pitch >= lw, OG_E_ARG, "labels invalid");
 	OG_REQUIRE(lh < 32767 && lw < 32767, OG_E_RANGE, "label map exceeds OpenCV's 32767 limit");
+	OG_REQUIRE((int64_t)lh * labels_pitch < ((int64_t)1 << 31), OG_E_RANGE, "label map larger than 2 GiB");
 	OG_REQUIRE(H > 0 && W > 0, OG_E_ARG, "page size invalid");
 	OG_REQUIRE(counts_out != nullptr, OG_E_ARG, "counts_out is NULL");
 	cudaStream_t st = (cudaStream_t)stream;
@@ -492,12 +610,12 @@ extern "C" int og_sample_labels(const uint8_t *labels, int lh, int lw, int64_t l
 	p.lines = lines; p.n = n;
 	p.steps = steps; p.chunk_offsets = chunk_offsets;
 	p.pix_offsets = nullptr;
-	p.src = labels; p.H = lh; p.W = lw; p.src_pitch = labels_pitch;
+	p.src = labels; p.H = lh; p.W = lw; p.src_pitch = (int)labels_pitch;
 	// scale_grid: grid[:, :, 0] *= w1 / w0 with the ratio rounded to fp32
 	p.scale_x = (float)((double)lw / (double)W);
 	p.scale_y = (float)((double)lh / (double)H);
 	p.n_classes = n_classes;
 	p.counts_out = reinterpret_cast<unsigned long long *>(counts_out);
 	p.overflow_out = reinterpret_cast<unsigned long long *>(overflow_out);
-	return launch_lines<MODE_LABELS>(p, st);
+	return launch_lines<MODE_LABELS, false>(p, st);
 }

@@ -5,11 +5,13 @@
 // dewarped pixel; no tensor cores.
 //
 // Layout: one CTA = 64 x 4 threads covers a 256 x 32 pixel tile of the dewarped page.  A
-// thread owns 4 consecutive pixels of a row (one uchar4 image store, two float4 map stores:
+// thread owns 4 consecutive pixels of a row (one 32-bit image store, two float4 map stores:
 // a warp writes 128 B / 1 KiB contiguous per row) and walks 8 consecutive rows, so the
 // x-axis interpolation state and the horizontally interpolated sparse rows stay in
 // registers; they are refreshed only when the row crosses into the next sparse cell, which
-// is uniform across the CTA.
+// is uniform across the CTA.  The y-axis state of the tile's 32 rows is computed once per
+// CTA into shared memory.  Source taps are gathered through the read-only path with 32-bit
+// offsets; the smooth warp makes neighbouring threads hit the same 128-byte lines.
 #include "og_common.cuh"
 
 namespace {
@@ -34,44 +36,70 @@ struct PageParams {
 };
 
 template <bool LINEAR>
-__global__ void __launch_bounds__(TBX *TBY) og_page_kernel(PageParams p) {
+__device__ __forceinline__ int sample_px(const uint8_t *__restrict__ src, int H, int W, int pitch, float mx, float my) {
+	return LINEAR ? og_sample_linear_fast(src, H, W, pitch, mx, my) : og_sample_nearest_fast(src, H, W, pitch, mx, my);
+}
+
+struct RowAxis {
+	int r0, r1;
+	float b0, b1;
+};
+
+template <bool LINEAR, bool SCALED, bool WRITE_MAP, bool WRITE_IMG>
+__global__ void __launch_bounds__(TBX *TBY, 3) og_page_kernel(const __grid_constant__ PageParams p) {
+	__shared__ RowAxis s_rows[TILE_H];
 	const int Wd = p.gw * p.cell, Hd = p.gh * p.cell;
 	const int x0 = (blockIdx.x * TBX + threadIdx.x) * TPX;
-	const int ybeg = blockIdx.y * TILE_H + threadIdx.y * TROWS;
-	if (x0 >= Wd || ybeg >= Hd) return;
+	const int ytile = blockIdx.y * TILE_H;
 	const double inv_cell = 1.0 / (double)p.cell;
+	const int tid = threadIdx.y * TBX + threadIdx.x;
+	if (tid < TILE_H) {
+		// y axis of cv2.resize for the 32 rows of this tile, computed once per CTA
+		og_axis ay = og_resize_axis(min(ytile + tid, Hd - 1), inv_cell);
+		RowAxis ra;
+		ra.r0 = min(max(ay.i, 0), p.gh - 1);
+		ra.r1 = min(max(ay.i + 1, 0), p.gh - 1);
+		ra.b1 = ay.f;
+		ra.b0 = __fsub_rn(1.f, ay.f);
+		s_rows[tid] = ra;
+	}
+	__syncthreads();
+	const int ybeg = ytile + threadIdx.y * TROWS;
+	if (x0 >= Wd || ybeg >= Hd) return;
 	const int npx = min(TPX, Wd - x0);
+	const int gw = p.gw;
+	const float2 *__restrict__ grid = p.grid;
 
 	int sx[TPX], sx1[TPX];
 	float a0[TPX], a1[TPX];
 #pragma unroll
 	for (int k = 0; k < TPX; ++k) {
-		og_axis ax = og_resize_axis_x(min(x0 + k, Wd - 1), inv_cell, p.gw);
+		og_axis ax = og_resize_axis_x(min(x0 + k, Wd - 1), inv_cell, gw);
 		sx[k] = ax.i;
-		sx1[k] = min(ax.i + 1, p.gw - 1);
+		sx1[k] = min(ax.i + 1, gw - 1);
 		a1[k] = ax.f;
 		a0[k] = __fsub_rn(1.f, ax.f);
 	}
 
-	const bool vec_map = p.map_out != nullptr && npx == TPX && (Wd & 1) == 0 &&
-		((reinterpret_cast<uintptr_t>(p.map_out) & 15) == 0);
-	const bool vec_img = p.dst != nullptr && npx == TPX && (p.dst_pitch & 3) == 0 &&
-		((reinterpret_cast<uintptr_t>(p.dst) & 3) == 0);
+	const bool vec_map = WRITE_MAP && npx == TPX && (Wd & 1) == 0 && ((reinterpret_cast<uintptr_t>(p.map_out) & 15) == 0);
+	const bool vec_img = WRITE_IMG && npx == TPX && (p.dst_pitch & 3) == 0 && ((reinterpret_cast<uintptr_t>(p.dst) & 3) == 0);
+	const uint8_t *__restrict__ src = p.src;
+	const int H = p.H, W = p.W, spitch = (int)p.src_pitch;
+	const float scx = p.scale_x, scy = p.scale_y;
 
 	int cur_r0 = -1, cur_r1 = -1;
 	float2 h0[TPX], h1[TPX];
+	float *mrow = WRITE_MAP ? p.map_out + ((size_t)ybeg * Wd + x0) * 2 : nullptr;
+	uint8_t *orow = WRITE_IMG ? p.dst + (int64_t)ybeg * p.dst_pitch + x0 : nullptr;
 
-	const int yend = min(ybeg + TROWS, Hd);
-	for (int y = ybeg; y < yend; ++y) {
-		og_axis ay = og_resize_axis(y, inv_cell);
-		const int r0 = min(max(ay.i, 0), p.gh - 1);
-		const int r1 = min(max(ay.i + 1, 0), p.gh - 1);
-		const float b1 = ay.f, b0 = __fsub_rn(1.f, ay.f);
-		if (r0 != cur_r0 || r1 != cur_r1) {
-			cur_r0 = r0;
-			cur_r1 = r1;
-			const float2 *g0 = p.grid + (size_t)r0 * p.gw;
-			const float2 *g1 = p.grid + (size_t)r1 * p.gw;
+	const int nrows = min(TROWS, Hd - ybeg);
+	for (int yy = 0; yy < nrows; ++yy) {
+		const RowAxis ra = s_rows[threadIdx.y * TROWS + yy];
+		if (ra.r0 != cur_r0 || ra.r1 != cur_r1) {
+			cur_r0 = ra.r0;
+			cur_r1 = ra.r1;
+			const float2 *g0 = grid + ra.r0 * gw;
+			const float2 *g1 = grid + ra.r1 * gw;
 #pragma unroll
 			for (int k = 0; k < TPX; ++k) {
 				float2 s00 = __ldg(g0 + sx[k]), s01 = __ldg(g0 + sx1[k]);
@@ -85,51 +113,63 @@ __global__ void __launch_bounds__(TBX *TBY) og_page_kernel(PageParams p) {
 		float2 d[TPX];
 #pragma unroll
 		for (int k = 0; k < TPX; ++k) {
-			d[k].x = og_lerp_cv(h0[k].x, h1[k].x, b0, b1);
-			d[k].y = og_lerp_cv(h0[k].y, h1[k].y, b0, b1);
+			d[k].x = og_lerp_cv(h0[k].x, h1[k].x, ra.b0, ra.b1);
+			d[k].y = og_lerp_cv(h0[k].y, h1[k].y, ra.b0, ra.b1);
 		}
-		if (p.map_out != nullptr) {
-			float *row = p.map_out + ((size_t)y * Wd + x0) * 2;
+		if (WRITE_MAP) {
 			if (vec_map) {
-				__stcs(reinterpret_cast<float4 *>(row), make_float4(d[0].x, d[0].y, d[1].x, d[1].y));
-				__stcs(reinterpret_cast<float4 *>(row) + 1, make_float4(d[2].x, d[2].y, d[3].x, d[3].y));
+				__stcs(reinterpret_cast<float4 *>(mrow), make_float4(d[0].x, d[0].y, d[1].x, d[1].y));
+				__stcs(reinterpret_cast<float4 *>(mrow) + 1, make_float4(d[2].x, d[2].y, d[3].x, d[3].y));
 			} else {
 #pragma unroll
 				for (int k = 0; k < TPX; ++k)
-					if (k < npx) __stcs(reinterpret_cast<float2 *>(row) + k, d[k]);
+					if (k < npx) __stcs(reinterpret_cast<float2 *>(mrow) + k, d[k]);
 			}
+			mrow += (size_t)Wd * 2;
 		}
-		if (p.dst != nullptr) {
+		if (WRITE_IMG) {
 			int v[TPX];
 #pragma unroll
 			for (int k = 0; k < TPX; ++k) {
-				float mx = __fmul_rn(d[k].x, p.scale_x);
-				float my = __fmul_rn(d[k].y, p.scale_y);
-				v[k] = LINEAR ? og_sample_linear(p.src, p.H, p.W, p.src_pitch, mx, my, 0)
-							  : og_sample_nearest(p.src, p.H, p.W, p.src_pitch, mx, my, 0);
+				const float mx = SCALED ? __fmul_rn(d[k].x, scx) : d[k].x;
+				const float my = SCALED ? __fmul_rn(d[k].y, scy) : d[k].y;
+				v[k] = sample_px<LINEAR>(src, H, W, spitch, mx, my);
 			}
-			uint8_t *orow = p.dst + (int64_t)y * p.dst_pitch + x0;
 			if (vec_img) {
-				uint32_t pk = (uint32_t)v[0] | ((uint32_t)v[1] << 8) | ((uint32_t)v[2] << 16) |
-					((uint32_t)v[3] << 24);
+				const uint32_t pk = (uint32_t)v[0] | ((uint32_t)v[1] << 8) | ((uint32_t)v[2] << 16) | ((uint32_t)v[3] << 24);
 				__stcs(reinterpret_cast<uint32_t *>(orow), pk);
 			} else {
 #pragma unroll
 				for (int k = 0; k < TPX; ++k)
 					if (k < npx) orow[k] = (uint8_t)v[k];
 			}
+			orow += p.dst_pitch;
 		}
 	}
+}
+
+template <bool LINEAR, bool SCALED>
+void launch_variant(const PageParams &p, dim3 grid, dim3 block, cudaStream_t st) {
+	if (p.map_out != nullptr && p.dst != nullptr)
+		og_page_kernel<LINEAR, SCALED, true, true><<<grid, block, 0, st>>>(p);
+	else if (p.dst != nullptr)
+		og_page_kernel<LINEAR, SCALED, false, true><<<grid, block, 0, st>>>(p);
+	else
+		og_page_kernel<true, false, true, false><<<grid, block, 0, st>>>(p);
 }
 
 int launch_page(const PageParams &p, int interp, cudaStream_t st) {
 	const int Wd = p.gw * p.cell, Hd = p.gh * p.cell;
 	dim3 block(TBX, TBY);
 	dim3 grid((Wd + TILE_W - 1) / TILE_W, (Hd + TILE_H - 1) / TILE_H);
-	if (interp == OG_INTER_LINEAR)
-		og_page_kernel<true><<<grid, block, 0, st>>>(p);
-	else
-		og_page_kernel<false><<<grid, block, 0, st>>>(p);
+	const bool scaled = !(p.scale_x == 1.f && p.scale_y == 1.f);
+	if (interp == OG_INTER_LINEAR) {
+		if (scaled) launch_variant<true, true>(p, grid, block, st);
+		else launch_variant<true, false>(p, grid, block, st);
+	} else {
+		if (scaled) launch_variant<false, true>(p, grid, block, st);
+		else launch_variant<false, false>(p, grid, block, st);
+	}
 	return og_check_launch("og_page_kernel");
 }
 
@@ -172,6 +212,7 @@ extern "C" int og_remap_page(const uint8_t *src, int H, int W, int64_t src_pitch
 		OG_REQUIRE(src != nullptr && H > 0 && W > 0, OG_E_ARG, "src is NULL or empty (%d x %d)", W, H);
 		OG_REQUIRE(H < 32767 && W < 32767, OG_E_RANGE, "source %d x %d exceeds OpenCV's 32767 limit", W, H);
 		OG_REQUIRE(src_pitch >= W && dst_pitch >= (int64_t)gw * cell, OG_E_ARG, "pitch smaller than row");
+		OG_REQUIRE((int64_t)H * src_pitch < ((int64_t)1 << 31), OG_E_RANGE, "source image larger than 2 GiB");
 	}
 	if (map_out != nullptr)
 		OG_REQUIRE((reinterpret_cast<uintptr_t>(map_out) & 7) == 0, OG_E_ALIGN, "map_out must be 8-byte aligned");
