@@ -149,6 +149,51 @@ __device__ __forceinline__ int og_sample_linear_fast(
 	return og_blend(q, p00, p01, p10, p11);
 }
 
+// N pixels at once: when every tap of every pixel is inside the image (the common case) all
+// 4N byte loads are issued back to back before the first blend, so their latencies overlap.
+template <int N>
+__device__ __forceinline__ void og_sample_linear_batch(
+	const uint8_t *__restrict__ src, int H, int W, int pitch,
+	const float (&mx)[N], const float (&my)[N], int (&out)[N]) {
+	int ix[N], iy[N];
+	og_fix q[N];
+	bool all_in = true;
+#pragma unroll
+	for (int k = 0; k < N; ++k) {
+		const int sx = __float2int_rn(__fmul_rn(mx[k], 32.f));
+		const int sy = __float2int_rn(__fmul_rn(my[k], 32.f));
+		ix[k] = sx >> 5;
+		iy[k] = sy >> 5;
+		q[k].fx = sx & 31;
+		q[k].fy = sy & 31;
+		all_in = all_in && (unsigned)ix[k] < (unsigned)(W - 1) && (unsigned)iy[k] < (unsigned)(H - 1);
+	}
+	if (all_in) {
+		int p00[N], p01[N], p10[N], p11[N];
+#pragma unroll
+		for (int k = 0; k < N; ++k) {
+			const uint8_t *s = src + (iy[k] * pitch + ix[k]);
+			p00[k] = __ldg(s);
+			p01[k] = __ldg(s + 1);
+			p10[k] = __ldg(s + pitch);
+			p11[k] = __ldg(s + pitch + 1);
+		}
+#pragma unroll
+		for (int k = 0; k < N; ++k) out[k] = og_blend(q[k], p00[k], p01[k], p10[k], p11[k]);
+	} else {
+#pragma unroll
+		for (int k = 0; k < N; ++k) {
+			q[k].ix = og_sat_short(ix[k]);
+			q[k].iy = og_sat_short(iy[k]);
+			const int a = og_tap(src, H, W, pitch, q[k].iy, q[k].ix, 0);
+			const int b = og_tap(src, H, W, pitch, q[k].iy, q[k].ix + 1, 0);
+			const int c = og_tap(src, H, W, pitch, q[k].iy + 1, q[k].ix, 0);
+			const int d = og_tap(src, H, W, pitch, q[k].iy + 1, q[k].ix + 1, 0);
+			out[k] = og_blend(q[k], a, b, c, d);
+		}
+	}
+}
+
 __device__ __forceinline__ int og_sample_nearest_fast(
 	const uint8_t *__restrict__ src, int H, int W, int pitch, float mx, float my) {
 	const int ix = og_sat_short(__float2int_rn(mx));

@@ -31,6 +31,7 @@ constexpr int RSPLIT = WORKERS / CW;    // rows are dealt round-robin to 4 threa
 constexpr int SMEM_BUDGET = 100 * 1024;
 constexpr int MAX_ROWS = 128;           // rows with a precomputed lattice offset
 constexpr int MAX_CLASSES = 256;
+constexpr int RB = 2;                   // strip rows a thread processes together (load batching)
 
 __device__ __forceinline__ void bar_sync(int id, int nthreads) {
 	asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(nthreads) : "memory");
@@ -333,19 +334,28 @@ __global__ void __launch_bounds__(LTHREADS, 2) og_lines_kernel(const __grid_cons
 				rows[i] = e;
 			}
 			bar_sync(1, WORKERS);
-			// vertical pass (VResizeLinear) -> float64 nodes; (i, j) advance without division
-			int i = tid / NC, j = tid - i * NC;
-			const int di = WORKERS / NC, dj = WORKERS - di * NC;
-			for (int q = tid; q < NR * NC; q += WORKERS) {
-				const RowEntry e = rows[i];
-				const float2 u = hs[e.r0 + j], v = hs[e.r1 + j];
-				nodes[q] = make_double2((double)og_lerp_cv(u.x, v.x, e.b0, e.b1),
-					(double)og_lerp_cv(u.y, v.y, e.b0, e.b1));
-				i += di;
-				j += dj;
-				if (j >= NC) {
-					j -= NC;
-					++i;
+			// vertical pass (VResizeLinear) -> float64 nodes.  A thread owns one column and a
+			// band of rows; the two horizontally interpolated sparse rows stay in registers
+			// until the row crosses into the next sparse cell.
+			{
+				const int groups = max(1, WORKERS / NC);
+				const int g = tid / NC, j = tid - g * NC;
+				if (g < groups) {
+					const int band = (NR + groups - 1) / groups;
+					const int ibeg = g * band, iend = min(NR, ibeg + band);
+					int cr0 = -1, cr1 = -1;
+					float2 u = make_float2(0.f, 0.f), v = u;
+					const int jstep = (NC <= WORKERS) ? NC * groups : WORKERS;  // NC > WORKERS: several passes
+					for (int jj = j; jj < NC; jj += jstep) {
+						cr0 = cr1 = -1;
+						for (int i = ibeg; i < iend; ++i) {
+							const RowEntry e = rows[i];
+							if (e.r0 != cr0) { cr0 = e.r0; u = hs[e.r0 + jj]; }
+							if (e.r1 != cr1) { cr1 = e.r1; v = hs[e.r1 + jj]; }
+							nodes[i * NC + jj] = make_double2((double)og_lerp_cv(u.x, v.x, e.b0, e.b1),
+								(double)og_lerp_cv(u.y, v.y, e.b0, e.b1));
+						}
+					}
 				}
 			}
 		}
@@ -364,55 +374,77 @@ __global__ void __launch_bounds__(LTHREADS, 2) og_lines_kernel(const __grid_cons
 			float2 *gout = (MODE == MODE_GRID) ? reinterpret_cast<float2 *>(p.grids_out) + c.pix0 + cc : nullptr;
 			const uint8_t *__restrict__ src = p.src;
 			const int H = p.H, W = p.W, spitch = p.src_pitch;
-#pragma unroll 2
-			for (int r = rq; r < ysteps; r += RSPLIT) {
-				double2 rb;
-				if (tabled) {
-					rb = c.rowbase[r];
-				} else {
-					og_d2 yr = og_linspace_at(c.ly, r);
-					rb = make_double2(__dadd_rn(yr.x, c.cpx), __dadd_rn(yr.y, c.cpy));
-				}
-				// dewarped_grid = (ys + p0)[:, None] + xs[None, :]   (block.py:241)
-				const double px = __dadd_rn(rb.x, xc.x);
-				const double py = __dadd_rn(rb.y, xc.y);
-				og_d2 w;
-				bool done = false;
-				if (staged) {
-					// i = clip(floor(y), 0, n - 2) (SciPy find_indices); |y| < 1e9 here
-					const int i0 = min(max(__double2int_rd(py), 0), Hm);
-					const int i1 = min(max(__double2int_rd(px), 0), Wm);
-					const int ri = i0 - R0, ci = i1 - C0;
-					if ((unsigned)ri < (unsigned)NRm && (unsigned)ci < (unsigned)NCm) {
-						const double a = __dsub_rn(py, (double)i0), b = __dsub_rn(px, (double)i1);
-						const double wa = __dsub_rn(1.0, a), wb = __dsub_rn(1.0, b);
-						const double w00 = __dmul_rn(wa, wb), w01 = __dmul_rn(wa, b);
-						const double w10 = __dmul_rn(a, wb), w11 = __dmul_rn(a, b);
-						const double2 *nd = nodes + (ri * NC + ci);
-						const double2 v00 = nd[0], v01 = nd[1], v10 = nd[NC], v11 = nd[NC + 1];
-						w.x = __dadd_rn(__dadd_rn(__dadd_rn(__dmul_rn(v00.x, w00), __dmul_rn(v01.x, w01)),
-							__dmul_rn(v10.x, w10)), __dmul_rn(v11.x, w11));
-						w.y = __dadd_rn(__dadd_rn(__dadd_rn(__dmul_rn(v00.y, w00), __dmul_rn(v01.y, w01)),
-							__dmul_rn(v10.y, w10)), __dmul_rn(v11.y, w11));
-						done = true;
+			for (int rbase = rq; rbase < ysteps; rbase += RB * RSPLIT) {
+				float gx[RB], gy[RB];
+				bool live[RB];
+#pragma unroll
+				for (int u = 0; u < RB; ++u) {
+					const int r = rbase + u * RSPLIT;
+					live[u] = r < ysteps;
+					const int rr = live[u] ? r : rbase;
+					double2 rb;
+					if (tabled) {
+						rb = c.rowbase[rr];
+					} else {
+						og_d2 yr = og_linspace_at(c.ly, rr);
+						rb = make_double2(__dadd_rn(yr.x, c.cpx), __dadd_rn(yr.y, c.cpy));
 					}
+					// dewarped_grid = (ys + p0)[:, None] + xs[None, :]   (block.py:241)
+					const double px = __dadd_rn(rb.x, xc.x);
+					const double py = __dadd_rn(rb.y, xc.y);
+					og_d2 w;
+					bool done = false;
+					if (staged) {
+						// i = clip(floor(y), 0, n - 2) (SciPy find_indices); |y| < 1e9 here
+						const int i0 = min(max(__double2int_rd(py), 0), Hm);
+						const int i1 = min(max(__double2int_rd(px), 0), Wm);
+						const int ri = i0 - R0, ci = i1 - C0;
+						if ((unsigned)ri < (unsigned)NRm && (unsigned)ci < (unsigned)NCm) {
+							const double a = __dsub_rn(py, (double)i0), b = __dsub_rn(px, (double)i1);
+							const double wa = __dsub_rn(1.0, a), wb = __dsub_rn(1.0, b);
+							const double w00 = __dmul_rn(wa, wb), w01 = __dmul_rn(wa, b);
+							const double w10 = __dmul_rn(a, wb), w11 = __dmul_rn(a, b);
+							const double2 *nd = nodes + (ri * NC + ci);
+							const double2 v00 = nd[0], v01 = nd[1], v10 = nd[NC], v11 = nd[NC + 1];
+							w.x = __dadd_rn(__dadd_rn(__dadd_rn(__dmul_rn(v00.x, w00), __dmul_rn(v01.x, w01)),
+								__dmul_rn(v10.x, w10)), __dmul_rn(v11.x, w11));
+							w.y = __dadd_rn(__dadd_rn(__dadd_rn(__dmul_rn(v00.y, w00), __dmul_rn(v01.y, w01)),
+								__dmul_rn(v10.y, w10)), __dmul_rn(v11.y, w11));
+							done = true;
+						}
+					}
+					if (!done) w = og_inverse_point(p.grid, p.gh, p.gw, p.cell, inv_cell, py, px);
+					gx[u] = __double2float_rn(w.x);
+					gy[u] = __double2float_rn(w.y);
 				}
-				if (!done) w = og_inverse_point(p.grid, p.gh, p.gw, p.cell, inv_cell, py, px);
-				const float gx = __double2float_rn(w.x), gy = __double2float_rn(w.y);
 				if (MODE == MODE_GRID) {
-					gout[r * xsteps] = make_float2(gx, gy);
+#pragma unroll
+					for (int u = 0; u < RB; ++u)
+						if (live[u]) gout[(rbase + u * RSPLIT) * xsteps] = make_float2(gx[u], gy[u]);
 				} else if (MODE == MODE_STRIP) {
-					// pixels[::-1, :]  (block.py:257)
-					strip[(ysteps - 1 - r) * xsteps] = (uint8_t)og_sample_linear_fast(src, H, W, spitch, gx, gy);
-					if (BBOX) {
-						bx0 = fminf(bx0, gx); bx1 = fmaxf(bx1, gx);
-						by0 = fminf(by0, gy); by1 = fmaxf(by1, gy);
+					int v[RB];
+					og_sample_linear_batch<RB>(src, H, W, spitch, gx, gy, v);
+#pragma unroll
+					for (int u = 0; u < RB; ++u) {
+						if (live[u]) {
+							// pixels[::-1, :]  (block.py:257)
+							strip[(ysteps - 1 - (rbase + u * RSPLIT)) * xsteps] = (uint8_t)v[u];
+							if (BBOX) {
+								bx0 = fminf(bx0, gx[u]); bx1 = fmaxf(bx1, gx[u]);
+								by0 = fminf(by0, gy[u]); by1 = fmaxf(by1, gy[u]);
+							}
+						}
 					}
 				} else {
-					// scale_grid (batch/detect/lines.py:18-22) then cv2.remap INTER_NEAREST
-					const float sx = __fmul_rn(gx, p.scale_x), sy = __fmul_rn(gy, p.scale_y);
-					const int lab = og_sample_nearest_fast(src, H, W, spitch, sx, sy);
-					atomicAdd(&s_hist[min(lab, p.n_classes)], 1u);
+#pragma unroll
+					for (int u = 0; u < RB; ++u) {
+						if (live[u]) {
+							// scale_grid (batch/detect/lines.py:18-22) then cv2.remap INTER_NEAREST
+							const float sx = __fmul_rn(gx[u], p.scale_x), sy = __fmul_rn(gy[u], p.scale_y);
+							const int lab = og_sample_nearest_fast(src, H, W, spitch, sx, sy);
+							atomicAdd(&s_hist[min(lab, p.n_classes)], 1u);
+						}
+					}
 				}
 			}
 		}

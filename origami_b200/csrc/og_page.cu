@@ -5,8 +5,9 @@
 // dewarped pixel; no tensor cores.
 //
 // Layout: one CTA = 64 x 4 threads covers a 256 x 32 pixel tile of the dewarped page.  A
-// thread owns 4 consecutive pixels of a row (one 32-bit image store, two float4 map stores:
-// a warp writes 128 B / 1 KiB contiguous per row) and walks 8 consecutive rows, so the
+// warp covers 128 consecutive pixels of a row; a lane owns two pixel pairs placed so that
+// every warp-wide float4 map store writes 512 contiguous bytes (full 32-byte sectors) and
+// every 16-bit image store 64 contiguous bytes.  A thread walks 8 consecutive rows, so the
 // x-axis interpolation state and the horizontally interpolated sparse rows stay in
 // registers; they are refreshed only when the row crosses into the next sparse cell, which
 // is uniform across the CTA.  The y-axis state of the tile's 32 rows is computed once per
@@ -35,11 +36,6 @@ struct PageParams {
 	float scale_x, scale_y;
 };
 
-template <bool LINEAR>
-__device__ __forceinline__ int sample_px(const uint8_t *__restrict__ src, int H, int W, int pitch, float mx, float my) {
-	return LINEAR ? og_sample_linear_fast(src, H, W, pitch, mx, my) : og_sample_nearest_fast(src, H, W, pitch, mx, my);
-}
-
 struct RowAxis {
 	int r0, r1;
 	float b0, b1;
@@ -49,7 +45,6 @@ template <bool LINEAR, bool SCALED, bool WRITE_MAP, bool WRITE_IMG>
 __global__ void __launch_bounds__(TBX *TBY, 3) og_page_kernel(const __grid_constant__ PageParams p) {
 	__shared__ RowAxis s_rows[TILE_H];
 	const int Wd = p.gw * p.cell, Hd = p.gh * p.cell;
-	const int x0 = (blockIdx.x * TBX + threadIdx.x) * TPX;
 	const int ytile = blockIdx.y * TILE_H;
 	const double inv_cell = 1.0 / (double)p.cell;
 	const int tid = threadIdx.y * TBX + threadIdx.x;
@@ -64,9 +59,15 @@ __global__ void __launch_bounds__(TBX *TBY, 3) og_page_kernel(const __grid_const
 		s_rows[tid] = ra;
 	}
 	__syncthreads();
+	// A warp covers 128 consecutive pixels of a row.  Lane l owns the pixel pairs
+	// {2l, 2l+1} and {64+2l, 64+2l+1} of that segment, so that each of its two float4 map
+	// stores lands in a fully written, warp-contiguous 512-byte run (a thread writing its own
+	// 32 bytes as two 16-byte halves costs 45 % of the write bandwidth, measured).
+	const int lane = threadIdx.x & 31;
+	const int xw = (blockIdx.x * TBX + (threadIdx.x & ~31)) * TPX;
+	const int xa = xw + 2 * lane, xb = xa + 64;
 	const int ybeg = ytile + threadIdx.y * TROWS;
-	if (x0 >= Wd || ybeg >= Hd) return;
-	const int npx = min(TPX, Wd - x0);
+	if (xa >= Wd || ybeg >= Hd) return;
 	const int gw = p.gw;
 	const float2 *__restrict__ grid = p.grid;
 
@@ -74,23 +75,25 @@ __global__ void __launch_bounds__(TBX *TBY, 3) og_page_kernel(const __grid_const
 	float a0[TPX], a1[TPX];
 #pragma unroll
 	for (int k = 0; k < TPX; ++k) {
-		og_axis ax = og_resize_axis_x(min(x0 + k, Wd - 1), inv_cell, gw);
+		const int x = ((k & 2) ? xb : xa) + (k & 1);
+		og_axis ax = og_resize_axis_x(min(x, Wd - 1), inv_cell, gw);
 		sx[k] = ax.i;
 		sx1[k] = min(ax.i + 1, gw - 1);
 		a1[k] = ax.f;
 		a0[k] = __fsub_rn(1.f, ax.f);
 	}
-
-	const bool vec_map = WRITE_MAP && npx == TPX && (Wd & 1) == 0 && ((reinterpret_cast<uintptr_t>(p.map_out) & 15) == 0);
-	const bool vec_img = WRITE_IMG && npx == TPX && (p.dst_pitch & 3) == 0 && ((reinterpret_cast<uintptr_t>(p.dst) & 3) == 0);
+	// pixels of each pair that exist (Wd need not be a multiple of the tile)
+	const int na = min(2, Wd - xa), nb = max(0, min(2, Wd - xb));
+	const bool map_al = WRITE_MAP && (Wd & 1) == 0 && ((reinterpret_cast<uintptr_t>(p.map_out) & 15) == 0);
+	const bool img_al = WRITE_IMG && (p.dst_pitch & 1) == 0 && ((reinterpret_cast<uintptr_t>(p.dst) & 1) == 0);
 	const uint8_t *__restrict__ src = p.src;
 	const int H = p.H, W = p.W, spitch = (int)p.src_pitch;
 	const float scx = p.scale_x, scy = p.scale_y;
 
 	int cur_r0 = -1, cur_r1 = -1;
 	float2 h0[TPX], h1[TPX];
-	float *mrow = WRITE_MAP ? p.map_out + ((size_t)ybeg * Wd + x0) * 2 : nullptr;
-	uint8_t *orow = WRITE_IMG ? p.dst + (int64_t)ybeg * p.dst_pitch + x0 : nullptr;
+	float *mrow = WRITE_MAP ? p.map_out + ((size_t)ybeg * Wd + xa) * 2 : nullptr;
+	uint8_t *orow = WRITE_IMG ? p.dst + (int64_t)ybeg * p.dst_pitch + xa : nullptr;
 
 	const int nrows = min(TROWS, Hd - ybeg);
 	for (int yy = 0; yy < nrows; ++yy) {
@@ -117,31 +120,41 @@ __global__ void __launch_bounds__(TBX *TBY, 3) og_page_kernel(const __grid_const
 			d[k].y = og_lerp_cv(h0[k].y, h1[k].y, ra.b0, ra.b1);
 		}
 		if (WRITE_MAP) {
-			if (vec_map) {
-				__stcs(reinterpret_cast<float4 *>(mrow), make_float4(d[0].x, d[0].y, d[1].x, d[1].y));
-				__stcs(reinterpret_cast<float4 *>(mrow) + 1, make_float4(d[2].x, d[2].y, d[3].x, d[3].y));
-			} else {
-#pragma unroll
-				for (int k = 0; k < TPX; ++k)
-					if (k < npx) __stcs(reinterpret_cast<float2 *>(mrow) + k, d[k]);
+			if (map_al && na == 2) __stcs(reinterpret_cast<float4 *>(mrow), make_float4(d[0].x, d[0].y, d[1].x, d[1].y));
+			else {
+				if (na > 0) __stcs(reinterpret_cast<float2 *>(mrow), d[0]);
+				if (na > 1) __stcs(reinterpret_cast<float2 *>(mrow) + 1, d[1]);
+			}
+			if (map_al && nb == 2) __stcs(reinterpret_cast<float4 *>(mrow + 128), make_float4(d[2].x, d[2].y, d[3].x, d[3].y));
+			else {
+				if (nb > 0) __stcs(reinterpret_cast<float2 *>(mrow + 128), d[2]);
+				if (nb > 1) __stcs(reinterpret_cast<float2 *>(mrow + 128) + 1, d[3]);
 			}
 			mrow += (size_t)Wd * 2;
 		}
 		if (WRITE_IMG) {
 			int v[TPX];
+			float mx[TPX], my[TPX];
 #pragma unroll
 			for (int k = 0; k < TPX; ++k) {
-				const float mx = SCALED ? __fmul_rn(d[k].x, scx) : d[k].x;
-				const float my = SCALED ? __fmul_rn(d[k].y, scy) : d[k].y;
-				v[k] = sample_px<LINEAR>(src, H, W, spitch, mx, my);
+				mx[k] = SCALED ? __fmul_rn(d[k].x, scx) : d[k].x;
+				my[k] = SCALED ? __fmul_rn(d[k].y, scy) : d[k].y;
 			}
-			if (vec_img) {
-				const uint32_t pk = (uint32_t)v[0] | ((uint32_t)v[1] << 8) | ((uint32_t)v[2] << 16) | ((uint32_t)v[3] << 24);
-				__stcs(reinterpret_cast<uint32_t *>(orow), pk);
+			if (LINEAR) {
+				og_sample_linear_batch<TPX>(src, H, W, spitch, mx, my, v);
 			} else {
 #pragma unroll
-				for (int k = 0; k < TPX; ++k)
-					if (k < npx) orow[k] = (uint8_t)v[k];
+				for (int k = 0; k < TPX; ++k) v[k] = og_sample_nearest_fast(src, H, W, spitch, mx[k], my[k]);
+			}
+			if (img_al && na == 2) __stcs(reinterpret_cast<unsigned short *>(orow), (unsigned short)(v[0] | (v[1] << 8)));
+			else {
+				if (na > 0) orow[0] = (uint8_t)v[0];
+				if (na > 1) orow[1] = (uint8_t)v[1];
+			}
+			if (img_al && nb == 2) __stcs(reinterpret_cast<unsigned short *>(orow + 64), (unsigned short)(v[2] | (v[3] << 8)));
+			else {
+				if (nb > 0) orow[64] = (uint8_t)v[2];
+				if (nb > 1) orow[65] = (uint8_t)v[3];
 			}
 			orow += p.dst_pitch;
 		}
