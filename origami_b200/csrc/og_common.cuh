@@ -194,6 +194,55 @@ __device__ __forceinline__ void og_sample_linear_batch(
 	}
 }
 
+// Split form of the sampler for software pipelining: load the taps now, blend them later.
+struct og_taps {
+	int p00, p01, p10, p11;
+	int fx, fy;
+};
+
+template <int N>
+__device__ __forceinline__ void og_load_taps_batch(
+	const uint8_t *__restrict__ src, int H, int W, int pitch,
+	const float (&mx)[N], const float (&my)[N], og_taps (&t)[N]) {
+	int ix[N], iy[N];
+	bool all_in = true;
+#pragma unroll
+	for (int k = 0; k < N; ++k) {
+		const int sx = __float2int_rn(__fmul_rn(mx[k], 32.f));
+		const int sy = __float2int_rn(__fmul_rn(my[k], 32.f));
+		ix[k] = sx >> 5;
+		iy[k] = sy >> 5;
+		t[k].fx = sx & 31;
+		t[k].fy = sy & 31;
+		all_in = all_in && (unsigned)ix[k] < (unsigned)(W - 1) && (unsigned)iy[k] < (unsigned)(H - 1);
+	}
+	if (all_in) {
+#pragma unroll
+		for (int k = 0; k < N; ++k) {
+			const uint8_t *s = src + (iy[k] * pitch + ix[k]);
+			t[k].p00 = __ldg(s);
+			t[k].p01 = __ldg(s + 1);
+			t[k].p10 = __ldg(s + pitch);
+			t[k].p11 = __ldg(s + pitch + 1);
+		}
+	} else {
+#pragma unroll
+		for (int k = 0; k < N; ++k) {
+			const int x = og_sat_short(ix[k]), y = og_sat_short(iy[k]);
+			t[k].p00 = og_tap(src, H, W, pitch, y, x, 0);
+			t[k].p01 = og_tap(src, H, W, pitch, y, x + 1, 0);
+			t[k].p10 = og_tap(src, H, W, pitch, y + 1, x, 0);
+			t[k].p11 = og_tap(src, H, W, pitch, y + 1, x + 1, 0);
+		}
+	}
+}
+
+__device__ __forceinline__ int og_blend_taps(const og_taps &t) {
+	const int wx0 = 32 - t.fx, wy0 = 32 - t.fy;
+	const int acc = wy0 * (wx0 * t.p00 + t.fx * t.p01) + t.fy * (wx0 * t.p10 + t.fx * t.p11);
+	return (acc + 512) >> 10;
+}
+
 __device__ __forceinline__ int og_sample_nearest_fast(
 	const uint8_t *__restrict__ src, int H, int W, int pitch, float mx, float my) {
 	const int ix = og_sat_short(__float2int_rn(mx));

@@ -313,16 +313,16 @@ __global__ void __launch_bounds__(LTHREADS, 2) og_lines_kernel(const __grid_cons
 			for (int q = tid; q <= MAX_CLASSES; q += WORKERS) s_hist[q] = 0;
 		if (BBOX && tid < 4) s_bbox[tid] = (tid < 2) ? INT_MAX : INT_MIN;
 		if (staged) {
-			// horizontal pass over the sparse rows of the band (HResizeLinear)
-			for (int j = tid; j < NC; j += WORKERS) {
+			// horizontal pass over the sparse rows of the band (HResizeLinear), one (row, column)
+			// entry per thread
+			for (int e = tid; e < NSR * NC; e += WORKERS) {
+				const int r = e / NC, j = e - r * NC;
 				og_axis ax = og_resize_axis_x(C0 + j, inv_cell, p.gw);
 				const int c1 = min(ax.i + 1, p.gw - 1);
 				const float w0 = __fsub_rn(1.f, ax.f), w1 = ax.f;
-				for (int r = 0; r < NSR; ++r) {
-					const float2 *g = p.grid + (c.SR0 + r) * p.gw;
-					float2 s0 = __ldg(g + ax.i), s1 = __ldg(g + c1);
-					hs[r * NC + j] = make_float2(og_lerp_cv(s0.x, s1.x, w0, w1), og_lerp_cv(s0.y, s1.y, w0, w1));
-				}
+				const float2 *g = p.grid + (c.SR0 + r) * p.gw;
+				const float2 s0 = __ldg(g + ax.i), s1 = __ldg(g + c1);
+				hs[e] = make_float2(og_lerp_cv(s0.x, s1.x, w0, w1), og_lerp_cv(s0.y, s1.y, w0, w1));
 			}
 			for (int i = tid; i < NR; i += WORKERS) {
 				og_axis ay = og_resize_axis(R0 + i, inv_cell);
@@ -361,27 +361,32 @@ __global__ void __launch_bounds__(LTHREADS, 2) og_lines_kernel(const __grid_cons
 		}
 		bar_sync(1, WORKERS);
 
-		// ---- sample phase: thread = (column, row group)
+		// ---- sample phase: thread = (column, row group).  Software pipeline: the taps of
+		// batch t are loaded before the blend of batch t-1, so their latency hides behind
+		// the float64 work of the next batch.
 		const int col = tid & (CW - 1), rq = tid / CW;
 		const int xsteps = c.xsteps, ysteps = c.ysteps;
 		float bx0 = 3.0e38f, by0 = 3.0e38f, bx1 = -3.0e38f, by1 = -3.0e38f;
 		if (col < c.ncols) {
 			const int cc = c.c0 + col;
 			const og_d2 xc = og_linspace_at(c.lx, cc);
-			const int NRm = NR - 1, NCm = NC - 1, Hm = Hd - 2, Wm = Wd - 2;
+			const int NRm = NR - 2, NCm = NC - 2, Hm = Hd - 2, Wm = Wd - 2;
 			const bool tabled = c.rows_tabled != 0;
 			uint8_t *strip = (MODE == MODE_STRIP) ? p.strips_out + c.pix0 + cc : nullptr;
 			float2 *gout = (MODE == MODE_GRID) ? reinterpret_cast<float2 *>(p.grids_out) + c.pix0 + cc : nullptr;
 			const uint8_t *__restrict__ src = p.src;
 			const int H = p.H, W = p.W, spitch = p.src_pitch;
+			og_taps pend[RB];
+			int pend_row[RB];
+			bool have_pend = false;
 			for (int rbase = rq; rbase < ysteps; rbase += RB * RSPLIT) {
 				float gx[RB], gy[RB];
-				bool live[RB];
+				int row[RB];
 #pragma unroll
 				for (int u = 0; u < RB; ++u) {
 					const int r = rbase + u * RSPLIT;
-					live[u] = r < ysteps;
-					const int rr = live[u] ? r : rbase;
+					row[u] = r < ysteps ? r : -1;
+					const int rr = r < ysteps ? r : rbase;
 					double2 rb;
 					if (tabled) {
 						rb = c.rowbase[rr];
@@ -393,52 +398,60 @@ __global__ void __launch_bounds__(LTHREADS, 2) og_lines_kernel(const __grid_cons
 					const double px = __dadd_rn(rb.x, xc.x);
 					const double py = __dadd_rn(rb.y, xc.y);
 					og_d2 w;
-					bool done = false;
 					if (staged) {
 						// i = clip(floor(y), 0, n - 2) (SciPy find_indices); |y| < 1e9 here
 						const int i0 = min(max(__double2int_rd(py), 0), Hm);
 						const int i1 = min(max(__double2int_rd(px), 0), Wm);
 						const int ri = i0 - R0, ci = i1 - C0;
-						if ((unsigned)ri < (unsigned)NRm && (unsigned)ci < (unsigned)NCm) {
-							const double a = __dsub_rn(py, (double)i0), b = __dsub_rn(px, (double)i1);
-							const double wa = __dsub_rn(1.0, a), wb = __dsub_rn(1.0, b);
-							const double w00 = __dmul_rn(wa, wb), w01 = __dmul_rn(wa, b);
-							const double w10 = __dmul_rn(a, wb), w11 = __dmul_rn(a, b);
-							const double2 *nd = nodes + (ri * NC + ci);
-							const double2 v00 = nd[0], v01 = nd[1], v10 = nd[NC], v11 = nd[NC + 1];
-							w.x = __dadd_rn(__dadd_rn(__dadd_rn(__dmul_rn(v00.x, w00), __dmul_rn(v01.x, w01)),
-								__dmul_rn(v10.x, w10)), __dmul_rn(v11.x, w11));
-							w.y = __dadd_rn(__dadd_rn(__dadd_rn(__dmul_rn(v00.y, w00), __dmul_rn(v01.y, w01)),
-								__dmul_rn(v10.y, w10)), __dmul_rn(v11.y, w11));
-							done = true;
-						}
+						// the staged region covers the chunk by construction; the clamp keeps the
+						// shared-memory reads in bounds and `ok` sends a (never observed) outlier
+						// through the unstaged path below
+						const bool ok = (unsigned)ri <= (unsigned)NRm && (unsigned)ci <= (unsigned)NCm;
+						const int rs = min(max(ri, 0), NRm), cs = min(max(ci, 0), NCm);
+						const double a = __dsub_rn(py, (double)i0), b = __dsub_rn(px, (double)i1);
+						const double wa = __dsub_rn(1.0, a), wb = __dsub_rn(1.0, b);
+						const double w00 = __dmul_rn(wa, wb), w01 = __dmul_rn(wa, b);
+						const double w10 = __dmul_rn(a, wb), w11 = __dmul_rn(a, b);
+						const double2 *nd = nodes + (rs * NC + cs);
+						const double2 v00 = nd[0], v01 = nd[1], v10 = nd[NC], v11 = nd[NC + 1];
+						w.x = __dadd_rn(__dadd_rn(__dadd_rn(__dmul_rn(v00.x, w00), __dmul_rn(v01.x, w01)),
+							__dmul_rn(v10.x, w10)), __dmul_rn(v11.x, w11));
+						w.y = __dadd_rn(__dadd_rn(__dadd_rn(__dmul_rn(v00.y, w00), __dmul_rn(v01.y, w01)),
+							__dmul_rn(v10.y, w10)), __dmul_rn(v11.y, w11));
+						if (!ok) w = og_inverse_point(p.grid, p.gh, p.gw, p.cell, inv_cell, py, px);
+					} else {
+						w = og_inverse_point(p.grid, p.gh, p.gw, p.cell, inv_cell, py, px);
 					}
-					if (!done) w = og_inverse_point(p.grid, p.gh, p.gw, p.cell, inv_cell, py, px);
 					gx[u] = __double2float_rn(w.x);
 					gy[u] = __double2float_rn(w.y);
 				}
 				if (MODE == MODE_GRID) {
 #pragma unroll
 					for (int u = 0; u < RB; ++u)
-						if (live[u]) gout[(rbase + u * RSPLIT) * xsteps] = make_float2(gx[u], gy[u]);
+						if (row[u] >= 0) gout[row[u] * xsteps] = make_float2(gx[u], gy[u]);
 				} else if (MODE == MODE_STRIP) {
-					int v[RB];
-					og_sample_linear_batch<RB>(src, H, W, spitch, gx, gy, v);
+					og_taps cur[RB];
+					og_load_taps_batch<RB>(src, H, W, spitch, gx, gy, cur);
+					if (have_pend) {
+#pragma unroll
+						for (int u = 0; u < RB; ++u)
+							if (pend_row[u] >= 0)  // pixels[::-1, :]  (block.py:257)
+								strip[(ysteps - 1 - pend_row[u]) * xsteps] = (uint8_t)og_blend_taps(pend[u]);
+					}
 #pragma unroll
 					for (int u = 0; u < RB; ++u) {
-						if (live[u]) {
-							// pixels[::-1, :]  (block.py:257)
-							strip[(ysteps - 1 - (rbase + u * RSPLIT)) * xsteps] = (uint8_t)v[u];
-							if (BBOX) {
-								bx0 = fminf(bx0, gx[u]); bx1 = fmaxf(bx1, gx[u]);
-								by0 = fminf(by0, gy[u]); by1 = fmaxf(by1, gy[u]);
-							}
+						pend[u] = cur[u];
+						pend_row[u] = row[u];
+						if (BBOX && row[u] >= 0) {
+							bx0 = fminf(bx0, gx[u]); bx1 = fmaxf(bx1, gx[u]);
+							by0 = fminf(by0, gy[u]); by1 = fmaxf(by1, gy[u]);
 						}
 					}
+					have_pend = true;
 				} else {
 #pragma unroll
 					for (int u = 0; u < RB; ++u) {
-						if (live[u]) {
+						if (row[u] >= 0) {
 							// scale_grid (batch/detect/lines.py:18-22) then cv2.remap INTER_NEAREST
 							const float sx = __fmul_rn(gx[u], p.scale_x), sy = __fmul_rn(gy[u], p.scale_y);
 							const int lab = og_sample_nearest_fast(src, H, W, spitch, sx, sy);
@@ -446,6 +459,12 @@ __global__ void __launch_bounds__(LTHREADS, 2) og_lines_kernel(const __grid_cons
 						}
 					}
 				}
+			}
+			if (MODE == MODE_STRIP && have_pend) {
+#pragma unroll
+				for (int u = 0; u < RB; ++u)
+					if (pend_row[u] >= 0)
+						strip[(ysteps - 1 - pend_row[u]) * xsteps] = (uint8_t)og_blend_taps(pend[u]);
 			}
 		}
 		if (BBOX) {
