@@ -276,7 +276,7 @@ def run_step(ps, args, events=None):
 		ps.steps.data_ptr(), ps.pix.data_ptr(), ps.chunks.data_ptr(), st)
 	mark("og_line_steps_kernel")
 	_lib.call("og_extract_lines", ps.src.data_ptr(), ps.H, ps.W, ps.src.stride(0), ps.grid.data_ptr(), ps.gh, ps.gw, CELL,
-		ps.lines.data_ptr(), ps.n, ps.steps.data_ptr(), ps.pix.data_ptr(), ps.chunks.data_ptr(),
+		ps.map.data_ptr(), ps.lines.data_ptr(), ps.n, ps.steps.data_ptr(), ps.pix.data_ptr(), ps.chunks.data_ptr(),
 		ps.gray.data_ptr(), ps.gray.numel(), ps.bbox.data_ptr(), st)
 	mark("og_lines_kernel")
 	launches = 5

@@ -99,10 +99,16 @@ int og_line_steps(const float *grid, int gh, int gw, int cell,
 	const og_line *lines, int n,
 	int32_t *steps_out, int64_t *pix_offsets_out, int32_t *chunk_offsets_out, void *stream);
 
+/* The three line entry points below take `map`: the dense map (gh*cell, gw*cell, 2) fp32 that
+ * og_expand_map / og_remap_page wrote for the SAME grid, or NULL.  With a map the four nodes
+ * of every sample are gathered from it (fast path: the reference, too, interpolates in its
+ * cached Grid.points("full")); with NULL they are recomputed from the sparse grid on chip.
+ * Both paths produce identical bits. */
+
 /* A8  Line.warped_grid -- origami/core/block.py:223-248.  Writes the fp32 (ysteps, xsteps, 2)
  * warped sampling grid of every line, packed at 2*pix_offsets[i] floats.  capacity is in
  * grid points (pixels); lines that would not fit are skipped (check pix_offsets[n]). */
-int og_warped_grids(const float *grid, int gh, int gw, int cell,
+int og_warped_grids(const float *grid, int gh, int gw, int cell, const float *map,
 	const og_line *lines, int n,
 	const int32_t *steps, const int64_t *pix_offsets, const int32_t *chunk_offsets,
 	float *grids_out, int64_t capacity, void *stream);
@@ -115,7 +121,7 @@ int og_warped_grids(const float *grid, int gh, int gw, int cell,
  * (floor min x, floor min y, ceil max x, ceil max y) of its fp32 warped grid as int32
  * (origami/core/mask.py:10-12 convention).  capacity in bytes of strips_out. */
 int og_extract_lines(const uint8_t *src, int H, int W, int64_t src_pitch,
-	const float *grid, int gh, int gw, int cell,
+	const float *grid, int gh, int gw, int cell, const float *map,
 	const og_line *lines, int n,
 	const int32_t *steps, const int64_t *pix_offsets, const int32_t *chunk_offsets,
 	uint8_t *strips_out, int64_t capacity, int32_t *bbox_out, void *stream);
@@ -147,7 +153,7 @@ int og_otsu(const uint8_t *src, int h, int w, int64_t src_pitch,
  * overflow_out[i] (n int64, may be NULL; np.bincount would have grown the array). */
 int og_sample_labels(const uint8_t *labels, int lh, int lw, int64_t labels_pitch,
 	int H, int W,
-	const float *grid, int gh, int gw, int cell,
+	const float *grid, int gh, int gw, int cell, const float *map,
 	const og_line *lines, int n,
 	const int32_t *steps, const int32_t *chunk_offsets,
 	int n_classes, int64_t *counts_out, int64_t *overflow_out, void *stream);

@@ -42,14 +42,14 @@ _SIGNATURES = {
 		c_void_p, c_int64, c_void_p, c_float, c_float, c_int, c_void_p],
 	"og_inverse_yx": [c_void_p, c_int, c_int, c_int, c_void_p, c_int64, c_void_p, c_void_p],
 	"og_line_steps": [c_void_p, c_int, c_int, c_int, c_void_p, c_int, c_void_p, c_void_p, c_void_p, c_void_p],
-	"og_warped_grids": [c_void_p, c_int, c_int, c_int, c_void_p, c_int, c_void_p, c_void_p, c_void_p,
+	"og_warped_grids": [c_void_p, c_int, c_int, c_int, c_void_p, c_void_p, c_int, c_void_p, c_void_p, c_void_p,
 		c_void_p, c_int64, c_void_p],
-	"og_extract_lines": [c_void_p, c_int, c_int, c_int64, c_void_p, c_int, c_int, c_int, c_void_p, c_int,
+	"og_extract_lines": [c_void_p, c_int, c_int, c_int64, c_void_p, c_int, c_int, c_int, c_void_p, c_void_p, c_int,
 		c_void_p, c_void_p, c_void_p, c_void_p, c_int64, c_void_p, c_void_p],
 	"og_binarize_strips": [c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_void_p, c_void_p, c_void_p],
 	"og_sauvola": [c_void_p, c_int, c_int, c_int64, c_int, c_double, c_double, c_void_p, c_int64, c_void_p],
 	"og_otsu": [c_void_p, c_int, c_int, c_int64, c_void_p, c_int64, c_void_p, c_void_p, c_void_p],
-	"og_sample_labels": [c_void_p, c_int, c_int, c_int64, c_int, c_int, c_void_p, c_int, c_int, c_int,
+	"og_sample_labels": [c_void_p, c_int, c_int, c_int64, c_int, c_int, c_void_p, c_int, c_int, c_int, c_void_p,
 		c_void_p, c_int, c_void_p, c_void_p, c_int, c_void_p, c_void_p, c_void_p],
 	"og_argmax_labels": [c_void_p, c_int, c_int, c_int, c_int, c_void_p, c_void_p, c_void_p, c_int, c_void_p],
 	"og_class_masks": [c_void_p, c_int, c_int, c_int64, c_void_p, c_void_p, c_int, c_void_p],

@@ -498,6 +498,176 @@ __global__ void __launch_bounds__(LTHREADS, 2) og_lines_kernel(const __grid_cons
 	}
 }
 
+// ---------------------------------------------------------------------------------------
+// Map-gather engine: when the caller holds the materialised dense map (the page kernel
+// emits it, as the reference's lru_cached Grid.points("full") does), the four nodes of a
+// sample are read straight from it.  No staging, no shared-memory nodes, no CTA barriers:
+// a warp owns a (line, 32-column) item, a lane walks one strip column; node loads and tap
+// loads of two consecutive rows are in flight together and the byte blend of the previous
+// pair is deferred behind them.
+// ---------------------------------------------------------------------------------------
+constexpr int MW = 32;            // strip columns per warp item
+constexpr int MWARPS = 8;         // warps per CTA
+constexpr int MTHREADS = MWARPS * 32;
+
+template <int MODE, bool BBOX>
+__global__ void __launch_bounds__(MTHREADS, 3) og_lines_map_kernel(const __grid_constant__ LineParams p, const float2 *__restrict__ map) {
+	__shared__ double2 s_rowbase[MWARPS][MAX_ROWS];
+	__shared__ unsigned int s_whist[MODE == MODE_LABELS ? MWARPS : 1][MODE == MODE_LABELS ? MAX_CLASSES + 1 : 1];
+
+	const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+	const int total_items = 2 * __ldg(p.chunk_offsets + p.n);  // two 32-column halves per 64-column chunk
+	const int nwarps = gridDim.x * MWARPS;
+	const int Hd = p.gh * p.cell, Wd = p.gw * p.cell;
+	const int Hm = Hd - 2, Wm = Wd - 2;
+	const uint8_t *__restrict__ src = p.src;
+	const int H = p.H, W = p.W, spitch = p.src_pitch;
+	double2 *rowbase = s_rowbase[wid];
+
+	for (int item = blockIdx.x * MWARPS + wid; item < total_items; item += nwarps) {
+		const int chunk_item = item >> 1;
+		const int li = find_line(p.chunk_offsets, p.n, chunk_item);
+		const int xsteps = __ldg(p.steps + 2 * li), ysteps = __ldg(p.steps + 2 * li + 1);
+		const int c0 = (chunk_item - __ldg(p.chunk_offsets + li)) * CW + (item & 1) * MW;
+		if (c0 >= xsteps) continue;
+		const long long pix0 = (MODE != MODE_LABELS) ? __ldg(p.pix_offsets + li) : 0;
+		if (MODE != MODE_LABELS && pix0 + (long long)xsteps * ysteps > p.capacity) continue;
+		const og_line *ln = p.lines + li;
+		const double cpx = ln->cp[0], cpy = ln->cp[1];
+		const og_lin lx = og_linspace_setup(ln->cright[0], ln->cright[1], xsteps);
+		const og_lin ly = og_linspace_setup(ln->up[0], ln->up[1], ysteps);
+		const bool tabled = ysteps <= MAX_ROWS;
+		__syncwarp();
+		if (tabled) {
+			for (int r = lane; r < ysteps; r += 32) {
+				og_d2 yr = og_linspace_at(ly, r);
+				rowbase[r] = make_double2(__dadd_rn(yr.x, cpx), __dadd_rn(yr.y, cpy));
+			}
+		}
+		if (MODE == MODE_LABELS)
+			for (int q = lane; q <= MAX_CLASSES; q += 32) s_whist[wid][q] = 0;
+		__syncwarp();
+
+		float bx0 = 3.0e38f, by0 = 3.0e38f, bx1 = -3.0e38f, by1 = -3.0e38f;
+		const int cc = c0 + lane;
+		if (cc < xsteps) {
+			const og_d2 xc = og_linspace_at(lx, cc);
+			uint8_t *strip = (MODE == MODE_STRIP) ? p.strips_out + pix0 + cc : nullptr;
+			float2 *gout = (MODE == MODE_GRID) ? reinterpret_cast<float2 *>(p.grids_out) + pix0 + cc : nullptr;
+			og_taps pend[RB];
+			int pend_row[RB];
+			bool have_pend = false;
+			for (int rbase = 0; rbase < ysteps; rbase += RB) {
+				int row[RB], i0[RB], i1[RB];
+				double a[RB], b[RB];
+				float2 v00[RB], v01[RB], v10[RB], v11[RB];
+#pragma unroll
+				for (int u = 0; u < RB; ++u) {
+					const int r = rbase + u;
+					row[u] = r < ysteps ? r : -1;
+					const int rr = r < ysteps ? r : rbase;
+					double2 rb;
+					if (tabled) {
+						rb = rowbase[rr];
+					} else {
+						og_d2 yr = og_linspace_at(ly, rr);
+						rb = make_double2(__dadd_rn(yr.x, cpx), __dadd_rn(yr.y, cpy));
+					}
+					// dewarped_grid = (ys + p0)[:, None] + xs[None, :]   (block.py:241)
+					const double px = __dadd_rn(rb.x, xc.x);
+					const double py = __dadd_rn(rb.y, xc.y);
+					// i = clip(floor(y), 0, n - 2) (SciPy find_indices); the saturating
+					// conversion keeps even absurd coordinates inside the map
+					i0[u] = min(max(__double2int_rd(py), 0), Hm);
+					i1[u] = min(max(__double2int_rd(px), 0), Wm);
+					a[u] = __dsub_rn(py, (double)i0[u]);
+					b[u] = __dsub_rn(px, (double)i1[u]);
+					const float2 *nd = map + ((size_t)i0[u] * Wd + i1[u]);
+					v00[u] = __ldg(nd);
+					v01[u] = __ldg(nd + 1);
+					v10[u] = __ldg(nd + Wd);
+					v11[u] = __ldg(nd + Wd + 1);
+				}
+				float gx[RB], gy[RB];
+#pragma unroll
+				for (int u = 0; u < RB; ++u) {
+					const double wa = __dsub_rn(1.0, a[u]), wb = __dsub_rn(1.0, b[u]);
+					const double w00 = __dmul_rn(wa, wb), w01 = __dmul_rn(wa, b[u]);
+					const double w10 = __dmul_rn(a[u], wb), w11 = __dmul_rn(a[u], b[u]);
+					const double wx = __dadd_rn(__dadd_rn(__dadd_rn(__dmul_rn((double)v00[u].x, w00), __dmul_rn((double)v01[u].x, w01)),
+						__dmul_rn((double)v10[u].x, w10)), __dmul_rn((double)v11[u].x, w11));
+					const double wy = __dadd_rn(__dadd_rn(__dadd_rn(__dmul_rn((double)v00[u].y, w00), __dmul_rn((double)v01[u].y, w01)),
+						__dmul_rn((double)v10[u].y, w10)), __dmul_rn((double)v11[u].y, w11));
+					gx[u] = __double2float_rn(wx);
+					gy[u] = __double2float_rn(wy);
+				}
+				if (MODE == MODE_GRID) {
+#pragma unroll
+					for (int u = 0; u < RB; ++u)
+						if (row[u] >= 0) gout[row[u] * xsteps] = make_float2(gx[u], gy[u]);
+				} else if (MODE == MODE_STRIP) {
+					og_taps cur[RB];
+					og_load_taps_batch<RB>(src, H, W, spitch, gx, gy, cur);
+					if (have_pend) {
+#pragma unroll
+						for (int u = 0; u < RB; ++u)
+							if (pend_row[u] >= 0)  // pixels[::-1, :]  (block.py:257)
+								strip[(ysteps - 1 - pend_row[u]) * xsteps] = (uint8_t)og_blend_taps(pend[u]);
+					}
+#pragma unroll
+					for (int u = 0; u < RB; ++u) {
+						pend[u] = cur[u];
+						pend_row[u] = row[u];
+						if (BBOX && row[u] >= 0) {
+							bx0 = fminf(bx0, gx[u]); bx1 = fmaxf(bx1, gx[u]);
+							by0 = fminf(by0, gy[u]); by1 = fmaxf(by1, gy[u]);
+						}
+					}
+					have_pend = true;
+				} else {
+#pragma unroll
+					for (int u = 0; u < RB; ++u) {
+						if (row[u] >= 0) {
+							// scale_grid (batch/detect/lines.py:18-22) then cv2.remap INTER_NEAREST
+							const float sx = __fmul_rn(gx[u], p.scale_x), sy = __fmul_rn(gy[u], p.scale_y);
+							const int lab = og_sample_nearest_fast(src, H, W, spitch, sx, sy);
+							atomicAdd(&s_whist[wid][min(lab, p.n_classes)], 1u);
+						}
+					}
+				}
+			}
+			if (MODE == MODE_STRIP && have_pend) {
+#pragma unroll
+				for (int u = 0; u < RB; ++u)
+					if (pend_row[u] >= 0)
+						strip[(ysteps - 1 - pend_row[u]) * xsteps] = (uint8_t)og_blend_taps(pend[u]);
+			}
+		}
+		if (BBOX) {
+#pragma unroll
+			for (int o = 16; o > 0; o >>= 1) {
+				bx0 = fminf(bx0, __shfl_xor_sync(0xffffffffu, bx0, o));
+				by0 = fminf(by0, __shfl_xor_sync(0xffffffffu, by0, o));
+				bx1 = fmaxf(bx1, __shfl_xor_sync(0xffffffffu, bx1, o));
+				by1 = fmaxf(by1, __shfl_xor_sync(0xffffffffu, by1, o));
+			}
+			if (lane == 0 && bx0 <= bx1) {
+				atomicMin(p.bbox_out + 4 * li + 0, (int)floorf(bx0));
+				atomicMin(p.bbox_out + 4 * li + 1, (int)floorf(by0));
+				atomicMax(p.bbox_out + 4 * li + 2, (int)ceilf(bx1));
+				atomicMax(p.bbox_out + 4 * li + 3, (int)ceilf(by1));
+			}
+		}
+		if (MODE == MODE_LABELS) {
+			__syncwarp();
+			for (int q = lane; q < p.n_classes; q += 32)
+				if (s_whist[wid][q]) atomicAdd(p.counts_out + (size_t)li * p.n_classes + q, (unsigned long long)s_whist[wid][q]);
+			if (lane == 0 && s_whist[wid][p.n_classes] && p.overflow_out != nullptr)
+				atomicAdd(p.overflow_out + li, (unsigned long long)s_whist[wid][p.n_classes]);
+		}
+	}
+}
+
 __global__ void og_bbox_init_kernel(int32_t *bbox, int n) {
 	int i = blockIdx.x * blockDim.x + threadIdx.x;
 	if (i < n) {
@@ -527,6 +697,11 @@ int check_grid(const float *grid, int gh, int gw, int cell) {
 	return OG_OK;
 }
 
+int check_map(const float *map) {
+	OG_REQUIRE((reinterpret_cast<uintptr_t>(map) & 7) == 0, OG_E_ALIGN, "map must be 8-byte aligned");
+	return OG_OK;
+}
+
 int check_lines(const og_line *lines, int n, const int32_t *steps, const int32_t *chunk_offsets) {
 	OG_REQUIRE(n >= 0, OG_E_ARG, "n < 0");
 	OG_REQUIRE(n == 0 || lines != nullptr, OG_E_ARG, "lines is NULL");
@@ -542,6 +717,13 @@ int launch_lines(const LineParams &p, cudaStream_t st) {
 	// persistent grid: two CTAs per SM fit the staging budget
 	og_lines_kernel<MODE, BBOX><<<OG_NUM_SMS * 2, LTHREADS, SMEM_BUDGET, st>>>(p);
 	return og_check_launch("og_lines_kernel");
+}
+
+template <int MODE, bool BBOX>
+int launch_lines_any(const LineParams &p, const float *map, cudaStream_t st) {
+	if (map == nullptr) return launch_lines<MODE, BBOX>(p, st);
+	og_lines_map_kernel<MODE, BBOX><<<OG_NUM_SMS * 3, MTHREADS, 0, st>>>(p, reinterpret_cast<const float2 *>(map));
+	return og_check_launch("og_lines_map_kernel");
 }
 
 }  // namespace
@@ -580,13 +762,15 @@ extern "C" int og_line_steps(const float *grid, int gh, int gw, int cell,
 	return og_check_launch("og_line_scan_kernel");
 }
 
-extern "C" int og_warped_grids(const float *grid, int gh, int gw, int cell,
+extern "C" int og_warped_grids(const float *grid, int gh, int gw, int cell, const float *map,
 	const og_line *lines, int n,
 	const int32_t *steps, const int64_t *pix_offsets, const int32_t *chunk_offsets,
 	float *grids_out, int64_t capacity, void *stream) {
 	int rc = check_grid(grid, gh, gw, cell);
 	if (rc) return rc;
 	rc = check_lines(lines, n, steps, chunk_offsets);
+	if (rc) return rc;
+	rc = check_map(map);
 	if (rc) return rc;
 	if (n == 0) return OG_OK;
 	OG_REQUIRE(pix_offsets != nullptr && grids_out != nullptr, OG_E_ARG, "pix_offsets / grids_out is NULL");
@@ -598,17 +782,19 @@ extern "C" int og_warped_grids(const float *grid, int gh, int gw, int cell,
 	p.steps = steps; p.pix_offsets = pix_offsets; p.chunk_offsets = chunk_offsets;
 	p.grids_out = grids_out;
 	p.capacity = capacity;
-	return launch_lines<MODE_GRID, false>(p, (cudaStream_t)stream);
+	return launch_lines_any<MODE_GRID, false>(p, map, (cudaStream_t)stream);
 }
 
 extern "C" int og_extract_lines(const uint8_t *src, int H, int W, int64_t src_pitch,
-	const float *grid, int gh, int gw, int cell,
+	const float *grid, int gh, int gw, int cell, const float *map,
 	const og_line *lines, int n,
 	const int32_t *steps, const int64_t *pix_offsets, const int32_t *chunk_offsets,
 	uint8_t *strips_out, int64_t capacity, int32_t *bbox_out, void *stream) {
 	int rc = check_grid(grid, gh, gw, cell);
 	if (rc) return rc;
 	rc = check_lines(lines, n, steps, chunk_offsets);
+	if (rc) return rc;
+	rc = check_map(map);
 	if (rc) return rc;
 	if (n == 0) return OG_OK;
 	OG_REQUIRE(src != nullptr && H > 0 && W > 0 && src_pitch >= W, OG_E_ARG, "src invalid");
@@ -629,20 +815,22 @@ extern "C" int og_extract_lines(const uint8_t *src, int H, int W, int64_t src_pi
 		og_bbox_init_kernel<<<(n + 255) / 256, 256, 0, st>>>(bbox_out, n);
 		rc = og_check_launch("og_bbox_init_kernel");
 		if (rc) return rc;
-		return launch_lines<MODE_STRIP, true>(p, st);
+		return launch_lines_any<MODE_STRIP, true>(p, map, st);
 	}
-	return launch_lines<MODE_STRIP, false>(p, st);
+	return launch_lines_any<MODE_STRIP, false>(p, map, st);
 }
 
 extern "C" int og_sample_labels(const uint8_t *labels, int lh, int lw, int64_t labels_pitch,
 	int H, int W,
-	const float *grid, int gh, int gw, int cell,
+	const float *grid, int gh, int gw, int cell, const float *map,
 	const og_line *lines, int n,
 	const int32_t *steps, const int32_t *chunk_offsets,
 	int n_classes, int64_t *counts_out, int64_t *overflow_out, void *stream) {
 	int rc = check_grid(grid, gh, gw, cell);
 	if (rc) return rc;
 	rc = check_lines(lines, n, steps, chunk_offsets);
+	if (rc) return rc;
+	rc = check_map(map);
 	if (rc) return rc;
 	OG_REQUIRE(n_classes >= 1 && n_classes <= MAX_CLASSES, OG_E_ARG, "n_classes %d outside [1, %d]", n_classes, MAX_CLASSES);
 	if (n == 0) return OG_OK;
@@ -668,5 +856,5 @@ extern "C" int og_sample_labels(const uint8_t *labels, int lh, int lw, int64_t l
 	p.n_classes = n_classes;
 	p.counts_out = reinterpret_cast<unsigned long long *>(counts_out);
 	p.overflow_out = reinterpret_cast<unsigned long long *>(overflow_out);
-	return launch_lines<MODE_LABELS, false>(p, st);
+	return launch_lines_any<MODE_LABELS, false>(p, map, st);
 }

@@ -161,21 +161,30 @@ def line_steps(grid, cell, lines_dev, n):
 	return LinePlan(lines_dev, n, steps, pix, chunks)
 
 
-def warped_grids(grid, cell, plan, out):
+def _check_map(dense_map, gh, gw, cell):
+	if dense_map is None:
+		return 0
+	if (dense_map.dtype != torch.float32 or not dense_map.is_cuda or not dense_map.is_contiguous()
+			or tuple(dense_map.shape) != (gh * cell, gw * cell, 2)):
+		raise ValueError("dense_map must be the contiguous float32 CUDA tensor (gh*cell, gw*cell, 2) of this grid")
+	return dense_map.data_ptr()
+
+
+def warped_grids(grid, cell, plan, out, dense_map=None):
 	"""Line.warped_grid for every line; out: float32 buffer of 2*capacity elements."""
 	gh, gw = _check_grid(grid)
-	_lib.call("og_warped_grids", grid.data_ptr(), gh, gw, cell, plan.lines.data_ptr(), plan.n,
+	_lib.call("og_warped_grids", grid.data_ptr(), gh, gw, cell, _check_map(dense_map, gh, gw, cell), plan.lines.data_ptr(), plan.n,
 		plan.steps.data_ptr(), plan.pix_offsets.data_ptr(), plan.chunk_offsets.data_ptr(),
 		out.data_ptr(), out.numel() // 2, _stream())
 	return out
 
 
-def extract_lines(src, grid, cell, plan, out, bbox=None):
+def extract_lines(src, grid, cell, plan, out, bbox=None, dense_map=None):
 	"""Line.dewarped_image for every line into the packed uint8 buffer `out`."""
 	gh, gw = _check_grid(grid)
 	_check_u8_image(src, "src")
 	_lib.call("og_extract_lines", src.data_ptr(), int(src.shape[0]), int(src.shape[1]), src.stride(0),
-		grid.data_ptr(), gh, gw, cell, plan.lines.data_ptr(), plan.n,
+		grid.data_ptr(), gh, gw, cell, _check_map(dense_map, gh, gw, cell), plan.lines.data_ptr(), plan.n,
 		plan.steps.data_ptr(), plan.pix_offsets.data_ptr(), plan.chunk_offsets.data_ptr(),
 		out.data_ptr(), out.numel(), _ptr(bbox), _stream())
 	return out
@@ -217,14 +226,15 @@ def otsu(src, dst=None, hist_scratch=None, threshold=None):
 	return dst, threshold
 
 
-def sample_labels(labels, page_shape, grid, cell, plan, n_classes):
+def sample_labels(labels, page_shape, grid, cell, plan, n_classes, dense_map=None):
 	"""ConfidenceSampler counts (reference origami/batch/detect/lines.py:34-54)."""
 	gh, gw = _check_grid(grid)
 	_check_u8_image(labels, "labels")
 	counts = torch.empty((max(plan.n, 1), n_classes), dtype=torch.int64, device=grid.device)
 	overflow = torch.empty((max(plan.n, 1),), dtype=torch.int64, device=grid.device)
 	_lib.call("og_sample_labels", labels.data_ptr(), int(labels.shape[0]), int(labels.shape[1]), labels.stride(0),
-		int(page_shape[0]), int(page_shape[1]), grid.data_ptr(), gh, gw, cell, plan.lines.data_ptr(), plan.n,
+		int(page_shape[0]), int(page_shape[1]), grid.data_ptr(), gh, gw, cell, _check_map(dense_map, gh, gw, cell),
+		plan.lines.data_ptr(), plan.n,
 		plan.steps.data_ptr(), plan.chunk_offsets.data_ptr(), n_classes, counts.data_ptr(), overflow.data_ptr(), _stream())
 	return counts[:plan.n], overflow[:plan.n]
 

@@ -42,6 +42,8 @@ def main():
 	res["line_steps"] = timeit(lambda: ops.line_steps(g, cell, ld, n_lines)), 0
 	res["extract"] = timeit(lambda: ops.extract_lines(src, g, cell, plan, strips, bbox)), 2 * total
 	res["extract nobbox"] = timeit(lambda: ops.extract_lines(src, g, cell, plan, strips)), 2 * total
+	res["extract map"] = timeit(lambda: ops.extract_lines(src, g, cell, plan, strips, bbox, dense_map=mp)), 2 * total
+	res["extract map nobbox"] = timeit(lambda: ops.extract_lines(src, g, cell, plan, strips, dense_map=mp)), 2 * total
 	res["otsu strips"] = timeit(lambda: ops.binarize_strips(strips, plan, ops.OG_BIN_OTSU, out=strips2)), 2 * total
 	res["sauvola strips"] = timeit(lambda: ops.binarize_strips(strips, plan, ops.OG_BIN_SAUVOLA, 15, out=strips2)), 2 * total
 	bin_dst = ops.alloc_image(H, W, dev)
@@ -54,6 +56,7 @@ def main():
 	plan2 = ops.line_steps(g, cell, ld2, n_lines)
 	labels = ops.to_device_image(synth.make_labels(1280, 2400), dev)
 	res["sample labels"] = timeit(lambda: ops.sample_labels(labels, (H, W), g, cell, plan2, 4)), 0
+	res["sample labels map"] = timeit(lambda: ops.sample_labels(labels, (H, W), g, cell, plan2, 4, dense_map=mp)), 0
 	for k, ((med, best), nbytes) in res.items():
 		print("%-16s median %8.3f ms  best %8.3f ms  %8.1f GB/s" % (k, med, best, nbytes / best / 1e6))
 

@@ -38,10 +38,12 @@ def test_inverse_yx_bit_exact(cuda):
 	assert np.array_equal(got, want)
 
 
+@pytest.mark.parametrize("use_map", [False, True])
 @pytest.mark.parametrize("target_height", [48, 56, 7])
-def test_strips_bit_exact(cuda, target_height):
+def test_strips_bit_exact(cuda, target_height, use_map):
 	page, grid, dense, lines = _setup(cuda)
 	g = torch.from_numpy(grid).to(cuda)
+	dmap = ops.expand_map(g, 25) if use_map else None
 	src = ops.to_device_image(page, cuda)
 	la = ops.pack_lines(_records(lines, ysteps=target_height))
 	plan = ops.line_steps(g, 25, ops.lines_to_device(la, cuda), len(lines))
@@ -49,7 +51,7 @@ def test_strips_bit_exact(cuda, target_height):
 	offs = plan.pix_offsets.cpu().numpy()
 	out = torch.zeros((int(offs[-1]),), dtype=torch.uint8, device=cuda)
 	bbox = torch.zeros((len(lines), 4), dtype=torch.int32, device=cuda)
-	ops.extract_lines(src, g, 25, plan, out, bbox)
+	ops.extract_lines(src, g, 25, plan, out, bbox, dense_map=dmap)
 	out = out.cpu().numpy()
 	bbox = bbox.cpu().numpy()
 	for i, ln in enumerate(lines):
@@ -61,15 +63,17 @@ def test_strips_bit_exact(cuda, target_height):
 		assert tuple(bbox[i]) == exact.grid_bbox(wg), i
 
 
-def test_warped_grids_half_res_bit_exact(cuda):
+@pytest.mark.parametrize("use_map", [False, True])
+def test_warped_grids_half_res_bit_exact(cuda, use_map):
 	_, grid, dense, lines = _setup(cuda, seed=4)
 	g = torch.from_numpy(grid).to(cuda)
+	dmap = ops.expand_map(g, 25) if use_map else None
 	la = ops.pack_lines(_records(lines, xres=0.5, yres=0.5))
 	plan = ops.line_steps(g, 25, ops.lines_to_device(la, cuda), len(lines))
 	offs = plan.pix_offsets.cpu().numpy()
 	steps = plan.steps.cpu().numpy()
 	out = torch.zeros((int(offs[-1]) * 2,), dtype=torch.float32, device=cuda)
-	ops.warped_grids(g, 25, plan, out)
+	ops.warped_grids(g, 25, plan, out, dense_map=dmap)
 	out = out.cpu().numpy()
 	for i, ln in enumerate(lines):
 		want = exact.warped_grid(dense, ln["p"], ln["right"], ln["up"], xres=0.5, yres=0.5)
@@ -78,10 +82,12 @@ def test_warped_grids_half_res_bit_exact(cuda):
 		assert np.array_equal(got, want), i
 
 
-def test_column_clipped_lines(cuda):
+@pytest.mark.parametrize("use_map", [False, True])
+def test_column_clipped_lines(cuda, use_map):
 	"""Table rows split into column cells (LineRewriter + Line._position)."""
 	page, grid, dense, lines = _setup(cuda, seed=6)
 	g = torch.from_numpy(grid).to(cuda)
+	dmap = ops.expand_map(g, 25) if use_map else None
 	src = ops.to_device_image(page, cuda)
 	recs, cases = [], []
 	for ln in lines[:30]:
@@ -95,7 +101,7 @@ def test_column_clipped_lines(cuda):
 	plan = ops.line_steps(g, 25, ops.lines_to_device(la, cuda), len(recs))
 	offs = plan.pix_offsets.cpu().numpy()
 	out = torch.zeros((int(offs[-1]),), dtype=torch.uint8, device=cuda)
-	ops.extract_lines(src, g, 25, plan, out)
+	ops.extract_lines(src, g, 25, plan, out, dense_map=dmap)
 	out = out.cpu().numpy()
 	for i, (ln, col) in enumerate(cases):
 		want = exact.dewarped_line_image(page, dense, ln["p"], ln["right"], ln["up"], 48, column=col)
@@ -103,14 +109,16 @@ def test_column_clipped_lines(cuda):
 		assert np.array_equal(out[offs[i]:offs[i + 1]].reshape(want.shape), want), i
 
 
-def test_label_counts_bit_exact(cuda):
+@pytest.mark.parametrize("use_map", [False, True])
+def test_label_counts_bit_exact(cuda, use_map):
 	page, grid, dense, lines = _setup(cuda, seed=8)
 	labels = synth.make_labels(320, 600, seed=3)
 	g = torch.from_numpy(grid).to(cuda)
 	lab = ops.to_device_image(labels, cuda)
 	la = ops.pack_lines(_records(lines, xres=0.5, yres=0.5))
 	plan = ops.line_steps(g, 25, ops.lines_to_device(la, cuda), len(lines))
-	counts, overflow = ops.sample_labels(lab, page.shape, g, 25, plan, 4)
+	dmap = ops.expand_map(g, 25) if use_map else None
+	counts, overflow = ops.sample_labels(lab, page.shape, g, 25, plan, 4, dense_map=dmap)
 	counts = counts.cpu().numpy()
 	assert int(overflow.sum()) == 0
 	for i, ln in enumerate(lines):
