@@ -256,8 +256,8 @@ KERNELS = ["og_page_kernel", "og_line_steps_kernel", "og_lines_kernel", "og_bina
 
 
 def run_step(ps, args, events=None):
-	"""One page through the path: 4 C-ABI calls = 6 kernel launches (page, steps, scan, bbox init,
-	lines, otsu); 5 without binarization."""
+	"""One page through the path: 4 C-ABI calls = 5 kernel launches (page, steps, scan, lines, otsu);
+	4 without binarization."""
 	import torch
 	from origami_b200 import _lib, ops
 	st = torch.cuda.current_stream().cuda_stream
@@ -277,9 +277,9 @@ def run_step(ps, args, events=None):
 	mark("og_line_steps_kernel")
 	_lib.call("og_extract_lines", ps.src.data_ptr(), ps.H, ps.W, ps.src.stride(0), ps.grid.data_ptr(), ps.gh, ps.gw, CELL,
 		ps.map.data_ptr(), ps.lines.data_ptr(), ps.n, ps.steps.data_ptr(), ps.pix.data_ptr(), ps.chunks.data_ptr(),
-		ps.gray.data_ptr(), ps.gray.numel(), ps.bbox.data_ptr(), st)
+		ps.gray.data_ptr(), ps.gray.numel(), 0, st)
 	mark("og_lines_kernel")
-	launches = 5
+	launches = 4
 	if args.binarize != "none":
 		mode = ops.OG_BIN_OTSU if args.binarize == "otsu" else ops.OG_BIN_SAUVOLA
 		_lib.call("og_binarize_strips", ps.gray.data_ptr(), ps.steps.data_ptr(), ps.pix.data_ptr(), ps.chunks.data_ptr(),

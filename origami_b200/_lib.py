@@ -64,7 +64,8 @@ class OrigamiB200Error(RuntimeError):
 
 
 def lib_path():
-	return _build.LIB_PATH
+	# ORIGAMI_B200_LIB selects another build of the same library (kernel tuning experiments)
+	return os.environ.get("ORIGAMI_B200_LIB") or _build.LIB_PATH
 
 
 def load():

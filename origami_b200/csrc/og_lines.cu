@@ -31,7 +31,10 @@ constexpr int RSPLIT = WORKERS / CW;    // rows are dealt round-robin to 4 threa
 constexpr int SMEM_BUDGET = 100 * 1024;
 constexpr int MAX_ROWS = 128;           // rows with a precomputed lattice offset
 constexpr int MAX_CLASSES = 256;
-constexpr int RB = 2;                   // strip rows a thread processes together (load batching)
+#ifndef OG_RB
+#define OG_RB 2
+#endif
+constexpr int RB = OG_RB;                   // strip rows a thread processes together (load batching)
 
 __device__ __forceinline__ void bar_sync(int id, int nthreads) {
 	asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(nthreads) : "memory");
@@ -442,7 +445,7 @@ __global__ void __launch_bounds__(LTHREADS, 2) og_lines_kernel(const __grid_cons
 					for (int u = 0; u < RB; ++u) {
 						pend[u] = cur[u];
 						pend_row[u] = row[u];
-						if (BBOX && row[u] >= 0) {
+						if (BBOX) {  // a dead slot repeats a live row's coordinates: harmless for min/max
 							bx0 = fminf(bx0, gx[u]); bx1 = fmaxf(bx1, gx[u]);
 							by0 = fminf(by0, gy[u]); by1 = fmaxf(by1, gy[u]);
 						}
@@ -509,9 +512,12 @@ __global__ void __launch_bounds__(LTHREADS, 2) og_lines_kernel(const __grid_cons
 constexpr int MW = 32;            // strip columns per warp item
 constexpr int MWARPS = 8;         // warps per CTA
 constexpr int MTHREADS = MWARPS * 32;
+#ifndef OG_MAP_MINBLOCKS
+#define OG_MAP_MINBLOCKS 3
+#endif
 
 template <int MODE, bool BBOX>
-__global__ void __launch_bounds__(MTHREADS, 3) og_lines_map_kernel(const __grid_constant__ LineParams p, const float2 *__restrict__ map) {
+__global__ void __launch_bounds__(MTHREADS, OG_MAP_MINBLOCKS) og_lines_map_kernel(const __grid_constant__ LineParams p, const float2 *__restrict__ map) {
 	__shared__ double2 s_rowbase[MWARPS][MAX_ROWS];
 	__shared__ unsigned int s_whist[MODE == MODE_LABELS ? MWARPS : 1][MODE == MODE_LABELS ? MAX_CLASSES + 1 : 1];
 
@@ -582,7 +588,7 @@ __global__ void __launch_bounds__(MTHREADS, 3) og_lines_map_kernel(const __grid_
 					i1[u] = min(max(__double2int_rd(px), 0), Wm);
 					a[u] = __dsub_rn(py, (double)i0[u]);
 					b[u] = __dsub_rn(px, (double)i1[u]);
-					const float2 *nd = map + ((size_t)i0[u] * Wd + i1[u]);
+					const float2 *nd = map + (i0[u] * Wd + i1[u]);  // < 2^30 elements (dims < 32767)
 					v00[u] = __ldg(nd);
 					v01[u] = __ldg(nd + 1);
 					v10[u] = __ldg(nd + Wd);
@@ -618,7 +624,7 @@ __global__ void __launch_bounds__(MTHREADS, 3) og_lines_map_kernel(const __grid_
 					for (int u = 0; u < RB; ++u) {
 						pend[u] = cur[u];
 						pend_row[u] = row[u];
-						if (BBOX && row[u] >= 0) {
+						if (BBOX) {  // a dead slot repeats a live row's coordinates: harmless for min/max
 							bx0 = fminf(bx0, gx[u]); bx1 = fmaxf(bx1, gx[u]);
 							by0 = fminf(by0, gy[u]); by1 = fmaxf(by1, gy[u]);
 						}
@@ -722,7 +728,7 @@ int launch_lines(const LineParams &p, cudaStream_t st) {
 template <int MODE, bool BBOX>
 int launch_lines_any(const LineParams &p, const float *map, cudaStream_t st) {
 	if (map == nullptr) return launch_lines<MODE, BBOX>(p, st);
-	og_lines_map_kernel<MODE, BBOX><<<OG_NUM_SMS * 3, MTHREADS, 0, st>>>(p, reinterpret_cast<const float2 *>(map));
+	og_lines_map_kernel<MODE, BBOX><<<OG_NUM_SMS * OG_MAP_MINBLOCKS, MTHREADS, 0, st>>>(p, reinterpret_cast<const float2 *>(map));
 	return og_check_launch("og_lines_map_kernel");
 }
 
