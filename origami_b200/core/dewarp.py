@@ -45,8 +45,13 @@ class Grid:
 			raise ValueError("grid must have shape (gh, gw, 2)")
 		self._grid_hv = hv
 		self._grid_res = int(res)
-		self._device = _device(device)
+		self._device_arg = device
 		self._points_cache = dict()
+
+	@cached_property
+	def _device(self):
+		# resolved on first GPU use, so artifacts can be opened / saved on a host without CUDA
+		return _device(self._device_arg)
 
 	# -- container (reference :501-511, :528-553)
 	@property

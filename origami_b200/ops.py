@@ -59,7 +59,7 @@ def to_device_image(a, device=None):
 	h, w = a.shape
 	out = alloc_image(h, w, device)
 	stage = pinned_staging(h * w).view(h, w)
-	stage.copy_(torch.from_numpy(a))
+	stage.numpy()[...] = a  # host copy into page-locked memory (PIL arrays are read-only views)
 	out.copy_(stage, non_blocking=True)
 	torch.cuda.current_stream().synchronize()  # the staging buffer is reused by the next call
 	return out

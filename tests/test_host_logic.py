@@ -1,0 +1,136 @@
+"""CPU tests of the host-side mirror of the reference interface (no GPU needed)."""
+
+import json
+import os
+import subprocess
+import sys
+import tempfile
+
+import numpy as np
+import pytest
+
+from oracle import exact
+from origami_b200 import shard, synth
+from origami_b200.batch.core.lines import LineExtractor, LineRewriter
+from origami_b200.core import binarize
+from origami_b200.core.block import Block, Line, Stage, affine_transform, position
+from origami_b200.core.dewarp import Grid
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def test_stage_is_dewarped():
+	assert not Stage.WARPED.is_dewarped and Stage.DEWARPED.is_dewarped and Stage.RELIABLE.is_dewarped
+
+
+def test_grid_container_and_zip_roundtrip(tmp_path):
+	g = synth.make_grid(300, 200, 25, seed=2)
+	grid = Grid(g, 25)
+	assert grid.geometry.size == (g.shape[1] * 25, g.shape[0] * 25)
+	assert grid.resolution == 25
+	assert grid.points("sample") is not None and np.array_equal(grid.points("sample"), g)
+	path = tmp_path / "dewarp.zip"
+	grid.save(path)
+	back = Grid.open(path)
+	assert np.array_equal(back.points("sample"), g) and back.resolution == 25
+	with pytest.raises(ValueError):
+		grid.points("half")
+	with pytest.raises(ValueError):
+		Grid(np.zeros((4, 4)), 25)
+
+
+def test_binarizer_spec_strings():
+	assert binarize.from_string("otsu").spec == ("otsu",)
+	assert binarize.from_string("otsu()").spec == ("otsu",)
+	assert binarize.from_string("sauvola").spec == ("sauvola", 15)
+	assert binarize.from_string("sauvola(window_size=31)").spec == ("sauvola", 31)
+	with pytest.raises(ValueError):
+		binarize.from_string("niblack(3)")
+
+
+def test_position_matches_oracle():
+	rng = np.random.default_rng(0)
+	for _ in range(50):
+		p = rng.uniform(10, 500, 2)
+		right = np.array([rng.uniform(50, 400), rng.uniform(-3, 3)])
+		up = np.array([rng.uniform(-1, 1), -rng.uniform(10, 40)])
+		x0 = p[0] + rng.uniform(0.05, 0.45) * right[0]
+		x1 = p[0] + rng.uniform(0.55, 0.95) * right[0]
+		for col in (None, (None, x0), (x0, x1), (x1, None), (p[0] - 50, x1)):
+			a = position(p, right, up, 1, col)
+			b = exact.line_position(p, right, up, 1, col)
+			for u, v in zip(a, b):
+				assert np.array_equal(np.asarray(u), np.asarray(v))
+
+
+def test_line_rewriter_splits_table_rows():
+	tables = dict(columns={"regions/TABULAR/3.1.2.1": [120.0, 260.0]})
+	rw = LineRewriter(tables)
+	lines = {("regions", "TEXT", "7", "0"): "a", ("regions", "TABULAR", "3.1.2.1", "4"): "b"}
+	parts = rw(lines)
+	assert parts[0] == (("regions", "TEXT", "7", "0"), "a", None)
+	cols = parts[1:]
+	assert [c[2] for c in cols] == [(None, 120.0), (120.0, 260.0), (260.0, None)]
+	assert [c[0] for c in cols] == [("regions", "TABULAR", "3.1.5.%d" % k, "0") for k in (1, 2, 3)]
+	with pytest.raises(RuntimeError):
+		LineRewriter(dict(columns={"regions/TABULAR/3": [1.0]}))({("regions", "TABULAR", "3", "0"): "x"})
+
+
+def test_line_extractor_filters_confidence():
+	ex = LineExtractor(dict(columns={}), 48, dict(binarize="", do_not_dewarp=False, do_not_deskew=False), min_confidence=0.5)
+	block = Block(None, None, Stage.RELIABLE)
+	lines = {
+		("regions", "TEXT", "1", "0"): Line(block, [0, 10], [100, 0], [0, -10], confidence=0.9),
+		("regions", "TEXT", "1", "1"): Line(block, [0, 30], [100, 0], [0, -10], confidence=0.2),
+		("illustrations", "X", "2", "0"): Line(block, [0, 50], [100, 0], [0, -10], confidence=1.0),
+	}
+	parts = ex._filtered_parts(lines, ignored=lambda k: k[0] == "illustrations")
+	assert [p[0] for p in parts] == [("regions", "TEXT", "1", "0")]
+	with pytest.raises(ValueError):
+		LineExtractor(dict(columns={}), 48, dict(binarize="foo"))
+
+
+def test_line_record_and_info():
+	block = Block(None, None, Stage.RELIABLE)
+	ln = Line(block, [10.0, 20.0], [200.0, 1.0], [0.1, -30.0], tesseract_data=dict(baseline=[[0, 0], [1, 1]], descent=1, ascent=2, height=3))
+	rec = ln.record(ysteps=48, column=(50.0, 150.0))
+	assert rec["ysteps"] == 48 and rec["xsteps"] is None
+	assert rec["cp"][0] == 50.0 and abs(rec["cright"][0] - 100.0) < 1e-12
+	assert abs(rec["xres"] - 0.5) < 1e-12
+	info = ln.info
+	assert info["p"] == [10.0, 20.0] and info["tesseract_data"]["height"] == 3
+
+
+def test_affine_transform_is_cv2():
+	cv2 = pytest.importorskip("cv2")
+	src = np.array([[10.5, 20.25], [210.0, 24.0], [9.0, -8.0]], dtype=np.float32)
+	dst = np.array([[0, 47], [200, 47], [0, 0]], dtype=np.float32)
+	assert np.allclose(affine_transform(src, dst), cv2.getAffineTransform(src, dst), atol=1e-9)
+
+
+def test_pages_of_rank_partition():
+	for n, world in [(256, 8), (7, 2), (3, 4), (0, 2)]:
+		seen = sorted(p for r in range(world) for p in shard.pages_of_rank(n, r, world))
+		assert seen == list(range(n))
+	assert shard.pages_of_rank(256, 3, 8)[:3] == [3, 11, 19]
+	assert shard.max_over_ranks(1.5) == 1.5  # single process: no group
+
+
+def test_sharding_two_ranks_gloo():
+	"""world_size 2 on CPU: page shards are disjoint and the job time is the max over ranks."""
+	with tempfile.TemporaryDirectory() as tmp:
+		cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node", "2",
+			"--master-addr", "127.0.0.1", "--master-port", "29617",
+			os.path.join(ROOT, "tests", "_gloo_worker.py"), tmp]
+		res = subprocess.run(cmd, capture_output=True, text=True, timeout=240)
+		assert res.returncode == 0, res.stderr[-2000:]
+		outs = [json.load(open(os.path.join(tmp, "rank%d.json" % r))) for r in range(2)]
+	assert outs[0]["pages"] == [0, 2, 4, 6] and outs[1]["pages"] == [1, 3, 5]
+	assert all(o["tmax"] == 11.0 and o["total"] == 7.0 and o["world"] == 2 for o in outs)
+
+
+def test_bench_reference_arm_noop_on_other_ranks():
+	env = dict(os.environ, RANK="1", WORLD_SIZE="2")
+	res = subprocess.run([sys.executable, os.path.join(ROOT, "bench.py"), "--impl", "reference", "--steps", "1", "--warmup", "0"],
+		capture_output=True, text=True, env=env, timeout=120)
+	assert res.returncode == 0 and res.stdout.strip() == ""
