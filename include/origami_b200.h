@@ -146,6 +146,22 @@ int og_otsu(const uint8_t *src, int h, int w, int64_t src_pitch,
 	uint8_t *dst, int64_t dst_pitch, uint32_t *hist_scratch, int32_t *threshold_out,
 	void *stream);
 
+/* og_otsu without caller scratch.  This entry point has no counterpart in the reference: it
+ * exists for callers that cannot allocate device memory -- an Origami stage plugin living in
+ * the same process as the TensorFlow segmentation nets (TensorFlow reserves the device for its
+ * own arena, so cudaMalloc fails afterwards), a worker that was handed a fixed set of buffers,
+ * or code that must not trigger the device-wide synchronisation of cudaMalloc / cudaFree.
+ * The 256-counter histogram lives in a static device array inside the library (1 KiB per GPU
+ * that loads it, held until exit); the call allocates nothing.  Limits and rules:
+ *  - h * w <= 2^30 pixels (OG_E_RANGE beyond that; use og_otsu with your own scratch);
+ *  - all calls on a device share the array: it is cleared at the start of each call, and calls
+ *    whose GPU work overlaps (other streams / unordered host threads) race -- serialise them;
+ *  - the first call on each device (with that device current) looks the array's address up
+ *    once; make that first call before any stream capture.
+ * Output is identical to og_otsu. */
+int og_otsu_noalloc(const uint8_t *src, int h, int w, int64_t src_pitch,
+	uint8_t *dst, int64_t dst_pitch, int32_t *threshold_out, void *stream);
+
 /* A15  ConfidenceSampler.__call__ -- origami/batch/detect/lines.py:34-54.  For every line:
  * warped grid at (xres, yres) from the descriptors, scaled to the label map by
  * fp32(lw/W), fp32(lh/H), NEAREST lookup (OOB -> label 0), histogram.  counts_out

@@ -6,6 +6,8 @@
 // (origami/batch/detect/layout.py:157-169).  The thresholds are scikit-image 0.16.2's
 // threshold_otsu / threshold_sauvola; both are restated with exact integer window sums /
 // histograms followed by the same float64 operations in the same order.
+#include <mutex>
+
 #include "og_common.cuh"
 
 namespace {
@@ -342,5 +344,82 @@ extern "C" int og_otsu(const uint8_t *src, int h, int w, int64_t src_pitch,
 	int rc = og_check_launch("og_hist_kernel");
 	if (rc) return rc;
 	og_otsu_apply_kernel<<<blocks, BTHREADS, 0, st>>>(src, h, w, src_pitch, dst, dst_pitch, hist_scratch, threshold_out);
+	return og_check_launch("og_otsu_apply_kernel");
+}
+
+// ---------------------------------------------------------------------------------------
+// og_otsu_noalloc: page Otsu for callers that cannot obtain device memory.
+//
+// Who that is: an Origami stage plugin that shares its process with the segmentation
+// networks.  TensorFlow reserves (nearly) the whole device for its own arena when it starts,
+// so a later cudaMalloc from the plugin fails; the same holds for a worker that was handed a
+// fixed set of buffers by a host application and has no allocator of its own, and for code
+// on a latency-critical stream, where cudaMalloc / cudaFree would synchronise the device.
+// Such a caller still owns its input and output images; what it lacks is the 1 KiB of
+// histogram scratch that og_otsu expects from it.  Here that scratch lives in the library's
+// own device image: a file-scope array that every GPU which loads the library holds until
+// the process exits.
+//
+// Consequences of sharing one array:
+//  - every call on a device uses the same 256 counters, and they keep the previous call's
+//    counts, so each call clears them (cudaMemsetAsync on the caller's stream) before the
+//    histogram kernel runs;
+//  - two calls whose work overlaps on the GPU (different streams, or different host threads
+//    without ordering between them) race on the counters and produce wrong thresholds:
+//    serialise calls per device;
+//  - the counters are 32 bit and the array has a fixed size, so the image size is capped
+//    (OG_OTSU_NOALLOC_MAX_PIXELS); larger images are rejected with OG_E_RANGE.
+//
+// The array's name is only a host-side handle in host code, not a device address.  The
+// first call on each device (with that device current) resolves the address once with
+// cudaGetSymbolAddress and remembers it; make that first call outside any stream capture.
+// The call itself performs no cudaMalloc / cudaFree and calls no allocating library routine.
+// ---------------------------------------------------------------------------------------
+#define OG_OTSU_NOALLOC_MAX_PIXELS ((int64_t)1 << 30)
+#define OG_NOALLOC_MAX_DEVICES 64
+
+static __device__ __align__(256) uint32_t g_otsu_noalloc_hist[256];
+
+namespace {
+
+std::mutex g_noalloc_mutex;
+uint32_t *g_noalloc_hist_ptr[OG_NOALLOC_MAX_DEVICES] = {nullptr};
+
+int noalloc_hist_address(uint32_t **out) {
+	int dev = -1;
+	cudaError_t e = cudaGetDevice(&dev);
+	if (e != cudaSuccess) return og_set_error((int)e, "cudaGetDevice: %s", cudaGetErrorString(e));
+	OG_REQUIRE(dev >= 0 && dev < OG_NOALLOC_MAX_DEVICES, OG_E_RANGE, "device ordinal %d beyond %d", dev, OG_NOALLOC_MAX_DEVICES);
+	std::lock_guard<std::mutex> lock(g_noalloc_mutex);
+	if (g_noalloc_hist_ptr[dev] == nullptr) {
+		void *ptr = nullptr;
+		e = cudaGetSymbolAddress(&ptr, g_otsu_noalloc_hist);
+		if (e != cudaSuccess) return og_set_error((int)e, "cudaGetSymbolAddress: %s", cudaGetErrorString(e));
+		g_noalloc_hist_ptr[dev] = static_cast<uint32_t *>(ptr);
+	}
+	*out = g_noalloc_hist_ptr[dev];
+	return OG_OK;
+}
+
+}  // namespace
+
+extern "C" int og_otsu_noalloc(const uint8_t *src, int h, int w, int64_t src_pitch,
+	uint8_t *dst, int64_t dst_pitch, int32_t *threshold_out, void *stream) {
+	OG_REQUIRE(src != nullptr && dst != nullptr, OG_E_ARG, "NULL pointer");
+	OG_REQUIRE(h > 0 && w > 0 && src_pitch >= w && dst_pitch >= w, OG_E_ARG, "image %d x %d / pitch invalid", w, h);
+	OG_REQUIRE((int64_t)h * w <= OG_OTSU_NOALLOC_MAX_PIXELS, OG_E_RANGE,
+		"image of %lld pixels exceeds the %lld-pixel limit of the built-in scratch; use og_otsu with caller scratch",
+		(long long)h * w, (long long)OG_OTSU_NOALLOC_MAX_PIXELS);
+	uint32_t *hist = nullptr;
+	int rc = noalloc_hist_address(&hist);
+	if (rc) return rc;
+	cudaStream_t st = (cudaStream_t)stream;
+	cudaError_t e = cudaMemsetAsync(hist, 0, 256 * sizeof(uint32_t), st);  // the array keeps the last call's counts
+	if (e != cudaSuccess) return og_set_error((int)e, "cudaMemsetAsync: %s", cudaGetErrorString(e));
+	const int blocks = OG_NUM_SMS * 8;
+	og_hist_kernel<<<blocks, BTHREADS, 0, st>>>(src, h, w, src_pitch, hist);
+	rc = og_check_launch("og_hist_kernel");
+	if (rc) return rc;
+	og_otsu_apply_kernel<<<blocks, BTHREADS, 0, st>>>(src, h, w, src_pitch, dst, dst_pitch, hist, threshold_out);
 	return og_check_launch("og_otsu_apply_kernel");
 }
