@@ -100,17 +100,48 @@ __device__ int otsu_from_hist_warp(const unsigned int *hist) {
 // ---------------------------------------------------------------------------------------
 // strips, Otsu: one CTA per line -- histogram in shared memory, threshold, apply
 // ---------------------------------------------------------------------------------------
+// Histogram of text strips: most pixels are paper, so a warp's 32 lanes mostly hit the same few
+// bins and plain shared-memory atomics serialise.  The counters are replicated HREP times
+// ([bin][replica], replica = lane % HREP), so equal values from different lanes land on
+// different addresses and banks; the replicas are summed before the threshold is computed.
+constexpr int HREP = 8;
+
 __global__ void __launch_bounds__(BTHREADS) og_otsu_strips_kernel(
 	const uint8_t *__restrict__ gray, const int32_t *__restrict__ steps, const int64_t *__restrict__ pix_offsets,
 	int n, uint8_t *__restrict__ out, int32_t *__restrict__ thresholds) {
+	__shared__ unsigned int rep[256 * HREP];
 	__shared__ unsigned int hist[256];
 	__shared__ int s_t;
+	const int r = threadIdx.x & (HREP - 1);
 	for (int li = blockIdx.x; li < n; li += gridDim.x) {
 		const int64_t off = pix_offsets[li];
 		const int64_t npix = (int64_t)steps[2 * li] * steps[2 * li + 1];
-		for (int k = threadIdx.x; k < 256; k += BTHREADS) hist[k] = 0;
+		const uint8_t *g = gray + off;
+		uint8_t *o = out + off;
+		for (int k = threadIdx.x; k < 256 * HREP; k += BTHREADS) rep[k] = 0;
 		__syncthreads();
-		for (int64_t i = threadIdx.x; i < npix; i += BTHREADS) atomicAdd(&hist[gray[off + i]], 1u);
+		// 16-byte vector body between the unaligned head and tail
+		const int64_t head = min(npix, (int64_t)((16 - (reinterpret_cast<uintptr_t>(g) & 15)) & 15));
+		const int64_t nvec = (npix - head) / 16;
+		for (int64_t i = threadIdx.x; i < head; i += BTHREADS) atomicAdd(&rep[g[i] * HREP + r], 1u);
+		const uint4 *gv = reinterpret_cast<const uint4 *>(g + head);
+		for (int64_t i = threadIdx.x; i < nvec; i += BTHREADS) {
+			const uint4 v = gv[i];
+			const unsigned int wds[4] = {v.x, v.y, v.z, v.w};
+#pragma unroll
+			for (int q = 0; q < 4; ++q) {
+#pragma unroll
+				for (int b = 0; b < 4; ++b) atomicAdd(&rep[((wds[q] >> (8 * b)) & 255u) * HREP + r], 1u);
+			}
+		}
+		for (int64_t i = head + nvec * 16 + threadIdx.x; i < npix; i += BTHREADS) atomicAdd(&rep[g[i] * HREP + r], 1u);
+		__syncthreads();
+		for (int k = threadIdx.x; k < 256; k += BTHREADS) {
+			unsigned int sum = 0;
+#pragma unroll
+			for (int q = 0; q < HREP; ++q) sum += rep[k * HREP + q];
+			hist[k] = sum;
+		}
 		__syncthreads();
 		if (threadIdx.x < 32) {
 			const int t = otsu_from_hist_warp(hist);
@@ -120,8 +151,28 @@ __global__ void __launch_bounds__(BTHREADS) og_otsu_strips_kernel(
 			}
 		}
 		__syncthreads();
-		const int t = s_t;
-		for (int64_t i = threadIdx.x; i < npix; i += BTHREADS) out[off + i] = gray[off + i] > t ? 255 : 0;
+		const unsigned int t = (unsigned int)s_t;
+		for (int64_t i = threadIdx.x; i < head; i += BTHREADS) o[i] = g[i] > t ? 255 : 0;
+		const bool out_al = ((reinterpret_cast<uintptr_t>(o + head)) & 15) == 0;
+		for (int64_t i = threadIdx.x; i < nvec; i += BTHREADS) {
+			const uint4 v = gv[i];
+			unsigned int wds[4] = {v.x, v.y, v.z, v.w};
+#pragma unroll
+			for (int q = 0; q < 4; ++q) {
+				unsigned int m = 0;
+#pragma unroll
+				for (int b = 0; b < 4; ++b) m |= (((wds[q] >> (8 * b)) & 255u) > t ? 255u : 0u) << (8 * b);
+				wds[q] = m;
+			}
+			if (out_al) {
+				reinterpret_cast<uint4 *>(o + head)[i] = make_uint4(wds[0], wds[1], wds[2], wds[3]);
+			} else {
+				uint8_t *ob = o + head + i * 16;
+#pragma unroll
+				for (int q = 0; q < 16; ++q) ob[q] = (uint8_t)(wds[q >> 2] >> (8 * (q & 3)));
+			}
+		}
+		for (int64_t i = head + nvec * 16 + threadIdx.x; i < npix; i += BTHREADS) o[i] = g[i] > t ? 255 : 0;
 		__syncthreads();
 	}
 }

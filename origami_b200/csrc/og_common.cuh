@@ -151,7 +151,13 @@ __device__ __forceinline__ int og_sample_linear_fast(
 
 // N pixels at once: when every tap of every pixel is inside the image (the common case) all
 // 4N byte loads are issued back to back before the first blend, so their latencies overlap.
-template <int N>
+__device__ __forceinline__ void og_prefetch_l1(const void *ptr) {
+	asm volatile("prefetch.global.L1 [%0];" ::"l"(ptr));
+}
+
+// PF > 0: also prefetch the source row PF rows below the taps of every other pixel -- the row
+// the same thread will need PF-1 destination rows later when it walks down a page.
+template <int N, int PF = 0>
 __device__ __forceinline__ void og_sample_linear_batch(
 	const uint8_t *__restrict__ src, int H, int W, int pitch,
 	const float (&mx)[N], const float (&my)[N], int (&out)[N]) {
@@ -177,6 +183,7 @@ __device__ __forceinline__ void og_sample_linear_batch(
 			p01[k] = __ldg(s + 1);
 			p10[k] = __ldg(s + pitch);
 			p11[k] = __ldg(s + pitch + 1);
+			if (PF > 0 && (k & 1) == 0 && iy[k] + PF < H) og_prefetch_l1(s + PF * pitch);
 		}
 #pragma unroll
 		for (int k = 0; k < N; ++k) out[k] = og_blend(q[k], p00[k], p01[k], p10[k], p11[k]);

@@ -529,6 +529,7 @@ __global__ void __launch_bounds__(MTHREADS, OG_MAP_MINBLOCKS) og_lines_map_kerne
 	const uint8_t *__restrict__ src = p.src;
 	const int H = p.H, W = p.W, spitch = p.src_pitch;
 	double2 *rowbase = s_rowbase[wid];
+	const unsigned rb_saddr = (unsigned)__cvta_generic_to_shared(rowbase);
 
 	for (int item = blockIdx.x * MWARPS + wid; item < total_items; item += nwarps) {
 		const int chunk_item = item >> 1;
@@ -560,41 +561,42 @@ __global__ void __launch_bounds__(MTHREADS, OG_MAP_MINBLOCKS) og_lines_map_kerne
 			const og_d2 xc = og_linspace_at(lx, cc);
 			uint8_t *strip = (MODE == MODE_STRIP) ? p.strips_out + pix0 + cc : nullptr;
 			float2 *gout = (MODE == MODE_GRID) ? reinterpret_cast<float2 *>(p.grids_out) + pix0 + cc : nullptr;
-			og_taps pend[RB];
-			int pend_row[RB];
-			bool have_pend = false;
-			for (int rbase = 0; rbase < ysteps; rbase += RB) {
-				int row[RB], i0[RB], i1[RB];
+			const float2 *__restrict__ map_lo = map;
+			const float2 *__restrict__ map_hi = map + Wd;
+
+			// one batch of RB consecutive rows: coordinates, node gather, float64 blend -> (gx, gy)
+			auto coords = [&](int rbase, float (&gx)[RB], float (&gy)[RB], int (&row)[RB]) {
+				int idx[RB];
 				double a[RB], b[RB];
 				float2 v00[RB], v01[RB], v10[RB], v11[RB];
 #pragma unroll
 				for (int u = 0; u < RB; ++u) {
 					const int r = rbase + u;
 					row[u] = r < ysteps ? r : -1;
-					const int rr = r < ysteps ? r : rbase;
-					double2 rb;
+					const int rr = r < ysteps ? r : ysteps - 1;
+					double rbx, rby;
 					if (tabled) {
-						rb = rowbase[rr];
+						asm volatile("ld.shared.v2.f64 {%0, %1}, [%2];" : "=d"(rbx), "=d"(rby) : "r"(rb_saddr + rr * 16));
 					} else {
 						og_d2 yr = og_linspace_at(ly, rr);
-						rb = make_double2(__dadd_rn(yr.x, cpx), __dadd_rn(yr.y, cpy));
+						rbx = __dadd_rn(yr.x, cpx);
+						rby = __dadd_rn(yr.y, cpy);
 					}
 					// dewarped_grid = (ys + p0)[:, None] + xs[None, :]   (block.py:241)
-					const double px = __dadd_rn(rb.x, xc.x);
-					const double py = __dadd_rn(rb.y, xc.y);
+					const double px = __dadd_rn(rbx, xc.x);
+					const double py = __dadd_rn(rby, xc.y);
 					// i = clip(floor(y), 0, n - 2) (SciPy find_indices); the saturating
 					// conversion keeps even absurd coordinates inside the map
-					i0[u] = min(max(__double2int_rd(py), 0), Hm);
-					i1[u] = min(max(__double2int_rd(px), 0), Wm);
-					a[u] = __dsub_rn(py, (double)i0[u]);
-					b[u] = __dsub_rn(px, (double)i1[u]);
-					const float2 *nd = map + (i0[u] * Wd + i1[u]);  // < 2^30 elements (dims < 32767)
-					v00[u] = __ldg(nd);
-					v01[u] = __ldg(nd + 1);
-					v10[u] = __ldg(nd + Wd);
-					v11[u] = __ldg(nd + Wd + 1);
+					const int i0 = min(max(__double2int_rd(py), 0), Hm);
+					const int i1 = min(max(__double2int_rd(px), 0), Wm);
+					a[u] = __dsub_rn(py, (double)i0);
+					b[u] = __dsub_rn(px, (double)i1);
+					idx[u] = i0 * Wd + i1;  // < 2^30 elements (dims < 32767)
+					v00[u] = __ldg(map_lo + idx[u]);
+					v01[u] = __ldg(map_lo + idx[u] + 1);
+					v10[u] = __ldg(map_hi + idx[u]);
+					v11[u] = __ldg(map_hi + idx[u] + 1);
 				}
-				float gx[RB], gy[RB];
 #pragma unroll
 				for (int u = 0; u < RB; ++u) {
 					const double wa = __dsub_rn(1.0, a[u]), wb = __dsub_rn(1.0, b[u]);
@@ -607,33 +609,56 @@ __global__ void __launch_bounds__(MTHREADS, OG_MAP_MINBLOCKS) og_lines_map_kerne
 					gx[u] = __double2float_rn(wx);
 					gy[u] = __double2float_rn(wy);
 				}
-				if (MODE == MODE_GRID) {
+			};
+			auto flush = [&](const og_taps (&t)[RB], const int (&trow)[RB]) {
 #pragma unroll
-					for (int u = 0; u < RB; ++u)
-						if (row[u] >= 0) gout[row[u] * xsteps] = make_float2(gx[u], gy[u]);
-				} else if (MODE == MODE_STRIP) {
-					og_taps cur[RB];
-					og_load_taps_batch<RB>(src, H, W, spitch, gx, gy, cur);
-					if (have_pend) {
+				for (int u = 0; u < RB; ++u)
+					if (trow[u] >= 0)  // pixels[::-1, :]  (block.py:257)
+						strip[(ysteps - 1 - trow[u]) * xsteps] = (uint8_t)og_blend_taps(t[u]);
+			};
+
+			if (MODE == MODE_STRIP) {
+				// two tap buffers in rotation: the taps of a batch are requested, then the previous
+				// batch is blended and stored while they are in flight
+				og_taps t0[RB], t1[RB];
+				int r0[RB], r1[RB];
 #pragma unroll
-						for (int u = 0; u < RB; ++u)
-							if (pend_row[u] >= 0)  // pixels[::-1, :]  (block.py:257)
-								strip[(ysteps - 1 - pend_row[u]) * xsteps] = (uint8_t)og_blend_taps(pend[u]);
-					}
+				for (int u = 0; u < RB; ++u) r1[u] = -1;
+				for (int rbase = 0; rbase < ysteps; rbase += 2 * RB) {
+					float gx[RB], gy[RB];
+					coords(rbase, gx, gy, r0);
+					og_load_taps_batch<RB>(src, H, W, spitch, gx, gy, t0);
+					flush(t1, r1);
+					if (BBOX) {
 #pragma unroll
-					for (int u = 0; u < RB; ++u) {
-						pend[u] = cur[u];
-						pend_row[u] = row[u];
-						if (BBOX) {  // a dead slot repeats a live row's coordinates: harmless for min/max
+						for (int u = 0; u < RB; ++u) {  // a dead slot repeats a live row: harmless for min/max
 							bx0 = fminf(bx0, gx[u]); bx1 = fmaxf(bx1, gx[u]);
 							by0 = fminf(by0, gy[u]); by1 = fmaxf(by1, gy[u]);
 						}
 					}
-					have_pend = true;
-				} else {
+					coords(rbase + RB, gx, gy, r1);
+					og_load_taps_batch<RB>(src, H, W, spitch, gx, gy, t1);
+					flush(t0, r0);
+					if (BBOX) {
+#pragma unroll
+						for (int u = 0; u < RB; ++u) {
+							bx0 = fminf(bx0, gx[u]); bx1 = fmaxf(bx1, gx[u]);
+							by0 = fminf(by0, gy[u]); by1 = fmaxf(by1, gy[u]);
+						}
+					}
+				}
+				flush(t1, r1);
+			} else {
+				for (int rbase = 0; rbase < ysteps; rbase += RB) {
+					float gx[RB], gy[RB];
+					int row[RB];
+					coords(rbase, gx, gy, row);
 #pragma unroll
 					for (int u = 0; u < RB; ++u) {
-						if (row[u] >= 0) {
+						if (row[u] < 0) continue;
+						if (MODE == MODE_GRID) {
+							gout[row[u] * xsteps] = make_float2(gx[u], gy[u]);
+						} else {
 							// scale_grid (batch/detect/lines.py:18-22) then cv2.remap INTER_NEAREST
 							const float sx = __fmul_rn(gx[u], p.scale_x), sy = __fmul_rn(gy[u], p.scale_y);
 							const int lab = og_sample_nearest_fast(src, H, W, spitch, sx, sy);
@@ -641,12 +666,6 @@ __global__ void __launch_bounds__(MTHREADS, OG_MAP_MINBLOCKS) og_lines_map_kerne
 						}
 					}
 				}
-			}
-			if (MODE == MODE_STRIP && have_pend) {
-#pragma unroll
-				for (int u = 0; u < RB; ++u)
-					if (pend_row[u] >= 0)
-						strip[(ysteps - 1 - pend_row[u]) * xsteps] = (uint8_t)og_blend_taps(pend[u]);
 			}
 		}
 		if (BBOX) {

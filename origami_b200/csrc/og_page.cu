@@ -15,6 +15,16 @@
 // offsets; the smooth warp makes neighbouring threads hit the same 128-byte lines.
 #include "og_common.cuh"
 
+#ifndef OG_PAGE_PF
+#define OG_PAGE_PF 0
+#endif
+#ifndef OG_PAGE_PIPE
+#define OG_PAGE_PIPE 0
+#endif
+#ifndef OG_PAGE_MINB
+#define OG_PAGE_MINB 3
+#endif
+
 namespace {
 
 constexpr int TPX = 4;    // pixels per thread along x
@@ -36,13 +46,27 @@ struct PageParams {
 	float scale_x, scale_y;
 };
 
+// image bytes of a thread's two pixel pairs (16-bit stores when aligned and complete)
+__device__ __forceinline__ void store_quad(uint8_t *orow, const int (&v)[TPX], int na, int nb, bool img_al) {
+	if (img_al && na == 2) __stcs(reinterpret_cast<unsigned short *>(orow), (unsigned short)(v[0] | (v[1] << 8)));
+	else {
+		if (na > 0) orow[0] = (uint8_t)v[0];
+		if (na > 1) orow[1] = (uint8_t)v[1];
+	}
+	if (img_al && nb == 2) __stcs(reinterpret_cast<unsigned short *>(orow + 64), (unsigned short)(v[2] | (v[3] << 8)));
+	else {
+		if (nb > 0) orow[64] = (uint8_t)v[2];
+		if (nb > 1) orow[65] = (uint8_t)v[3];
+	}
+}
+
 struct RowAxis {
 	int r0, r1;
 	float b0, b1;
 };
 
 template <bool LINEAR, bool SCALED, bool WRITE_MAP, bool WRITE_IMG>
-__global__ void __launch_bounds__(TBX *TBY, 3) og_page_kernel(const __grid_constant__ PageParams p) {
+__global__ void __launch_bounds__(TBX *TBY, OG_PAGE_MINB) og_page_kernel(const __grid_constant__ PageParams p) {
 	__shared__ RowAxis s_rows[TILE_H];
 	const int Wd = p.gw * p.cell, Hd = p.gh * p.cell;
 	const int ytile = blockIdx.y * TILE_H;
@@ -95,6 +119,9 @@ __global__ void __launch_bounds__(TBX *TBY, 3) og_page_kernel(const __grid_const
 	float *mrow = WRITE_MAP ? p.map_out + ((size_t)ybeg * Wd + xa) * 2 : nullptr;
 	uint8_t *orow = WRITE_IMG ? p.dst + (int64_t)ybeg * p.dst_pitch + xa : nullptr;
 
+	og_taps pend[TPX];
+#pragma unroll
+	for (int k = 0; k < TPX; ++k) pend[k] = og_taps{0, 0, 0, 0, 0, 0};
 	const int nrows = min(TROWS, Hd - ybeg);
 	for (int yy = 0; yy < nrows; ++yy) {
 		const RowAxis ra = s_rows[threadIdx.y * TROWS + yy];
@@ -133,31 +160,44 @@ __global__ void __launch_bounds__(TBX *TBY, 3) og_page_kernel(const __grid_const
 			mrow += (size_t)Wd * 2;
 		}
 		if (WRITE_IMG) {
-			int v[TPX];
 			float mx[TPX], my[TPX];
 #pragma unroll
 			for (int k = 0; k < TPX; ++k) {
 				mx[k] = SCALED ? __fmul_rn(d[k].x, scx) : d[k].x;
 				my[k] = SCALED ? __fmul_rn(d[k].y, scy) : d[k].y;
 			}
-			if (LINEAR) {
-				og_sample_linear_batch<TPX>(src, H, W, spitch, mx, my, v);
-			} else {
+			if (LINEAR && OG_PAGE_PIPE) {
+				// software pipeline: the taps of this row are requested now and blended after the
+				// next row's taps have been requested
+				og_taps cur[TPX];
+				og_load_taps_batch<TPX>(src, H, W, spitch, mx, my, cur);
+				if (yy > 0) {
+					int v[TPX];
 #pragma unroll
-				for (int k = 0; k < TPX; ++k) v[k] = og_sample_nearest_fast(src, H, W, spitch, mx[k], my[k]);
+					for (int k = 0; k < TPX; ++k) v[k] = og_blend_taps(pend[k]);
+					store_quad(orow, v, na, nb, img_al);
+					orow += p.dst_pitch;
+				}
+#pragma unroll
+				for (int k = 0; k < TPX; ++k) pend[k] = cur[k];
+			} else {
+				int v[TPX];
+				if (LINEAR) {
+					og_sample_linear_batch<TPX, OG_PAGE_PF>(src, H, W, spitch, mx, my, v);
+				} else {
+#pragma unroll
+					for (int k = 0; k < TPX; ++k) v[k] = og_sample_nearest_fast(src, H, W, spitch, mx[k], my[k]);
+				}
+				store_quad(orow, v, na, nb, img_al);
+				orow += p.dst_pitch;
 			}
-			if (img_al && na == 2) __stcs(reinterpret_cast<unsigned short *>(orow), (unsigned short)(v[0] | (v[1] << 8)));
-			else {
-				if (na > 0) orow[0] = (uint8_t)v[0];
-				if (na > 1) orow[1] = (uint8_t)v[1];
-			}
-			if (img_al && nb == 2) __stcs(reinterpret_cast<unsigned short *>(orow + 64), (unsigned short)(v[2] | (v[3] << 8)));
-			else {
-				if (nb > 0) orow[64] = (uint8_t)v[2];
-				if (nb > 1) orow[65] = (uint8_t)v[3];
-			}
-			orow += p.dst_pitch;
 		}
+	}
+	if (WRITE_IMG && LINEAR && OG_PAGE_PIPE && nrows > 0) {
+		int v[TPX];
+#pragma unroll
+		for (int k = 0; k < TPX; ++k) v[k] = og_blend_taps(pend[k]);
+		store_quad(orow, v, na, nb, img_al);
 	}
 }
 
