@@ -8,6 +8,7 @@ import logging
 
 import PIL.Image
 
+from ... import ops
 from ...core import binarize as _binarize
 from ...core.block import extract_strips
 
@@ -87,7 +88,13 @@ class LineExtractor:
 				out.append((path, im))
 			return out
 		dewarper = line_parts[0][1].block.page.dewarper
-		records = [line.record(ysteps=self._line_height, column=column) for _, line, column in line_parts]
+		if all(column is None for _, _, column in line_parts):
+			# no table cells on this page: pack the descriptors in one vectorised step
+			records = ops.pack_line_arrays(
+				[line._p for _, line, _ in line_parts], [line._right for _, line, _ in line_parts],
+				[line._up for _, line, _ in line_parts], ysteps=self._line_height)
+		else:
+			records = [line.record(ysteps=self._line_height, column=column) for _, line, column in line_parts]
 		spec = self._binarizer.spec if self._binarizer is not None else None
 		strips, _ = extract_strips(dewarper, records, binarize=spec)
 		return [(part[0], strip) for part, strip in zip(line_parts, strips)]

@@ -238,14 +238,13 @@ def affine_transform(src_tri, dst_tri):
 # ---------------------------------------------------------------------------------------
 
 def _plan(grid, records):
-	la = ops.pack_lines(records)
+	la = records if isinstance(records, np.ndarray) else ops.pack_lines(records)
 	dev = grid._device
 	ld = ops.lines_to_device(la, dev) if len(records) else torch.zeros((8,), dtype=torch.uint8, device=dev)
 	plan = ops.line_steps(grid.device_grid, grid.resolution, ld, len(records))
-	host = torch.empty((len(records) + 1,), dtype=torch.int64).pin_memory()
+	host = torch.empty((len(records) + 1,), dtype=torch.int64, pin_memory=True)
 	host.copy_(plan.pix_offsets, non_blocking=True)
-	steps = plan.steps.cpu().numpy()[:len(records)]
-	torch.cuda.current_stream().synchronize()
+	steps = ops.to_host(plan.steps)[:len(records)]
 	offs = host.numpy()
 	if len(records) and (steps <= 0).any():
 		bad = int(np.argmax((steps <= 0).any(axis=1)))
@@ -258,7 +257,7 @@ def warped_grids(grid, records):
 	plan, steps, offs = _plan(grid, records)
 	out = torch.empty((max(int(offs[-1]), 1) * 2,), dtype=torch.float32, device=grid._device)
 	ops.warped_grids(grid.device_grid, grid.resolution, plan, out)
-	flat = out.cpu().numpy()
+	flat = ops.to_host(out)
 	res = [flat[2 * offs[i]:2 * offs[i + 1]].reshape(steps[i][1], steps[i][0], 2) for i in range(len(records))]
 	return res, steps
 
@@ -279,10 +278,7 @@ def extract_strips(dewarper, records, binarize=None, want_bbox=False):
 		mode = ops.OG_BIN_OTSU if binarize[0] == "otsu" else ops.OG_BIN_SAUVOLA
 		window = binarize[1] if len(binarize) > 1 else 15
 		gray = ops.binarize_strips(gray, plan, mode, window)
-	host = torch.empty((total,), dtype=torch.uint8).pin_memory()
-	host.copy_(gray, non_blocking=True)
-	bb = bbox.cpu().numpy()[:len(records)] if want_bbox else None
-	torch.cuda.current_stream().synchronize()
-	flat = host.numpy()
+	bb = ops.to_host(bbox)[:len(records)] if want_bbox else None
+	flat = ops.to_host(gray)
 	strips = [flat[offs[i]:offs[i + 1]].reshape(steps[i][1], steps[i][0]) for i in range(len(records))]
 	return strips, bb

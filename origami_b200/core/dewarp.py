@@ -109,7 +109,7 @@ class Grid:
 				raise ValueError("only INTER_LINEAR map expansion is implemented")
 			key = (resolution, interpolation)
 			if key not in self._points_cache:  # the reference lru_caches 8 of these
-				self._points_cache[key] = self.device_points().cpu().numpy()
+				self._points_cache[key] = ops.to_host(self.device_points())
 			return self._points_cache[key]
 		else:
 			raise ValueError(resolution)
@@ -136,9 +136,10 @@ class Grid:
 
 
 class Dewarper:
-	def __init__(self, im, grid):
+	def __init__(self, im, grid, pixels=None):
 		self._im = im
 		self._grid = grid
+		self._pixels = pixels  # optional ndarray view of `im` (saves a PIL -> bytes round trip)
 
 	@property
 	def grid(self):
@@ -147,7 +148,8 @@ class Dewarper:
 	@cached_property
 	def device_image(self):
 		"""The warped page as a pitched CUDA uint8 image (uploaded once)."""
-		return ops.to_device_image(np.asarray(self._im, dtype=np.uint8), self._grid._device)
+		pixels = self._pixels if self._pixels is not None else np.asarray(self._im, dtype=np.uint8)
+		return ops.to_device_image(pixels, self._grid._device)
 
 	def device_dewarped(self, map_out=None):
 		dst, _ = ops.remap_page(self.device_image, self._grid.device_grid, self._grid.resolution, map_out=map_out)
@@ -155,7 +157,7 @@ class Dewarper:
 
 	@cached_property
 	def dewarped(self):
-		return PIL.Image.fromarray(self.device_dewarped().cpu().numpy())
+		return PIL.Image.fromarray(ops.to_host(self.device_dewarped()))
 
 	def dewarp_image(self, im, interpolation=INTER_LINEAR):
 		w0, h0 = self._im.size
@@ -166,4 +168,4 @@ class Dewarper:
 		src = ops.to_device_image(pixels, self._grid._device)
 		dst, _ = ops.remap_page(src, self._grid.device_grid, self._grid.resolution,
 			scale=(w1 / w0, h1 / h0), interpolation=interpolation)
-		return PIL.Image.fromarray(dst.cpu().numpy())
+		return PIL.Image.fromarray(ops.to_host(dst))

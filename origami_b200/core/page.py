@@ -28,15 +28,17 @@ def _find_image_path(path):
 
 class Page:
 	def __init__(self, path, dewarping_transform=None):
+		pixels = None
 		if isinstance(path, PIL.Image.Image):
 			self._warped = path.convert("L")
 		elif isinstance(path, np.ndarray):
-			self._warped = PIL.Image.fromarray(np.ascontiguousarray(path, dtype=np.uint8))
+			pixels = np.ascontiguousarray(path, dtype=np.uint8)
+			self._warped = PIL.Image.fromarray(pixels)  # shares the array's memory
 		else:
 			self._warped = PIL.Image.open(str(_find_image_path(path))).convert("L")
 
 		if dewarping_transform is not None:
-			self._dewarper = Dewarper(self._warped, dewarping_transform)
+			self._dewarper = Dewarper(self._warped, dewarping_transform, pixels=pixels)
 			self._dewarped = self._dewarper.dewarped
 		else:
 			self._dewarper = None

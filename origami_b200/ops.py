@@ -65,6 +65,15 @@ def to_device_image(a, device=None):
 	return out
 
 
+def to_host(t):
+	"""Device tensor -> NumPy array through page-locked memory (torch caches pinned blocks, so
+	this is one DMA at PCIe speed instead of a staged pageable copy)."""
+	host = torch.empty(t.shape, dtype=t.dtype, pin_memory=True)
+	host.copy_(t, non_blocking=True)
+	torch.cuda.current_stream().synchronize()
+	return host.numpy()
+
+
 def _check_grid(grid):
 	if grid.dtype != torch.float32 or grid.dim() != 3 or grid.shape[2] != 2 or not grid.is_cuda or not grid.is_contiguous():
 		raise ValueError("grid must be a contiguous float32 CUDA tensor of shape (gh, gw, 2)")
@@ -117,24 +126,44 @@ def pack_lines(records):
 	"""records: iterable of dicts with p, right, up and optional cp, cright, xres, yres, xsteps,
 	ysteps -> structured ndarray of og_line."""
 	records = list(records)
-	a = np.zeros(len(records), dtype=LINE_DTYPE)
-	for i, r in enumerate(records):
-		a["p"][i] = r["p"]
-		a["right"][i] = r["right"]
-		a["up"][i] = r["up"]
-		a["cp"][i] = r.get("cp", r["p"])
-		a["cright"][i] = r.get("cright", r["right"])
-		a["xres"][i] = r.get("xres", 1.0)
-		a["yres"][i] = r.get("yres", 1.0)
-		a["xsteps"][i] = r.get("xsteps") or 0
-		a["ysteps"][i] = r.get("ysteps") or 0
+	n = len(records)
+	a = np.zeros(n, dtype=LINE_DTYPE)
+	if n == 0:
+		return a
+	a["p"] = np.array([r["p"] for r in records], dtype=np.float64).reshape(n, 2)
+	a["right"] = np.array([r["right"] for r in records], dtype=np.float64).reshape(n, 2)
+	a["up"] = np.array([r["up"] for r in records], dtype=np.float64).reshape(n, 2)
+	a["cp"] = np.array([r.get("cp", r["p"]) for r in records], dtype=np.float64).reshape(n, 2)
+	a["cright"] = np.array([r.get("cright", r["right"]) for r in records], dtype=np.float64).reshape(n, 2)
+	a["xres"] = [r.get("xres", 1.0) for r in records]
+	a["yres"] = [r.get("yres", 1.0) for r in records]
+	a["xsteps"] = [r.get("xsteps") or 0 for r in records]
+	a["ysteps"] = [r.get("ysteps") or 0 for r in records]
+	return a
+
+
+def pack_line_arrays(p, right, up, xsteps=0, ysteps=0, xres=1.0, yres=1.0):
+	"""Vectorised pack_lines for un-clipped lines: p, right, up are (n, 2) float64 arrays."""
+	p = np.asarray(p, dtype=np.float64).reshape(-1, 2)
+	a = np.zeros(p.shape[0], dtype=LINE_DTYPE)
+	a["p"] = p
+	a["cp"] = p
+	a["right"] = right
+	a["cright"] = right
+	a["up"] = up
+	a["xres"] = xres
+	a["yres"] = yres
+	a["xsteps"] = xsteps
+	a["ysteps"] = ysteps
 	return a
 
 
 def lines_to_device(lines_np, device=None):
 	_require_cuda()
-	raw = torch.from_numpy(lines_np.view(np.uint8).reshape(-1).copy())
-	return raw.to(device or "cuda", non_blocking=True)
+	raw = lines_np.view(np.uint8).reshape(-1)
+	stage = torch.empty((raw.shape[0],), dtype=torch.uint8, pin_memory=True)
+	stage.numpy()[...] = raw
+	return stage.to(device or "cuda", non_blocking=True)
 
 
 class LinePlan:
