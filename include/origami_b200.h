@@ -36,6 +36,9 @@ extern "C" {
 
 #define OG_INTER_NEAREST 0 /* == cv2.INTER_NEAREST */
 #define OG_INTER_LINEAR 1  /* == cv2.INTER_LINEAR  */
+/* OR-ed into og_remap_page's `interp`: copy each tile's source window to shared memory first
+ * (same bits; measured slower than the direct gather on B200, kept as a tuning switch). */
+#define OG_FLAG_STAGE_SMEM 0x100
 
 #define OG_BIN_NONE 0
 #define OG_BIN_OTSU 1

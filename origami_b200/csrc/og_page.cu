@@ -24,13 +24,22 @@
 #ifndef OG_PAGE_MINB
 #define OG_PAGE_MINB 3
 #endif
+#ifndef OG_PAGE_STAGE
+#define OG_PAGE_STAGE 0
+#endif
 
 namespace {
 
 constexpr int TPX = 4;    // pixels per thread along x
 constexpr int TBX = 64;   // threads along x
-constexpr int TBY = 4;    // thread rows
-constexpr int TROWS = 8;  // rows walked per thread
+#ifndef OG_TBY
+#define OG_TBY 4
+#endif
+#ifndef OG_TROWS
+#define OG_TROWS 8
+#endif
+constexpr int TBY = OG_TBY;      // thread rows
+constexpr int TROWS = OG_TROWS;  // rows walked per thread
 constexpr int TILE_W = TPX * TBX;
 constexpr int TILE_H = TBY * TROWS;
 
@@ -201,14 +210,223 @@ __global__ void __launch_bounds__(TBX *TBY, OG_PAGE_MINB) og_page_kernel(const _
 	}
 }
 
+// ---------------------------------------------------------------------------------------
+// Staged variant (LINEAR image output): the source window a tile samples is copied to shared
+// memory with 16-byte cp.async transfers (zero-filled outside the image, which is exactly
+// cv2.remap's BORDER_CONSTANT 0 per tap), so the four taps of a pixel are shared-memory loads
+// instead of a dependent global gather.
+//
+// Pass A walks the thread's rows once: it evaluates the map (and streams it out when the map is
+// wanted) and tracks the bounding box of the sampling coordinates; a block reduction gives the
+// window.  After the copy, pass B evaluates the map again (6 flops per pixel, cheaper than
+// keeping 64 coordinates in registers), quantises and blends from shared memory.  A pixel
+// outside the window (cannot happen: the box is exact) or a tile whose window exceeds the
+// shared-memory budget takes the global-memory path.
+// ---------------------------------------------------------------------------------------
+constexpr int WIN_BYTES = 20 * 1024;
+
+__device__ __forceinline__ void og_cp_async16(void *smem_dst, const void *gmem_src, int src_bytes) {
+	const unsigned d = (unsigned)__cvta_generic_to_shared(smem_dst);
+	asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;" ::"r"(d), "l"(gmem_src), "r"(src_bytes) : "memory");
+}
+
+template <bool SCALED, bool WRITE_MAP>
+__global__ void __launch_bounds__(TBX *TBY, OG_PAGE_MINB) og_page_staged_kernel(const __grid_constant__ PageParams p) {
+	__shared__ RowAxis s_rows[TILE_H];
+	__shared__ int s_box[4];
+	__shared__ __align__(16) uint8_t s_win[WIN_BYTES];
+	const int Wd = p.gw * p.cell, Hd = p.gh * p.cell;
+	const int ytile = blockIdx.y * TILE_H;
+	const double inv_cell = 1.0 / (double)p.cell;
+	const int tid = threadIdx.y * TBX + threadIdx.x;
+	if (tid < TILE_H) {
+		og_axis ay = og_resize_axis(min(ytile + tid, Hd - 1), inv_cell);
+		RowAxis ra;
+		ra.r0 = min(max(ay.i, 0), p.gh - 1);
+		ra.r1 = min(max(ay.i + 1, 0), p.gh - 1);
+		ra.b1 = ay.f;
+		ra.b0 = __fsub_rn(1.f, ay.f);
+		s_rows[tid] = ra;
+	}
+	if (tid < 4) s_box[tid] = (tid < 2) ? INT_MAX : INT_MIN;
+	__syncthreads();
+
+	const int lane = threadIdx.x & 31;
+	const int xw = (blockIdx.x * TBX + (threadIdx.x & ~31)) * TPX;
+	const int xa = xw + 2 * lane, xb = xa + 64;
+	const int ybeg = ytile + threadIdx.y * TROWS;
+	const bool active = xa < Wd && ybeg < Hd;
+	const int gw = p.gw;
+	const float2 *__restrict__ grid = p.grid;
+
+	int sx[TPX], sx1[TPX];
+	float a0[TPX], a1[TPX];
+#pragma unroll
+	for (int k = 0; k < TPX; ++k) {
+		const int x = ((k & 2) ? xb : xa) + (k & 1);
+		og_axis ax = og_resize_axis_x(min(x, Wd - 1), inv_cell, gw);
+		sx[k] = ax.i;
+		sx1[k] = min(ax.i + 1, gw - 1);
+		a1[k] = ax.f;
+		a0[k] = __fsub_rn(1.f, ax.f);
+	}
+	const int na = active ? min(2, Wd - xa) : 0, nb = active ? max(0, min(2, Wd - xb)) : 0;
+	const bool map_al = WRITE_MAP && (Wd & 1) == 0 && ((reinterpret_cast<uintptr_t>(p.map_out) & 15) == 0);
+	const bool img_al = (p.dst_pitch & 1) == 0 && ((reinterpret_cast<uintptr_t>(p.dst) & 1) == 0);
+	const uint8_t *__restrict__ src = p.src;
+	const int H = p.H, W = p.W, spitch = (int)p.src_pitch;
+	const float scx = p.scale_x, scy = p.scale_y;
+	const int nrows = active ? min(TROWS, Hd - ybeg) : 0;
+
+	int cur_r0 = -1, cur_r1 = -1;
+	float2 h0[TPX], h1[TPX];
+	auto eval_row = [&](int yy, float2 (&d)[TPX]) {
+		const RowAxis ra = s_rows[threadIdx.y * TROWS + yy];
+		if (ra.r0 != cur_r0 || ra.r1 != cur_r1) {
+			cur_r0 = ra.r0;
+			cur_r1 = ra.r1;
+			const float2 *g0 = grid + ra.r0 * gw;
+			const float2 *g1 = grid + ra.r1 * gw;
+#pragma unroll
+			for (int k = 0; k < TPX; ++k) {
+				float2 s00 = __ldg(g0 + sx[k]), s01 = __ldg(g0 + sx1[k]);
+				float2 s10 = __ldg(g1 + sx[k]), s11 = __ldg(g1 + sx1[k]);
+				h0[k].x = og_lerp_cv(s00.x, s01.x, a0[k], a1[k]);
+				h0[k].y = og_lerp_cv(s00.y, s01.y, a0[k], a1[k]);
+				h1[k].x = og_lerp_cv(s10.x, s11.x, a0[k], a1[k]);
+				h1[k].y = og_lerp_cv(s10.y, s11.y, a0[k], a1[k]);
+			}
+		}
+#pragma unroll
+		for (int k = 0; k < TPX; ++k) {
+			d[k].x = og_lerp_cv(h0[k].x, h1[k].x, ra.b0, ra.b1);
+			d[k].y = og_lerp_cv(h0[k].y, h1[k].y, ra.b0, ra.b1);
+		}
+	};
+
+	// ---- pass A: the map itself + bounding box of the sampling coordinates
+	float bx0 = 3.0e38f, by0 = 3.0e38f, bx1 = -3.0e38f, by1 = -3.0e38f;
+	{
+		float *mrow = WRITE_MAP ? p.map_out + ((size_t)ybeg * Wd + xa) * 2 : nullptr;
+		for (int yy = 0; yy < nrows; ++yy) {
+			float2 d[TPX];
+			eval_row(yy, d);
+			if (WRITE_MAP) {
+				if (map_al && na == 2) __stcs(reinterpret_cast<float4 *>(mrow), make_float4(d[0].x, d[0].y, d[1].x, d[1].y));
+				else {
+					if (na > 0) __stcs(reinterpret_cast<float2 *>(mrow), d[0]);
+					if (na > 1) __stcs(reinterpret_cast<float2 *>(mrow) + 1, d[1]);
+				}
+				if (map_al && nb == 2) __stcs(reinterpret_cast<float4 *>(mrow + 128), make_float4(d[2].x, d[2].y, d[3].x, d[3].y));
+				else {
+					if (nb > 0) __stcs(reinterpret_cast<float2 *>(mrow + 128), d[2]);
+					if (nb > 1) __stcs(reinterpret_cast<float2 *>(mrow + 128) + 1, d[3]);
+				}
+				mrow += (size_t)Wd * 2;
+			}
+#pragma unroll
+			for (int k = 0; k < TPX; ++k) {  // columns beyond Wd repeat column Wd-1: harmless
+				const float mx = SCALED ? __fmul_rn(d[k].x, scx) : d[k].x;
+				const float my = SCALED ? __fmul_rn(d[k].y, scy) : d[k].y;
+				bx0 = fminf(bx0, mx); bx1 = fmaxf(bx1, mx);
+				by0 = fminf(by0, my); by1 = fmaxf(by1, my);
+			}
+		}
+	}
+#pragma unroll
+	for (int o = 16; o > 0; o >>= 1) {
+		bx0 = fminf(bx0, __shfl_xor_sync(0xffffffffu, bx0, o));
+		by0 = fminf(by0, __shfl_xor_sync(0xffffffffu, by0, o));
+		bx1 = fmaxf(bx1, __shfl_xor_sync(0xffffffffu, bx1, o));
+		by1 = fmaxf(by1, __shfl_xor_sync(0xffffffffu, by1, o));
+	}
+	if (lane == 0 && bx0 <= bx1) {
+		// fminf / fmaxf drop NaNs; huge or NaN-only boxes fail the size test below
+		const bool sane = bx0 > -1.0e6f && bx1 < 1.0e6f && by0 > -1.0e6f && by1 < 1.0e6f;
+		atomicMin(&s_box[0], sane ? (int)floorf(bx0) : INT_MIN);
+		atomicMin(&s_box[1], sane ? (int)floorf(by0) : INT_MIN);
+		atomicMax(&s_box[2], sane ? (int)floorf(bx1) : INT_MAX);
+		atomicMax(&s_box[3], sane ? (int)floorf(by1) : INT_MAX);
+	}
+	__syncthreads();
+	// window [wx0, wx0 + WP) x [wy0, wy0 + WH): taps ix .. ix+1 of every sample plus one pixel of
+	// margin; wx0 is rounded down to 16 so that rows are copied as aligned 16-byte chunks
+	const long long bw = (long long)s_box[2] - s_box[0], bh = (long long)s_box[3] - s_box[1];
+	const bool box_ok = s_box[0] <= s_box[2] && bw < 4096 && bh < 4096;
+	const int wx0 = box_ok ? ((s_box[0] - 1) & ~15) : 0, wy0 = box_ok ? s_box[1] - 1 : 0;
+	const int WP = box_ok ? (((s_box[2] + 3 - wx0) + 15) & ~15) : 0, WH = box_ok ? s_box[3] + 3 - wy0 : 0;
+	const bool staged = box_ok && WP * WH <= WIN_BYTES && ((reinterpret_cast<uintptr_t>(src) | (uintptr_t)spitch) & 15) == 0;
+	if (staged) {
+		const int cpr = WP >> 4;  // 16-byte chunks per window row
+		for (int c = tid; c < cpr * WH; c += TBX * TBY) {
+			const int row = c / cpr, cx = (c - row * cpr) << 4;
+			const int y = wy0 + row, x = wx0 + cx;
+			// bytes of this chunk that lie inside the image; cp.async zero-fills the rest
+			const int valid = ((unsigned)y < (unsigned)H && x >= 0) ? max(0, min(16, W - x)) : 0;
+			og_cp_async16(s_win + row * WP + cx, valid > 0 ? src + y * spitch + x : src, valid);
+		}
+		asm volatile("cp.async.commit_group;" ::: "memory");
+		asm volatile("cp.async.wait_group 0;" ::: "memory");
+	}
+	__syncthreads();
+	if (!active) return;
+
+	// ---- pass B: image
+	uint8_t *orow = p.dst + (int64_t)ybeg * p.dst_pitch + xa;
+	for (int yy = 0; yy < nrows; ++yy) {
+		float2 d[TPX];
+		eval_row(yy, d);
+		float mx[TPX], my[TPX];
+#pragma unroll
+		for (int k = 0; k < TPX; ++k) {
+			mx[k] = SCALED ? __fmul_rn(d[k].x, scx) : d[k].x;
+			my[k] = SCALED ? __fmul_rn(d[k].y, scy) : d[k].y;
+		}
+		int v[TPX];
+		int ox[TPX], oy[TPX];
+		og_fix q[TPX];
+		bool all_in = staged;
+#pragma unroll
+		for (int k = 0; k < TPX; ++k) {
+			const int sxq = __float2int_rn(__fmul_rn(mx[k], 32.f));
+			const int syq = __float2int_rn(__fmul_rn(my[k], 32.f));
+			q[k].fx = sxq & 31;
+			q[k].fy = syq & 31;
+			ox[k] = (sxq >> 5) - wx0;
+			oy[k] = (syq >> 5) - wy0;
+			all_in = all_in && (unsigned)ox[k] < (unsigned)(WP - 1) && (unsigned)oy[k] < (unsigned)(WH - 1);
+		}
+		if (all_in) {
+			int p00[TPX], p01[TPX], p10[TPX], p11[TPX];
+#pragma unroll
+			for (int k = 0; k < TPX; ++k) {
+				const uint8_t *t = s_win + (oy[k] * WP + ox[k]);
+				p00[k] = t[0];
+				p01[k] = t[1];
+				p10[k] = t[WP];
+				p11[k] = t[WP + 1];
+			}
+#pragma unroll
+			for (int k = 0; k < TPX; ++k) v[k] = og_blend(q[k], p00[k], p01[k], p10[k], p11[k]);
+		} else {
+			og_sample_linear_batch<TPX>(src, H, W, spitch, mx, my, v);
+		}
+		store_quad(orow, v, na, nb, img_al);
+		orow += p.dst_pitch;
+	}
+}
+
 template <bool LINEAR, bool SCALED>
-void launch_variant(const PageParams &p, dim3 grid, dim3 block, cudaStream_t st) {
-	if (p.map_out != nullptr && p.dst != nullptr)
-		og_page_kernel<LINEAR, SCALED, true, true><<<grid, block, 0, st>>>(p);
-	else if (p.dst != nullptr)
-		og_page_kernel<LINEAR, SCALED, false, true><<<grid, block, 0, st>>>(p);
-	else
+void launch_variant(const PageParams &p, bool stage, dim3 grid, dim3 block, cudaStream_t st) {
+	if (p.map_out != nullptr && p.dst != nullptr) {
+		if (LINEAR && stage) og_page_staged_kernel<SCALED, true><<<grid, block, 0, st>>>(p);
+		else og_page_kernel<LINEAR, SCALED, true, true><<<grid, block, 0, st>>>(p);
+	} else if (p.dst != nullptr) {
+		if (LINEAR && stage) og_page_staged_kernel<SCALED, false><<<grid, block, 0, st>>>(p);
+		else og_page_kernel<LINEAR, SCALED, false, true><<<grid, block, 0, st>>>(p);
+	} else {
 		og_page_kernel<true, false, true, false><<<grid, block, 0, st>>>(p);
+	}
 }
 
 int launch_page(const PageParams &p, int interp, cudaStream_t st) {
@@ -216,12 +434,13 @@ int launch_page(const PageParams &p, int interp, cudaStream_t st) {
 	dim3 block(TBX, TBY);
 	dim3 grid((Wd + TILE_W - 1) / TILE_W, (Hd + TILE_H - 1) / TILE_H);
 	const bool scaled = !(p.scale_x == 1.f && p.scale_y == 1.f);
-	if (interp == OG_INTER_LINEAR) {
-		if (scaled) launch_variant<true, true>(p, grid, block, st);
-		else launch_variant<true, false>(p, grid, block, st);
+	const bool stage = (interp & OG_FLAG_STAGE_SMEM) != 0 || OG_PAGE_STAGE;
+	if ((interp & 0xff) == OG_INTER_LINEAR) {
+		if (scaled) launch_variant<true, true>(p, stage, grid, block, st);
+		else launch_variant<true, false>(p, stage, grid, block, st);
 	} else {
-		if (scaled) launch_variant<false, true>(p, grid, block, st);
-		else launch_variant<false, false>(p, grid, block, st);
+		if (scaled) launch_variant<false, true>(p, stage, grid, block, st);
+		else launch_variant<false, false>(p, stage, grid, block, st);
 	}
 	return og_check_launch("og_page_kernel");
 }
@@ -260,7 +479,8 @@ extern "C" int og_remap_page(const uint8_t *src, int H, int W, int64_t src_pitch
 	int rc = check_grid(grid, gh, gw, cell);
 	if (rc) return rc;
 	OG_REQUIRE(dst != nullptr || map_out != nullptr, OG_E_ARG, "both dst and map_out are NULL");
-	OG_REQUIRE(interp == OG_INTER_LINEAR || interp == OG_INTER_NEAREST, OG_E_ARG, "interp %d unsupported", interp);
+	OG_REQUIRE((interp & 0xff) == OG_INTER_LINEAR || (interp & 0xff) == OG_INTER_NEAREST, OG_E_ARG, "interp %d unsupported", interp);
+	OG_REQUIRE((interp & ~(0xff | OG_FLAG_STAGE_SMEM)) == 0, OG_E_ARG, "interp %d has unknown flag bits", interp);
 	if (dst != nullptr) {
 		OG_REQUIRE(src != nullptr && H > 0 && W > 0, OG_E_ARG, "src is NULL or empty (%d x %d)", W, H);
 		OG_REQUIRE(H < 32767 && W < 32767, OG_E_RANGE, "source %d x %d exceeds OpenCV's 32767 limit", W, H);

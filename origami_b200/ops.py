@@ -10,6 +10,8 @@ import torch
 from . import _lib
 from ._lib import LINE_DTYPE, OG_BIN_NONE, OG_BIN_OTSU, OG_BIN_SAUVOLA, OG_INTER_LINEAR, OG_INTER_NEAREST
 
+OG_FLAG_STAGE_SMEM = 0x100
+
 PITCH_ALIGN = 128
 
 

@@ -27,6 +27,7 @@ def main():
 		("extract map bbox", lambda: ops.extract_lines(src, g, cell, plan, strips, bbox, dense_map=mp)),
 		("line_steps", lambda: ops.line_steps(g, cell, ld, n_lines)),
 		("remap+map", lambda: ops.remap_page(src, g, cell, map_out=mp)),
+		("remap+map staged", lambda: ops.remap_page(src, g, cell, map_out=mp, interpolation=ops.OG_INTER_LINEAR | ops.OG_FLAG_STAGE_SMEM)),
 	]:
 		med, best = timeit(fn)
 		print("%-20s %s median %.3f ms best %.3f ms" % (name, os.environ.get("ORIGAMI_B200_LIB", "default")[-12:], med, best))

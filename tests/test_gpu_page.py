@@ -40,6 +40,12 @@ def test_remap_page_bit_exact(cuda, width, height, cell, kind):
 	# image-only mode gives the same pixels
 	dst2, _ = ops.remap_page(src, g, cell)
 	assert torch.equal(dst, dst2)
+	# ... and so does the shared-memory staged variant, with and without the map
+	map3 = torch.empty_like(map_out)
+	dst3, _ = ops.remap_page(src, g, cell, map_out=map3, interpolation=ops.OG_INTER_LINEAR | ops.OG_FLAG_STAGE_SMEM)
+	assert torch.equal(dst, dst3) and torch.equal(map3, map_out)
+	dst4, _ = ops.remap_page(src, g, cell, interpolation=ops.OG_INTER_LINEAR | ops.OG_FLAG_STAGE_SMEM)
+	assert torch.equal(dst, dst4)
 
 
 def test_remap_page_unaligned_buffers(cuda):
@@ -65,6 +71,9 @@ def test_dewarp_image_other_resolution(cuda, interp):
 	src = ops.to_device_image(labels, cuda)
 	dst, _ = ops.remap_page(src, g, cell, scale=(320 / width, 600 / height), interpolation=interp)
 	assert np.array_equal(dst.cpu().numpy(), want)
+	if interp == exact.INTER_LINEAR:
+		dst2, _ = ops.remap_page(src, g, cell, scale=(320 / width, 600 / height), interpolation=interp | ops.OG_FLAG_STAGE_SMEM)
+		assert torch.equal(dst, dst2)
 
 
 def test_page_argument_errors(cuda):
