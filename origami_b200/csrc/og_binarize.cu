@@ -26,6 +26,14 @@ __device__ __forceinline__ int reflect_index(int i, int n) {
 	return i >= n ? period - i : i;
 }
 
+// same map, but the common cases (inside, or one reflection) avoid the integer division
+__device__ __forceinline__ int reflect_index_fast(int i, int n) {
+	if ((unsigned)i < (unsigned)n) return i;
+	const int j = i < 0 ? -i : 2 * (n - 1) - i;
+	if ((unsigned)j < (unsigned)n) return j;
+	return reflect_index(i, n);
+}
+
 // ---------------------------------------------------------------------------------------
 // Otsu threshold from an exact 256-bin histogram (skimage 0.16.2 threshold_otsu on uint8:
 // bins = the integers [min, max], float64 cumulative sums, first argmax of
@@ -233,28 +241,47 @@ __device__ void sauvola_tile(const uint8_t *__restrict__ img, int h, int w, int6
 	unsigned int *v2 = v1 + ST_H * PW;
 	const int tid = threadIdx.x;
 	__syncthreads();
-	for (int k = tid; k < PH * PW; k += BTHREADS) {
-		const int py = k / PW, px = k - py * PW;
-		const int y = reflect_index(ty0 - rad + py, h), x = reflect_index(tx0 - rad + px, w);
-		tile[k] = __ldg(img + (int64_t)y * pitch + x);
+	{
+		// halo tile: a warp per padded row, lanes along x (no per-element division); only tiles
+		// that touch the image border pay for the reflect-101 index arithmetic
+		const int wid = tid >> 5, lane = tid & 31;
+		const bool interior = ty0 - rad >= 0 && ty0 + ST_H + rad <= h && tx0 - rad >= 0 && tx0 + ST_W + rad <= w;
+		for (int py = wid; py < PH; py += BTHREADS / 32) {
+			if (interior) {
+				const uint8_t *rowp = img + (int64_t)(ty0 - rad + py) * pitch + (tx0 - rad);
+				for (int px = lane; px < PW; px += 32) tile[py * PW + px] = __ldg(rowp + px);
+			} else {
+				const uint8_t *rowp = img + (int64_t)reflect_index_fast(ty0 - rad + py, h) * pitch;
+				for (int px = lane; px < PW; px += 32) tile[py * PW + px] = __ldg(rowp + reflect_index_fast(tx0 - rad + px, w));
+			}
+		}
 	}
 	__syncthreads();
-	// vertical running sums, one padded column per thread
-	for (int px = tid; px < PW; px += BTHREADS) {
-		unsigned int s1 = 0, s2 = 0;
-		for (int py = 0; py < win; ++py) {
-			const unsigned int v = tile[py * PW + px];
-			s1 += v;
-			s2 += v * v;
-		}
-		v1[px] = s1;
-		v2[px] = s2;
-		for (int y = 1; y < ST_H; ++y) {
-			const unsigned int a = tile[(y - 1) * PW + px], b = tile[(y + win - 1) * PW + px];
-			s1 += b - a;
-			s2 += b * b - a * a;
-			v1[y * PW + px] = s1;
-			v2[y * PW + px] = s2;
+	// vertical running sums: a thread owns a padded column and a band of output rows
+	{
+		const int groups = max(1, min(BTHREADS / PW, ST_H));
+		const int g = tid / PW, px0 = tid - g * PW;
+		const int band = (ST_H + groups - 1) / groups;
+		const int pstep = (PW <= BTHREADS) ? PW * groups : BTHREADS;  // PW > BTHREADS: several passes
+		if (g < groups) {
+			const int ybeg = g * band, yend = min(ST_H, ybeg + band);
+			for (int px = px0; px < PW; px += pstep) {
+				unsigned int s1 = 0, s2 = 0;
+				for (int py = ybeg; py < ybeg + win; ++py) {
+					const unsigned int v = tile[py * PW + px];
+					s1 += v;
+					s2 += v * v;
+				}
+				v1[ybeg * PW + px] = s1;
+				v2[ybeg * PW + px] = s2;
+				for (int y = ybeg + 1; y < yend; ++y) {
+					const unsigned int a = tile[(y - 1) * PW + px], b = tile[(y + win - 1) * PW + px];
+					s1 += b - a;
+					s2 += b * b - a * a;
+					v1[y * PW + px] = s1;
+					v2[y * PW + px] = s2;
+				}
+			}
 		}
 	}
 	__syncthreads();
@@ -271,6 +298,8 @@ __device__ void sauvola_tile(const uint8_t *__restrict__ img, int h, int w, int6
 			s2 += r2[xb + j];
 		}
 		const double n = (double)(win * win);
+		const unsigned int nwin = (unsigned int)(win * win);
+		const float c1 = (float)((1.0 - kk) / n), c2 = (float)(kk / (n * n * rr));
 		for (int j = 0; j < SEG; ++j) {
 			const int x = tx0 + xb + j;
 			if (j > 0) {
@@ -278,14 +307,27 @@ __device__ void sauvola_tile(const uint8_t *__restrict__ img, int h, int w, int6
 				s2 += r2[xb + j + win - 1] - r2[xb + j - 1];
 			}
 			if (x < w) {
-				const double m = __ddiv_rn((double)s1, n);
-				const double g2 = __ddiv_rn((double)s2, n);
-				double var = __dsub_rn(g2, __dmul_rn(m, m));
-				var = var > 0.0 ? var : 0.0;
-				const double s = __dsqrt_rn(var);
-				const double t = __dmul_rn(m, __dadd_rn(1.0, __dmul_rn(kk, __dsub_rn(__ddiv_rn(s, rr), 1.0))));
 				const int pv = tile[(row + rad) * PW + xb + j + rad];
-				out[(int64_t)y * out_pitch + x] = ((double)pv > t) ? 255 : 0;
+				// Screening in fp32: t = (A/n)(1 - k + k sqrt(nB - A^2)/(n r)) with the variance
+				// numerator D = nB - A^2 formed exactly in 64-bit integers (no cancellation).  Its
+				// error is < 2e-4 gray levels, so a pixel further than 1e-3 from the estimate is
+				// decided by it; the few others take the float64 sequence of the reference.
+				const unsigned long long D = (unsigned long long)nwin * s2 - (unsigned long long)s1 * s1;
+				const float ta = __fmul_rn((float)s1, __fadd_rn(c1, __fmul_rn(c2, sqrtf((float)D))));
+				const float diff = __fsub_rn((float)pv, ta);
+				bool white;
+				if (fabsf(diff) > 1.0e-3f) {
+					white = diff > 0.f;
+				} else {
+					const double m = __ddiv_rn((double)s1, n);
+					const double g2 = __ddiv_rn((double)s2, n);
+					double var = __dsub_rn(g2, __dmul_rn(m, m));
+					var = var > 0.0 ? var : 0.0;
+					const double s = __dsqrt_rn(var);
+					const double t = __dmul_rn(m, __dadd_rn(1.0, __dmul_rn(kk, __dsub_rn(__ddiv_rn(s, rr), 1.0))));
+					white = (double)pv > t;
+				}
+				out[(int64_t)y * out_pitch + x] = white ? 255 : 0;
 			}
 		}
 	}
