@@ -190,6 +190,17 @@ int og_argmax_labels(const float *probs, int M, int C, int h, int w,
 int og_class_masks(const uint8_t *labels, int h, int w, int64_t pitch,
 	uint8_t *masks_out, const uint8_t *mask_values, int n_mask, void *stream);
 
+/* A20  Regions.binarized helpers -- origami/batch/detect/layout.py:157-186.
+ * og_label_mask_ne: out = 255 where labels != background else 0 (layout.py:175-176, the separator mask
+ * that is then dewarped with og_remap_page(OG_INTER_NEAREST)).
+ * og_or_dilate3: out (h, w) fp32 = 1.0 where bin != 0 or the 3x3 neighbourhood of mask holds a non-zero
+ * (skimage binary_dilation with square(3), zero outside the image), else 0.0 (layout.py:179-186);
+ * mask may be NULL. */
+int og_label_mask_ne(const uint8_t *labels, int h, int w, int64_t pitch, int background,
+	uint8_t *out, int64_t out_pitch, void *stream);
+int og_or_dilate3(const uint8_t *bin, int64_t bin_pitch, const uint8_t *mask, int64_t mask_pitch,
+	int h, int w, float *out, void *stream);
+
 /* A11  warpAffine stage of Line._extract_deskewed -- origami/core/block.py:155-172
  * (--do-not-dewarp path; the cairo polygon cut-out that follows is not reproduced).
  * M is a HOST 2x3 float64 forward matrix as returned by cv2.getAffineTransform. */

@@ -523,3 +523,34 @@ def warp_affine_linear(src, M, width, height, border=0):
 	acc = ((32 - fx) * (32 - fy) * p00 + fx * (32 - fy) * p01
 		+ (32 - fx) * fy * p10 + fx * fy * p11)
 	return ((acc + 512) >> 10).astype(np.uint8)
+
+
+# --------------------------------------------------------------------------------------
+# A20  Regions.binarized            origami/batch/detect/layout.py:157-186
+# --------------------------------------------------------------------------------------
+
+def dilate3(mask):
+	"""skimage.morphology.binary_dilation(mask, square(3)): 3x3 maximum, False outside."""
+	m = np.asarray(mask, dtype=bool)
+	p = np.pad(m, 1, mode="constant", constant_values=False)
+	out = np.zeros_like(m)
+	for dy in range(3):
+		for dx in range(3):
+			out |= p[dy:dy + m.shape[0], dx:dx + m.shape[1]]
+	return out
+
+
+def regions_binarized(page, grid, s, median_line_height, separator_labels=()):
+	"""Regions.binarized: Sauvola (window from the median line height) on the dewarped page, OR the
+	dilated NEAREST-dewarped separator masks, as float32."""
+	gray = dewarp_page(page, grid, s)
+	window_size = int(median_line_height) // 2
+	if window_size % 2 == 0:
+		window_size += 1
+	window_size = max(window_size, 3)
+	binary = gray > threshold_sauvola(gray, window_size)
+	for labels, bg in separator_labels:
+		mask = (np.asarray(labels) != bg).astype(np.uint8) * 255
+		mask = dewarp_image(mask, (page.shape[1], page.shape[0]), grid, s, INTER_NEAREST)
+		binary = np.logical_or(binary, dilate3(mask > 0))
+	return binary.astype(np.float32)

@@ -96,6 +96,31 @@ __global__ void __launch_bounds__(256) og_masks_kernel(
 	for (int j = 0; j < n_mask; ++j) masks[(int64_t)j * npix + i] = (v == mv.v[j]);
 }
 
+// Regions.binarized helpers (origami/batch/detect/layout.py:157-186)
+__global__ void __launch_bounds__(256) og_label_ne_kernel(
+	const uint8_t *__restrict__ labels, int h, int w, int64_t pitch, int bg, uint8_t *__restrict__ out, int64_t out_pitch) {
+	const int x = blockIdx.x * blockDim.x + threadIdx.x, y = blockIdx.y;
+	if (x < w && y < h) out[(int64_t)y * out_pitch + x] = labels[(int64_t)y * pitch + x] != bg ? 255 : 0;
+}
+
+__global__ void __launch_bounds__(256) og_or_dilate3_kernel(
+	const uint8_t *__restrict__ bin, int64_t bin_pitch, const uint8_t *__restrict__ mask, int64_t mask_pitch,
+	int h, int w, float *__restrict__ out) {
+	const int x = blockIdx.x * blockDim.x + threadIdx.x, y = blockIdx.y;
+	if (x >= w || y >= h) return;
+	bool on = bin[(int64_t)y * bin_pitch + x] != 0;
+	if (!on && mask != nullptr) {
+		// skimage binary_dilation with square(3): 3x3 maximum, outside the image counts as 0
+		for (int dy = -1; dy <= 1 && !on; ++dy) {
+			const int yy = y + dy;
+			if ((unsigned)yy >= (unsigned)h) continue;
+			const uint8_t *r = mask + (int64_t)yy * mask_pitch;
+			on = (x > 0 && r[x - 1]) || r[x] || (x + 1 < w && r[x + 1]);
+		}
+	}
+	out[(int64_t)y * w + x] = on ? 1.f : 0.f;
+}
+
 struct AffineParams {
 	double m00, m01, b1, m10, m11, b2;  // inverse map
 };
@@ -187,4 +212,23 @@ extern "C" int og_warp_affine(const uint8_t *src, int H, int W, int64_t src_pitc
 	og_warp_affine_kernel<<<grid, block, 0, (cudaStream_t)stream>>>(src, H, W, src_pitch, a, dst, width, height, dst_pitch,
 		border_value & 255);
 	return og_check_launch("og_warp_affine_kernel");
+}
+
+extern "C" int og_label_mask_ne(const uint8_t *labels, int h, int w, int64_t pitch, int background,
+	uint8_t *out, int64_t out_pitch, void *stream) {
+	OG_REQUIRE(labels != nullptr && out != nullptr, OG_E_ARG, "NULL pointer");
+	OG_REQUIRE(h > 0 && w > 0 && pitch >= w && out_pitch >= w && h < 65536, OG_E_ARG, "image %d x %d / pitch invalid", w, h);
+	dim3 block(256), grid((w + 255) / 256, h);
+	og_label_ne_kernel<<<grid, block, 0, (cudaStream_t)stream>>>(labels, h, w, pitch, background, out, out_pitch);
+	return og_check_launch("og_label_ne_kernel");
+}
+
+extern "C" int og_or_dilate3(const uint8_t *bin, int64_t bin_pitch, const uint8_t *mask, int64_t mask_pitch,
+	int h, int w, float *out, void *stream) {
+	OG_REQUIRE(bin != nullptr && out != nullptr, OG_E_ARG, "NULL pointer");
+	OG_REQUIRE(h > 0 && w > 0 && bin_pitch >= w && (mask == nullptr || mask_pitch >= w) && h < 65536, OG_E_ARG,
+		"image %d x %d / pitch invalid", w, h);
+	dim3 block(256), grid((w + 255) / 256, h);
+	og_or_dilate3_kernel<<<grid, block, 0, (cudaStream_t)stream>>>(bin, bin_pitch, mask, mask_pitch, h, w, out);
+	return og_check_launch("og_or_dilate3_kernel");
 }

@@ -309,3 +309,28 @@ def warp_affine(src, M, width, height, border_value=0):
 	_lib.call("og_warp_affine", src.data_ptr(), int(src.shape[0]), int(src.shape[1]), src.stride(0),
 		Mh.ctypes.data, dst.data_ptr(), width, height, dst.stride(0), int(border_value), _stream())
 	return dst
+
+
+def label_mask_ne(labels, background):
+	"""(labels != background) * 255 on a device label map."""
+	_require_cuda()
+	_check_u8_image(labels, "labels")
+	h, w = int(labels.shape[0]), int(labels.shape[1])
+	out = alloc_image(h, w, labels.device)
+	_lib.call("og_label_mask_ne", labels.data_ptr(), h, w, labels.stride(0), int(background), out.data_ptr(), out.stride(0), _stream())
+	return out
+
+
+def or_dilate3(binary, mask=None):
+	"""float32 (h, w): binary != 0 OR 3x3-dilated mask != 0."""
+	_require_cuda()
+	_check_u8_image(binary, "binary")
+	h, w = int(binary.shape[0]), int(binary.shape[1])
+	if mask is not None:
+		_check_u8_image(mask, "mask")
+		if tuple(mask.shape) != (h, w):
+			raise ValueError("mask shape differs from the binary image")
+	out = torch.empty((h, w), dtype=torch.float32, device=binary.device)
+	_lib.call("og_or_dilate3", binary.data_ptr(), binary.stride(0), _ptr(mask), mask.stride(0) if mask is not None else 0,
+		h, w, out.data_ptr(), _stream())
+	return out

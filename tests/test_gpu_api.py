@@ -218,3 +218,13 @@ def test_full_size_page_against_opencv(cuda):
 	o1 = ops.binarize_strips(torch.from_numpy(a).to(cuda), plan, ops.OG_BIN_OTSU)
 	o2 = ops.binarize_strips(o1, plan, ops.OG_BIN_OTSU)
 	assert torch.equal(o1, o2)
+
+
+def test_regions_binarized(small):
+	from origami_b200.batch.detect.layout import regions_binarized, sauvola_window
+	assert [sauvola_window(v) for v in (4, 20, 31, 60)] == [3, 11, 15, 31]
+	labels = (synth.make_labels(350, 250, seed=9) == 2).astype(np.uint8) * 3  # sparse "separator" pixels, bg = 0
+	got = regions_binarized(small.pg, 31, [(labels, 0)])
+	want = exact.regions_binarized(small.page, small.g, small.s, 31, [(labels, 0)])
+	assert got.dtype == np.float32 and np.array_equal(got, want)
+	assert np.array_equal(regions_binarized(small.pg, 20), exact.regions_binarized(small.page, small.g, small.s, 20))

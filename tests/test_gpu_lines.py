@@ -138,3 +138,68 @@ def test_empty_and_degenerate_lines(cuda):
 	plan = ops.line_steps(g, 25, ops.lines_to_device(la, cuda), 1)
 	want = exact.warped_grid(dense, rec["p"], rec["right"], rec["up"], ysteps=48)
 	assert plan.steps.cpu().numpy()[0].tolist() == [want.shape[1], want.shape[0]]
+
+
+def _check_lines(cuda, page, grid, dense, recs, use_map, cell=25):
+	g = torch.from_numpy(grid).to(cuda)
+	src = ops.to_device_image(page, cuda)
+	dmap = ops.expand_map(g, cell) if use_map else None
+	plan = ops.line_steps(g, cell, ops.lines_to_device(ops.pack_lines(recs), cuda), len(recs))
+	offs = plan.pix_offsets.cpu().numpy()
+	out = torch.zeros((int(offs[-1]),), dtype=torch.uint8, device=cuda)
+	ops.extract_lines(src, g, cell, plan, out, dense_map=dmap)
+	out = out.cpu().numpy()
+	for i, r in enumerate(recs):
+		wg = exact.warped_grid(dense, r["p"], r["right"], r["up"], xsteps=r.get("xsteps"), ysteps=r.get("ysteps"),
+			xres=r.get("xres", 1), yres=r.get("yres", 1))
+		want = exact.remap_linear(page, wg)[::-1]
+		assert offs[i + 1] - offs[i] == want.size, (i, want.shape)
+		assert np.array_equal(out[offs[i]:offs[i + 1]].reshape(want.shape), want), i
+
+
+@pytest.mark.parametrize("use_map", [False, True])
+def test_unusual_lines_take_the_general_paths(cuda, use_map):
+	"""Steep, very tall, very high (more rows than the row table holds), upsampled, tiny and
+	partly off-page lines: the staged engine must fall back to its unstaged path where the node
+	region does not fit, and both engines must still match the oracle bit for bit."""
+	page, grid, dense, _ = _setup(cuda, seed=13)
+	Hd, Wd = dense.shape[:2]
+	recs = [
+		dict(p=[60.0, 400.0], right=[180.0, 170.0], up=[14.0, -15.0], ysteps=48),            # 43 degrees
+		dict(p=[300.0, 700.0], right=[120.0, -3.0], up=[2.0, -420.0], ysteps=48),            # 420 px tall
+		dict(p=[100.0, 300.0], right=[90.0, 1.0], up=[0.5, -60.0], ysteps=200),              # ysteps > row table
+		dict(p=[200.0, 200.0], right=[40.0, 0.0], up=[0.0, -12.0], xres=3.0, yres=3.0),      # upsampled, derived steps
+		dict(p=[350.5, 120.25], right=[3.0, 0.0], up=[0.0, -2.0], ysteps=5),                 # tiny
+		dict(p=[-30.0, 40.0], right=[200.0, 2.0], up=[1.0, -70.0], ysteps=48),               # leaves the page (extrapolation)
+		dict(p=[Wd - 90.0, Hd - 5.0], right=[150.0, 0.0], up=[0.0, -40.0], ysteps=48),       # beyond the right / bottom edge
+		dict(p=[120.0, 500.0], right=[-100.0, 4.0], up=[1.0, 30.0], ysteps=33),              # reversed directions
+		dict(p=[64.0, 256.0], right=[128.0, 0.0], up=[0.0, -32.0], ysteps=48, xsteps=300),   # fixed xsteps, integral lattice
+	]
+	_check_lines(cuda, page, grid, dense, recs, use_map)
+
+
+def test_capacity_guard_skips_lines_that_do_not_fit(cuda):
+	page, grid, dense, lines = _setup(cuda)
+	g = torch.from_numpy(grid).to(cuda)
+	src = ops.to_device_image(page, cuda)
+	recs = _records(lines[:8], ysteps=48)
+	plan = ops.line_steps(g, 25, ops.lines_to_device(ops.pack_lines(recs), cuda), len(recs))
+	offs = plan.pix_offsets.cpu().numpy()
+	cap = int(offs[5])  # room for the first five strips only
+	for dmap in (None, ops.expand_map(g, 25)):
+		out = torch.full((int(offs[-1]),), 7, dtype=torch.uint8, device=cuda)
+		ops.extract_lines(src, g, 25, plan, out[:cap], dense_map=dmap)
+		out = out.cpu().numpy()
+		assert (out[cap:] == 7).all()  # nothing written past the capacity
+		want = exact.dewarped_line_image(page, dense, lines[4]["p"], lines[4]["right"], lines[4]["up"], 48)
+		assert np.array_equal(out[offs[4]:offs[5]].reshape(want.shape), want)
+
+
+def test_degenerate_coordinates_are_flagged(cuda):
+	_, grid, dense, _ = _setup(cuda)
+	g = torch.from_numpy(grid).to(cuda)
+	recs = [dict(p=[float("nan"), 10.0], right=[50.0, 0.0], up=[0.0, -20.0]),
+		dict(p=[10.0, 10.0], right=[50.0, 0.0], up=[0.0, -20.0])]
+	plan = ops.line_steps(g, 25, ops.lines_to_device(ops.pack_lines(recs), cuda), 2)
+	steps = plan.steps.cpu().numpy()
+	assert steps[0].tolist() == [0, 0] and steps[1].min() >= 2

@@ -248,3 +248,10 @@ def test_warp_affine_is_cv2():
 def test_grid_bbox_convention():
 	g = np.array([[[1.2, 5.0], [7.9, -0.5]]], dtype=np.float32)
 	assert exact.grid_bbox(g) == (1, -1, 8, 5)
+
+
+def test_dilate3_is_3x3_maximum_with_zero_border():
+	rng = np.random.default_rng(2)
+	m = rng.random((23, 31)) < 0.05
+	want = cv2.dilate(m.astype(np.uint8), np.ones((3, 3), np.uint8), borderType=cv2.BORDER_CONSTANT, borderValue=0) > 0
+	assert np.array_equal(exact.dilate3(m), want)
