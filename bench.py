@@ -44,7 +44,7 @@ def parse_args():
 	ap.add_argument("--page-sets", type=int, default=3, help="distinct resident pages rotated through")
 	ap.add_argument("--lines", type=int, default=N_LINES)
 	ap.add_argument("--binarize", default="otsu", choices=["none", "otsu", "sauvola"])
-	ap.add_argument("--e2e-steps", type=int, default=4)
+	ap.add_argument("--e2e-steps", type=int, default=6)
 	ap.add_argument("--no-cpu-baseline", action="store_true")
 	ap.add_argument("--no-e2e", action="store_true")
 	return ap.parse_args()
@@ -310,8 +310,8 @@ def run_e2e(args, inputs, device, n_steps):
 		strips = ex.extract_arrays(ldict)
 		return dewarped, strips
 
-	page, grid_hv, lines = inputs[0]
-	dw, strips = one(page, grid_hv, lines)  # warm-up
+	for page, grid_hv, lines in inputs:  # warm-up: every page once (allocator and pinned-memory caches)
+		dw, strips = one(page, grid_hv, lines)
 	strip_bytes = int(sum(s.size for _, s in strips))
 	torch.cuda.synchronize()
 	t0 = time.perf_counter()
@@ -363,9 +363,22 @@ def run_ours(args):
 		n_launch += run_step(sets[i % len(sets)], args, events)
 	end.record()
 	torch.cuda.synchronize()
+	ms_timed = start.elapsed_time(end)
+	if sampler and ms_timed < 250.0:
+		# the timed region is too short for a meaningful clock sample at NVML's rate: keep the same
+		# load running (untimed) until 0.25 s of it have been observed
+		t_end = time.perf_counter() + (250.0 - ms_timed) * 1e-3
+		i = 0
+		while time.perf_counter() < t_end:
+			for _ in range(8):
+				run_step(sets[i % len(sets)], args)
+				i += 1
+			torch.cuda.synchronize()
 	clocks = sampler.stop() if sampler else None
+	if clocks is not None:
+		clocks["window"] = "timed region + identical untimed steps up to 0.25 s" if ms_timed < 250.0 else "timed region"
 	shard.barrier()
-	ms_local = start.elapsed_time(end)
+	ms_local = ms_timed
 	ms = shard.max_over_ranks(ms_local, device)
 
 	# per-kernel device time inside the timed region
