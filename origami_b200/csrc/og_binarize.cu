@@ -188,19 +188,38 @@ __global__ void __launch_bounds__(BTHREADS) og_otsu_strips_kernel(
 // ---------------------------------------------------------------------------------------
 // page, Otsu: global histogram (scratch), then threshold + apply
 // ---------------------------------------------------------------------------------------
+// A CTA walks whole rows (grid-stride); a row is read as 16-byte vectors between an unaligned
+// head and tail, so no per-pixel division is needed and loads are 128 bit.
 __global__ void __launch_bounds__(BTHREADS) og_hist_kernel(
 	const uint8_t *__restrict__ src, int h, int w, int64_t pitch, unsigned int *__restrict__ hist_out) {
-	__shared__ unsigned int hist[256];
-	for (int k = threadIdx.x; k < 256; k += BTHREADS) hist[k] = 0;
+	__shared__ unsigned int rep[256 * HREP];
+	for (int k = threadIdx.x; k < 256 * HREP; k += BTHREADS) rep[k] = 0;
 	__syncthreads();
-	const int64_t total = (int64_t)h * w;
-	for (int64_t i = (int64_t)blockIdx.x * BTHREADS + threadIdx.x; i < total; i += (int64_t)gridDim.x * BTHREADS) {
-		const int y = (int)(i / w), x = (int)(i - (int64_t)y * w);
-		atomicAdd(&hist[src[(int64_t)y * pitch + x]], 1u);
+	const int r = threadIdx.x & (HREP - 1);
+	for (int y = blockIdx.x; y < h; y += gridDim.x) {
+		const uint8_t *g = src + (int64_t)y * pitch;
+		const int head = min(w, (int)((16 - (reinterpret_cast<uintptr_t>(g) & 15)) & 15));
+		const int nvec = (w - head) / 16;
+		for (int i = threadIdx.x; i < head; i += BTHREADS) atomicAdd(&rep[g[i] * HREP + r], 1u);
+		const uint4 *gv = reinterpret_cast<const uint4 *>(g + head);
+		for (int i = threadIdx.x; i < nvec; i += BTHREADS) {
+			const uint4 v = __ldg(gv + i);
+			const unsigned int wds[4] = {v.x, v.y, v.z, v.w};
+#pragma unroll
+			for (int q = 0; q < 4; ++q) {
+#pragma unroll
+				for (int b = 0; b < 4; ++b) atomicAdd(&rep[((wds[q] >> (8 * b)) & 255u) * HREP + r], 1u);
+			}
+		}
+		for (int i = head + nvec * 16 + threadIdx.x; i < w; i += BTHREADS) atomicAdd(&rep[g[i] * HREP + r], 1u);
 	}
 	__syncthreads();
-	for (int k = threadIdx.x; k < 256; k += BTHREADS)
-		if (hist[k]) atomicAdd(hist_out + k, hist[k]);
+	for (int k = threadIdx.x; k < 256; k += BTHREADS) {
+		unsigned int sum = 0;
+#pragma unroll
+		for (int q = 0; q < HREP; ++q) sum += rep[k * HREP + q];
+		if (sum) atomicAdd(hist_out + k, sum);
+	}
 }
 
 __global__ void __launch_bounds__(BTHREADS) og_otsu_apply_kernel(
@@ -218,11 +237,34 @@ __global__ void __launch_bounds__(BTHREADS) og_otsu_apply_kernel(
 		}
 	}
 	__syncthreads();
-	const int t = s_t;
-	const int64_t total = (int64_t)h * w;
-	for (int64_t i = (int64_t)blockIdx.x * BTHREADS + threadIdx.x; i < total; i += (int64_t)gridDim.x * BTHREADS) {
-		const int y = (int)(i / w), x = (int)(i - (int64_t)y * w);
-		dst[(int64_t)y * dst_pitch + x] = src[(int64_t)y * src_pitch + x] > t ? 255 : 0;
+	const unsigned int t = (unsigned int)s_t;
+	for (int y = blockIdx.x; y < h; y += gridDim.x) {
+		const uint8_t *g = src + (int64_t)y * src_pitch;
+		uint8_t *o = dst + (int64_t)y * dst_pitch;
+		const int head = min(w, (int)((16 - (reinterpret_cast<uintptr_t>(g) & 15)) & 15));
+		const int nvec = (w - head) / 16;
+		const bool out_al = ((reinterpret_cast<uintptr_t>(o + head)) & 15) == 0;
+		for (int i = threadIdx.x; i < head; i += BTHREADS) o[i] = g[i] > t ? 255 : 0;
+		const uint4 *gv = reinterpret_cast<const uint4 *>(g + head);
+		for (int i = threadIdx.x; i < nvec; i += BTHREADS) {
+			const uint4 v = __ldg(gv + i);
+			unsigned int wds[4] = {v.x, v.y, v.z, v.w};
+#pragma unroll
+			for (int q = 0; q < 4; ++q) {
+				unsigned int m = 0;
+#pragma unroll
+				for (int b = 0; b < 4; ++b) m |= (((wds[q] >> (8 * b)) & 255u) > t ? 255u : 0u) << (8 * b);
+				wds[q] = m;
+			}
+			if (out_al) {
+				__stcs(reinterpret_cast<uint4 *>(o + head) + i, make_uint4(wds[0], wds[1], wds[2], wds[3]));
+			} else {
+				uint8_t *ob = o + head + i * 16;
+#pragma unroll
+				for (int q = 0; q < 16; ++q) ob[q] = (uint8_t)(wds[q >> 2] >> (8 * (q & 3)));
+			}
+		}
+		for (int i = head + nvec * 16 + threadIdx.x; i < w; i += BTHREADS) o[i] = g[i] > t ? 255 : 0;
 	}
 }
 
