@@ -13,7 +13,8 @@
 namespace {
 
 constexpr int BTHREADS = 256;
-constexpr int ST_W = 64;  // Sauvola output tile (== line chunk width)
+constexpr int ST_W = 128;  // Sauvola output tile on pages: 32 rows x 128 columns
+constexpr int ST_WS = 64;  // ... on strips: one 64-column line chunk
 constexpr int ST_H = 32;
 constexpr int MAX_WINDOW = 127;
 
@@ -273,21 +274,24 @@ __global__ void __launch_bounds__(BTHREADS) og_otsu_apply_kernel(
 // reflect-padded centred window, m = S1/w^2, s = sqrt(max(S2/w^2 - m*m, 0)),
 // t = m * (1 + k * ((s / r) - 1)) in float64).  Window sums are exact integers.
 // ---------------------------------------------------------------------------------------
+template <int TW>
 __device__ void sauvola_tile(const uint8_t *__restrict__ img, int h, int w, int64_t pitch,
 	uint8_t *__restrict__ out, int64_t out_pitch, int ty0, int tx0, int win, double kk, double rr,
 	unsigned char *smem) {
 	const int rad = win / 2;
-	const int PW = ST_W + 2 * rad, PH = ST_H + 2 * rad;
-	uint8_t *tile = smem;                                          // PH x PW
-	unsigned int *v1 = reinterpret_cast<unsigned int *>(smem + ((PH * PW + 15) & ~15));  // ST_H x PW
-	unsigned int *v2 = v1 + ST_H * PW;
+	const int PW = TW + 2 * rad, PH = ST_H + 2 * rad;
+	const int PV = PW | 1;  // odd row stride: lanes that own different rows hit different banks
+	uint8_t *tile = smem;                                          // PH x PW halo tile
+	unsigned int *v1 = reinterpret_cast<unsigned int *>(smem + ((PH * PW + 15) & ~15));  // ST_H x PV vertical sums of p
+	unsigned int *v2 = v1 + ST_H * PV;                                                   // ... of p^2
+	uint8_t *otile = reinterpret_cast<uint8_t *>(v2 + ST_H * PV);  // ST_H x (TW + 16) results
 	const int tid = threadIdx.x;
+	const int wid = tid >> 5, lane = tid & 31;
 	__syncthreads();
 	{
 		// halo tile: a warp per padded row, lanes along x (no per-element division); only tiles
 		// that touch the image border pay for the reflect-101 index arithmetic
-		const int wid = tid >> 5, lane = tid & 31;
-		const bool interior = ty0 - rad >= 0 && ty0 + ST_H + rad <= h && tx0 - rad >= 0 && tx0 + ST_W + rad <= w;
+		const bool interior = ty0 - rad >= 0 && ty0 + ST_H + rad <= h && tx0 - rad >= 0 && tx0 + TW + rad <= w;
 		for (int py = wid; py < PH; py += BTHREADS / 32) {
 			if (interior) {
 				const uint8_t *rowp = img + (int64_t)(ty0 - rad + py) * pitch + (tx0 - rad);
@@ -314,26 +318,25 @@ __device__ void sauvola_tile(const uint8_t *__restrict__ img, int h, int w, int6
 					s1 += v;
 					s2 += v * v;
 				}
-				v1[ybeg * PW + px] = s1;
-				v2[ybeg * PW + px] = s2;
+				v1[ybeg * PV + px] = s1;
+				v2[ybeg * PV + px] = s2;
 				for (int y = ybeg + 1; y < yend; ++y) {
 					const unsigned int a = tile[(y - 1) * PW + px], b = tile[(y + win - 1) * PW + px];
 					s1 += b - a;
 					s2 += b * b - a * a;
-					v1[y * PW + px] = s1;
-					v2[y * PW + px] = s2;
+					v1[y * PV + px] = s1;
+					v2[y * PV + px] = s2;
 				}
 			}
 		}
 	}
 	__syncthreads();
-	// horizontal running sums: thread = (row, 8-column segment)
-	constexpr int SEG = ST_W * ST_H / BTHREADS;  // 8
-	const int row = tid / (ST_W / SEG), seg = tid % (ST_W / SEG);
-	const int y = ty0 + row;
-	if (y < h) {
-		const unsigned int *r1 = v1 + row * PW, *r2 = v2 + row * PW;
-		const int xb = seg * SEG;
+	// horizontal running sums + threshold: lane = row (conflict-free with the odd stride), warp =
+	// a run of SEG consecutive columns, so the window slides SEG - 1 times per initial sum
+	{
+		constexpr int SEG = TW / (BTHREADS / 32);
+		const int row = lane, xb = wid * SEG;
+		const unsigned int *r1 = v1 + row * PV, *r2 = v2 + row * PV;
 		unsigned int s1 = 0, s2 = 0;
 		for (int j = 0; j < win; ++j) {
 			s1 += r1[xb + j];
@@ -343,42 +346,65 @@ __device__ void sauvola_tile(const uint8_t *__restrict__ img, int h, int w, int6
 		const unsigned int nwin = (unsigned int)(win * win);
 		const float c1 = (float)((1.0 - kk) / n), c2 = (float)(kk / (n * n * rr));
 		for (int j = 0; j < SEG; ++j) {
-			const int x = tx0 + xb + j;
 			if (j > 0) {
 				s1 += r1[xb + j + win - 1] - r1[xb + j - 1];
 				s2 += r2[xb + j + win - 1] - r2[xb + j - 1];
 			}
-			if (x < w) {
-				const int pv = tile[(row + rad) * PW + xb + j + rad];
-				// Screening in fp32: t = (A/n)(1 - k + k sqrt(nB - A^2)/(n r)) with the variance
-				// numerator D = nB - A^2 formed exactly in 64-bit integers (no cancellation).  Its
-				// error is < 2e-4 gray levels, so a pixel further than 1e-3 from the estimate is
-				// decided by it; the few others take the float64 sequence of the reference.
-				const unsigned long long D = (unsigned long long)nwin * s2 - (unsigned long long)s1 * s1;
-				const float ta = __fmul_rn((float)s1, __fadd_rn(c1, __fmul_rn(c2, sqrtf((float)D))));
-				const float diff = __fsub_rn((float)pv, ta);
-				bool white;
-				if (fabsf(diff) > 1.0e-3f) {
-					white = diff > 0.f;
+			const int pv = tile[(row + rad) * PW + xb + j + rad];
+			// Screening in fp32: t = (A/n)(1 - k + k sqrt(nB - A^2)/(n r)) with the variance
+			// numerator D = nB - A^2 formed exactly in 64-bit integers (no cancellation).  Its
+			// error is < 2e-4 gray levels, so a pixel further than 1e-3 from the estimate is
+			// decided by it; the few others take the float64 sequence of the reference.
+			const unsigned long long D = (unsigned long long)nwin * s2 - (unsigned long long)s1 * s1;
+			const float ta = __fmul_rn((float)s1, __fadd_rn(c1, __fmul_rn(c2, sqrtf((float)D))));
+			const float diff = __fsub_rn((float)pv, ta);
+			bool white;
+			if (fabsf(diff) > 1.0e-3f) {
+				white = diff > 0.f;
+			} else {
+				const double m = __ddiv_rn((double)s1, n);
+				const double g2 = __ddiv_rn((double)s2, n);
+				double var = __dsub_rn(g2, __dmul_rn(m, m));
+				var = var > 0.0 ? var : 0.0;
+				const double sd = __dsqrt_rn(var);
+				const double t = __dmul_rn(m, __dadd_rn(1.0, __dmul_rn(kk, __dsub_rn(__ddiv_rn(sd, rr), 1.0))));
+				white = (double)pv > t;
+			}
+			otile[row * (TW + 16) + xb + j] = white ? 255 : 0;
+		}
+	}
+	__syncthreads();
+	// coalesced write-out: 16-byte chunks when the destination allows it, else one byte per lane
+	{
+		const int rows = min(ST_H, h - ty0), cols = min(TW, w - tx0);
+		const bool al = ((reinterpret_cast<uintptr_t>(out) | (uintptr_t)out_pitch | (uintptr_t)tx0) & 15) == 0;
+		if (al) {
+			constexpr int CPR = TW / 16;
+			for (int c = tid; c < ST_H * CPR; c += BTHREADS) {
+				const int row = c / CPR, cx = (c % CPR) * 16;
+				if (row >= rows || cx >= cols) continue;
+				uint8_t *o = out + (int64_t)(ty0 + row) * out_pitch + tx0 + cx;
+				const uint8_t *t = otile + row * (TW + 16) + cx;
+				if (cx + 16 <= cols) {
+					*reinterpret_cast<uint4 *>(o) = *reinterpret_cast<const uint4 *>(t);
 				} else {
-					const double m = __ddiv_rn((double)s1, n);
-					const double g2 = __ddiv_rn((double)s2, n);
-					double var = __dsub_rn(g2, __dmul_rn(m, m));
-					var = var > 0.0 ? var : 0.0;
-					const double s = __dsqrt_rn(var);
-					const double t = __dmul_rn(m, __dadd_rn(1.0, __dmul_rn(kk, __dsub_rn(__ddiv_rn(s, rr), 1.0))));
-					white = (double)pv > t;
+					for (int q = 0; cx + q < cols; ++q) o[q] = t[q];
 				}
-				out[(int64_t)y * out_pitch + x] = white ? 255 : 0;
+			}
+		} else {
+			for (int c = tid; c < ST_H * TW; c += BTHREADS) {
+				const int row = c / TW, cx = c % TW;
+				if (row < rows && cx < cols) out[(int64_t)(ty0 + row) * out_pitch + tx0 + cx] = otile[row * (TW + 16) + cx];
 			}
 		}
 	}
 }
 
+template <int TW>
 __host__ __device__ inline size_t sauvola_smem_bytes(int win) {
 	const int rad = win / 2;
-	const int PW = ST_W + 2 * rad, PH = ST_H + 2 * rad;
-	return (size_t)((PH * PW + 15) & ~15) + (size_t)2 * ST_H * PW * sizeof(unsigned int);
+	const int PW = TW + 2 * rad, PH = ST_H + 2 * rad;
+	return (size_t)((PH * PW + 15) & ~15) + (size_t)2 * ST_H * (PW | 1) * sizeof(unsigned int) + (size_t)ST_H * (TW + 16);
 }
 
 __global__ void __launch_bounds__(BTHREADS) og_sauvola_page_kernel(
@@ -389,7 +415,7 @@ __global__ void __launch_bounds__(BTHREADS) og_sauvola_page_kernel(
 	const int64_t total = (int64_t)tiles_x * tiles_y;
 	for (int64_t t = blockIdx.x; t < total; t += gridDim.x) {
 		const int ty = (int)(t / tiles_x), tx = (int)(t - (int64_t)ty * tiles_x);
-		sauvola_tile(src, h, w, src_pitch, dst, dst_pitch, ty * ST_H, tx * ST_W, win, kk, rr, smem_raw);
+		sauvola_tile<ST_W>(src, h, w, src_pitch, dst, dst_pitch, ty * ST_H, tx * ST_W, win, kk, rr, smem_raw);
 	}
 }
 
@@ -413,7 +439,7 @@ __global__ void __launch_bounds__(BTHREADS) og_sauvola_strips_kernel(
 		const int w = steps[2 * li], h = steps[2 * li + 1];
 		const int64_t off = pix_offsets[li];
 		for (int ty0 = 0; ty0 < h; ty0 += ST_H)
-			sauvola_tile(gray + off, h, w, w, out + off, w, ty0, chunk * ST_W, win, kk, rr, smem_raw);
+			sauvola_tile<ST_WS>(gray + off, h, w, w, out + off, w, ty0, chunk * ST_WS, win, kk, rr, smem_raw);
 	}
 }
 
@@ -442,7 +468,7 @@ extern "C" int og_binarize_strips(const uint8_t *gray, const int32_t *steps, con
 	int rc = check_window(window);
 	if (rc) return rc;
 	OG_REQUIRE(gray != out, OG_E_ARG, "Sauvola cannot run in place");
-	const size_t smem = sauvola_smem_bytes(window);
+	const size_t smem = sauvola_smem_bytes<ST_WS>(window);
 	cudaError_t e = cudaFuncSetAttribute(og_sauvola_strips_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
 	if (e != cudaSuccess) return og_set_error((int)e, "cudaFuncSetAttribute: %s", cudaGetErrorString(e));
 	og_sauvola_strips_kernel<<<OG_NUM_SMS * 4, BTHREADS, smem, st>>>(gray, steps, pix_offsets, chunk_offsets, n, out,
@@ -457,7 +483,7 @@ extern "C" int og_sauvola(const uint8_t *src, int h, int w, int64_t src_pitch, i
 	OG_REQUIRE(src != dst, OG_E_ARG, "Sauvola cannot run in place");
 	int rc = check_window(window);
 	if (rc) return rc;
-	const size_t smem = sauvola_smem_bytes(window);
+	const size_t smem = sauvola_smem_bytes<ST_W>(window);
 	cudaError_t e = cudaFuncSetAttribute(og_sauvola_page_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
 	if (e != cudaSuccess) return og_set_error((int)e, "cudaFuncSetAttribute: %s", cudaGetErrorString(e));
 	const int64_t tiles = (int64_t)((w + ST_W - 1) / ST_W) * ((h + ST_H - 1) / ST_H);
