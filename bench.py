@@ -168,7 +168,7 @@ def cpu_reference_step(page, grid, lines, n_sample, binarize):
 	return t_page + t_lines * (len(lines) / max(len(sel), 1)), t2 - t0, t_page, t_lines
 
 
-def cpu_baseline(args, page, grid, lines, n_sample=96, reps=2):
+def cpu_baseline(args, page, grid, lines, n_sample=512, reps=3):
 	import cv2
 	gh, gw = grid.shape[:2]
 	mp = gh * CELL * gw * CELL / 1e6

@@ -85,18 +85,6 @@ struct og_fix {
 	int ix, iy, fx, fy;
 };
 
-__device__ __forceinline__ og_fix og_quantise(float x, float y) {
-	// cvRound(x * INTER_TAB_SIZE): fp32 product, round half to even
-	int sx = __float2int_rn(__fmul_rn(x, 32.f));
-	int sy = __float2int_rn(__fmul_rn(y, 32.f));
-	og_fix q;
-	q.ix = og_sat_short(sx >> 5);
-	q.iy = og_sat_short(sy >> 5);
-	q.fx = sx & 31;
-	q.fy = sy & 31;
-	return q;
-}
-
 __device__ __forceinline__ int og_blend(og_fix q, int p00, int p01, int p10, int p11) {
 	int wx0 = 32 - q.fx, wy0 = 32 - q.fy;
 	int acc = wy0 * (wx0 * p00 + q.fx * p01) + q.fy * (wx0 * p10 + q.fx * p11);
@@ -110,54 +98,11 @@ __device__ __forceinline__ int og_tap(
 	return border;
 }
 
-__device__ __forceinline__ int og_sample_linear(
-	const uint8_t *__restrict__ src, int H, int W, int64_t pitch, float x, float y, int border) {
-	og_fix q = og_quantise(x, y);
-	int p00 = og_tap(src, H, W, pitch, q.iy, q.ix, border);
-	int p01 = og_tap(src, H, W, pitch, q.iy, q.ix + 1, border);
-	int p10 = og_tap(src, H, W, pitch, q.iy + 1, q.ix, border);
-	int p11 = og_tap(src, H, W, pitch, q.iy + 1, q.ix + 1, border);
-	return og_blend(q, p00, p01, p10, p11);
-}
-
-// 4 taps of one pixel with a fast interior path: when all taps lie inside the image one
-// address is formed in 32-bit arithmetic (H * pitch < 2^31 is checked on the host); border
-// pixels take the per-tap test that yields OpenCV's BORDER_CONSTANT value per tap.
-__device__ __forceinline__ int og_sample_linear_fast(
-	const uint8_t *__restrict__ src, int H, int W, int pitch, float mx, float my) {
-	const int sx = __float2int_rn(__fmul_rn(mx, 32.f));
-	const int sy = __float2int_rn(__fmul_rn(my, 32.f));
-	const int ix = sx >> 5, iy = sy >> 5;
-	og_fix q;
-	q.fx = sx & 31;
-	q.fy = sy & 31;
-	int p00, p01, p10, p11;
-	if ((unsigned)ix < (unsigned)(W - 1) && (unsigned)iy < (unsigned)(H - 1)) {
-		const uint8_t *s = src + (iy * pitch + ix);
-		p00 = __ldg(s);
-		p01 = __ldg(s + 1);
-		p10 = __ldg(s + pitch);
-		p11 = __ldg(s + pitch + 1);
-	} else {
-		q.ix = og_sat_short(ix);
-		q.iy = og_sat_short(iy);
-		p00 = og_tap(src, H, W, pitch, q.iy, q.ix, 0);
-		p01 = og_tap(src, H, W, pitch, q.iy, q.ix + 1, 0);
-		p10 = og_tap(src, H, W, pitch, q.iy + 1, q.ix, 0);
-		p11 = og_tap(src, H, W, pitch, q.iy + 1, q.ix + 1, 0);
-	}
-	return og_blend(q, p00, p01, p10, p11);
-}
-
 // N pixels at once: when every tap of every pixel is inside the image (the common case) all
-// 4N byte loads are issued back to back before the first blend, so their latencies overlap.
-__device__ __forceinline__ void og_prefetch_l1(const void *ptr) {
-	asm volatile("prefetch.global.L1 [%0];" ::"l"(ptr));
-}
-
-// PF > 0: also prefetch the source row PF rows below the taps of every other pixel -- the row
-// the same thread will need PF-1 destination rows later when it walks down a page.
-template <int N, int PF = 0>
+// 4N byte loads are issued back to back before the first blend, so their latencies overlap;
+// the address is formed in 32-bit arithmetic (H * pitch < 2^31 is checked on the host).  Border
+// pixels take the per-tap test that yields OpenCV's BORDER_CONSTANT value per tap.
+template <int N>
 __device__ __forceinline__ void og_sample_linear_batch(
 	const uint8_t *__restrict__ src, int H, int W, int pitch,
 	const float (&mx)[N], const float (&my)[N], int (&out)[N]) {
@@ -183,7 +128,6 @@ __device__ __forceinline__ void og_sample_linear_batch(
 			p01[k] = __ldg(s + 1);
 			p10[k] = __ldg(s + pitch);
 			p11[k] = __ldg(s + pitch + 1);
-			if (PF > 0 && (k & 1) == 0 && iy[k] + PF < H) og_prefetch_l1(s + PF * pitch);
 		}
 #pragma unroll
 		for (int k = 0; k < N; ++k) out[k] = og_blend(q[k], p00[k], p01[k], p10[k], p11[k]);
@@ -250,20 +194,13 @@ __device__ __forceinline__ int og_blend_taps(const og_taps &t) {
 	return (acc + 512) >> 10;
 }
 
+// A4: cv2.remap INTER_NEAREST: saturate_cast<short>(float) = round half to even, OOB -> 0.
 __device__ __forceinline__ int og_sample_nearest_fast(
 	const uint8_t *__restrict__ src, int H, int W, int pitch, float mx, float my) {
 	const int ix = og_sat_short(__float2int_rn(mx));
 	const int iy = og_sat_short(__float2int_rn(my));
 	if ((unsigned)ix < (unsigned)W && (unsigned)iy < (unsigned)H) return (int)__ldg(src + (iy * pitch + ix));
 	return 0;
-}
-
-// A4: cv2.remap INTER_NEAREST: saturate_cast<short>(float) = round half to even.
-__device__ __forceinline__ int og_sample_nearest(
-	const uint8_t *__restrict__ src, int H, int W, int64_t pitch, float x, float y, int border) {
-	int ix = og_sat_short(__float2int_rn(x));
-	int iy = og_sat_short(__float2int_rn(y));
-	return og_tap(src, H, W, pitch, iy, ix, border);
 }
 
 // ---------------------------------------------------------------------------------------

@@ -15,12 +15,6 @@
 // offsets; the smooth warp makes neighbouring threads hit the same 128-byte lines.
 #include "og_common.cuh"
 
-#ifndef OG_PAGE_PF
-#define OG_PAGE_PF 0
-#endif
-#ifndef OG_PAGE_PIPE
-#define OG_PAGE_PIPE 0
-#endif
 #ifndef OG_PAGE_MINB
 #define OG_PAGE_MINB 3
 #endif
@@ -128,9 +122,6 @@ __global__ void __launch_bounds__(TBX *TBY, OG_PAGE_MINB) og_page_kernel(const _
 	float *mrow = WRITE_MAP ? p.map_out + ((size_t)ybeg * Wd + xa) * 2 : nullptr;
 	uint8_t *orow = WRITE_IMG ? p.dst + (int64_t)ybeg * p.dst_pitch + xa : nullptr;
 
-	og_taps pend[TPX];
-#pragma unroll
-	for (int k = 0; k < TPX; ++k) pend[k] = og_taps{0, 0, 0, 0, 0, 0};
 	const int nrows = min(TROWS, Hd - ybeg);
 	for (int yy = 0; yy < nrows; ++yy) {
 		const RowAxis ra = s_rows[threadIdx.y * TROWS + yy];
@@ -175,24 +166,10 @@ __global__ void __launch_bounds__(TBX *TBY, OG_PAGE_MINB) og_page_kernel(const _
 				mx[k] = SCALED ? __fmul_rn(d[k].x, scx) : d[k].x;
 				my[k] = SCALED ? __fmul_rn(d[k].y, scy) : d[k].y;
 			}
-			if (LINEAR && OG_PAGE_PIPE) {
-				// software pipeline: the taps of this row are requested now and blended after the
-				// next row's taps have been requested
-				og_taps cur[TPX];
-				og_load_taps_batch<TPX>(src, H, W, spitch, mx, my, cur);
-				if (yy > 0) {
-					int v[TPX];
-#pragma unroll
-					for (int k = 0; k < TPX; ++k) v[k] = og_blend_taps(pend[k]);
-					store_quad(orow, v, na, nb, img_al);
-					orow += p.dst_pitch;
-				}
-#pragma unroll
-				for (int k = 0; k < TPX; ++k) pend[k] = cur[k];
-			} else {
+			{
 				int v[TPX];
 				if (LINEAR) {
-					og_sample_linear_batch<TPX, OG_PAGE_PF>(src, H, W, spitch, mx, my, v);
+					og_sample_linear_batch<TPX>(src, H, W, spitch, mx, my, v);
 				} else {
 #pragma unroll
 					for (int k = 0; k < TPX; ++k) v[k] = og_sample_nearest_fast(src, H, W, spitch, mx[k], my[k]);
@@ -201,12 +178,6 @@ __global__ void __launch_bounds__(TBX *TBY, OG_PAGE_MINB) og_page_kernel(const _
 				orow += p.dst_pitch;
 			}
 		}
-	}
-	if (WRITE_IMG && LINEAR && OG_PAGE_PIPE && nrows > 0) {
-		int v[TPX];
-#pragma unroll
-		for (int k = 0; k < TPX; ++k) v[k] = og_blend_taps(pend[k]);
-		store_quad(orow, v, na, nb, img_al);
 	}
 }
 
