@@ -97,7 +97,9 @@ int og_inverse_yx(const float *grid, int gh, int gw, int cell,
  * For every line: steps_out[i] = (xsteps, ysteps); pix_offsets_out[i] = sum over j<i of
  * xsteps*ysteps (n+1 entries, element offsets of each strip in a packed buffer);
  * chunk_offsets_out (n+1 entries) = prefix sum of the work items the extraction kernels
- * split each line into.  One launch, no host synchronisation. */
+ * split each line into (64 strip columns each).  Two small kernels, no host synchronisation.
+ * A line whose extent is not finite, or whose strip would exceed 2^31 pixels, gets steps (0, 0)
+ * and no work items. */
 int og_line_steps(const float *grid, int gh, int gw, int cell,
 	const og_line *lines, int n,
 	int32_t *steps_out, int64_t *pix_offsets_out, int32_t *chunk_offsets_out, void *stream);
@@ -122,7 +124,8 @@ int og_warped_grids(const float *grid, int gh, int gw, int cell, const float *ma
  * (ysteps, xsteps) u8, row 0 = top of the text (the reference's pixels[::-1]), at byte
  * offset pix_offsets[i] of strips_out.  bbox_out, if not NULL, receives per line
  * (floor min x, floor min y, ceil max x, ceil max y) of its fp32 warped grid as int32
- * (origami/core/mask.py:10-12 convention).  capacity in bytes of strips_out. */
+ * (origami/core/mask.py:10-12 convention).  capacity in bytes of strips_out; strips that do not fit
+ * are skipped whole (compare pix_offsets[n] with the capacity). */
 int og_extract_lines(const uint8_t *src, int H, int W, int64_t src_pitch,
 	const float *grid, int gh, int gw, int cell, const float *map,
 	const og_line *lines, int n,
