@@ -110,10 +110,13 @@ __device__ int otsu_from_hist_warp(const unsigned int *hist) {
 // strips, Otsu: one CTA per line -- histogram in shared memory, threshold, apply
 // ---------------------------------------------------------------------------------------
 // Histogram of text strips: most pixels are paper, so a warp's 32 lanes mostly hit the same few
-// bins and plain shared-memory atomics serialise.  The counters are replicated HREP times
+// bins and plain shared-memory atomics serialise.  The counters are replicated HREP (4) times
 // ([bin][replica], replica = lane % HREP), so equal values from different lanes land on
 // different addresses and banks; the replicas are summed before the threshold is computed.
-constexpr int HREP = 8;
+#ifndef OG_HREP
+#define OG_HREP 4
+#endif
+constexpr int HREP = OG_HREP;
 
 __global__ void __launch_bounds__(BTHREADS) og_otsu_strips_kernel(
 	const uint8_t *__restrict__ gray, const int32_t *__restrict__ steps, const int64_t *__restrict__ pix_offsets,
