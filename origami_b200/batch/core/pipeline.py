@@ -1,0 +1,231 @@
+"""
+Multi-page pipeline for the page-geometry path: while the GPU works on page i, the host
+packs and uploads page i+1 and the results of page i-1 travel back -- pinned staging
+buffers, two CUDA streams, no synchronisation inside a page.
+
+The reference processes its page queue one page at a time inside `Processor.process`
+(origami/batch/core/processor.py:396-441); every page is independent, so nothing but host
+scheduling changes here.  Per page the work is what `Page(..., grid).dewarped` plus
+`LineExtractor(...)(lines)` do: fused map expansion + remap, line step counts, strip
+extraction and optional strip binarization, with bit-identical results.
+"""
+
+import collections
+import collections.abc
+import concurrent.futures
+
+import numpy as np
+import torch
+
+from ... import _lib, ops
+from ...core import binarize as _binarize
+
+PageResult = collections.namedtuple("PageResult", ["dewarped", "strips", "steps"])
+
+class StripList(collections.abc.Sequence):
+	"""The strips of one page as a read-only sequence of (ysteps, xsteps) uint8 views into the
+	packed result buffer; a view is only made when an item is accessed."""
+
+	def __init__(self, flat, offsets, steps):
+		self._flat, self._offs, self._steps = flat, offsets, steps
+
+	def __len__(self):
+		return int(self._steps.shape[0])
+
+	def __getitem__(self, i):
+		if isinstance(i, slice):
+			return [self[k] for k in range(*i.indices(len(self)))]
+		if i < 0:
+			i += len(self)
+		if not 0 <= i < len(self):
+			raise IndexError(i)
+		return self._flat[self._offs[i]:self._offs[i + 1]].reshape(self._steps[i, 1], self._steps[i, 0])
+
+
+_COPY_POOL = concurrent.futures.ThreadPoolExecutor(max_workers=4)
+
+
+def _parallel_copy(dst, src):
+	"""dst[...] = src for large contiguous uint8 arrays, split over a few threads (NumPy
+	releases the GIL while copying; one thread reaches only a fraction of the host bandwidth)."""
+	n = src.shape[0]
+	if n < (4 << 20):
+		dst[:n] = src
+		return
+	step = (n + 3) // 4
+	futs = [_COPY_POOL.submit(np.copyto, dst[i:min(n, i + step)], src[i:min(n, i + step)]) for i in range(0, n, step)]
+	for f in futs:
+		f.result()
+
+
+class _Slot:
+	"""Buffers of one in-flight page (reused across pages; grown on demand)."""
+
+	def __init__(self, device):
+		self.device = device
+		self.stream = torch.cuda.Stream(device=device)
+		self.done = None
+		self.h_in = self.h_out = None
+		self.d_in = self.d_out = self.d_gray = self.d_chunks = self.d_map = None
+		self.meta = None
+		self.bytes = (0, 0)
+
+	@staticmethod
+	def _grow(t, nbytes, **kw):
+		if t is None or t.numel() < nbytes:
+			# 25 % headroom: pages of a batch differ a little in size, and growing a pinned or
+			# device buffer in the middle of a run synchronises the device
+			return torch.empty((max(nbytes + nbytes // 4, 1 << 20),), dtype=torch.uint8, **kw)
+		return t
+
+
+_PINNED = {}  # data pointer -> pinned tensor backing an array handed out by pinned_page()
+
+
+def pinned_page(pixels_or_shape):
+	"""A page-locked uint8 (H, W) array (a copy of `pixels`, or uninitialised for a shape) that an
+	image decoder can fill in place.  Pages that live in such arrays are uploaded straight from
+	them; any other array is first copied into the pipeline's own pinned staging buffer."""
+	if isinstance(pixels_or_shape, np.ndarray):
+		src = np.ascontiguousarray(pixels_or_shape, dtype=np.uint8)
+		shape = src.shape
+	else:
+		src, shape = None, tuple(pixels_or_shape)
+	t = torch.empty(shape, dtype=torch.uint8, pin_memory=True)
+	a = t.numpy()
+	if src is not None:
+		a[...] = src
+	_PINNED[a.ctypes.data] = t
+	return a
+
+
+class PagePipeline:
+	"""pipeline = PagePipeline(line_height=48, binarize="otsu"); for res in pipeline.run(jobs): ...
+
+	A job is (page uint8 (H, W) ndarray, grid (gh, gw, 2) float32 ndarray, cell, lines) with
+	`lines` an (n, 3, 2) float64 array or list of (p, right, up) in dewarped space (the fields
+	of lines.zip).  Results come back in job order as PageResult(dewarped ndarray, sequence of
+	strip ndarrays, steps (n, 2) int32 (xsteps, ysteps)).  The arrays of a result are views into a
+	pinned buffer that is recycled when the NEXT result is requested: copy what must outlive that."""
+
+	def __init__(self, line_height=48, binarize="", depth=2, device=None, use_map=True):
+		if not torch.cuda.is_available():
+			raise _lib.OrigamiB200Error("origami_b200 needs a CUDA device (there is no CPU fallback)")
+		self.device = torch.device(device) if device is not None else torch.device("cuda", torch.cuda.current_device())
+		self.line_height = int(line_height)
+		spec = _binarize.from_string(binarize).spec if binarize.strip() else None
+		self.binarize = spec
+		self.use_map = use_map
+		self.slots = [_Slot(self.device) for _ in range(max(2, depth))]
+
+	# -- one page: everything is enqueued on the slot's stream, nothing waits
+	def _submit(self, slot, job):
+		page, grid, cell, lines = job
+		page = np.ascontiguousarray(page, dtype=np.uint8)
+		grid = np.ascontiguousarray(grid, dtype=np.float32)
+		lines = np.ascontiguousarray(lines, dtype=np.float64).reshape(-1, 3, 2)
+		H, W = page.shape
+		gh, gw = grid.shape[:2]
+		Hd, Wd = gh * cell, gw * cell
+		n = lines.shape[0]
+		desc = ops.pack_line_arrays(lines[:, 0], lines[:, 1], lines[:, 2], ysteps=self.line_height)
+		lengths = np.hypot(lines[:, 1, 0], lines[:, 1, 1])
+		cap = int(np.sum(self.line_height * (np.ceil(lengths * 1.1) + 16))) if n else 1
+
+		pitch = W  # the source is only read with byte loads: no row padding, one contiguous copy
+		dpitch = (Wd + 127) // 128 * 128
+		al = lambda v: (v + 255) // 256 * 256  # noqa: E731
+		# input block: page rows (pitched) | grid | line descriptors
+		o_grid = al(H * pitch)
+		o_desc = o_grid + al(grid.nbytes)
+		n_in = o_desc + al(max(desc.nbytes, 1))
+		# output block: dewarped page (pitched) | strips | steps | pix offsets
+		o_strips = al(Hd * dpitch)
+		o_steps = o_strips + al(cap)
+		o_offs = o_steps + al(8 * max(n, 1))
+		n_out = o_offs + al(8 * (n + 1))
+
+		if slot.done is not None:
+			slot.done.synchronize()  # the slot's previous results must have been consumed
+		slot.h_in = _Slot._grow(slot.h_in, n_in, pin_memory=True)
+		slot.h_out = _Slot._grow(slot.h_out, n_out, pin_memory=True)
+		slot.d_in = _Slot._grow(slot.d_in, n_in, device=self.device)
+		slot.d_out = _Slot._grow(slot.d_out, n_out, device=self.device)
+		slot.d_gray = _Slot._grow(slot.d_gray, cap, device=self.device)
+		slot.d_chunks = _Slot._grow(slot.d_chunks, 4 * (n + 1), device=self.device)
+		if self.use_map:
+			slot.d_map = _Slot._grow(slot.d_map, Hd * Wd * 8, device=self.device)
+
+		hin = slot.h_in.numpy()
+		pinned_src = _PINNED.get(page.ctypes.data)
+		if pinned_src is not None and tuple(pinned_src.shape) != (H, W):
+			pinned_src = None
+		if pinned_src is None:
+			_parallel_copy(hin, page.reshape(-1))
+		hin[o_grid:o_grid + grid.nbytes] = grid.view(np.uint8).reshape(-1)
+		if n:
+			hin[o_desc:o_desc + desc.nbytes] = desc.view(np.uint8).reshape(-1)
+		slot.keep = (page, pinned_src)  # the source must stay alive until the upload has run
+
+		st = slot.stream
+		with torch.cuda.stream(st):
+			if pinned_src is None:
+				slot.d_in[:n_in].copy_(slot.h_in[:n_in], non_blocking=True)
+			else:
+				slot.d_in[:H * W].copy_(pinned_src.reshape(-1), non_blocking=True)
+				slot.d_in[o_grid:n_in].copy_(slot.h_in[o_grid:n_in], non_blocking=True)
+			base_in, base_out = slot.d_in.data_ptr(), slot.d_out.data_ptr()
+			s = st.cuda_stream
+			p_map = slot.d_map.data_ptr() if self.use_map else 0
+			_lib.call("og_remap_page", base_in, H, W, pitch, base_in + o_grid, gh, gw, cell,
+				base_out, dpitch, p_map, 1.0, 1.0, ops.OG_INTER_LINEAR, s)
+			if n:
+				_lib.call("og_line_steps", base_in + o_grid, gh, gw, cell, base_in + o_desc, n,
+					base_out + o_steps, base_out + o_offs, slot.d_chunks.data_ptr(), s)
+				target = slot.d_gray.data_ptr() if self.binarize is not None else base_out + o_strips
+				_lib.call("og_extract_lines", base_in, H, W, pitch, base_in + o_grid, gh, gw, cell, p_map,
+					base_in + o_desc, n, base_out + o_steps, base_out + o_offs, slot.d_chunks.data_ptr(),
+					target, cap, 0, s)
+				if self.binarize is not None:
+					mode = ops.OG_BIN_OTSU if self.binarize[0] == "otsu" else ops.OG_BIN_SAUVOLA
+					window = self.binarize[1] if len(self.binarize) > 1 else 15
+					_lib.call("og_binarize_strips", target, base_out + o_steps, base_out + o_offs, slot.d_chunks.data_ptr(),
+						n, mode, window, base_out + o_strips, 0, s)
+			slot.h_out[:n_out].copy_(slot.d_out[:n_out], non_blocking=True)
+			slot.done = torch.cuda.Event()
+			slot.done.record(st)
+		slot.meta = (Hd, Wd, dpitch, n, cap, o_strips, o_steps, o_offs)
+		slot.bytes = (n_in, n_out)
+
+	def _collect(self, slot):
+		slot.done.synchronize()
+		Hd, Wd, dpitch, n, cap, o_strips, o_steps, o_offs = slot.meta
+		hout = slot.h_out.numpy()
+		dewarped = hout[:Hd * dpitch].reshape(Hd, dpitch)[:, :Wd]
+		steps = hout[o_steps:o_steps + 8 * n].view(np.int32).reshape(n, 2)
+		offs = hout[o_offs:o_offs + 8 * (n + 1)].view(np.int64)
+		if n and int(offs[n]) > cap:
+			raise _lib.OrigamiB200Error("strip buffer estimate too small (%d > %d)" % (int(offs[n]), cap))
+		if n and (steps <= 0).any():
+			raise ValueError("line %d has a degenerate or non-finite extent" % int(np.argmax((steps <= 0).any(axis=1))))
+		flat = hout[o_strips:o_strips + cap]
+		return PageResult(dewarped, StripList(flat, offs, steps), steps)
+
+	def run(self, jobs):
+		"""Generator over results, in job order; `depth` pages are in flight."""
+		pending = collections.deque()
+		k = 0
+		for job in jobs:
+			slot = self.slots[k % len(self.slots)]
+			if len(pending) == len(self.slots):
+				yield self._collect(pending.popleft())
+			self._submit(slot, job)
+			pending.append(slot)
+			k += 1
+		while pending:
+			yield self._collect(pending.popleft())
+
+	@property
+	def bytes_per_page(self):
+		"""(host->device, device->host) bytes of the most recently submitted page."""
+		return self.slots[0].bytes

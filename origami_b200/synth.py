@@ -67,6 +67,8 @@ def make_lines(width_d, height_d, n_lines, seed=0, dpi=600, table_fraction=0.05)
 	p (bottom-left), right, up (docs/formats.md:245-246; `up` points to smaller y),
 	confidence, and an optional column (x0, x1) split for table rows
 	(origami/batch/core/lines.py:68-82)."""
+	if n_lines <= 0:
+		return []
 	rng = np.random.default_rng(9876 + seed)
 	n_cols = 8
 	col_w = width_d / n_cols

@@ -228,3 +228,30 @@ def test_regions_binarized(small):
 	want = exact.regions_binarized(small.page, small.g, small.s, 31, [(labels, 0)])
 	assert got.dtype == np.float32 and np.array_equal(got, want)
 	assert np.array_equal(regions_binarized(small.pg, 20), exact.regions_binarized(small.page, small.g, small.s, 20))
+
+
+@pytest.mark.parametrize("spec", ["", "otsu"])
+def test_page_pipeline_matches_per_page_api(cuda, spec):
+	"""The multi-page pipeline (pinned staging, two streams) returns the same bytes as the
+	per-page objects, in job order, for pages of different sizes."""
+	from origami_b200.batch.core.pipeline import PagePipeline, pinned_page
+	jobs, want = [], []
+	for k, (W, H, n) in enumerate([(700, 500, 40), (333, 421, 25), (900, 300, 30), (512, 512, 0), (640, 480, 33)]):
+		page = synth.make_page(W, H, seed=50 + k, kind="noise")
+		g = synth.make_grid(W, H, 25, seed=50 + k)
+		lines = synth.make_lines(g.shape[1] * 25, g.shape[0] * 25, n, seed=50 + k, dpi=300, table_fraction=0.0)
+		arr = np.array([[l["p"], l["right"], l["up"]] for l in lines], dtype=np.float64).reshape(-1, 3, 2)
+		jobs.append((pinned_page(page) if k % 2 else page, g, 25, arr))  # pinned and pageable inputs
+		dense = exact.expand_map(g, 25)
+		strips = [exact.binarize(exact.dewarped_line_image(page, dense, l["p"], l["right"], l["up"], 48),
+			("otsu",) if spec else None) for l in lines]
+		want.append((exact.remap_linear(page, dense), strips))
+	pipe = PagePipeline(line_height=48, binarize=spec)
+	n_seen = 0
+	for res, (wd, ws) in zip(pipe.run(jobs), want):
+		assert np.array_equal(res.dewarped, wd)
+		assert len(res.strips) == len(ws)
+		for a, b in zip(res.strips, ws):
+			assert a.shape == b.shape and np.array_equal(a, b)
+		n_seen += 1
+	assert n_seen == len(jobs)
