@@ -512,6 +512,7 @@ __global__ void __launch_bounds__(LTHREADS, 2) og_lines_kernel(const __grid_cons
 constexpr int MW = 32;            // strip columns per warp item
 constexpr int MWARPS = 8;         // warps per CTA
 constexpr int MTHREADS = MWARPS * 32;
+constexpr int MAP_OFFS_CAP = 4096;  // line prefix sums cached in shared memory up to this many lines
 #ifndef OG_MAP_MINBLOCKS
 #define OG_MAP_MINBLOCKS 3
 #endif
@@ -521,8 +522,17 @@ __global__ void __launch_bounds__(MTHREADS, OG_MAP_MINBLOCKS) og_lines_map_kerne
 	__shared__ double2 s_rowbase[MWARPS][MAX_ROWS];
 	__shared__ unsigned int s_whist[MODE == MODE_LABELS ? MWARPS : 1][MODE == MODE_LABELS ? MAX_CLASSES + 1 : 1];
 
+	// the work-item -> line lookup is a binary search per item: keep the prefix sums in shared
+	// memory when they fit, so its 11 dependent loads cost 30 instead of 300+ cycles each
+	__shared__ int s_chunk_offsets[MAP_OFFS_CAP];
+	const bool offs_cached = p.n + 1 <= MAP_OFFS_CAP;
+	if (offs_cached) {
+		for (int i = threadIdx.x; i <= p.n; i += MTHREADS) s_chunk_offsets[i] = __ldg(p.chunk_offsets + i);
+		__syncthreads();
+	}
+	const int32_t *chunk_offsets = offs_cached ? s_chunk_offsets : p.chunk_offsets;
 	const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
-	const int total_items = 2 * __ldg(p.chunk_offsets + p.n);  // two 32-column halves per 64-column chunk
+	const int total_items = 2 * chunk_offsets[p.n];  // two 32-column halves per 64-column chunk
 	const int nwarps = gridDim.x * MWARPS;
 	const int Hd = p.gh * p.cell, Wd = p.gw * p.cell;
 	const int Hm = Hd - 2, Wm = Wd - 2;
@@ -533,9 +543,16 @@ __global__ void __launch_bounds__(MTHREADS, OG_MAP_MINBLOCKS) og_lines_map_kerne
 
 	for (int item = blockIdx.x * MWARPS + wid; item < total_items; item += nwarps) {
 		const int chunk_item = item >> 1;
-		const int li = find_line(p.chunk_offsets, p.n, chunk_item);
+		int li = 0;
+		{
+			int hi = p.n;  // invariant: chunk_offsets[li] <= chunk_item < chunk_offsets[hi]
+			while (hi - li > 1) {
+				const int mid = (li + hi) >> 1;
+				if (chunk_offsets[mid] <= chunk_item) li = mid; else hi = mid;
+			}
+		}
 		const int xsteps = __ldg(p.steps + 2 * li), ysteps = __ldg(p.steps + 2 * li + 1);
-		const int c0 = (chunk_item - __ldg(p.chunk_offsets + li)) * CW + (item & 1) * MW;
+		const int c0 = (chunk_item - chunk_offsets[li]) * CW + (item & 1) * MW;
 		if (c0 >= xsteps) continue;
 		const long long pix0 = (MODE != MODE_LABELS) ? __ldg(p.pix_offsets + li) : 0;
 		if (MODE != MODE_LABELS && pix0 + (long long)xsteps * ysteps > p.capacity) continue;
