@@ -104,7 +104,8 @@ class PagePipeline:
 
 	A job is (page uint8 (H, W) ndarray, grid (gh, gw, 2) float32 ndarray, cell, lines) with
 	`lines` an (n, 3, 2) float64 array or list of (p, right, up) in dewarped space (the fields
-	of lines.zip).  Results come back in job order as PageResult(dewarped ndarray, sequence of
+	of lines.zip), or a structured array of og_line descriptors (ops.pack_lines) when table rows
+	are split into column cells.  Results come back in job order as PageResult(dewarped ndarray, sequence of
 	strip ndarrays, steps (n, 2) int32 (xsteps, ysteps)).  The arrays of a result are views into a
 	pinned buffer that is recycled when the NEXT result is requested: copy what must outlive that."""
 
@@ -123,13 +124,21 @@ class PagePipeline:
 		page, grid, cell, lines = job
 		page = np.ascontiguousarray(page, dtype=np.uint8)
 		grid = np.ascontiguousarray(grid, dtype=np.float32)
-		lines = np.ascontiguousarray(lines, dtype=np.float64).reshape(-1, 3, 2)
 		H, W = page.shape
 		gh, gw = grid.shape[:2]
 		Hd, Wd = gh * cell, gw * cell
-		n = lines.shape[0]
-		desc = ops.pack_line_arrays(lines[:, 0], lines[:, 1], lines[:, 2], ysteps=self.line_height)
-		lengths = np.hypot(lines[:, 1, 0], lines[:, 1, 1])
+		if isinstance(lines, np.ndarray) and lines.dtype == ops.LINE_DTYPE:
+			# ready-made og_line descriptors (e.g. table rows clipped to their columns by
+			# Line.record / ops.pack_lines); the strip height is this pipeline's
+			desc = lines.copy()
+			desc["ysteps"] = self.line_height
+			right = desc["cright"]
+		else:
+			lines = np.ascontiguousarray(lines, dtype=np.float64).reshape(-1, 3, 2)
+			desc = ops.pack_line_arrays(lines[:, 0], lines[:, 1], lines[:, 2], ysteps=self.line_height)
+			right = lines[:, 1]
+		n = desc.shape[0]
+		lengths = np.hypot(right[:, 0], right[:, 1]) * np.maximum(desc["xres"], 1e-9)
 		cap = int(np.sum(self.line_height * (np.ceil(lengths * 1.1) + 16))) if n else 1
 
 		pitch = W  # the source is only read with byte loads: no row padding, one contiguous copy

@@ -255,3 +255,21 @@ def test_page_pipeline_matches_per_page_api(cuda, spec):
 			assert a.shape == b.shape and np.array_equal(a, b)
 		n_seen += 1
 	assert n_seen == len(jobs)
+
+
+def test_page_pipeline_with_column_descriptors(small):
+	"""Table rows split into column cells travel through the pipeline as og_line descriptors."""
+	from origami_b200.batch.core.pipeline import PagePipeline
+	block = Block(small.pg, None, Stage.RELIABLE)
+	recs, want = [], []
+	for ln in small.lines[:12]:
+		line = Line(block, ln["p"], ln["right"], ln["up"])
+		x0 = ln["p"][0] + 0.3 * ln["right"][0]
+		for col in ((None, x0), (x0, None)):
+			recs.append(line.record(ysteps=48, column=col))
+			want.append(reference_path.line_image(small.pil, small.ref, ln["p"], ln["right"], ln["up"], 48, column=col))
+	pipe = PagePipeline(line_height=48)
+	(res,) = list(pipe.run([(small.page, small.g, small.s, ops.pack_lines(recs))]))
+	assert len(res.strips) == len(want)
+	for a, b in zip(res.strips, want):
+		assert a.shape == b.shape and np.array_equal(a, b)
