@@ -1,7 +1,7 @@
 """
 Multi-page pipeline for the page-geometry path: while the GPU works on page i, the host
 packs and uploads page i+1 and the results of page i-1 travel back -- pinned staging
-buffers, two CUDA streams, no synchronisation inside a page.
+buffers, one CUDA stream per in-flight page, no synchronisation inside a page.
 
 The reference processes its page queue one page at a time inside `Processor.process`
 (origami/batch/core/processor.py:396-441); every page is independent, so nothing but host
@@ -105,8 +105,8 @@ class PagePipeline:
 	A job is (page uint8 (H, W) ndarray, grid (gh, gw, 2) float32 ndarray, cell, lines) with
 	`lines` an (n, 3, 2) float64 array or list of (p, right, up) in dewarped space (the fields
 	of lines.zip), or a structured array of og_line descriptors (ops.pack_lines) when table rows
-	are split into column cells.  Results come back in job order as PageResult(dewarped ndarray, sequence of
-	strip ndarrays, steps (n, 2) int32 (xsteps, ysteps)).  The arrays of a result are views into a
+	are split into column cells.  Results come back in job order as PageResult(dewarped ndarray,
+	sequence of strip ndarrays, steps (n, 2) int32 (xsteps, ysteps)).  The arrays of a result are views into a
 	pinned buffer that is recycled when the NEXT result is requested: copy what must outlive that."""
 
 	def __init__(self, line_height=48, binarize="", depth=2, device=None, use_map=True):
