@@ -248,7 +248,7 @@ class PageSet:
 		self.bbox = torch.empty((self.n, 4), dtype=torch.int32, device=device)
 		self.steps = torch.empty((self.n, 2), dtype=torch.int32, device=device)
 		self.pix = torch.empty((self.n + 1,), dtype=torch.int64, device=device)
-		self.chunks = torch.empty((self.n + 1,), dtype=torch.int32, device=device)
+		self.chunks = torch.empty((self.n + 2,), dtype=torch.int32, device=device)
 		self.plan = ops.LinePlan(self.lines, self.n, self.steps, self.pix, self.chunks)
 
 

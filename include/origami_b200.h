@@ -96,8 +96,10 @@ int og_inverse_yx(const float *grid, int gh, int gw, int cell,
 /* A8 (step counts) + A21  Line.warped_grid step derivation -- origami/core/block.py:226-236.
  * For every line: steps_out[i] = (xsteps, ysteps); pix_offsets_out[i] = sum over j<i of
  * xsteps*ysteps (n+1 entries, element offsets of each strip in a packed buffer);
- * chunk_offsets_out (n+1 entries) = prefix sum of the work items the extraction kernels
- * split each line into (64 strip columns each).  Two small kernels, no host synchronisation.
+ * chunk_offsets_out (n+2 entries) = n+1 prefix sums of the work items the extraction kernels
+ * split each line into (64 strip columns each), followed by one work-ticket word that this call
+ * zeroes and og_extract_lines uses while it runs (and leaves at zero).  A plan therefore serves
+ * one og_extract_lines call at a time.  Two small kernels, no host synchronisation.
  * A line whose extent is not finite, or whose strip would exceed 2^31 pixels, gets steps (0, 0)
  * and no work items. */
 int og_line_steps(const float *grid, int gh, int gw, int cell,
@@ -129,7 +131,7 @@ int og_warped_grids(const float *grid, int gh, int gw, int cell, const float *ma
 int og_extract_lines(const uint8_t *src, int H, int W, int64_t src_pitch,
 	const float *grid, int gh, int gw, int cell, const float *map,
 	const og_line *lines, int n,
-	const int32_t *steps, const int64_t *pix_offsets, const int32_t *chunk_offsets,
+	const int32_t *steps, const int64_t *pix_offsets, int32_t *chunk_offsets,
 	uint8_t *strips_out, int64_t capacity, int32_t *bbox_out, void *stream);
 
 /* A12  binarizers on packed strips -- origami/core/binarize.py:11-43 as applied per line by

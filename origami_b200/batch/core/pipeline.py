@@ -161,7 +161,7 @@ class PagePipeline:
 		slot.d_in = _Slot._grow(slot.d_in, n_in, device=self.device)
 		slot.d_out = _Slot._grow(slot.d_out, n_out, device=self.device)
 		slot.d_gray = _Slot._grow(slot.d_gray, cap, device=self.device)
-		slot.d_chunks = _Slot._grow(slot.d_chunks, 4 * (n + 1), device=self.device)
+		slot.d_chunks = _Slot._grow(slot.d_chunks, 4 * (n + 2), device=self.device)
 		if self.use_map:
 			slot.d_map = _Slot._grow(slot.d_map, Hd * Wd * 8, device=self.device)
 

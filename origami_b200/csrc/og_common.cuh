@@ -151,20 +151,19 @@ struct og_taps {
 	int fx, fy;
 };
 
+// taps of N samples given in OpenCV's 1/32-px fixed point (sx = cvRound(x * 32))
 template <int N>
-__device__ __forceinline__ void og_load_taps_batch(
+__device__ __forceinline__ void og_load_taps_fixed(
 	const uint8_t *__restrict__ src, int H, int W, int pitch,
-	const float (&mx)[N], const float (&my)[N], og_taps (&t)[N]) {
+	const int (&sx)[N], const int (&sy)[N], og_taps (&t)[N]) {
 	int ix[N], iy[N];
 	bool all_in = true;
 #pragma unroll
 	for (int k = 0; k < N; ++k) {
-		const int sx = __float2int_rn(__fmul_rn(mx[k], 32.f));
-		const int sy = __float2int_rn(__fmul_rn(my[k], 32.f));
-		ix[k] = sx >> 5;
-		iy[k] = sy >> 5;
-		t[k].fx = sx & 31;
-		t[k].fy = sy & 31;
+		ix[k] = sx[k] >> 5;
+		iy[k] = sy[k] >> 5;
+		t[k].fx = sx[k] & 31;
+		t[k].fy = sy[k] & 31;
 		all_in = all_in && (unsigned)ix[k] < (unsigned)(W - 1) && (unsigned)iy[k] < (unsigned)(H - 1);
 	}
 	if (all_in) {
@@ -186,6 +185,19 @@ __device__ __forceinline__ void og_load_taps_batch(
 			t[k].p11 = og_tap(src, H, W, pitch, y + 1, x + 1, 0);
 		}
 	}
+}
+
+template <int N>
+__device__ __forceinline__ void og_load_taps_batch(
+	const uint8_t *__restrict__ src, int H, int W, int pitch,
+	const float (&mx)[N], const float (&my)[N], og_taps (&t)[N]) {
+	int sx[N], sy[N];
+#pragma unroll
+	for (int k = 0; k < N; ++k) {
+		sx[k] = __float2int_rn(__fmul_rn(mx[k], 32.f));
+		sy[k] = __float2int_rn(__fmul_rn(my[k], 32.f));
+	}
+	og_load_taps_fixed<N>(src, H, W, pitch, sx, sy, t);
 }
 
 __device__ __forceinline__ int og_blend_taps(const og_taps &t) {

@@ -150,6 +150,7 @@ __global__ void __launch_bounds__(1024) og_line_scan_kernel(
 	if (threadIdx.x == 0) {
 		pix_offsets[n] = carry_pix;
 		chunk_offsets[n] = carry_chunks;
+		chunk_offsets[n + 1] = 0;  // the work ticket of og_strips_screened_kernel (zero between calls)
 	}
 }
 
@@ -180,6 +181,11 @@ struct LineParams {
 	int n_classes;
 	unsigned long long *counts_out;
 	unsigned long long *overflow_out;
+	// map-gather engine: derived scalars, filled in by the launcher so that the kernels read them
+	// straight from the constant bank
+	int Wd, Hm, Wm, W1, H1;
+	unsigned one_bits;  // 0x3F800000, kept opaque to the compiler (one LOP3 instead of two per fraction)
+	int *ticket;        // = chunk_offsets + n + 1
 };
 
 struct RowEntry {
@@ -517,6 +523,308 @@ constexpr int MAP_OFFS_CAP = 4096;  // line prefix sums cached in shared memory 
 #define OG_MAP_MINBLOCKS 3
 #endif
 
+#ifndef OG_LINES_SCREEN
+#define OG_LINES_SCREEN 1
+#endif
+
+// One sample of the dense map in the reference's float64 order (SciPy _evaluate_linear), cast to
+// float32 and quantised as cv2.remap does: the slow, always-valid path behind the screening below.
+__device__ __noinline__ int2 og_map_sample_exact_fixed(const float2 *__restrict__ map, int Wd, int Hm, int Wm, double px, double py) {
+	const int i0 = min(max(__double2int_rd(py), 0), Hm);
+	const int i1 = min(max(__double2int_rd(px), 0), Wm);
+	const double a = __dsub_rn(py, (double)i0), b = __dsub_rn(px, (double)i1);
+	const float2 *m = map + (i0 * Wd + i1);
+	const float2 v00 = __ldg(m), v01 = __ldg(m + 1), v10 = __ldg(m + Wd), v11 = __ldg(m + Wd + 1);
+	const double wa = __dsub_rn(1.0, a), wb = __dsub_rn(1.0, b);
+	const double w00 = __dmul_rn(wa, wb), w01 = __dmul_rn(wa, b);
+	const double w10 = __dmul_rn(a, wb), w11 = __dmul_rn(a, b);
+	const double wx = __dadd_rn(__dadd_rn(__dadd_rn(__dmul_rn((double)v00.x, w00), __dmul_rn((double)v01.x, w01)),
+		__dmul_rn((double)v10.x, w10)), __dmul_rn((double)v11.x, w11));
+	const double wy = __dadd_rn(__dadd_rn(__dadd_rn(__dmul_rn((double)v00.y, w00), __dmul_rn((double)v01.y, w01)),
+		__dmul_rn((double)v10.y, w10)), __dmul_rn((double)v11.y, w11));
+	return make_int2(__float2int_rn(__fmul_rn(__double2float_rn(wx), 32.f)), __float2int_rn(__fmul_rn(__double2float_rn(wy), 32.f)));
+}
+
+// Screening constants.  OG_FIX_MAGIC = 1.5 * 2^29: a double in [2^29, 2^30) has an ulp of 2^-23,
+// so (v + OG_FIX_MAGIC) rounded DOWN holds floor(v * 2^23) in its mantissa: the integer part
+// of v in bits 23.. and 23 fraction bits below, without a conversion instruction.
+// OG_RINT_MAGIC = 1.5 * 2^23: fl32(32 x + OG_RINT_MAGIC) holds cvRound(32 x) in its low mantissa bits.
+#define OG_FIX_MAGIC 805306368.0
+#define OG_RINT_MAGIC 12582912.0f
+#define OG_RINT_BITS 0x4B400000
+
+// ---------------------------------------------------------------------------------------
+// Screened strip sampling.  What cv2.remap uses of a sample is cvRound(32 * fl32(X)), with X
+// SciPy's float64 blend of the four dense-map nodes.  The blend is evaluated in float32 as
+// v00 + delta with |delta - exact| <= 26 u G (u = 2^-24, G = the largest node difference of the
+// cell; derivation in DESIGN.md), so with eps = 32 u G + 2^-30 the exact X lies in
+// [v00 + delta - eps, v00 + delta + eps].  Rounding to float32 and cvRound are monotone: when
+// both ends of the interval quantise to the same fixed-point value, that IS the reference's
+// value.  Otherwise (a few samples in 10^4), and for samples outside the interior of the map or
+// of the page, the float64 path decides, so the strips stay bit-identical.
+// ---------------------------------------------------------------------------------------
+struct og_nodes {
+	float2 v00, v01, v10, v11;
+	float a, b;
+	bool ok;
+};
+
+// stage 1: cell index + fractions of (px, py) without a conversion instruction, node loads.
+// The caller guarantees |px|, |py| < 2^27, so px + OG_FIX_MAGIC stays in [2^29, 2^30).
+__device__ __forceinline__ void og_nodes_load(og_nodes &n, double px, double py,
+	const float2 *__restrict__ map, int Wd, int Hm, int Wm, unsigned one_bits) {
+	const double tx = __dadd_rd(px, OG_FIX_MAGIC), ty = __dadd_rd(py, OG_FIX_MAGIC);
+	const int txl = __double2loint(tx), tyl = __double2loint(ty);
+	// mantissa = 2^51 + floor(v * 2^23); the three bits above it belong to the exponent 0x41C
+	const unsigned i1 = __funnelshift_r(txl, __double2hiint(tx), 23) - 0x90000000u;
+	const unsigned i0 = __funnelshift_r(tyl, __double2hiint(ty), 23) - 0x90000000u;
+	n.ok = i0 <= (unsigned)Hm && i1 <= (unsigned)Wm;  // a negative floor wraps to a huge index
+	n.a = __fsub_rn(__int_as_float((tyl & 0x7FFFFF) | one_bits), 1.f);
+	n.b = __fsub_rn(__int_as_float((txl & 0x7FFFFF) | one_bits), 1.f);
+	const float2 *m = map + (n.ok ? i0 * (unsigned)Wd + i1 : 0u);
+	n.v00 = __ldg(m);
+	n.v01 = __ldg(m + 1);
+	n.v10 = __ldg(m + Wd);
+	n.v11 = __ldg(m + Wd + 1);
+}
+
+// stage 2: float32 interval of the blend -> fixed-point coordinates; false when undecided
+__device__ __forceinline__ bool og_nodes_screen(const og_nodes &n, int W1, int H1, int &sx, int &sy) {
+	const float d01x = __fsub_rn(n.v01.x, n.v00.x), d10x = __fsub_rn(n.v10.x, n.v00.x), d11x = __fsub_rn(n.v11.x, n.v10.x);
+	const float d01y = __fsub_rn(n.v01.y, n.v00.y), d10y = __fsub_rn(n.v10.y, n.v00.y), d11y = __fsub_rn(n.v11.y, n.v10.y);
+	const float g = fmaxf(fmaxf(fmaxf(fabsf(d01x), fabsf(d10x)), fmaxf(fabsf(d11x), fabsf(d01y))), fmaxf(fabsf(d10y), fabsf(d11y)));
+	const float eps = __fmaf_rn(g, 0x1p-19f, 0x1p-30f);
+	const float dx = __fmaf_rn(n.a, __fmaf_rn(n.b, __fsub_rn(d11x, d01x), d10x), __fmul_rn(n.b, d01x));
+	const float dy = __fmaf_rn(n.a, __fmaf_rn(n.b, __fsub_rn(d11y, d01y), d10y), __fmul_rn(n.b, d01y));
+	const float uxl = __fmaf_rn(__fadd_rn(n.v00.x, __fsub_rn(dx, eps)), 32.f, OG_RINT_MAGIC);
+	const float uxh = __fmaf_rn(__fadd_rn(n.v00.x, __fadd_rn(dx, eps)), 32.f, OG_RINT_MAGIC);
+	const float uyl = __fmaf_rn(__fadd_rn(n.v00.y, __fsub_rn(dy, eps)), 32.f, OG_RINT_MAGIC);
+	const float uyh = __fmaf_rn(__fadd_rn(n.v00.y, __fadd_rn(dy, eps)), 32.f, OG_RINT_MAGIC);
+	sx = __float_as_int(uxl) - OG_RINT_BITS;
+	sy = __float_as_int(uyl) - OG_RINT_BITS;
+	// the mantissa only holds cvRound(32 x) while 32 x stays below 2^22: the interior test keeps
+	// x inside the page (< 32767), and a NaN compares unequal
+	return n.ok && uxl == uxh && uyl == uyh && (unsigned)(sx >> 5) < (unsigned)W1 && (unsigned)(sy >> 5) < (unsigned)H1;
+}
+
+// the undecided sample, start to finish in the reference's arithmetic
+__device__ __noinline__ og_taps og_sample_taps_exact(const uint8_t *__restrict__ src, int H, int W, int pitch,
+	const float2 *__restrict__ map, int Wd, int Hm, int Wm, double px, double py) {
+	const int2 s = og_map_sample_exact_fixed(map, Wd, Hm, Wm, px, py);
+	const int sx[1] = {s.x}, sy[1] = {s.y};
+	og_taps t[1];
+	og_load_taps_fixed<1>(src, H, W, pitch, sx, sy, t);
+	return t[0];
+}
+
+__device__ __forceinline__ void og_taps_interior(og_taps &t, const uint8_t *__restrict__ src, int pitch, int sx, int sy) {
+	const uint8_t *q = src + ((sy >> 5) * pitch + (sx >> 5));
+	t.fx = sx & 31;
+	t.fy = sy & 31;
+	t.p00 = __ldg(q);
+	t.p01 = __ldg(q + 1);
+	t.p10 = __ldg(q + pitch);
+	t.p11 = __ldg(q + pitch + 1);
+}
+
+// One strip column: `rows` rows whose (ys + p0) sit in the warp's shared-memory table at
+// tab_saddr; `out` points at the column's pixel of the FIRST row and moves up the flipped strip
+// (pixels[::-1, :], block.py:257).  Three batches of RB rows are in flight: node loads of batch
+// k+1, tap loads of batch k, blend + store of batch k-1.
+template <int NB>
+__device__ __forceinline__ void og_strip_column_screened(const LineParams &p, const float2 *__restrict__ map,
+	unsigned tab_saddr, int rows, og_d2 xc, uint8_t *__restrict__ out, int xsteps) {
+	const uint8_t *__restrict__ src = p.src;
+	auto point = [&](int r, double &px, double &py) {
+		double rbx, rby;
+		asm volatile("ld.shared.v2.f64 {%0, %1}, [%2];" : "=d"(rbx), "=d"(rby) : "r"(tab_saddr + r * 16));
+		px = __dadd_rn(rbx, xc.x);  // dewarped_grid = (ys + p0)[:, None] + xs[None, :]   (block.py:241)
+		py = __dadd_rn(rby, xc.y);
+	};
+	auto load = [&](og_nodes (&n)[NB], int r) {
+#pragma unroll
+		for (int u = 0; u < NB; ++u) {
+			double px, py;
+			point(r + u, px, py);
+			og_nodes_load(n[u], px, py, map, p.Wd, p.Hm, p.Wm, p.one_bits);
+		}
+	};
+	auto taps = [&](const og_nodes (&n)[NB], og_taps (&t)[NB], int r) {
+		int sx[NB], sy[NB];
+		bool ok[NB], good = true;
+#pragma unroll
+		for (int u = 0; u < NB; ++u) {
+			ok[u] = og_nodes_screen(n[u], p.W1, p.H1, sx[u], sy[u]);
+			good = good && ok[u];
+		}
+		if (good) {
+#pragma unroll
+			for (int u = 0; u < NB; ++u) og_taps_interior(t[u], src, p.src_pitch, sx[u], sy[u]);
+		} else {
+#pragma unroll
+			for (int u = 0; u < NB; ++u) {
+				if (ok[u]) {
+					og_taps_interior(t[u], src, p.src_pitch, sx[u], sy[u]);
+				} else {
+					double px, py;
+					point(r + u, px, py);
+					t[u] = og_sample_taps_exact(src, p.H, p.W, p.src_pitch, map, p.Wd, p.Hm, p.Wm, px, py);
+				}
+			}
+		}
+	};
+	auto store = [&](const og_taps (&t)[NB]) {
+#pragma unroll
+		for (int u = 0; u < NB; ++u) {
+			*out = (uint8_t)og_blend_taps(t[u]);
+			out -= xsteps;
+		}
+	};
+
+	const int nb = rows / NB;  // full batches; the caller handles rows % NB with NB = 1
+	if (nb == 0) return;
+	og_nodes n0[NB], n1[NB];
+	og_taps t0[NB], t1[NB];
+	load(n0, 0);
+	load(n1, min(1, nb - 1) * NB);
+	taps(n0, t0, 0);
+	int b = 1;
+	for (; b + 1 < nb; b += 2) {  // on entry: t0 = taps of batch b-1, n1 = nodes of batch b
+		load(n0, (b + 1) * NB);
+		store(t0);  // before the next taps are requested: only one tap buffer is live at a time
+		taps(n1, t1, b * NB);
+		load(n1, min(b + 2, nb - 1) * NB);
+		store(t1);
+		taps(n0, t0, (b + 1) * NB);
+	}
+	store(t0);
+	if (b < nb) {
+		taps(n1, t1, b * NB);
+		store(t1);
+	}
+}
+
+// the same column in the reference's arithmetic only (lines with absurd coordinates)
+__device__ __noinline__ void og_strip_column_exact(const LineParams &p, const float2 *__restrict__ map,
+	unsigned tab_saddr, int rows, og_d2 xc, uint8_t *__restrict__ out, int xsteps) {
+	for (int r = 0; r < rows; ++r) {
+		double rbx, rby;
+		asm volatile("ld.shared.v2.f64 {%0, %1}, [%2];" : "=d"(rbx), "=d"(rby) : "r"(tab_saddr + r * 16));
+		const og_taps t = og_sample_taps_exact(p.src, p.H, p.W, p.src_pitch, map, p.Wd, p.Hm, p.Wm,
+			__dadd_rn(rbx, xc.x), __dadd_rn(rby, xc.y));
+		*out = (uint8_t)og_blend_taps(t);
+		out -= xsteps;
+	}
+}
+
+// Strips through the screened path: a warp owns a (line, 32-column) item, a lane one column.
+// Items are dealt round-robin, so the warps that run together work on neighbouring items and
+// share the DRAM pages / L2 lines of the map rows under them (one contiguous range of items per
+// warp was measured: twice the DRAM traffic, 314 vs 290 us).
+#ifndef OG_SCR_WARPS
+#define OG_SCR_WARPS 8
+#endif
+#ifndef OG_SCR_BLOCKS
+#define OG_SCR_BLOCKS 3
+#endif
+constexpr int SWARPS = OG_SCR_WARPS;  // warps per CTA: there is no CTA-wide barrier in the item loop
+constexpr int STHREADS = SWARPS * 32;
+
+__global__ void __launch_bounds__(STHREADS, OG_SCR_BLOCKS) og_strips_screened_kernel(const __grid_constant__ LineParams p, const float2 *__restrict__ map) {
+	__shared__ double2 s_rowbase[SWARPS][MAX_ROWS];
+	__shared__ int s_chunk_offsets[MAP_OFFS_CAP];
+	const bool offs_cached = p.n + 1 <= MAP_OFFS_CAP;
+	if (offs_cached) {
+		for (int i = threadIdx.x; i <= p.n; i += STHREADS) s_chunk_offsets[i] = __ldg(p.chunk_offsets + i);
+		__syncthreads();
+	}
+	const int32_t *chunk_offsets = offs_cached ? s_chunk_offsets : p.chunk_offsets;
+	const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+	const int total_items = 2 * chunk_offsets[p.n];  // two 32-column halves per 64-column chunk
+	const int nwarps = gridDim.x * SWARPS;
+	double2 *rowbase = s_rowbase[wid];
+	const unsigned rb_saddr = (unsigned)__cvta_generic_to_shared(rowbase);
+
+	// Work is handed out through a ticket counter (the extra entry behind the prefix sums): the SMs
+	// differ by +-13 % in speed on this kernel, which a static deal turns into idle time.  Tickets
+	// are items in order, so the warps that run together still work on neighbouring items; the last
+	// two rounds' worth of items is cut into row quarters so that everybody finishes together.  A
+	// warp draws its next ticket before it starts on the current one (the atomic's latency hides
+	// behind the item), and the warp that draws the very last ticket resets the counter.
+	constexpr int PIECES = 4;
+	const int tail_items = min(total_items, 2 * nwarps), head_items = total_items - tail_items;
+	const int total_tickets = head_items + tail_items * PIECES;
+	auto draw = [&]() {
+		int t = 0;
+		if (lane == 0) t = atomicAdd(p.ticket, 1);
+		return __shfl_sync(0xffffffffu, t, 0);
+	};
+	auto work = [&](int tk) {
+		int item = tk, piece = 0, npieces = 1;
+		if (tk >= head_items) {
+			item = head_items + (tk - head_items) / PIECES;
+			piece = (tk - head_items) % PIECES;
+			npieces = PIECES;
+		}
+		const int chunk_item = item >> 1;
+		int li = 0;
+		{
+			int hi = p.n;  // invariant: chunk_offsets[li] <= chunk_item < chunk_offsets[hi]
+			while (hi - li > 1) {
+				const int mid = (li + hi) >> 1;
+				if (chunk_offsets[mid] <= chunk_item) li = mid; else hi = mid;
+			}
+		}
+		const int xsteps = __ldg(p.steps + 2 * li), ysteps = __ldg(p.steps + 2 * li + 1);
+		const int c0 = (chunk_item - chunk_offsets[li]) * CW + (item & 1) * MW;
+		if (c0 >= xsteps) return;
+		const long long pix0 = __ldg(p.pix_offsets + li);
+		if (pix0 + (long long)xsteps * ysteps > p.capacity) return;
+		// this warp's rows of the item (an even count, so that only the strip's own last row can be odd)
+		const int row_a = (int)((long long)ysteps * piece / npieces) & ~1;
+		const int row_z = piece + 1 == npieces ? ysteps : (int)((long long)ysteps * (piece + 1) / npieces) & ~1;
+		if (row_a >= row_z) return;
+		const og_line *ln = p.lines + li;
+		const double cpx = ln->cp[0], cpy = ln->cp[1];
+		const double crx = ln->cright[0], cry = ln->cright[1], upx = ln->up[0], upy = ln->up[1];
+		const og_lin lx = og_linspace_setup(crx, cry, xsteps);
+		const og_lin ly = og_linspace_setup(upx, upy, ysteps);
+		// every sample is cp + s * cright + t * up with s, t in [0, 1]: below this bound the
+		// fixed-point trick of og_nodes_load is valid for the whole line (false for NaN / inf)
+		const bool sane = fabs(cpx) + fabs(cpy) + fabs(crx) + fabs(cry) + fabs(upx) + fabs(upy) < 134217728.0;
+		const int cc = c0 + lane;
+		const og_d2 xc = og_linspace_at(lx, min(cc, xsteps - 1));
+		for (int rb0 = row_a; rb0 < row_z; rb0 += MAX_ROWS) {
+			const int rows = min(row_z - rb0, MAX_ROWS);
+			__syncwarp();
+			for (int r = lane; r < rows; r += 32) {  // (ys + p0) of the block's rows   (block.py:241)
+				const og_d2 yr = og_linspace_at(ly, rb0 + r);
+				rowbase[r] = make_double2(__dadd_rn(yr.x, cpx), __dadd_rn(yr.y, cpy));
+			}
+			__syncwarp();
+			if (cc >= xsteps) continue;
+			uint8_t *out = p.strips_out + pix0 + cc + (long long)(ysteps - 1 - rb0) * xsteps;
+			if (sane) {
+				og_strip_column_screened<RB>(p, map, rb_saddr, rows, xc, out, xsteps);
+				const int done = rows / RB * RB;
+				if (done < rows)
+					og_strip_column_screened<1>(p, map, rb_saddr + done * 16, rows - done, xc, out - (long long)done * xsteps, xsteps);
+			} else {
+				og_strip_column_exact(p, map, rb_saddr, rows, xc, out, xsteps);
+			}
+		}
+	};
+
+	int tk = draw();
+	while (tk < total_tickets) {
+		const int tk_next = draw();
+		work(tk);
+		tk = tk_next;
+	}
+	// every warp draws exactly one ticket past the end
+	if (lane == 0 && tk == total_tickets + nwarps - 1) *p.ticket = 0;
+}
+
 template <int MODE, bool BBOX>
 __global__ void __launch_bounds__(MTHREADS, OG_MAP_MINBLOCKS) og_lines_map_kernel(const __grid_constant__ LineParams p, const float2 *__restrict__ map) {
 	__shared__ double2 s_rowbase[MWARPS][MAX_ROWS];
@@ -560,22 +868,22 @@ __global__ void __launch_bounds__(MTHREADS, OG_MAP_MINBLOCKS) og_lines_map_kerne
 		const double cpx = ln->cp[0], cpy = ln->cp[1];
 		const og_lin lx = og_linspace_setup(ln->cright[0], ln->cright[1], xsteps);
 		const og_lin ly = og_linspace_setup(ln->up[0], ln->up[1], ysteps);
-		const bool tabled = ysteps <= MAX_ROWS;
-		__syncwarp();
-		if (tabled) {
-			for (int r = lane; r < ysteps; r += 32) {
-				og_d2 yr = og_linspace_at(ly, r);
-				rowbase[r] = make_double2(__dadd_rn(yr.x, cpx), __dadd_rn(yr.y, cpy));
-			}
-		}
 		if (MODE == MODE_LABELS)
 			for (int q = lane; q <= MAX_CLASSES; q += 32) s_whist[wid][q] = 0;
-		__syncwarp();
-
 		float bx0 = 3.0e38f, by0 = 3.0e38f, bx1 = -3.0e38f, by1 = -3.0e38f;
 		const int cc = c0 + lane;
+		const og_d2 xc = og_linspace_at(lx, min(cc, xsteps - 1));
+		// rows in blocks of MAX_ROWS (one block for any OCR strip height): (ys + p0) of the block's
+		// rows goes to the warp's shared-memory table   (block.py:241)
+		for (int rb0 = 0; rb0 < ysteps; rb0 += MAX_ROWS) {
+		const int rb_end = min(ysteps, rb0 + MAX_ROWS);
+		__syncwarp();
+		for (int r = rb0 + lane; r < rb_end; r += 32) {
+			og_d2 yr = og_linspace_at(ly, r);
+			rowbase[r - rb0] = make_double2(__dadd_rn(yr.x, cpx), __dadd_rn(yr.y, cpy));
+		}
+		__syncwarp();
 		if (cc < xsteps) {
-			const og_d2 xc = og_linspace_at(lx, cc);
 			uint8_t *strip = (MODE == MODE_STRIP) ? p.strips_out + pix0 + cc : nullptr;
 			float2 *gout = (MODE == MODE_GRID) ? reinterpret_cast<float2 *>(p.grids_out) + pix0 + cc : nullptr;
 			const float2 *__restrict__ map_lo = map;
@@ -589,16 +897,10 @@ __global__ void __launch_bounds__(MTHREADS, OG_MAP_MINBLOCKS) og_lines_map_kerne
 #pragma unroll
 				for (int u = 0; u < RB; ++u) {
 					const int r = rbase + u;
-					row[u] = r < ysteps ? r : -1;
-					const int rr = r < ysteps ? r : ysteps - 1;
+					row[u] = r < rb_end ? r : -1;
+					const int rr = min(r, rb_end - 1) - rb0;
 					double rbx, rby;
-					if (tabled) {
-						asm volatile("ld.shared.v2.f64 {%0, %1}, [%2];" : "=d"(rbx), "=d"(rby) : "r"(rb_saddr + rr * 16));
-					} else {
-						og_d2 yr = og_linspace_at(ly, rr);
-						rbx = __dadd_rn(yr.x, cpx);
-						rby = __dadd_rn(yr.y, cpy);
-					}
+					asm volatile("ld.shared.v2.f64 {%0, %1}, [%2];" : "=d"(rbx), "=d"(rby) : "r"(rb_saddr + rr * 16));
 					// dewarped_grid = (ys + p0)[:, None] + xs[None, :]   (block.py:241)
 					const double px = __dadd_rn(rbx, xc.x);
 					const double py = __dadd_rn(rby, xc.y);
@@ -641,7 +943,7 @@ __global__ void __launch_bounds__(MTHREADS, OG_MAP_MINBLOCKS) og_lines_map_kerne
 				int r0[RB], r1[RB];
 #pragma unroll
 				for (int u = 0; u < RB; ++u) r1[u] = -1;
-				for (int rbase = 0; rbase < ysteps; rbase += 2 * RB) {
+				for (int rbase = rb0; rbase < rb_end; rbase += 2 * RB) {
 					float gx[RB], gy[RB];
 					coords(rbase, gx, gy, r0);
 					og_load_taps_batch<RB>(src, H, W, spitch, gx, gy, t0);
@@ -666,7 +968,7 @@ __global__ void __launch_bounds__(MTHREADS, OG_MAP_MINBLOCKS) og_lines_map_kerne
 				}
 				flush(t1, r1);
 			} else {
-				for (int rbase = 0; rbase < ysteps; rbase += RB) {
+				for (int rbase = rb0; rbase < rb_end; rbase += RB) {
 					float gx[RB], gy[RB];
 					int row[RB];
 					coords(rbase, gx, gy, row);
@@ -685,6 +987,7 @@ __global__ void __launch_bounds__(MTHREADS, OG_MAP_MINBLOCKS) og_lines_map_kerne
 				}
 			}
 		}
+		}  // row block
 		if (BBOX) {
 #pragma unroll
 			for (int o = 16; o > 0; o >>= 1) {
@@ -764,6 +1067,18 @@ int launch_lines(const LineParams &p, cudaStream_t st) {
 template <int MODE, bool BBOX>
 int launch_lines_any(const LineParams &p, const float *map, cudaStream_t st) {
 	if (map == nullptr) return launch_lines<MODE, BBOX>(p, st);
+	if (MODE == MODE_STRIP && !BBOX && OG_LINES_SCREEN) {
+		LineParams q = p;
+		q.Wd = p.gw * p.cell;
+		q.Hm = p.gh * p.cell - 2;
+		q.Wm = q.Wd - 2;
+		q.W1 = p.W - 1;
+		q.H1 = p.H - 1;
+		q.one_bits = 0x3F800000u;
+		q.ticket = const_cast<int *>(p.chunk_offsets) + p.n + 1;
+		og_strips_screened_kernel<<<OG_NUM_SMS * OG_SCR_BLOCKS, STHREADS, 0, st>>>(q, reinterpret_cast<const float2 *>(map));
+		return og_check_launch("og_strips_screened_kernel");
+	}
 	og_lines_map_kernel<MODE, BBOX><<<OG_NUM_SMS * OG_MAP_MINBLOCKS, MTHREADS, 0, st>>>(p, reinterpret_cast<const float2 *>(map));
 	return og_check_launch("og_lines_map_kernel");
 }
@@ -830,7 +1145,7 @@ extern "C" int og_warped_grids(const float *grid, int gh, int gw, int cell, cons
 extern "C" int og_extract_lines(const uint8_t *src, int H, int W, int64_t src_pitch,
 	const float *grid, int gh, int gw, int cell, const float *map,
 	const og_line *lines, int n,
-	const int32_t *steps, const int64_t *pix_offsets, const int32_t *chunk_offsets,
+	const int32_t *steps, const int64_t *pix_offsets, int32_t *chunk_offsets,
 	uint8_t *strips_out, int64_t capacity, int32_t *bbox_out, void *stream) {
 	int rc = check_grid(grid, gh, gw, cell);
 	if (rc) return rc;

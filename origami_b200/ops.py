@@ -186,7 +186,7 @@ def line_steps(grid, cell, lines_dev, n):
 	dev = grid.device
 	steps = torch.empty((max(n, 1), 2), dtype=torch.int32, device=dev)
 	pix = torch.empty((n + 1,), dtype=torch.int64, device=dev)
-	chunks = torch.empty((n + 1,), dtype=torch.int32, device=dev)
+	chunks = torch.empty((n + 2,), dtype=torch.int32, device=dev)  # n + 1 prefix sums + the work ticket
 	_lib.call("og_line_steps", grid.data_ptr(), gh, gw, cell, lines_dev.data_ptr(), n,
 		steps.data_ptr(), pix.data_ptr(), chunks.data_ptr(), _stream())
 	return LinePlan(lines_dev, n, steps, pix, chunks)
