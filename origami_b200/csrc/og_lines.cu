@@ -717,6 +717,39 @@ __device__ __noinline__ void og_strip_column_exact(const LineParams &p, const fl
 	}
 }
 
+// The line of a work item: 32-ary search of the prefix sums by the whole warp (three probes for
+// 2000 lines instead of eleven dependent loads).  offs[0] = 0 <= c < offs[n].
+__device__ __forceinline__ int og_find_line(const int32_t *offs, int n, int c, int lane) {
+	int lo = 0, hi = n;  // invariant: offs[lo] <= c < offs[hi]
+	while (hi - lo > 1) {
+		const int step = (hi - lo + 31) >> 5;
+		const int idx = lo + lane * step;
+		const bool le = idx < hi && offs[idx] <= c;  // true for a prefix of the lanes, lane 0 included
+		const int cnt = __popc(__ballot_sync(0xffffffffu, le));
+		lo += (cnt - 1) * step;
+		hi = min(lo + step, hi);
+	}
+	return lo;
+}
+
+// og_linspace_setup for the x and the y direction of a line at once: the four float64 divisions
+// run in four lanes side by side instead of one after the other in every lane.
+__device__ __forceinline__ void og_linspace_setup_pair(double crx, double cry, double upx, double upy,
+	int xsteps, int ysteps, int lane, og_lin &lx, og_lin &ly) {
+	const int k = lane & 3;
+	const double stop = k == 0 ? crx : k == 1 ? cry : k == 2 ? upx : upy;
+	const int num = k < 2 ? xsteps : ysteps;
+	const double q = num > 1 ? __ddiv_rn(stop, (double)(num - 1)) : stop;
+	lx.num = xsteps; lx.stopx = crx; lx.stopy = cry; lx.div = (double)(xsteps - 1);
+	lx.stepx = __shfl_sync(0xffffffffu, q, 0);
+	lx.stepy = __shfl_sync(0xffffffffu, q, 1);
+	lx.any_zero = xsteps > 1 && (lx.stepx == 0.0 || lx.stepy == 0.0);
+	ly.num = ysteps; ly.stopx = upx; ly.stopy = upy; ly.div = (double)(ysteps - 1);
+	ly.stepx = __shfl_sync(0xffffffffu, q, 2);
+	ly.stepy = __shfl_sync(0xffffffffu, q, 3);
+	ly.any_zero = ysteps > 1 && (ly.stepx == 0.0 || ly.stepy == 0.0);
+}
+
 // Strips through the screened path: a warp owns a (line, 32-column) item, a lane one column.
 // Items are dealt round-robin, so the warps that run together work on neighbouring items and
 // share the DRAM pages / L2 lines of the map rows under them (one contiguous range of items per
@@ -724,8 +757,11 @@ __device__ __noinline__ void og_strip_column_exact(const LineParams &p, const fl
 #ifndef OG_SCR_WARPS
 #define OG_SCR_WARPS 8
 #endif
+#ifndef OG_SCR_TAIL_HALVES
+#define OG_SCR_TAIL_HALVES 2  // items cut into row quarters at the end of the ticket list, in half rounds
+#endif
 #ifndef OG_SCR_BLOCKS
-#define OG_SCR_BLOCKS 3
+#define OG_SCR_BLOCKS 4
 #endif
 constexpr int SWARPS = OG_SCR_WARPS;  // warps per CTA: there is no CTA-wide barrier in the item loop
 constexpr int STHREADS = SWARPS * 32;
@@ -748,11 +784,11 @@ __global__ void __launch_bounds__(STHREADS, OG_SCR_BLOCKS) og_strips_screened_ke
 	// Work is handed out through a ticket counter (the extra entry behind the prefix sums): the SMs
 	// differ by +-13 % in speed on this kernel, which a static deal turns into idle time.  Tickets
 	// are items in order, so the warps that run together still work on neighbouring items; the last
-	// two rounds' worth of items is cut into row quarters so that everybody finishes together.  A
+	// items (two quarters per warp) are cut into row quarters so that everybody finishes together.  A
 	// warp draws its next ticket before it starts on the current one (the atomic's latency hides
 	// behind the item), and the warp that draws the very last ticket resets the counter.
 	constexpr int PIECES = 4;
-	const int tail_items = min(total_items, 2 * nwarps), head_items = total_items - tail_items;
+	const int tail_items = min(total_items, nwarps * OG_SCR_TAIL_HALVES / 2), head_items = total_items - tail_items;
 	const int total_tickets = head_items + tail_items * PIECES;
 	auto draw = [&]() {
 		int t = 0;
@@ -767,14 +803,7 @@ __global__ void __launch_bounds__(STHREADS, OG_SCR_BLOCKS) og_strips_screened_ke
 			npieces = PIECES;
 		}
 		const int chunk_item = item >> 1;
-		int li = 0;
-		{
-			int hi = p.n;  // invariant: chunk_offsets[li] <= chunk_item < chunk_offsets[hi]
-			while (hi - li > 1) {
-				const int mid = (li + hi) >> 1;
-				if (chunk_offsets[mid] <= chunk_item) li = mid; else hi = mid;
-			}
-		}
+		const int li = og_find_line(chunk_offsets, p.n, chunk_item, lane);
 		const int xsteps = __ldg(p.steps + 2 * li), ysteps = __ldg(p.steps + 2 * li + 1);
 		const int c0 = (chunk_item - chunk_offsets[li]) * CW + (item & 1) * MW;
 		if (c0 >= xsteps) return;
@@ -787,8 +816,8 @@ __global__ void __launch_bounds__(STHREADS, OG_SCR_BLOCKS) og_strips_screened_ke
 		const og_line *ln = p.lines + li;
 		const double cpx = ln->cp[0], cpy = ln->cp[1];
 		const double crx = ln->cright[0], cry = ln->cright[1], upx = ln->up[0], upy = ln->up[1];
-		const og_lin lx = og_linspace_setup(crx, cry, xsteps);
-		const og_lin ly = og_linspace_setup(upx, upy, ysteps);
+		og_lin lx, ly;
+		og_linspace_setup_pair(crx, cry, upx, upy, xsteps, ysteps, lane, lx, ly);
 		// every sample is cp + s * cright + t * up with s, t in [0, 1]: below this bound the
 		// fixed-point trick of og_nodes_load is valid for the whole line (false for NaN / inf)
 		const bool sane = fabs(cpx) + fabs(cpy) + fabs(crx) + fabs(cry) + fabs(upx) + fabs(upy) < 134217728.0;
