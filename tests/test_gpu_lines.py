@@ -203,3 +203,93 @@ def test_degenerate_coordinates_are_flagged(cuda):
 	plan = ops.line_steps(g, 25, ops.lines_to_device(ops.pack_lines(recs), cuda), 2)
 	steps = plan.steps.cpu().numpy()
 	assert steps[0].tolist() == [0, 0] and steps[1].min() >= 2
+
+
+# ---------------------------------------------------------------------------------------
+# The float32-screened strip path (dense map given, no bounding boxes asked for)
+# ---------------------------------------------------------------------------------------
+def _adversarial_maps(dense, seed=5):
+	"""Dense maps that are NOT the expansion of a grid: rough ones (large node differences, so a
+	wide screening interval), ones that leave the page, and ones whose values sit exactly on the
+	1/64-px lattice where cv2.remap's rounding flips."""
+	rng = np.random.default_rng(seed)
+	f32 = np.float32
+	return {
+		"noise 0.5 px": (dense + rng.normal(0, 0.5, dense.shape)).astype(f32),
+		"noise 30 px": (dense + rng.normal(0, 30, dense.shape)).astype(f32),
+		"partly outside": (dense * f32(1.7)).astype(f32),
+		"negative": (dense - f32(40)).astype(f32),
+		"constant": np.full_like(dense, 123.5),
+		"tiny": (dense * f32(1e-3)).astype(f32),
+		"on the 1/64 lattice": (np.round(dense * 64) / 64).astype(f32),
+		"on the rounding ties": (np.round(dense * 32) / 32 + f32(1 / 64)).astype(f32),
+		"far outside": (dense * f32(1e6)).astype(f32),
+	}
+
+
+@pytest.mark.parametrize("ysteps", [48, 7])
+def test_screened_strips_on_adversarial_maps(cuda, ysteps):
+	page, grid, dense, lines = _setup(cuda, n_lines=40, seed=3)
+	g = torch.from_numpy(grid).to(cuda)
+	src = ops.to_device_image(page, cuda)
+	recs = _records(lines, ysteps=ysteps, xsteps=150)
+	plan = ops.line_steps(g, 25, ops.lines_to_device(ops.pack_lines(recs), cuda), len(recs))
+	offs = plan.pix_offsets.cpu().numpy()
+	for name, m in _adversarial_maps(dense).items():
+		out = torch.zeros((int(offs[-1]),), dtype=torch.uint8, device=cuda)
+		ops.extract_lines(src, g, 25, plan, out, dense_map=torch.from_numpy(m).to(cuda))
+		out = out.cpu().numpy()
+		for i, r in enumerate(recs):
+			wg = exact.warped_grid(m, r["p"], r["right"], r["up"], xsteps=150, ysteps=ysteps)
+			want = exact.remap_linear(page, wg)[::-1]
+			assert np.array_equal(out[offs[i]:offs[i + 1]].reshape(want.shape), want), (name, i)
+
+
+def test_screened_strips_equal_the_float64_path(cuda):
+	"""A page-sized case: the screened kernel against the kernel that evaluates every sample in
+	float64 (the bounding-box variant), on the grid's own map and on rough ones."""
+	page, grid, dense, lines = _setup(cuda, width=1500, height=2000, n_lines=400, seed=21, dpi=600, kind="text")
+	g = torch.from_numpy(grid).to(cuda)
+	src = ops.to_device_image(page, cuda)
+	recs = _records(lines, ysteps=48)
+	recs += [dict(p=[40.0, 900.0], right=[700.0, 650.0], up=[30.0, -32.0], ysteps=48),      # steep
+		dict(p=[-50.0, 300.0], right=[400.0, 3.0], up=[1.0, -60.0], ysteps=51),               # off-page, odd height
+		dict(p=[200.0, 1500.0], right=[900.0, -8.0], up=[2.0, -70.0], ysteps=300)]            # taller than the row table
+	plan = ops.line_steps(g, 25, ops.lines_to_device(ops.pack_lines(recs), cuda), len(recs))
+	total = int(plan.pix_offsets[-1].item())
+	bbox = torch.zeros((len(recs), 4), dtype=torch.int32, device=cuda)
+	maps = {"grid": ops.expand_map(g, 25)}
+	maps.update({k: torch.from_numpy(v).to(cuda) for k, v in _adversarial_maps(dense).items()})
+	for name, m in maps.items():
+		a = torch.zeros((total,), dtype=torch.uint8, device=cuda)
+		b = torch.zeros((total,), dtype=torch.uint8, device=cuda)
+		ops.extract_lines(src, g, 25, plan, a, dense_map=m)
+		ops.extract_lines(src, g, 25, plan, b, bbox, dense_map=m)
+		assert torch.equal(a, b), name
+		# the work ticket behind the prefix sums is back at zero, so the plan can be used again
+		assert int(plan.chunk_offsets[len(recs) + 1].item()) == 0
+		a2 = torch.zeros_like(a)
+		ops.extract_lines(src, g, 25, plan, a2, dense_map=m)
+		assert torch.equal(a, a2), name
+
+
+def test_screened_strips_with_absurd_line_coordinates(cuda):
+	"""Coordinates beyond 2^27 switch the whole line to the float64 path (the fixed-point trick of
+	the screening needs |x| < 2^27); the result is whatever the reference's arithmetic gives."""
+	page, grid, dense, _ = _setup(cuda, seed=4)
+	g = torch.from_numpy(grid).to(cuda)
+	src = ops.to_device_image(page, cuda)
+	recs = [dict(p=[1.0e9, 50.0], right=[100.0, 0.0], up=[0.0, -20.0], ysteps=8, xsteps=64),
+		dict(p=[100.0, 200.0], right=[3.0e8, 0.0], up=[0.0, -20.0], ysteps=8, xsteps=64),
+		dict(p=[100.0, 200.0], right=[200.0, 0.0], up=[0.0, -20.0], ysteps=8, xsteps=64)]
+	plan = ops.line_steps(g, 25, ops.lines_to_device(ops.pack_lines(recs), cuda), len(recs))
+	total = int(plan.pix_offsets[-1].item())
+	bbox = torch.zeros((len(recs), 4), dtype=torch.int32, device=cuda)
+	m = ops.expand_map(g, 25)
+	a = torch.zeros((total,), dtype=torch.uint8, device=cuda)
+	b = torch.zeros((total,), dtype=torch.uint8, device=cuda)
+	ops.extract_lines(src, g, 25, plan, a, dense_map=m)
+	ops.extract_lines(src, g, 25, plan, b, bbox, dense_map=m)
+	assert total == 3 * 8 * 64 and torch.equal(a, b)
+	want = exact.remap_linear(page, exact.warped_grid(dense, recs[2]["p"], recs[2]["right"], recs[2]["up"], xsteps=64, ysteps=8))[::-1]
+	assert np.array_equal(a.cpu().numpy()[2 * 512:].reshape(want.shape), want)
