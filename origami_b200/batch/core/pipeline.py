@@ -99,6 +99,31 @@ def pinned_page(pixels_or_shape):
 	return a
 
 
+def _estimate_xsteps(grid, cell, desc):
+	"""Upper estimate of the strip widths og_line_steps will derive (Line.warped_grid's rough 2x2
+	grid, block.py:226-236), from a float64 bilinear evaluation of the sparse grid on the host.
+	It only sizes the strip buffer and the device->host copy: two columns of slack per line, and a
+	page whose strips still do not fit is run again with the exact size."""
+	xs = desc["xsteps"].astype(np.int64)
+	derive = xs <= 0
+	if derive.any():
+		gx = grid[..., 0].astype(np.float64)
+		gh, gw = gx.shape
+		p, right, up = desc["p"][derive], desc["right"][derive], desc["up"][derive]
+		corners = np.stack([p, p + right, up + p, up + p + right], axis=1)  # (m, 4, 2) dewarped (x, y)
+		u = (corners[..., 0] + 0.5) / cell - 0.5
+		v = (corners[..., 1] + 0.5) / cell - 0.5
+		with np.errstate(invalid="ignore"):
+			j0 = np.clip(np.floor(np.nan_to_num(u)), 0, gw - 2).astype(np.int64)
+			i0 = np.clip(np.floor(np.nan_to_num(v)), 0, gh - 2).astype(np.int64)
+			fu, fv = u - j0, v - i0
+			wx = (gx[i0, j0] * (1 - fu) + gx[i0, j0 + 1] * fu) * (1 - fv) + (gx[i0 + 1, j0] * (1 - fu) + gx[i0 + 1, j0 + 1] * fu) * fv
+			ext = np.maximum(np.abs(wx[:, 0] - wx[:, 1]), np.abs(wx[:, 2] - wx[:, 3])) * desc["xres"][derive]
+			ext = np.where(np.isfinite(ext), np.minimum(ext, 1.0e6), 0.0)
+		xs[derive] = np.maximum(2, np.ceil(ext * 1.002)) + 2
+	return xs
+
+
 class PagePipeline:
 	"""pipeline = PagePipeline(line_height=48, binarize="otsu"); for res in pipeline.run(jobs): ...
 
@@ -120,7 +145,7 @@ class PagePipeline:
 		self.slots = [_Slot(self.device) for _ in range(max(2, depth))]
 
 	# -- one page: everything is enqueued on the slot's stream, nothing waits
-	def _submit(self, slot, job):
+	def _submit(self, slot, job, cap=None):
 		page, grid, cell, lines = job
 		page = np.ascontiguousarray(page, dtype=np.uint8)
 		grid = np.ascontiguousarray(grid, dtype=np.float32)
@@ -132,14 +157,12 @@ class PagePipeline:
 			# Line.record / ops.pack_lines); the strip height is this pipeline's
 			desc = lines.copy()
 			desc["ysteps"] = self.line_height
-			right = desc["cright"]
 		else:
 			lines = np.ascontiguousarray(lines, dtype=np.float64).reshape(-1, 3, 2)
 			desc = ops.pack_line_arrays(lines[:, 0], lines[:, 1], lines[:, 2], ysteps=self.line_height)
-			right = lines[:, 1]
 		n = desc.shape[0]
-		lengths = np.hypot(right[:, 0], right[:, 1]) * np.maximum(desc["xres"], 1e-9)
-		cap = int(np.sum(self.line_height * (np.ceil(lengths * 1.1) + 16))) if n else 1
+		if cap is None:
+			cap = int(np.sum(self.line_height * _estimate_xsteps(grid, cell, desc))) if n else 1
 
 		pitch = W  # the source is only read with byte loads: no row padding, one contiguous copy
 		dpitch = (Wd + 127) // 128 * 128
@@ -175,6 +198,7 @@ class PagePipeline:
 		if n:
 			hin[o_desc:o_desc + desc.nbytes] = desc.view(np.uint8).reshape(-1)
 		slot.keep = (page, pinned_src)  # the source must stay alive until the upload has run
+		slot.job = job
 
 		st = slot.stream
 		with torch.cuda.stream(st):
@@ -199,7 +223,7 @@ class PagePipeline:
 					mode = ops.OG_BIN_OTSU if self.binarize[0] == "otsu" else ops.OG_BIN_SAUVOLA
 					window = self.binarize[1] if len(self.binarize) > 1 else 15
 					_lib.call("og_binarize_strips", target, base_out + o_steps, base_out + o_offs, slot.d_chunks.data_ptr(),
-						n, mode, window, base_out + o_strips, 0, s)
+						n, mode, window, base_out + o_strips, cap, 0, s)
 			slot.h_out[:n_out].copy_(slot.d_out[:n_out], non_blocking=True)
 			slot.done = torch.cuda.Event()
 			slot.done.record(st)
@@ -214,7 +238,10 @@ class PagePipeline:
 		steps = hout[o_steps:o_steps + 8 * n].view(np.int32).reshape(n, 2)
 		offs = hout[o_offs:o_offs + 8 * (n + 1)].view(np.int64)
 		if n and int(offs[n]) > cap:
-			raise _lib.OrigamiB200Error("strip buffer estimate too small (%d > %d)" % (int(offs[n]), cap))
+			# the host-side estimate of the strip widths fell short (it is not bit-exact): run the
+			# page again with the size the device computed
+			self._submit(slot, slot.job, cap=int(offs[n]))
+			return self._collect(slot)
 		if n and (steps <= 0).any():
 			raise ValueError("line %d has a degenerate or non-finite extent" % int(np.argmax((steps <= 0).any(axis=1))))
 		flat = hout[o_strips:o_strips + cap]

@@ -120,7 +120,7 @@ constexpr int HREP = OG_HREP;
 
 __global__ void __launch_bounds__(BTHREADS) og_otsu_strips_kernel(
 	const uint8_t *__restrict__ gray, const int32_t *__restrict__ steps, const int64_t *__restrict__ pix_offsets,
-	int n, uint8_t *__restrict__ out, int32_t *__restrict__ thresholds) {
+	int n, uint8_t *__restrict__ out, int64_t capacity, int32_t *__restrict__ thresholds) {
 	__shared__ unsigned int rep[256 * HREP];
 	__shared__ unsigned int hist[256];
 	__shared__ int s_t;
@@ -128,6 +128,7 @@ __global__ void __launch_bounds__(BTHREADS) og_otsu_strips_kernel(
 	for (int li = blockIdx.x; li < n; li += gridDim.x) {
 		const int64_t off = pix_offsets[li];
 		const int64_t npix = (int64_t)steps[2 * li] * steps[2 * li + 1];
+		if (off + npix > capacity) continue;  // as og_extract_lines: a strip that does not fit is skipped whole
 		const uint8_t *g = gray + off;
 		uint8_t *o = out + off;
 		for (int k = threadIdx.x; k < 256 * HREP; k += BTHREADS) rep[k] = 0;
@@ -433,7 +434,7 @@ __device__ __forceinline__ int find_line_b(const int32_t *__restrict__ chunk_off
 
 __global__ void __launch_bounds__(BTHREADS) og_sauvola_strips_kernel(
 	const uint8_t *__restrict__ gray, const int32_t *__restrict__ steps, const int64_t *__restrict__ pix_offsets,
-	const int32_t *__restrict__ chunk_offsets, int n, uint8_t *__restrict__ out, int win, double kk, double rr) {
+	const int32_t *__restrict__ chunk_offsets, int n, uint8_t *__restrict__ out, int64_t capacity, int win, double kk, double rr) {
 	extern __shared__ __align__(16) unsigned char smem_raw[];
 	const int total = __ldg(chunk_offsets + n);
 	for (int item = blockIdx.x; item < total; item += gridDim.x) {
@@ -441,6 +442,7 @@ __global__ void __launch_bounds__(BTHREADS) og_sauvola_strips_kernel(
 		const int chunk = item - __ldg(chunk_offsets + li);
 		const int w = steps[2 * li], h = steps[2 * li + 1];
 		const int64_t off = pix_offsets[li];
+		if (off + (int64_t)w * h > capacity) continue;
 		for (int ty0 = 0; ty0 < h; ty0 += ST_H)
 			sauvola_tile<ST_WS>(gray + off, h, w, w, out + off, w, ty0, chunk * ST_WS, win, kk, rr, smem_raw);
 	}
@@ -456,7 +458,7 @@ int check_window(int window) {
 }  // namespace
 
 extern "C" int og_binarize_strips(const uint8_t *gray, const int32_t *steps, const int64_t *pix_offsets,
-	const int32_t *chunk_offsets, int n, int mode, int window, uint8_t *out,
+	const int32_t *chunk_offsets, int n, int mode, int window, uint8_t *out, int64_t capacity,
 	int32_t *thresholds_out, void *stream) {
 	OG_REQUIRE(n >= 0, OG_E_ARG, "n < 0");
 	OG_REQUIRE(mode == OG_BIN_OTSU || mode == OG_BIN_SAUVOLA, OG_E_ARG, "mode %d unsupported", mode);
@@ -465,7 +467,7 @@ extern "C" int og_binarize_strips(const uint8_t *gray, const int32_t *steps, con
 		OG_E_ARG, "NULL pointer");
 	cudaStream_t st = (cudaStream_t)stream;
 	if (mode == OG_BIN_OTSU) {
-		og_otsu_strips_kernel<<<min(n, OG_NUM_SMS * 8), BTHREADS, 0, st>>>(gray, steps, pix_offsets, n, out, thresholds_out);
+		og_otsu_strips_kernel<<<min(n, OG_NUM_SMS * 8), BTHREADS, 0, st>>>(gray, steps, pix_offsets, n, out, capacity, thresholds_out);
 		return og_check_launch("og_otsu_strips_kernel");
 	}
 	int rc = check_window(window);
@@ -475,7 +477,7 @@ extern "C" int og_binarize_strips(const uint8_t *gray, const int32_t *steps, con
 	cudaError_t e = cudaFuncSetAttribute(og_sauvola_strips_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
 	if (e != cudaSuccess) return og_set_error((int)e, "cudaFuncSetAttribute: %s", cudaGetErrorString(e));
 	og_sauvola_strips_kernel<<<OG_NUM_SMS * 4, BTHREADS, smem, st>>>(gray, steps, pix_offsets, chunk_offsets, n, out,
-		window, 0.2, 127.5);
+		capacity, window, 0.2, 127.5);
 	return og_check_launch("og_sauvola_strips_kernel");
 }
 

@@ -225,7 +225,8 @@ def binarize_strips(gray, plan, mode, window=15, out=None, thresholds=None):
 	if out is None:
 		out = torch.empty_like(gray)
 	_lib.call("og_binarize_strips", gray.data_ptr(), plan.steps.data_ptr(), plan.pix_offsets.data_ptr(),
-		plan.chunk_offsets.data_ptr(), plan.n, int(mode), int(window), out.data_ptr(), _ptr(thresholds), _stream())
+		plan.chunk_offsets.data_ptr(), plan.n, int(mode), int(window), out.data_ptr(), min(gray.numel(), out.numel()),
+		_ptr(thresholds), _stream())
 	return out
 
 

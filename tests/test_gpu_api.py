@@ -273,3 +273,24 @@ def test_page_pipeline_with_column_descriptors(small):
 	assert len(res.strips) == len(want)
 	for a, b in zip(res.strips, want):
 		assert a.shape == b.shape and np.array_equal(a, b)
+
+
+def test_page_pipeline_reruns_a_page_whose_strip_estimate_fell_short(small, monkeypatch):
+	"""The strip buffer is sized from a host-side estimate of the strip widths; when that is too
+	small the kernels skip what does not fit (no write past the buffer) and the page runs again
+	with the size the device computed."""
+	from origami_b200.batch.core import pipeline
+	lines = small.lines[:20]
+	arr = np.array([[l["p"], l["right"], l["up"]] for l in lines], dtype=np.float64).reshape(-1, 3, 2)
+	want = [reference_path.line_image(small.pil, small.ref, l["p"], l["right"], l["up"], 48, binarize=("otsu",)) for l in lines]
+	good = pipeline._estimate_xsteps(small.g, small.s, ops.pack_line_arrays(arr[:, 0], arr[:, 1], arr[:, 2], ysteps=48))
+	monkeypatch.setattr(pipeline, "_estimate_xsteps", lambda grid, cell, desc: np.full(desc.shape[0], 3, dtype=np.int64))
+	pipe = pipeline.PagePipeline(line_height=48, binarize="otsu")
+	results = list(pipe.run([(small.page, small.g, small.s, arr)] * 2))
+	for res in results:
+		assert len(res.strips) == len(want)
+		for a, b in zip(res.strips, want):
+			assert a.shape == b.shape and np.array_equal(a, b)
+		# and the real estimate is tight: never below, at most a few columns above what the device derived
+		slack = good - res.steps[:, 0]
+		assert (slack >= 0).all() and (slack <= 16).all()
