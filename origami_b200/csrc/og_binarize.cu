@@ -118,7 +118,22 @@ __device__ int otsu_from_hist_warp(const unsigned int *hist) {
 #endif
 constexpr int HREP = OG_HREP;
 
-__global__ void __launch_bounds__(BTHREADS) og_otsu_strips_kernel(
+#ifndef OG_OTSU_STRIP_THREADS
+#define OG_OTSU_STRIP_THREADS 128
+#endif
+#ifndef OG_OTSU_STRIP_CTAS
+#define OG_OTSU_STRIP_CTAS 16
+#endif
+// a small CTA per line, all lines of a page resident at once: the kernel is a chain of short
+// dependent phases (histogram, threshold, apply) and not bound by the shared-memory atomics
+// (replacing them by plain reads does not change its time: 41 us for 2000 strips)
+constexpr int OTHREADS = OG_OTSU_STRIP_THREADS;
+#ifndef OG_OTSU_STRIP_UNROLL
+#define OG_OTSU_STRIP_UNROLL 2
+#endif
+constexpr int OU = OG_OTSU_STRIP_UNROLL;  // 16-byte vectors in flight per thread
+
+__global__ void __launch_bounds__(OTHREADS) og_otsu_strips_kernel(
 	const uint8_t *__restrict__ gray, const int32_t *__restrict__ steps, const int64_t *__restrict__ pix_offsets,
 	int n, uint8_t *__restrict__ out, int64_t capacity, int32_t *__restrict__ thresholds) {
 	__shared__ unsigned int rep[256 * HREP];
@@ -131,25 +146,33 @@ __global__ void __launch_bounds__(BTHREADS) og_otsu_strips_kernel(
 		if (off + npix > capacity) continue;  // as og_extract_lines: a strip that does not fit is skipped whole
 		const uint8_t *g = gray + off;
 		uint8_t *o = out + off;
-		for (int k = threadIdx.x; k < 256 * HREP; k += BTHREADS) rep[k] = 0;
+		for (int k = threadIdx.x; k < 256 * HREP; k += OTHREADS) rep[k] = 0;
 		__syncthreads();
 		// 16-byte vector body between the unaligned head and tail
 		const int64_t head = min(npix, (int64_t)((16 - (reinterpret_cast<uintptr_t>(g) & 15)) & 15));
 		const int64_t nvec = (npix - head) / 16;
-		for (int64_t i = threadIdx.x; i < head; i += BTHREADS) atomicAdd(&rep[g[i] * HREP + r], 1u);
+		for (int64_t i = threadIdx.x; i < head; i += OTHREADS) atomicAdd(&rep[g[i] * HREP + r], 1u);
 		const uint4 *gv = reinterpret_cast<const uint4 *>(g + head);
-		for (int64_t i = threadIdx.x; i < nvec; i += BTHREADS) {
-			const uint4 v = gv[i];
-			const unsigned int wds[4] = {v.x, v.y, v.z, v.w};
+		// OU vectors per thread are requested before the first one is counted: the shared-memory
+		// atomics keep the compiler from overlapping the loads of successive iterations itself
+		for (int64_t i0 = threadIdx.x; i0 < nvec; i0 += OTHREADS * OU) {
+			uint4 v[OU];
 #pragma unroll
-			for (int q = 0; q < 4; ++q) {
+			for (int u = 0; u < OU; ++u) v[u] = i0 + u * OTHREADS < nvec ? __ldg(gv + i0 + u * OTHREADS) : make_uint4(0, 0, 0, 0);
 #pragma unroll
-				for (int b = 0; b < 4; ++b) atomicAdd(&rep[((wds[q] >> (8 * b)) & 255u) * HREP + r], 1u);
+			for (int u = 0; u < OU; ++u) {
+				if (i0 + u * OTHREADS >= nvec) break;
+				const unsigned int wds[4] = {v[u].x, v[u].y, v[u].z, v[u].w};
+#pragma unroll
+				for (int q = 0; q < 4; ++q) {
+#pragma unroll
+					for (int b = 0; b < 4; ++b) atomicAdd(&rep[((wds[q] >> (8 * b)) & 255u) * HREP + r], 1u);
+				}
 			}
 		}
-		for (int64_t i = head + nvec * 16 + threadIdx.x; i < npix; i += BTHREADS) atomicAdd(&rep[g[i] * HREP + r], 1u);
+		for (int64_t i = head + nvec * 16 + threadIdx.x; i < npix; i += OTHREADS) atomicAdd(&rep[g[i] * HREP + r], 1u);
 		__syncthreads();
-		for (int k = threadIdx.x; k < 256; k += BTHREADS) {
+		for (int k = threadIdx.x; k < 256; k += OTHREADS) {
 			unsigned int sum = 0;
 #pragma unroll
 			for (int q = 0; q < HREP; ++q) sum += rep[k * HREP + q];
@@ -165,27 +188,34 @@ __global__ void __launch_bounds__(BTHREADS) og_otsu_strips_kernel(
 		}
 		__syncthreads();
 		const unsigned int t = (unsigned int)s_t;
-		for (int64_t i = threadIdx.x; i < head; i += BTHREADS) o[i] = g[i] > t ? 255 : 0;
+		for (int64_t i = threadIdx.x; i < head; i += OTHREADS) o[i] = g[i] > t ? 255 : 0;
 		const bool out_al = ((reinterpret_cast<uintptr_t>(o + head)) & 15) == 0;
-		for (int64_t i = threadIdx.x; i < nvec; i += BTHREADS) {
-			const uint4 v = gv[i];
-			unsigned int wds[4] = {v.x, v.y, v.z, v.w};
+		for (int64_t i0 = threadIdx.x; i0 < nvec; i0 += OTHREADS * OU) {
+			uint4 v[OU];
 #pragma unroll
-			for (int q = 0; q < 4; ++q) {
-				unsigned int m = 0;
+			for (int u = 0; u < OU; ++u) v[u] = i0 + u * OTHREADS < nvec ? __ldg(gv + i0 + u * OTHREADS) : make_uint4(0, 0, 0, 0);
 #pragma unroll
-				for (int b = 0; b < 4; ++b) m |= (((wds[q] >> (8 * b)) & 255u) > t ? 255u : 0u) << (8 * b);
-				wds[q] = m;
-			}
-			if (out_al) {
-				reinterpret_cast<uint4 *>(o + head)[i] = make_uint4(wds[0], wds[1], wds[2], wds[3]);
-			} else {
-				uint8_t *ob = o + head + i * 16;
+			for (int u = 0; u < OU; ++u) {
+				const int64_t i = i0 + u * OTHREADS;
+				if (i >= nvec) break;
+				unsigned int wds[4] = {v[u].x, v[u].y, v[u].z, v[u].w};
 #pragma unroll
-				for (int q = 0; q < 16; ++q) ob[q] = (uint8_t)(wds[q >> 2] >> (8 * (q & 3)));
+				for (int q = 0; q < 4; ++q) {
+					unsigned int m = 0;
+#pragma unroll
+					for (int b = 0; b < 4; ++b) m |= (((wds[q] >> (8 * b)) & 255u) > t ? 255u : 0u) << (8 * b);
+					wds[q] = m;
+				}
+				if (out_al) {
+					reinterpret_cast<uint4 *>(o + head)[i] = make_uint4(wds[0], wds[1], wds[2], wds[3]);
+				} else {
+					uint8_t *ob = o + head + i * 16;
+#pragma unroll
+					for (int q = 0; q < 16; ++q) ob[q] = (uint8_t)(wds[q >> 2] >> (8 * (q & 3)));
+				}
 			}
 		}
-		for (int64_t i = head + nvec * 16 + threadIdx.x; i < npix; i += BTHREADS) o[i] = g[i] > t ? 255 : 0;
+		for (int64_t i = head + nvec * 16 + threadIdx.x; i < npix; i += OTHREADS) o[i] = g[i] > t ? 255 : 0;
 		__syncthreads();
 	}
 }
@@ -467,7 +497,7 @@ extern "C" int og_binarize_strips(const uint8_t *gray, const int32_t *steps, con
 		OG_E_ARG, "NULL pointer");
 	cudaStream_t st = (cudaStream_t)stream;
 	if (mode == OG_BIN_OTSU) {
-		og_otsu_strips_kernel<<<min(n, OG_NUM_SMS * 8), BTHREADS, 0, st>>>(gray, steps, pix_offsets, n, out, capacity, thresholds_out);
+		og_otsu_strips_kernel<<<min(n, OG_NUM_SMS * OG_OTSU_STRIP_CTAS), OTHREADS, 0, st>>>(gray, steps, pix_offsets, n, out, capacity, thresholds_out);
 		return og_check_launch("og_otsu_strips_kernel");
 	}
 	int rc = check_window(window);
