@@ -43,10 +43,9 @@ __device__ __forceinline__ void bar_sync(int id, int nthreads) {
 // ---------------------------------------------------------------------------------------
 // step counts: 4 lanes per line (one per corner of the rough 2x2 grid), then one scan CTA
 // ---------------------------------------------------------------------------------------
-__global__ void __launch_bounds__(256) og_line_steps_kernel(
+__device__ __forceinline__ void og_line_steps_body(
 	const float2 *__restrict__ grid, int gh, int gw, int cell,
-	const og_line *__restrict__ lines, int n, int32_t *__restrict__ steps_out) {
-	const int t = blockIdx.x * blockDim.x + threadIdx.x;
+	const og_line *__restrict__ lines, int n, int32_t *steps_out, int t) {
 	const int i = min(t >> 2, n - 1), corner = t & 3;
 	const double inv_cell = 1.0 / (double)cell;
 	const og_line *ln = lines + i;
@@ -92,6 +91,12 @@ __global__ void __launch_bounds__(256) og_line_steps_kernel(
 	}
 }
 
+__global__ void __launch_bounds__(256) og_line_steps_kernel(
+	const float2 *__restrict__ grid, int gh, int gw, int cell,
+	const og_line *__restrict__ lines, int n, int32_t *__restrict__ steps_out) {
+	og_line_steps_body(grid, gh, gw, cell, lines, n, steps_out, blockIdx.x * blockDim.x + threadIdx.x);
+}
+
 template <typename T>
 __device__ __forceinline__ T block_exclusive_scan(T v, T *warp_sums, T &total) {
 	const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
@@ -121,10 +126,9 @@ __device__ __forceinline__ T block_exclusive_scan(T v, T *warp_sums, T &total) {
 	return res;
 }
 
-__global__ void __launch_bounds__(1024) og_line_scan_kernel(
-	const int32_t *__restrict__ steps, int n, int64_t *__restrict__ pix_offsets, int32_t *__restrict__ chunk_offsets) {
-	__shared__ long long ws64[33];
-	__shared__ int ws32[33];
+__device__ __forceinline__ void og_line_scan_body(
+	const int32_t *steps, int n, int64_t *__restrict__ pix_offsets, int32_t *__restrict__ chunk_offsets,
+	long long *ws64, int *ws32) {
 	long long carry_pix = 0;
 	int carry_chunks = 0;
 	for (int base = 0; base < n; base += blockDim.x) {
@@ -152,6 +156,32 @@ __global__ void __launch_bounds__(1024) og_line_scan_kernel(
 		chunk_offsets[n] = carry_chunks;
 		chunk_offsets[n + 1] = 0;  // the work ticket of og_strips_screened_kernel (zero between calls)
 	}
+}
+
+__global__ void __launch_bounds__(1024) og_line_scan_kernel(
+	const int32_t *__restrict__ steps, int n, int64_t *__restrict__ pix_offsets, int32_t *__restrict__ chunk_offsets) {
+	__shared__ long long ws64[33];
+	__shared__ int ws32[33];
+	og_line_scan_body(steps, n, pix_offsets, chunk_offsets, ws64, ws32);
+}
+
+// Both steps in one launch for a page's worth of lines: one cluster of eight CTAs computes the step
+// counts (four lanes per line, 2048 lines per pass), a cluster barrier publishes them, and the
+// first CTA runs the prefix sums.  Two dependent ~5 us launches become one.
+constexpr int PLAN_CTAS = 8;
+constexpr int PLAN_MAX_LINES = 8192;
+
+__global__ void __cluster_dims__(PLAN_CTAS, 1, 1) __launch_bounds__(1024) og_line_plan_kernel(
+	const float2 *__restrict__ grid, int gh, int gw, int cell,
+	const og_line *__restrict__ lines, int n, int32_t *steps_out,
+	int64_t *__restrict__ pix_offsets, int32_t *__restrict__ chunk_offsets) {
+	__shared__ long long ws64[33];
+	__shared__ int ws32[33];
+	for (int base = 0; base < 4 * n; base += PLAN_CTAS * 1024)
+		og_line_steps_body(grid, gh, gw, cell, lines, n, steps_out, base + blockIdx.x * 1024 + threadIdx.x);
+	// release / acquire at cluster scope orders the global stores of all eight CTAs before the scan
+	asm volatile("barrier.cluster.arrive.release.aligned;\n\tbarrier.cluster.wait.acquire.aligned;" ::: "memory");
+	if (blockIdx.x == 0) og_line_scan_body(steps_out, n, pix_offsets, chunk_offsets, ws64, ws32);
 }
 
 // ---------------------------------------------------------------------------------------
@@ -1137,6 +1167,11 @@ extern "C" int og_line_steps(const float *grid, int gh, int gw, int cell,
 	OG_REQUIRE(pix_offsets_out != nullptr && chunk_offsets_out != nullptr && (n == 0 || steps_out != nullptr),
 		OG_E_ARG, "output pointer is NULL");
 	cudaStream_t st = (cudaStream_t)stream;
+	if (n > 0 && n <= PLAN_MAX_LINES) {
+		og_line_plan_kernel<<<PLAN_CTAS, 1024, 0, st>>>(reinterpret_cast<const float2 *>(grid), gh, gw, cell, lines, n,
+			steps_out, pix_offsets_out, chunk_offsets_out);
+		return og_check_launch("og_line_plan_kernel");
+	}
 	if (n > 0) {
 		const int threads = 256, per_block = threads / 4;
 		og_line_steps_kernel<<<(n + per_block - 1) / per_block, threads, 0, st>>>(
