@@ -293,3 +293,23 @@ def test_screened_strips_with_absurd_line_coordinates(cuda):
 	assert total == 3 * 8 * 64 and torch.equal(a, b)
 	want = exact.remap_linear(page, exact.warped_grid(dense, recs[2]["p"], recs[2]["right"], recs[2]["up"], xsteps=64, ysteps=8))[::-1]
 	assert np.array_equal(a.cpu().numpy()[2 * 512:].reshape(want.shape), want)
+
+
+def test_line_plan_large_batches_take_the_two_kernel_path(cuda):
+	"""Up to 8192 lines the step counts and prefix sums come from one cluster launch, beyond that
+	from two kernels: same numbers either way."""
+	_, grid, dense, lines = _setup(cuda, n_lines=90, seed=8)
+	g = torch.from_numpy(grid).to(cuda)
+	recs = _records(lines)
+	small = ops.line_steps(g, 25, ops.lines_to_device(ops.pack_lines(recs), cuda), len(recs))
+	reps = 8192 // len(recs) + 1
+	big = ops.line_steps(g, 25, ops.lines_to_device(ops.pack_lines(recs * reps), cuda), len(recs) * reps)
+	s_small, s_big = small.steps.cpu().numpy(), big.steps.cpu().numpy()
+	assert len(recs) * reps > 8192 and np.array_equal(s_big, np.tile(s_small, (reps, 1)))
+	px = s_big[:, 0].astype(np.int64) * s_big[:, 1]
+	assert np.array_equal(big.pix_offsets.cpu().numpy(), np.concatenate([[0], np.cumsum(px)]))
+	chunks = (s_big[:, 0] + 63) // 64
+	assert np.array_equal(big.chunk_offsets.cpu().numpy()[:-1], np.concatenate([[0], np.cumsum(chunks)]))
+	assert int(big.chunk_offsets[-1].item()) == 0 and int(small.chunk_offsets[-1].item()) == 0
+	for i, r in enumerate(recs):
+		assert tuple(s_small[i]) == exact.line_steps(dense, r["p"], r["right"], r["up"])
