@@ -4,19 +4,16 @@ sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 import numpy as np, torch
 from origami_b200 import ops, synth
 
-_BUSY = None
-
 def timeit(fn, iters=20, warm=3):
-	"""Median / best device time of fn().  A few milliseconds of unrelated GPU work are queued first,
-	so that all timed launches are already in the stream when the GPU reaches them: without that a
-	kernel shorter than the host's launch cost (~40 us through ctypes) measures the host."""
-	global _BUSY
+	"""Median / best device time of fn(), launches back to back.  A few milliseconds of a spinning
+	kernel are queued first, so that all timed launches are already in the stream when the GPU
+	reaches them: without that a kernel shorter than the host's launch cost (~40 us through ctypes)
+	runs with idle gaps around it, which flatters bandwidth-bound kernels (the write-back of the
+	previous launch drains in the gap) -- and a compute-heavy filler would skew the clocks."""
 	for _ in range(warm): fn()
-	if _BUSY is None:
-		_BUSY = torch.empty((8192, 8192), dtype=torch.float16, device="cuda").normal_()
 	torch.cuda.synchronize()
 	ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(iters)]
-	for _ in range(4): torch.mm(_BUSY, _BUSY)
+	torch.cuda._sleep(8_000_000)
 	for a, b in ev:
 		a.record(); fn(); b.record()
 	torch.cuda.synchronize()
