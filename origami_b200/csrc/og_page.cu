@@ -14,6 +14,7 @@
 // CTA into shared memory.  Source taps are gathered through the read-only path with 32-bit
 // offsets; the smooth warp makes neighbouring threads hit the same 128-byte lines.
 #include "og_common.cuh"
+#include <type_traits>
 
 #ifndef OG_PAGE_MINB
 #define OG_PAGE_MINB 3
@@ -419,10 +420,14 @@ constexpr int P2_TILE_H = P2_TBY * P2_ROWS;
 template <bool SCALED, bool WRITE_MAP>
 __global__ void __launch_bounds__(P2_TBX *P2_TBY, OG_P2_MINB) og_page_pipelined_kernel(const __grid_constant__ PageParams p) {
 	__shared__ RowAxis s_rows[P2_TILE_H];
+	__shared__ int s_win[4];
 	const int Wd = p.gw * p.cell, Hd = p.gh * p.cell;
 	const int ytile = blockIdx.y * P2_TILE_H;
 	const double inv_cell = 1.0 / (double)p.cell;
 	const int tid = threadIdx.y * P2_TBX + threadIdx.x;
+	constexpr bool PREFETCH = OG_P2_PREFETCH && WRITE_MAP;
+	constexpr int PF_WARP = (P2_TILE_H + 31) / 32;  // the first warp that does not fill s_rows
+	static_assert(PF_WARP * 32 < P2_TBX * P2_TBY, "no warp left for the prefetch window");
 	if (tid < P2_TILE_H) {
 		og_axis ay = og_resize_axis(min(ytile + tid, Hd - 1), inv_cell);
 		RowAxis ra;
@@ -431,44 +436,30 @@ __global__ void __launch_bounds__(P2_TBX *P2_TBY, OG_P2_MINB) og_page_pipelined_
 		ra.b1 = ay.f;
 		ra.b0 = __fsub_rn(1.f, ay.f);
 		s_rows[tid] = ra;
-	}
-	if (OG_P2_PREFETCH && WRITE_MAP) {
-		// The source window of the tile, requested into L2 before the first tap: the 281 MB map
-		// stream keeps DRAM busy with writes, and a row's taps that miss L2 wait behind them (one
-		// new source row per output row).  The window is the bounding box of nine map samples.
-		__shared__ int s_win[4];
-		if (tid < 4) s_win[tid] = (tid < 2) ? INT_MAX : INT_MIN;
-		__syncthreads();
-		if (tid < 9) {
-			const int px = min(blockIdx.x * P2_TILE_W + (tid % 3) * (P2_TILE_W / 2), Wd - 1);
-			const int py = min(ytile + (tid / 3) * (P2_TILE_H / 2), Hd - 1);
-			const float2 v = og_dense_node(p.grid, p.gh, p.gw, inv_cell, py, px);
-			const float vx = SCALED ? __fmul_rn(v.x, p.scale_x) : v.x, vy = SCALED ? __fmul_rn(v.y, p.scale_y) : v.y;
-			if (fabsf(vx) < 1.0e6f && fabsf(vy) < 1.0e6f) {
-				atomicMin(&s_win[0], (int)floorf(vx) - 2);
-				atomicMin(&s_win[1], (int)floorf(vy) - 2);
-				atomicMax(&s_win[2], (int)floorf(vx) + 3);
-				atomicMax(&s_win[3], (int)floorf(vy) + 3);
-			}
+	} else if (PREFETCH && (tid >> 5) == PF_WARP) {
+		// The source window of the tile (bounding box of nine map samples), for the prefetch below
+		const int l = tid & 31, q = min(l, 8);
+		const int px = min(blockIdx.x * P2_TILE_W + (q % 3) * (P2_TILE_W / 2), Wd - 1);
+		const int py = min(ytile + (q / 3) * (P2_TILE_H / 2), Hd - 1);
+		const float2 v = og_dense_node(p.grid, p.gh, p.gw, inv_cell, py, px);
+		const float vx = SCALED ? __fmul_rn(v.x, p.scale_x) : v.x, vy = SCALED ? __fmul_rn(v.y, p.scale_y) : v.y;
+		const bool ok = fabsf(vx) < 1.0e6f && fabsf(vy) < 1.0e6f;  // false for NaN
+		int bx0 = ok ? (int)floorf(vx) - 2 : INT_MAX, by0 = ok ? (int)floorf(vy) - 2 : INT_MAX;
+		int bx1 = ok ? (int)floorf(vx) + 3 : INT_MIN, by1 = ok ? (int)floorf(vy) + 3 : INT_MIN;
+#pragma unroll
+		for (int o = 8; o > 0; o >>= 1) {
+			bx0 = min(bx0, __shfl_xor_sync(0xffffffffu, bx0, o));
+			by0 = min(by0, __shfl_xor_sync(0xffffffffu, by0, o));
+			bx1 = max(bx1, __shfl_xor_sync(0xffffffffu, bx1, o));
+			by1 = max(by1, __shfl_xor_sync(0xffffffffu, by1, o));
 		}
-		__syncthreads();
-		const int bx0 = max(s_win[0], 0), by0 = max(s_win[1], 0), bx1 = min(s_win[2], p.W - 1), by1 = min(s_win[3], p.H - 1);
-		if (bx0 <= bx1 && by0 <= by1 && by1 - by0 < 4 * P2_TILE_H && bx1 - bx0 < 4 * P2_TILE_W) {
-			const uintptr_t base = reinterpret_cast<uintptr_t>(p.src);
-			for (int y = by0 + (tid >> 3); y <= by1; y += (P2_TBX * P2_TBY) >> 3) {
-				const uintptr_t a = (base + (uintptr_t)((int64_t)y * p.src_pitch + bx0)) & ~(uintptr_t)127;
-				const uintptr_t z = base + (uintptr_t)((int64_t)y * p.src_pitch + bx1);
-				for (uintptr_t q = a + (tid & 7) * 128; q <= z; q += 8 * 128) asm volatile("prefetch.global.L2 [%0];" ::"l"(q));
-			}
+		if (l == 0) {
+			s_win[0] = bx0; s_win[1] = by0; s_win[2] = bx1; s_win[3] = by1;
 		}
-	} else {
-		__syncthreads();
 	}
+	// x-axis state (independent of the shared tables: ahead of the barrier)
 	const int x0 = (blockIdx.x * P2_TBX + threadIdx.x) * 2;
-	const int ybeg = ytile + threadIdx.y * P2_ROWS;
-	if (x0 >= Wd || ybeg >= Hd) return;
 	const int gw = p.gw;
-	const float2 *__restrict__ grid = p.grid;
 	int sx[2], sx1[2];
 	float a0[2], a1[2];
 #pragma unroll
@@ -479,6 +470,24 @@ __global__ void __launch_bounds__(P2_TBX *P2_TBY, OG_P2_MINB) og_page_pipelined_
 		a1[k] = ax.f;
 		a0[k] = __fsub_rn(1.f, ax.f);
 	}
+	__syncthreads();
+	if (PREFETCH) {
+		// The window is requested into L2 before the first tap: the 281 MB map stream keeps DRAM
+		// busy with writes, and a row's taps that miss L2 wait behind them (every output row
+		// touches a new source row).
+		const int bx0 = max(s_win[0], 0), by0 = max(s_win[1], 0), bx1 = min(s_win[2], p.W - 1), by1 = min(s_win[3], p.H - 1);
+		if (bx0 <= bx1 && by0 <= by1 && by1 - by0 < 4 * P2_TILE_H && bx1 - bx0 < 4 * P2_TILE_W) {
+			const uintptr_t base = reinterpret_cast<uintptr_t>(p.src);
+			for (int y = by0 + (tid >> 3); y <= by1; y += (P2_TBX * P2_TBY) >> 3) {
+				const uintptr_t a = (base + (uintptr_t)((int64_t)y * p.src_pitch + bx0)) & ~(uintptr_t)127;
+				const uintptr_t z = base + (uintptr_t)((int64_t)y * p.src_pitch + bx1);
+				for (uintptr_t q = a + (tid & 7) * 128; q <= z; q += 8 * 128) asm volatile("prefetch.global.L2 [%0];" ::"l"(q));
+			}
+		}
+	}
+	const int ybeg = ytile + threadIdx.y * P2_ROWS;
+	if (x0 >= Wd || ybeg >= Hd) return;
+	const float2 *__restrict__ grid = p.grid;
 	const int npx = min(2, Wd - x0);
 	const bool map_al = WRITE_MAP && npx == 2 && (Wd & 1) == 0 && ((reinterpret_cast<uintptr_t>(p.map_out) & 15) == 0);
 	const bool img_al = npx == 2 && (p.dst_pitch & 1) == 0 && ((reinterpret_cast<uintptr_t>(p.dst) & 1) == 0);
@@ -493,72 +502,79 @@ __global__ void __launch_bounds__(P2_TBX *P2_TBY, OG_P2_MINB) og_page_pipelined_
 	const RowAxis *rows = s_rows + threadIdx.y * P2_ROWS;
 	const int nrows = min(P2_ROWS, Hd - ybeg);
 
-	// map of one row (streamed out when wanted) and the request for its taps
-	auto request = [&](int yy, og_taps (&t)[2]) {
-		const RowAxis ra = rows[yy];
-		if (ra.r0 != cur_r0 || ra.r1 != cur_r1) {  // next sparse cell: uniform across the CTA row
-			cur_r0 = ra.r0;
-			cur_r1 = ra.r1;
-			const float2 *g0 = grid + ra.r0 * gw;
-			const float2 *g1 = grid + ra.r1 * gw;
+	// the row loop, compiled once for the aligned two-pixel case (vector stores, no per-row
+	// alignment branches) and once for the general one
+	auto run = [&](auto aligned_tag) {
+		constexpr bool AL = decltype(aligned_tag)::value;
+		// map of one row (streamed out when wanted) and the request for its taps
+		auto request = [&](int yy, og_taps (&t)[2]) {
+			const RowAxis ra = rows[yy];
+			if (ra.r0 != cur_r0 || ra.r1 != cur_r1) {  // next sparse cell: uniform across the CTA row
+				cur_r0 = ra.r0;
+				cur_r1 = ra.r1;
+				const float2 *g0 = grid + ra.r0 * gw;
+				const float2 *g1 = grid + ra.r1 * gw;
+#pragma unroll
+				for (int k = 0; k < 2; ++k) {
+					const float2 s00 = __ldg(g0 + sx[k]), s01 = __ldg(g0 + sx1[k]);
+					const float2 s10 = __ldg(g1 + sx[k]), s11 = __ldg(g1 + sx1[k]);
+					h0[k].x = og_lerp_cv(s00.x, s01.x, a0[k], a1[k]);
+					h0[k].y = og_lerp_cv(s00.y, s01.y, a0[k], a1[k]);
+					h1[k].x = og_lerp_cv(s10.x, s11.x, a0[k], a1[k]);
+					h1[k].y = og_lerp_cv(s10.y, s11.y, a0[k], a1[k]);
+				}
+			}
+			float2 d[2];
 #pragma unroll
 			for (int k = 0; k < 2; ++k) {
-				const float2 s00 = __ldg(g0 + sx[k]), s01 = __ldg(g0 + sx1[k]);
-				const float2 s10 = __ldg(g1 + sx[k]), s11 = __ldg(g1 + sx1[k]);
-				h0[k].x = og_lerp_cv(s00.x, s01.x, a0[k], a1[k]);
-				h0[k].y = og_lerp_cv(s00.y, s01.y, a0[k], a1[k]);
-				h1[k].x = og_lerp_cv(s10.x, s11.x, a0[k], a1[k]);
-				h1[k].y = og_lerp_cv(s10.y, s11.y, a0[k], a1[k]);
+				d[k].x = og_lerp_cv(h0[k].x, h1[k].x, ra.b0, ra.b1);
+				d[k].y = og_lerp_cv(h0[k].y, h1[k].y, ra.b0, ra.b1);
 			}
-		}
-		float2 d[2];
+			if (WRITE_MAP) {
+				if (AL) __stcs(reinterpret_cast<float4 *>(mrow), make_float4(d[0].x, d[0].y, d[1].x, d[1].y));
+				else {
+					__stcs(reinterpret_cast<float2 *>(mrow), d[0]);
+					if (npx > 1) __stcs(reinterpret_cast<float2 *>(mrow) + 1, d[1]);
+				}
+				mrow += (size_t)Wd * 2;
+			}
+			float mx[2], my[2];
 #pragma unroll
-		for (int k = 0; k < 2; ++k) {
-			d[k].x = og_lerp_cv(h0[k].x, h1[k].x, ra.b0, ra.b1);
-			d[k].y = og_lerp_cv(h0[k].y, h1[k].y, ra.b0, ra.b1);
-		}
-		if (WRITE_MAP) {
-			if (map_al) __stcs(reinterpret_cast<float4 *>(mrow), make_float4(d[0].x, d[0].y, d[1].x, d[1].y));
+			for (int k = 0; k < 2; ++k) {
+				mx[k] = SCALED ? __fmul_rn(d[k].x, scx) : d[k].x;
+				my[k] = SCALED ? __fmul_rn(d[k].y, scy) : d[k].y;
+			}
+			og_load_taps_batch<2>(src, H, W, spitch, mx, my, t);
+		};
+		auto finish = [&](const og_taps (&t)[2]) {
+			const int v0 = og_blend_taps(t[0]), v1 = og_blend_taps(t[1]);
+			if (AL) __stcs(reinterpret_cast<unsigned short *>(orow), (unsigned short)(v0 | (v1 << 8)));
 			else {
-				__stcs(reinterpret_cast<float2 *>(mrow), d[0]);
-				if (npx > 1) __stcs(reinterpret_cast<float2 *>(mrow) + 1, d[1]);
+				orow[0] = (uint8_t)v0;
+				if (npx > 1) orow[1] = (uint8_t)v1;
 			}
-			mrow += (size_t)Wd * 2;
-		}
-		float mx[2], my[2];
-#pragma unroll
-		for (int k = 0; k < 2; ++k) {
-			mx[k] = SCALED ? __fmul_rn(d[k].x, scx) : d[k].x;
-			my[k] = SCALED ? __fmul_rn(d[k].y, scy) : d[k].y;
-		}
-		og_load_taps_batch<2>(src, H, W, spitch, mx, my, t);
-	};
-	auto finish = [&](const og_taps (&t)[2]) {
-		const int v0 = og_blend_taps(t[0]), v1 = og_blend_taps(t[1]);
-		if (img_al) __stcs(reinterpret_cast<unsigned short *>(orow), (unsigned short)(v0 | (v1 << 8)));
-		else {
-			orow[0] = (uint8_t)v0;
-			if (npx > 1) orow[1] = (uint8_t)v1;
-		}
-		orow += p.dst_pitch;
-	};
+			orow += p.dst_pitch;
+		};
 
-	og_taps ta[2], tb[2];
-	request(0, ta);
-	int yy = 1;
-	for (; yy + 1 < nrows; yy += 2) {
-		request(yy, tb);
-		finish(ta);
-		request(yy + 1, ta);
-		finish(tb);
-	}
-	if (yy < nrows) {
-		request(yy, tb);
-		finish(ta);
-		finish(tb);
-	} else {
-		finish(ta);
-	}
+		og_taps ta[2], tb[2];
+		request(0, ta);
+		int yy = 1;
+		for (; yy + 1 < nrows; yy += 2) {
+			request(yy, tb);
+			finish(ta);
+			request(yy + 1, ta);
+			finish(tb);
+		}
+		if (yy < nrows) {
+			request(yy, tb);
+			finish(ta);
+			finish(tb);
+		} else {
+			finish(ta);
+		}
+	};
+	if ((!WRITE_MAP || map_al) && img_al) run(std::true_type{});
+	else run(std::false_type{});
 }
 
 template <bool LINEAR, bool SCALED>
