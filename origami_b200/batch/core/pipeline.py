@@ -132,16 +132,21 @@ class PagePipeline:
 	of lines.zip), or a structured array of og_line descriptors (ops.pack_lines) when table rows
 	are split into column cells.  Results come back in job order as PageResult(dewarped ndarray,
 	sequence of strip ndarrays, steps (n, 2) int32 (xsteps, ysteps)).  The arrays of a result are views into a
-	pinned buffer that is recycled when the NEXT result is requested: copy what must outlive that."""
+	pinned buffer that is recycled when the NEXT result is requested: copy what must outlive that.
+	With dewarped=False no dewarped page is computed (PageResult.dewarped is None): strips only."""
 
-	def __init__(self, line_height=48, binarize="", depth=2, device=None, use_map=True):
+	def __init__(self, line_height=48, binarize="", depth=2, device=None, use_map=True, dewarped=True):
 		if not torch.cuda.is_available():
 			raise _lib.OrigamiB200Error("origami_b200 needs a CUDA device (there is no CPU fallback)")
 		self.device = torch.device(device) if device is not None else torch.device("cuda", torch.cuda.current_device())
 		self.line_height = int(line_height)
 		spec = _binarize.from_string(binarize).spec if binarize.strip() else None
 		self.binarize = spec
-		self.use_map = use_map
+		# dewarped=False: the OCR stage's configuration (origami/batch/detect/ocr.py:227-249 samples the
+		# strips from the WARPED page and never touches the dewarped image): only the dense map is
+		# expanded on the device, no dewarped page is produced or downloaded
+		self.want_dewarped = bool(dewarped)
+		self.use_map = use_map or not self.want_dewarped
 		self.slots = [_Slot(self.device) for _ in range(max(2, depth))]
 
 	# -- one page: everything is enqueued on the slot's stream, nothing waits
@@ -172,7 +177,7 @@ class PagePipeline:
 		o_desc = o_grid + al(grid.nbytes)
 		n_in = o_desc + al(max(desc.nbytes, 1))
 		# output block: dewarped page (pitched) | strips | steps | pix offsets
-		o_strips = al(Hd * dpitch)
+		o_strips = al(Hd * dpitch) if self.want_dewarped else 0
 		o_steps = o_strips + al(cap)
 		o_offs = o_steps + al(8 * max(n, 1))
 		n_out = o_offs + al(8 * (n + 1))
@@ -210,8 +215,11 @@ class PagePipeline:
 			base_in, base_out = slot.d_in.data_ptr(), slot.d_out.data_ptr()
 			s = st.cuda_stream
 			p_map = slot.d_map.data_ptr() if self.use_map else 0
-			_lib.call("og_remap_page", base_in, H, W, pitch, base_in + o_grid, gh, gw, cell,
-				base_out, dpitch, p_map, 1.0, 1.0, ops.OG_INTER_LINEAR, s)
+			if self.want_dewarped:
+				_lib.call("og_remap_page", base_in, H, W, pitch, base_in + o_grid, gh, gw, cell,
+					base_out, dpitch, p_map, 1.0, 1.0, ops.OG_INTER_LINEAR, s)
+			elif n:
+				_lib.call("og_expand_map", base_in + o_grid, gh, gw, cell, p_map, s)
 			if n:
 				_lib.call("og_line_steps", base_in + o_grid, gh, gw, cell, base_in + o_desc, n,
 					base_out + o_steps, base_out + o_offs, slot.d_chunks.data_ptr(), s)
@@ -234,7 +242,7 @@ class PagePipeline:
 		slot.done.synchronize()
 		Hd, Wd, dpitch, n, cap, o_strips, o_steps, o_offs = slot.meta
 		hout = slot.h_out.numpy()
-		dewarped = hout[:Hd * dpitch].reshape(Hd, dpitch)[:, :Wd]
+		dewarped = hout[:Hd * dpitch].reshape(Hd, dpitch)[:, :Wd] if self.want_dewarped else None
 		steps = hout[o_steps:o_steps + 8 * n].view(np.int32).reshape(n, 2)
 		offs = hout[o_offs:o_offs + 8 * (n + 1)].view(np.int64)
 		if n and int(offs[n]) > cap:

@@ -255,6 +255,11 @@ def test_page_pipeline_matches_per_page_api(cuda, spec):
 			assert a.shape == b.shape and np.array_equal(a, b)
 		n_seen += 1
 	assert n_seen == len(jobs)
+	# strips only (the OCR stage never touches the dewarped image): same strips, no page
+	for res, (wd, ws) in zip(PagePipeline(line_height=48, binarize=spec, dewarped=False).run(jobs), want):
+		assert res.dewarped is None and len(res.strips) == len(ws)
+		for a, b in zip(res.strips, ws):
+			assert a.shape == b.shape and np.array_equal(a, b)
 
 
 def test_page_pipeline_with_column_descriptors(small):
