@@ -21,7 +21,7 @@ lines = ["# ncu --set full --clock-control none --import-source on (B200, 4800x7
 	"# command: python bench.py --steps 4 --warmup 3 --no-e2e --no-cpu-baseline --page-sets 1   (one launch of each kernel)", ""]
 traffic = {}
 scale = {'byte': 1, 'Kbyte': 1e3, 'Mbyte': 1e6, 'Gbyte': 1e9}
-names = {'og_page_kernel': 'og_page_kernel', 'og_strips_screened_kernel': 'og_strips_screened_kernel', 'og_lines_map_kernel': 'og_lines_map_kernel', 'og_otsu_strips_kernel': 'og_binarize',
+names = {'og_page_pipelined_kernel': 'og_page_kernel', 'og_page_kernel': 'og_page_kernel', 'og_strips_screened_kernel': 'og_strips_screened_kernel', 'og_lines_map_kernel': 'og_lines_map_kernel', 'og_otsu_strips_kernel': 'og_binarize',
 	'og_line_steps_kernel': 'og_line_steps_kernel', 'og_line_scan_kernel': 'og_line_scan_kernel', 'og_line_plan_kernel': 'og_line_plan_kernel'}
 for row in r[2:]:
 	short = row[h.index('Kernel Name')].split('(')[0].replace('void ', '').replace('<unnamed>::', '')
