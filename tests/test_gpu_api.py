@@ -299,3 +299,14 @@ def test_page_pipeline_reruns_a_page_whose_strip_estimate_fell_short(small, monk
 		# and the real estimate is tight: never below, at most a few columns above what the device derived
 		slack = good - res.steps[:, 0]
 		assert (slack >= 0).all() and (slack <= 16).all()
+
+
+def test_page_pipeline_without_lines_and_without_dewarped_page(small):
+	from origami_b200.batch.core.pipeline import PagePipeline
+	empty = np.zeros((0, 3, 2), dtype=np.float64)
+	for dewarped in (True, False):
+		(res,) = list(PagePipeline(line_height=48, dewarped=dewarped).run([(small.page, small.g, small.s, empty)]))
+		assert len(res.strips) == 0 and res.steps.shape == (0, 2)
+		assert (res.dewarped is None) == (not dewarped)
+		if dewarped:
+			assert np.array_equal(res.dewarped, exact.remap_linear(small.page, exact.expand_map(small.g, small.s)))

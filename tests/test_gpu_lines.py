@@ -313,3 +313,27 @@ def test_line_plan_large_batches_take_the_two_kernel_path(cuda):
 	assert int(big.chunk_offsets[-1].item()) == 0 and int(small.chunk_offsets[-1].item()) == 0
 	for i, r in enumerate(recs):
 		assert tuple(s_small[i]) == exact.line_steps(dense, r["p"], r["right"], r["up"])
+
+
+def test_screened_strips_with_more_lines_than_the_offset_cache(cuda):
+	"""More than 4096 lines: the prefix sums no longer fit the kernel's shared-memory cache and are
+	searched in global memory; few pixels per line, so most tickets are row quarters."""
+	page, grid, dense, lines = _setup(cuda, n_lines=60, seed=17)
+	g = torch.from_numpy(grid).to(cuda)
+	src = ops.to_device_image(page, cuda)
+	recs = (_records(lines, ysteps=9, xsteps=40) + _records(lines, ysteps=48)) * 40  # 4800 lines
+	plan = ops.line_steps(g, 25, ops.lines_to_device(ops.pack_lines(recs), cuda), len(recs))
+	total = int(plan.pix_offsets[-1].item())
+	m = ops.expand_map(g, 25)
+	a = torch.zeros((total,), dtype=torch.uint8, device=cuda)
+	b = torch.zeros((total,), dtype=torch.uint8, device=cuda)
+	bbox = torch.zeros((len(recs), 4), dtype=torch.int32, device=cuda)
+	ops.extract_lines(src, g, 25, plan, a, dense_map=m)
+	ops.extract_lines(src, g, 25, plan, b, bbox, dense_map=m)
+	assert len(recs) > 4096 and torch.equal(a, b)
+	offs = plan.pix_offsets.cpu().numpy()
+	out = a.cpu().numpy()
+	for i in (0, 59, 60, 119, len(recs) - 1):
+		r = recs[i]
+		want = exact.remap_linear(page, exact.warped_grid(dense, r["p"], r["right"], r["up"], xsteps=r.get("xsteps"), ysteps=r["ysteps"]))[::-1]
+		assert np.array_equal(out[offs[i]:offs[i + 1]].reshape(want.shape), want), i
