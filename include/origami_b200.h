@@ -98,8 +98,8 @@ int og_inverse_yx(const float *grid, int gh, int gw, int cell,
  * xsteps*ysteps (n+1 entries, element offsets of each strip in a packed buffer);
  * chunk_offsets_out (n+2 entries) = n+1 prefix sums of the work items the extraction kernels
  * split each line into (64 strip columns each), followed by one work-ticket word that this call
- * zeroes and og_extract_lines uses while it runs (and leaves at zero).  A plan therefore serves
- * one og_extract_lines call at a time.  Two small kernels, no host synchronisation.
+ * zeroes and og_extract_lines / og_sample_labels use while they run (and leave at zero).  A plan
+ * therefore serves one such call at a time.  Two small kernels, no host synchronisation.
  * A line whose extent is not finite, or whose strip would exceed 2^31 pixels, gets steps (0, 0)
  * and no work items. */
 int og_line_steps(const float *grid, int gh, int gw, int cell,
@@ -175,12 +175,13 @@ int og_otsu_noalloc(const uint8_t *src, int h, int w, int64_t src_pitch,
  * warped grid at (xres, yres) from the descriptors, scaled to the label map by
  * fp32(lw/W), fp32(lh/H), NEAREST lookup (OOB -> label 0), histogram.  counts_out
  * (n, n_classes) int64, zeroed by the call; labels >= n_classes are counted in
- * overflow_out[i] (n int64, may be NULL; np.bincount would have grown the array). */
+ * overflow_out[i] (n int64, may be NULL; np.bincount would have grown the array).  Like
+ * og_extract_lines it uses the plan's work-ticket word while it runs. */
 int og_sample_labels(const uint8_t *labels, int lh, int lw, int64_t labels_pitch,
 	int H, int W,
 	const float *grid, int gh, int gw, int cell, const float *map,
 	const og_line *lines, int n,
-	const int32_t *steps, const int32_t *chunk_offsets,
+	const int32_t *steps, int32_t *chunk_offsets,
 	int n_classes, int64_t *counts_out, int64_t *overflow_out, void *stream);
 
 /* A18+A19  label argmax and class masks -- origami/core/predict.py:281-285,

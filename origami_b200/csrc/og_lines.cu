@@ -559,7 +559,7 @@ constexpr int MAP_OFFS_CAP = 4096;  // line prefix sums cached in shared memory 
 
 // One sample of the dense map in the reference's float64 order (SciPy _evaluate_linear), cast to
 // float32 and quantised as cv2.remap does: the slow, always-valid path behind the screening below.
-__device__ __noinline__ int2 og_map_sample_exact_fixed(const float2 *__restrict__ map, int Wd, int Hm, int Wm, double px, double py) {
+__device__ __forceinline__ float2 og_map_sample_exact(const float2 *__restrict__ map, int Wd, int Hm, int Wm, double px, double py) {
 	const int i0 = min(max(__double2int_rd(py), 0), Hm);
 	const int i1 = min(max(__double2int_rd(px), 0), Wm);
 	const double a = __dsub_rn(py, (double)i0), b = __dsub_rn(px, (double)i1);
@@ -572,7 +572,12 @@ __device__ __noinline__ int2 og_map_sample_exact_fixed(const float2 *__restrict_
 		__dmul_rn((double)v10.x, w10)), __dmul_rn((double)v11.x, w11));
 	const double wy = __dadd_rn(__dadd_rn(__dadd_rn(__dmul_rn((double)v00.y, w00), __dmul_rn((double)v01.y, w01)),
 		__dmul_rn((double)v10.y, w10)), __dmul_rn((double)v11.y, w11));
-	return make_int2(__float2int_rn(__fmul_rn(__double2float_rn(wx), 32.f)), __float2int_rn(__fmul_rn(__double2float_rn(wy), 32.f)));
+	return make_float2(__double2float_rn(wx), __double2float_rn(wy));
+}
+
+__device__ __noinline__ int2 og_map_sample_exact_fixed(const float2 *__restrict__ map, int Wd, int Hm, int Wm, double px, double py) {
+	const float2 g = og_map_sample_exact(map, Wd, Hm, Wm, px, py);
+	return make_int2(__float2int_rn(__fmul_rn(g.x, 32.f)), __float2int_rn(__fmul_rn(g.y, 32.f)));
 }
 
 // Screening constants.  OG_FIX_MAGIC = 1.5 * 2^29: a double in [2^29, 2^30) has an ulp of 2^-23,
@@ -655,6 +660,34 @@ __device__ __forceinline__ void og_taps_interior(og_taps &t, const uint8_t *__re
 	t.p01 = __ldg(q + 1);
 	t.p10 = __ldg(q + pitch);
 	t.p11 = __ldg(q + pitch + 1);
+}
+
+// --- label sampling (A15) through the same screening: what the NEAREST lookup uses of a sample is
+// cvRound(fl32(fl32(X) * scale)) per coordinate, again monotone in X.
+__device__ __forceinline__ bool og_nodes_screen_nearest(const og_nodes &n, float scx, float scy, int &ix, int &iy) {
+	const float d01x = __fsub_rn(n.v01.x, n.v00.x), d10x = __fsub_rn(n.v10.x, n.v00.x), d11x = __fsub_rn(n.v11.x, n.v10.x);
+	const float d01y = __fsub_rn(n.v01.y, n.v00.y), d10y = __fsub_rn(n.v10.y, n.v00.y), d11y = __fsub_rn(n.v11.y, n.v10.y);
+	const float g = fmaxf(fmaxf(fmaxf(fabsf(d01x), fabsf(d10x)), fmaxf(fabsf(d11x), fabsf(d01y))), fmaxf(fabsf(d10y), fabsf(d11y)));
+	const float eps = __fmaf_rn(g, 0x1p-19f, 0x1p-30f);
+	const float dx = __fmaf_rn(n.a, __fmaf_rn(n.b, __fsub_rn(d11x, d01x), d10x), __fmul_rn(n.b, d01x));
+	const float dy = __fmaf_rn(n.a, __fmaf_rn(n.b, __fsub_rn(d11y, d01y), d10y), __fmul_rn(n.b, d01y));
+	// scale_grid (batch/detect/lines.py:18-22) rounds the product to float32 before cv2.remap rounds
+	// it to an integer: a multiply, then the magic add
+	const float uxl = __fadd_rn(__fmul_rn(__fadd_rn(n.v00.x, __fsub_rn(dx, eps)), scx), OG_RINT_MAGIC);
+	const float uxh = __fadd_rn(__fmul_rn(__fadd_rn(n.v00.x, __fadd_rn(dx, eps)), scx), OG_RINT_MAGIC);
+	const float uyl = __fadd_rn(__fmul_rn(__fadd_rn(n.v00.y, __fsub_rn(dy, eps)), scy), OG_RINT_MAGIC);
+	const float uyh = __fadd_rn(__fmul_rn(__fadd_rn(n.v00.y, __fadd_rn(dy, eps)), scy), OG_RINT_MAGIC);
+	ix = __float_as_int(uxl) - OG_RINT_BITS;
+	iy = __float_as_int(uyl) - OG_RINT_BITS;
+	// beyond |x| = 2^22 the mantissa no longer holds the integer, but then (ix, iy) cannot land
+	// inside the label map either; a NaN compares unequal
+	return n.ok && uxl == uxh && uyl == uyh;
+}
+
+__device__ __noinline__ int og_sample_label_exact(const uint8_t *__restrict__ src, int H, int W, int pitch,
+	const float2 *__restrict__ map, int Wd, int Hm, int Wm, double px, double py, float scx, float scy) {
+	const float2 g = og_map_sample_exact(map, Wd, Hm, Wm, px, py);
+	return og_sample_nearest_fast(src, H, W, pitch, __fmul_rn(g.x, scx), __fmul_rn(g.y, scy));
 }
 
 // One strip column: `rows` rows whose (ys + p0) sit in the warp's shared-memory table at
@@ -747,6 +780,79 @@ __device__ __noinline__ void og_strip_column_exact(const LineParams &p, const fl
 	}
 }
 
+// One column of a line's label samples (A15): as og_strip_column_screened, with one NEAREST byte
+// per sample instead of four taps and a shared-memory histogram instead of the strip.
+template <int NB>
+__device__ __forceinline__ void og_label_column_screened(const LineParams &p, const float2 *__restrict__ map,
+	unsigned tab_saddr, int rows, og_d2 xc, unsigned int *hist) {
+	const uint8_t *__restrict__ src = p.src;
+	auto point = [&](int r, double &px, double &py) {
+		double rbx, rby;
+		asm volatile("ld.shared.v2.f64 {%0, %1}, [%2];" : "=d"(rbx), "=d"(rby) : "r"(tab_saddr + r * 16));
+		px = __dadd_rn(rbx, xc.x);
+		py = __dadd_rn(rby, xc.y);
+	};
+	auto load = [&](og_nodes (&n)[NB], int r) {
+#pragma unroll
+		for (int u = 0; u < NB; ++u) {
+			double px, py;
+			point(r + u, px, py);
+			og_nodes_load(n[u], px, py, map, p.Wd, p.Hm, p.Wm, p.one_bits);
+		}
+	};
+	auto fetch = [&](const og_nodes (&n)[NB], int (&lab)[NB], int r) {
+#pragma unroll
+		for (int u = 0; u < NB; ++u) {
+			int ix, iy;
+			if (og_nodes_screen_nearest(n[u], p.scale_x, p.scale_y, ix, iy)) {
+				// cv2.remap INTER_NEAREST: outside the label map -> BORDER_CONSTANT 0
+				lab[u] = ((unsigned)ix < (unsigned)p.W && (unsigned)iy < (unsigned)p.H) ? (int)__ldg(src + (iy * p.src_pitch + ix)) : 0;
+			} else {
+				double px, py;
+				point(r + u, px, py);
+				lab[u] = og_sample_label_exact(src, p.H, p.W, p.src_pitch, map, p.Wd, p.Hm, p.Wm, px, py, p.scale_x, p.scale_y);
+			}
+		}
+	};
+	auto count = [&](const int (&lab)[NB]) {
+#pragma unroll
+		for (int u = 0; u < NB; ++u) atomicAdd(hist + min(lab[u], p.n_classes), 1u);
+	};
+
+	const int nb = rows / NB;
+	if (nb == 0) return;
+	og_nodes n0[NB], n1[NB];
+	int l0[NB], l1[NB];
+	load(n0, 0);
+	load(n1, min(1, nb - 1) * NB);
+	fetch(n0, l0, 0);
+	int b = 1;
+	for (; b + 1 < nb; b += 2) {  // on entry: l0 = labels of batch b-1, n1 = nodes of batch b
+		load(n0, (b + 1) * NB);
+		count(l0);
+		fetch(n1, l1, b * NB);
+		load(n1, min(b + 2, nb - 1) * NB);
+		count(l1);
+		fetch(n0, l0, (b + 1) * NB);
+	}
+	count(l0);
+	if (b < nb) {
+		fetch(n1, l1, b * NB);
+		count(l1);
+	}
+}
+
+__device__ __noinline__ void og_label_column_exact(const LineParams &p, const float2 *__restrict__ map,
+	unsigned tab_saddr, int rows, og_d2 xc, unsigned int *hist) {
+	for (int r = 0; r < rows; ++r) {
+		double rbx, rby;
+		asm volatile("ld.shared.v2.f64 {%0, %1}, [%2];" : "=d"(rbx), "=d"(rby) : "r"(tab_saddr + r * 16));
+		const int lab = og_sample_label_exact(p.src, p.H, p.W, p.src_pitch, map, p.Wd, p.Hm, p.Wm,
+			__dadd_rn(rbx, xc.x), __dadd_rn(rby, xc.y), p.scale_x, p.scale_y);
+		atomicAdd(hist + min(lab, p.n_classes), 1u);
+	}
+}
+
 // The line of a work item: 32-ary search of the prefix sums by the whole warp (three probes for
 // 2000 lines instead of eleven dependent loads).  offs[0] = 0 <= c < offs[n].
 __device__ __forceinline__ int og_find_line(const int32_t *offs, int n, int c, int lane) {
@@ -796,9 +902,11 @@ __device__ __forceinline__ void og_linspace_setup_pair(double crx, double cry, d
 constexpr int SWARPS = OG_SCR_WARPS;  // warps per CTA: there is no CTA-wide barrier in the item loop
 constexpr int STHREADS = SWARPS * 32;
 
+template <int MODE>  // MODE_STRIP or MODE_LABELS
 __global__ void __launch_bounds__(STHREADS, OG_SCR_BLOCKS) og_strips_screened_kernel(const __grid_constant__ LineParams p, const float2 *__restrict__ map) {
 	__shared__ double2 s_rowbase[SWARPS][MAX_ROWS];
 	__shared__ int s_chunk_offsets[MAP_OFFS_CAP];
+	__shared__ unsigned int s_whist[MODE == MODE_LABELS ? SWARPS : 1][MODE == MODE_LABELS ? MAX_CLASSES + 1 : 1];
 	const bool offs_cached = p.n + 1 <= MAP_OFFS_CAP;
 	if (offs_cached) {
 		for (int i = threadIdx.x; i <= p.n; i += STHREADS) s_chunk_offsets[i] = __ldg(p.chunk_offsets + i);
@@ -837,8 +945,8 @@ __global__ void __launch_bounds__(STHREADS, OG_SCR_BLOCKS) og_strips_screened_ke
 		const int xsteps = __ldg(p.steps + 2 * li), ysteps = __ldg(p.steps + 2 * li + 1);
 		const int c0 = (chunk_item - chunk_offsets[li]) * CW + (item & 1) * MW;
 		if (c0 >= xsteps) return;
-		const long long pix0 = __ldg(p.pix_offsets + li);
-		if (pix0 + (long long)xsteps * ysteps > p.capacity) return;
+		const long long pix0 = MODE == MODE_STRIP ? __ldg(p.pix_offsets + li) : 0;
+		if (MODE == MODE_STRIP && pix0 + (long long)xsteps * ysteps > p.capacity) return;
 		// this warp's rows of the item (an even count, so that only the strip's own last row can be odd)
 		const int row_a = (int)((long long)ysteps * piece / npieces) & ~1;
 		const int row_z = piece + 1 == npieces ? ysteps : (int)((long long)ysteps * (piece + 1) / npieces) & ~1;
@@ -853,6 +961,9 @@ __global__ void __launch_bounds__(STHREADS, OG_SCR_BLOCKS) og_strips_screened_ke
 		const bool sane = fabs(cpx) + fabs(cpy) + fabs(crx) + fabs(cry) + fabs(upx) + fabs(upy) < 134217728.0;
 		const int cc = c0 + lane;
 		const og_d2 xc = og_linspace_at(lx, min(cc, xsteps - 1));
+		if (MODE == MODE_LABELS) {
+			for (int q = lane; q <= MAX_CLASSES; q += 32) s_whist[wid][q] = 0;
+		}
 		for (int rb0 = row_a; rb0 < row_z; rb0 += MAX_ROWS) {
 			const int rows = min(row_z - rb0, MAX_ROWS);
 			__syncwarp();
@@ -862,6 +973,17 @@ __global__ void __launch_bounds__(STHREADS, OG_SCR_BLOCKS) og_strips_screened_ke
 			}
 			__syncwarp();
 			if (cc >= xsteps) continue;
+			if (MODE == MODE_LABELS) {
+				unsigned int *hist = s_whist[wid];
+				if (sane) {
+					og_label_column_screened<RB>(p, map, rb_saddr, rows, xc, hist);
+					const int done = rows / RB * RB;
+					if (done < rows) og_label_column_screened<1>(p, map, rb_saddr + done * 16, rows - done, xc, hist);
+				} else {
+					og_label_column_exact(p, map, rb_saddr, rows, xc, hist);
+				}
+				continue;
+			}
 			uint8_t *out = p.strips_out + pix0 + cc + (long long)(ysteps - 1 - rb0) * xsteps;
 			if (sane) {
 				og_strip_column_screened<RB>(p, map, rb_saddr, rows, xc, out, xsteps);
@@ -871,6 +993,14 @@ __global__ void __launch_bounds__(STHREADS, OG_SCR_BLOCKS) og_strips_screened_ke
 			} else {
 				og_strip_column_exact(p, map, rb_saddr, rows, xc, out, xsteps);
 			}
+		}
+		if (MODE == MODE_LABELS) {  // this ticket's share of the line's counts
+			__syncwarp();
+			for (int q = lane; q < p.n_classes; q += 32)
+				if (s_whist[wid][q]) atomicAdd(p.counts_out + (size_t)li * p.n_classes + q, (unsigned long long)s_whist[wid][q]);
+			if (lane == 0 && s_whist[wid][p.n_classes] && p.overflow_out != nullptr)
+				atomicAdd(p.overflow_out + li, (unsigned long long)s_whist[wid][p.n_classes]);
+			__syncwarp();
 		}
 	};
 
@@ -1126,7 +1256,7 @@ int launch_lines(const LineParams &p, cudaStream_t st) {
 template <int MODE, bool BBOX>
 int launch_lines_any(const LineParams &p, const float *map, cudaStream_t st) {
 	if (map == nullptr) return launch_lines<MODE, BBOX>(p, st);
-	if (MODE == MODE_STRIP && !BBOX && OG_LINES_SCREEN) {
+	if ((MODE == MODE_STRIP || MODE == MODE_LABELS) && !BBOX && OG_LINES_SCREEN) {
 		LineParams q = p;
 		q.Wd = p.gw * p.cell;
 		q.Hm = p.gh * p.cell - 2;
@@ -1135,7 +1265,7 @@ int launch_lines_any(const LineParams &p, const float *map, cudaStream_t st) {
 		q.H1 = p.H - 1;
 		q.one_bits = 0x3F800000u;
 		q.ticket = const_cast<int *>(p.chunk_offsets) + p.n + 1;
-		og_strips_screened_kernel<<<OG_NUM_SMS * OG_SCR_BLOCKS, STHREADS, 0, st>>>(q, reinterpret_cast<const float2 *>(map));
+		og_strips_screened_kernel<(MODE == MODE_LABELS ? MODE_LABELS : MODE_STRIP)><<<OG_NUM_SMS * OG_SCR_BLOCKS, STHREADS, 0, st>>>(q, reinterpret_cast<const float2 *>(map));
 		return og_check_launch("og_strips_screened_kernel");
 	}
 	og_lines_map_kernel<MODE, BBOX><<<OG_NUM_SMS * OG_MAP_MINBLOCKS, MTHREADS, 0, st>>>(p, reinterpret_cast<const float2 *>(map));
@@ -1245,7 +1375,7 @@ extern "C" int og_sample_labels(const uint8_t *labels, int lh, int lw, int64_t l
 	int H, int W,
 	const float *grid, int gh, int gw, int cell, const float *map,
 	const og_line *lines, int n,
-	const int32_t *steps, const int32_t *chunk_offsets,
+	const int32_t *steps, int32_t *chunk_offsets,
 	int n_classes, int64_t *counts_out, int64_t *overflow_out, void *stream) {
 	int rc = check_grid(grid, gh, gw, cell);
 	if (rc) return rc;

@@ -337,3 +337,28 @@ def test_screened_strips_with_more_lines_than_the_offset_cache(cuda):
 		r = recs[i]
 		want = exact.remap_linear(page, exact.warped_grid(dense, r["p"], r["right"], r["up"], xsteps=r.get("xsteps"), ysteps=r["ysteps"]))[::-1]
 		assert np.array_equal(out[offs[i]:offs[i + 1]].reshape(want.shape), want), i
+
+
+def test_screened_label_counts_on_adversarial_maps(cuda):
+	"""Label sampling through the screened engine: custom dense maps (rough, off-page, on the rounding
+	ties of the NEAREST lookup) against the oracle, overflow labels included; the ticket is reset."""
+	page, grid, dense, lines = _setup(cuda, n_lines=40, seed=6)
+	labels = synth.make_labels(320, 600, seed=4)
+	labels[::7, ::5] = 9  # labels beyond n_classes -> overflow
+	g = torch.from_numpy(grid).to(cuda)
+	lab = ops.to_device_image(labels, cuda)
+	recs = _records(lines, xsteps=70, ysteps=13)
+	plan = ops.line_steps(g, 25, ops.lines_to_device(ops.pack_lines(recs), cuda), len(recs))
+	maps = _adversarial_maps(dense)
+	sx, sy = np.float32(labels.shape[1] / page.shape[1]), np.float32(labels.shape[0] / page.shape[0])
+	maps["on the nearest ties"] = np.dstack([(np.round(dense[..., 0] * sx) + 0.5) / sx, (np.round(dense[..., 1] * sy) + 0.5) / sy]).astype(np.float32)
+	maps["grid"] = dense
+	for name, m in maps.items():
+		counts, overflow = ops.sample_labels(lab, page.shape, g, 25, plan, 4, dense_map=torch.from_numpy(np.ascontiguousarray(m)).to(cuda))
+		counts, overflow = counts.cpu().numpy(), overflow.cpu().numpy()
+		assert int(plan.chunk_offsets[len(recs) + 1].item()) == 0
+		for i, r in enumerate(recs):
+			wg = exact.warped_grid(m, r["p"], r["right"], r["up"], xsteps=70, ysteps=13)
+			got = exact.remap_nearest(labels, exact.scale_map(wg, page.shape[1], page.shape[0], labels.shape[1], labels.shape[0]))
+			want = np.bincount(got.reshape(-1), minlength=10)
+			assert np.array_equal(counts[i], want[:4]) and overflow[i] == want[4:].sum(), (name, i)
