@@ -1265,6 +1265,11 @@ int launch_lines_any(const LineParams &p, const float *map, cudaStream_t st) {
 		q.H1 = p.H - 1;
 		q.one_bits = 0x3F800000u;
 		q.ticket = const_cast<int *>(p.chunk_offsets) + p.n + 1;
+		// the ticket is zero after og_line_steps and after every completed call; it is cleared here
+		// all the same, so that a plan assembled elsewhere, or a call that failed half way, cannot
+		// make this one skip work
+		cudaError_t e = cudaMemsetAsync(q.ticket, 0, sizeof(int), st);
+		if (e != cudaSuccess) return og_set_error((int)e, "cudaMemsetAsync: %s", cudaGetErrorString(e));
 		og_strips_screened_kernel<(MODE == MODE_LABELS ? MODE_LABELS : MODE_STRIP)><<<OG_NUM_SMS * OG_SCR_BLOCKS, STHREADS, 0, st>>>(q, reinterpret_cast<const float2 *>(map));
 		return og_check_launch("og_strips_screened_kernel");
 	}
