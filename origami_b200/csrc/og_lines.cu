@@ -1065,117 +1065,117 @@ __global__ void __launch_bounds__(MTHREADS, OG_MAP_MINBLOCKS) og_lines_map_kerne
 		// rows in blocks of MAX_ROWS (one block for any OCR strip height): (ys + p0) of the block's
 		// rows goes to the warp's shared-memory table   (block.py:241)
 		for (int rb0 = 0; rb0 < ysteps; rb0 += MAX_ROWS) {
-		const int rb_end = min(ysteps, rb0 + MAX_ROWS);
-		__syncwarp();
-		for (int r = rb0 + lane; r < rb_end; r += 32) {
-			og_d2 yr = og_linspace_at(ly, r);
-			rowbase[r - rb0] = make_double2(__dadd_rn(yr.x, cpx), __dadd_rn(yr.y, cpy));
-		}
-		__syncwarp();
-		if (cc < xsteps) {
-			uint8_t *strip = (MODE == MODE_STRIP) ? p.strips_out + pix0 + cc : nullptr;
-			float2 *gout = (MODE == MODE_GRID) ? reinterpret_cast<float2 *>(p.grids_out) + pix0 + cc : nullptr;
-			const float2 *__restrict__ map_lo = map;
-			const float2 *__restrict__ map_hi = map + Wd;
+			const int rb_end = min(ysteps, rb0 + MAX_ROWS);
+			__syncwarp();
+			for (int r = rb0 + lane; r < rb_end; r += 32) {
+				og_d2 yr = og_linspace_at(ly, r);
+				rowbase[r - rb0] = make_double2(__dadd_rn(yr.x, cpx), __dadd_rn(yr.y, cpy));
+			}
+			__syncwarp();
+			if (cc < xsteps) {
+				uint8_t *strip = (MODE == MODE_STRIP) ? p.strips_out + pix0 + cc : nullptr;
+				float2 *gout = (MODE == MODE_GRID) ? reinterpret_cast<float2 *>(p.grids_out) + pix0 + cc : nullptr;
+				const float2 *__restrict__ map_lo = map;
+				const float2 *__restrict__ map_hi = map + Wd;
 
-			// one batch of RB consecutive rows: coordinates, node gather, float64 blend -> (gx, gy)
-			auto coords = [&](int rbase, float (&gx)[RB], float (&gy)[RB], int (&row)[RB]) {
-				int idx[RB];
-				double a[RB], b[RB];
-				float2 v00[RB], v01[RB], v10[RB], v11[RB];
-#pragma unroll
-				for (int u = 0; u < RB; ++u) {
-					const int r = rbase + u;
-					row[u] = r < rb_end ? r : -1;
-					const int rr = min(r, rb_end - 1) - rb0;
-					double rbx, rby;
-					asm volatile("ld.shared.v2.f64 {%0, %1}, [%2];" : "=d"(rbx), "=d"(rby) : "r"(rb_saddr + rr * 16));
-					// dewarped_grid = (ys + p0)[:, None] + xs[None, :]   (block.py:241)
-					const double px = __dadd_rn(rbx, xc.x);
-					const double py = __dadd_rn(rby, xc.y);
-					// i = clip(floor(y), 0, n - 2) (SciPy find_indices); the saturating
-					// conversion keeps even absurd coordinates inside the map
-					const int i0 = min(max(__double2int_rd(py), 0), Hm);
-					const int i1 = min(max(__double2int_rd(px), 0), Wm);
-					a[u] = __dsub_rn(py, (double)i0);
-					b[u] = __dsub_rn(px, (double)i1);
-					idx[u] = i0 * Wd + i1;  // < 2^30 elements (dims < 32767)
-					v00[u] = __ldg(map_lo + idx[u]);
-					v01[u] = __ldg(map_lo + idx[u] + 1);
-					v10[u] = __ldg(map_hi + idx[u]);
-					v11[u] = __ldg(map_hi + idx[u] + 1);
-				}
-#pragma unroll
-				for (int u = 0; u < RB; ++u) {
-					const double wa = __dsub_rn(1.0, a[u]), wb = __dsub_rn(1.0, b[u]);
-					const double w00 = __dmul_rn(wa, wb), w01 = __dmul_rn(wa, b[u]);
-					const double w10 = __dmul_rn(a[u], wb), w11 = __dmul_rn(a[u], b[u]);
-					const double wx = __dadd_rn(__dadd_rn(__dadd_rn(__dmul_rn((double)v00[u].x, w00), __dmul_rn((double)v01[u].x, w01)),
-						__dmul_rn((double)v10[u].x, w10)), __dmul_rn((double)v11[u].x, w11));
-					const double wy = __dadd_rn(__dadd_rn(__dadd_rn(__dmul_rn((double)v00[u].y, w00), __dmul_rn((double)v01[u].y, w01)),
-						__dmul_rn((double)v10[u].y, w10)), __dmul_rn((double)v11[u].y, w11));
-					gx[u] = __double2float_rn(wx);
-					gy[u] = __double2float_rn(wy);
-				}
-			};
-			auto flush = [&](const og_taps (&t)[RB], const int (&trow)[RB]) {
-#pragma unroll
-				for (int u = 0; u < RB; ++u)
-					if (trow[u] >= 0)  // pixels[::-1, :]  (block.py:257)
-						strip[(ysteps - 1 - trow[u]) * xsteps] = (uint8_t)og_blend_taps(t[u]);
-			};
-
-			if (MODE == MODE_STRIP) {
-				// two tap buffers in rotation: the taps of a batch are requested, then the previous
-				// batch is blended and stored while they are in flight
-				og_taps t0[RB], t1[RB];
-				int r0[RB], r1[RB];
-#pragma unroll
-				for (int u = 0; u < RB; ++u) r1[u] = -1;
-				for (int rbase = rb0; rbase < rb_end; rbase += 2 * RB) {
-					float gx[RB], gy[RB];
-					coords(rbase, gx, gy, r0);
-					og_load_taps_batch<RB>(src, H, W, spitch, gx, gy, t0);
-					flush(t1, r1);
-					if (BBOX) {
-#pragma unroll
-						for (int u = 0; u < RB; ++u) {  // a dead slot repeats a live row: harmless for min/max
-							bx0 = fminf(bx0, gx[u]); bx1 = fmaxf(bx1, gx[u]);
-							by0 = fminf(by0, gy[u]); by1 = fmaxf(by1, gy[u]);
-						}
-					}
-					coords(rbase + RB, gx, gy, r1);
-					og_load_taps_batch<RB>(src, H, W, spitch, gx, gy, t1);
-					flush(t0, r0);
-					if (BBOX) {
-#pragma unroll
-						for (int u = 0; u < RB; ++u) {
-							bx0 = fminf(bx0, gx[u]); bx1 = fmaxf(bx1, gx[u]);
-							by0 = fminf(by0, gy[u]); by1 = fmaxf(by1, gy[u]);
-						}
-					}
-				}
-				flush(t1, r1);
-			} else {
-				for (int rbase = rb0; rbase < rb_end; rbase += RB) {
-					float gx[RB], gy[RB];
-					int row[RB];
-					coords(rbase, gx, gy, row);
+				// one batch of RB consecutive rows: coordinates, node gather, float64 blend -> (gx, gy)
+				auto coords = [&](int rbase, float (&gx)[RB], float (&gy)[RB], int (&row)[RB]) {
+					int idx[RB];
+					double a[RB], b[RB];
+					float2 v00[RB], v01[RB], v10[RB], v11[RB];
 #pragma unroll
 					for (int u = 0; u < RB; ++u) {
-						if (row[u] < 0) continue;
-						if (MODE == MODE_GRID) {
-							gout[row[u] * xsteps] = make_float2(gx[u], gy[u]);
-						} else {
-							// scale_grid (batch/detect/lines.py:18-22) then cv2.remap INTER_NEAREST
-							const float sx = __fmul_rn(gx[u], p.scale_x), sy = __fmul_rn(gy[u], p.scale_y);
-							const int lab = og_sample_nearest_fast(src, H, W, spitch, sx, sy);
-							atomicAdd(&s_whist[wid][min(lab, p.n_classes)], 1u);
+						const int r = rbase + u;
+						row[u] = r < rb_end ? r : -1;
+						const int rr = min(r, rb_end - 1) - rb0;
+						double rbx, rby;
+						asm volatile("ld.shared.v2.f64 {%0, %1}, [%2];" : "=d"(rbx), "=d"(rby) : "r"(rb_saddr + rr * 16));
+						// dewarped_grid = (ys + p0)[:, None] + xs[None, :]   (block.py:241)
+						const double px = __dadd_rn(rbx, xc.x);
+						const double py = __dadd_rn(rby, xc.y);
+						// i = clip(floor(y), 0, n - 2) (SciPy find_indices); the saturating
+						// conversion keeps even absurd coordinates inside the map
+						const int i0 = min(max(__double2int_rd(py), 0), Hm);
+						const int i1 = min(max(__double2int_rd(px), 0), Wm);
+						a[u] = __dsub_rn(py, (double)i0);
+						b[u] = __dsub_rn(px, (double)i1);
+						idx[u] = i0 * Wd + i1;  // < 2^30 elements (dims < 32767)
+						v00[u] = __ldg(map_lo + idx[u]);
+						v01[u] = __ldg(map_lo + idx[u] + 1);
+						v10[u] = __ldg(map_hi + idx[u]);
+						v11[u] = __ldg(map_hi + idx[u] + 1);
+					}
+#pragma unroll
+					for (int u = 0; u < RB; ++u) {
+						const double wa = __dsub_rn(1.0, a[u]), wb = __dsub_rn(1.0, b[u]);
+						const double w00 = __dmul_rn(wa, wb), w01 = __dmul_rn(wa, b[u]);
+						const double w10 = __dmul_rn(a[u], wb), w11 = __dmul_rn(a[u], b[u]);
+						const double wx = __dadd_rn(__dadd_rn(__dadd_rn(__dmul_rn((double)v00[u].x, w00), __dmul_rn((double)v01[u].x, w01)),
+							__dmul_rn((double)v10[u].x, w10)), __dmul_rn((double)v11[u].x, w11));
+						const double wy = __dadd_rn(__dadd_rn(__dadd_rn(__dmul_rn((double)v00[u].y, w00), __dmul_rn((double)v01[u].y, w01)),
+							__dmul_rn((double)v10[u].y, w10)), __dmul_rn((double)v11[u].y, w11));
+						gx[u] = __double2float_rn(wx);
+						gy[u] = __double2float_rn(wy);
+					}
+				};
+				auto flush = [&](const og_taps (&t)[RB], const int (&trow)[RB]) {
+#pragma unroll
+					for (int u = 0; u < RB; ++u)
+						if (trow[u] >= 0)  // pixels[::-1, :]  (block.py:257)
+							strip[(ysteps - 1 - trow[u]) * xsteps] = (uint8_t)og_blend_taps(t[u]);
+				};
+
+				if (MODE == MODE_STRIP) {
+					// two tap buffers in rotation: the taps of a batch are requested, then the previous
+					// batch is blended and stored while they are in flight
+					og_taps t0[RB], t1[RB];
+					int r0[RB], r1[RB];
+#pragma unroll
+					for (int u = 0; u < RB; ++u) r1[u] = -1;
+					for (int rbase = rb0; rbase < rb_end; rbase += 2 * RB) {
+						float gx[RB], gy[RB];
+						coords(rbase, gx, gy, r0);
+						og_load_taps_batch<RB>(src, H, W, spitch, gx, gy, t0);
+						flush(t1, r1);
+						if (BBOX) {
+#pragma unroll
+							for (int u = 0; u < RB; ++u) {  // a dead slot repeats a live row: harmless for min/max
+								bx0 = fminf(bx0, gx[u]); bx1 = fmaxf(bx1, gx[u]);
+								by0 = fminf(by0, gy[u]); by1 = fmaxf(by1, gy[u]);
+							}
+						}
+						coords(rbase + RB, gx, gy, r1);
+						og_load_taps_batch<RB>(src, H, W, spitch, gx, gy, t1);
+						flush(t0, r0);
+						if (BBOX) {
+#pragma unroll
+							for (int u = 0; u < RB; ++u) {
+								bx0 = fminf(bx0, gx[u]); bx1 = fmaxf(bx1, gx[u]);
+								by0 = fminf(by0, gy[u]); by1 = fmaxf(by1, gy[u]);
+							}
+						}
+					}
+					flush(t1, r1);
+				} else {
+					for (int rbase = rb0; rbase < rb_end; rbase += RB) {
+						float gx[RB], gy[RB];
+						int row[RB];
+						coords(rbase, gx, gy, row);
+#pragma unroll
+						for (int u = 0; u < RB; ++u) {
+							if (row[u] < 0) continue;
+							if (MODE == MODE_GRID) {
+								gout[row[u] * xsteps] = make_float2(gx[u], gy[u]);
+							} else {
+								// scale_grid (batch/detect/lines.py:18-22) then cv2.remap INTER_NEAREST
+								const float sx = __fmul_rn(gx[u], p.scale_x), sy = __fmul_rn(gy[u], p.scale_y);
+								const int lab = og_sample_nearest_fast(src, H, W, spitch, sx, sy);
+								atomicAdd(&s_whist[wid][min(lab, p.n_classes)], 1u);
+							}
 						}
 					}
 				}
 			}
-		}
 		}  // row block
 		if (BBOX) {
 #pragma unroll
