@@ -36,6 +36,14 @@ def main():
 	maps["tiny"] = mp * 1e-3
 	maps["huge"] = mp * 1e6
 	nanmap = mp.clone(); nanmap[::97, ::89] = float("nan"); maps["nan holes"] = nanmap
+	infmap = mp.clone(); infmap[::101, ::83] = float("inf"); infmap[::103, ::79] = -float("inf"); maps["inf holes"] = infmap
+	maps["around 4096 (ulp step)"] = 4096.0 + (mp - mp.mean()) * 0.01
+	maps["around 8192 (off page)"] = 8192.0 + (mp - mp.mean()) * 0.003
+	maps["steep x50"] = (mp - mp.mean()) * 50.0 + 2000.0
+	maps["nearly flat"] = 1000.0 + mp * 1e-6
+	maps["page edges"] = torch.stack([mp[..., 0] * ((W - 1) / float(mp[..., 0].max())), mp[..., 1] * ((H - 1) / float(mp[..., 1].max()))], dim=-1)
+	maps["ties 1/32 + noise"] = torch.round(mp * 32) / 32 + 1.0 / 64 + 1e-6 * torch.randn(mp.shape, device=dev, generator=gen)
+	maps["negative zero"] = mp * -0.0
 	if "--kernel-only" in sys.argv:
 		for _ in range(3):
 			ops.extract_lines(src, g, cell, plan, s1, dense_map=mp)

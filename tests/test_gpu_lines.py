@@ -224,6 +224,10 @@ def _adversarial_maps(dense, seed=5):
 		"on the 1/64 lattice": (np.round(dense * 64) / 64).astype(f32),
 		"on the rounding ties": (np.round(dense * 32) / 32 + f32(1 / 64)).astype(f32),
 		"far outside": (dense * f32(1e6)).astype(f32),
+		"across a float32 ulp step": (f32(256) + (dense - dense.mean()) * f32(0.01)).astype(f32),
+		"steep": ((dense - dense.mean()) * f32(50) + f32(300)).astype(f32),
+		"nearly flat": (f32(100) + dense * f32(1e-6)).astype(f32),
+		"next to the ties": (np.round(dense * 32) / 32 + f32(1 / 64) + rng.normal(0, 1e-6, dense.shape)).astype(f32),
 	}
 
 
