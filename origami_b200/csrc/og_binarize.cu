@@ -315,8 +315,15 @@ __device__ void sauvola_tile(const uint8_t *__restrict__ img, int h, int w, int6
 	const int rad = win / 2;
 	const int PW = TW + 2 * rad, PH = ST_H + 2 * rad;
 	const int PV = PW | 1;  // odd row stride: lanes that own different rows hit different banks
-	uint8_t *tile = smem;                                          // PH x PW halo tile
-	unsigned int *v1 = reinterpret_cast<unsigned int *>(smem + ((PH * PW + 15) & ~15));  // ST_H x PV vertical sums of p
+	// The halo tile is stored with a left margin of XO >= rad columns, XO a multiple of 16, so that
+	// a tile row starts at a 16-byte aligned source address (tx0 is a multiple of TW) and is filled
+	// with 16-byte loads; padded column px lives at tile[py * TP + px].
+	const int XO = (rad + 15) & ~15;
+	const int TPITCH = TW + 2 * XO;
+	uint8_t *tile0 = smem;                                         // PH x TPITCH halo tile
+	uint8_t *tile = tile0 + (XO - rad);
+	const int TP = TPITCH;
+	unsigned int *v1 = reinterpret_cast<unsigned int *>(smem + ((PH * TPITCH + 15) & ~15));  // ST_H x PV vertical sums of p
 	unsigned int *v2 = v1 + ST_H * PV;                                                   // ... of p^2
 	uint8_t *otile = reinterpret_cast<uint8_t *>(v2 + ST_H * PV);  // ST_H x (TW + 16) results
 	const int tid = threadIdx.x;
@@ -326,13 +333,25 @@ __device__ void sauvola_tile(const uint8_t *__restrict__ img, int h, int w, int6
 		// halo tile: a warp per padded row, lanes along x (no per-element division); only tiles
 		// that touch the image border pay for the reflect-101 index arithmetic
 		const bool interior = ty0 - rad >= 0 && ty0 + ST_H + rad <= h && tx0 - rad >= 0 && tx0 + TW + rad <= w;
-		for (int py = wid; py < PH; py += BTHREADS / 32) {
-			if (interior) {
-				const uint8_t *rowp = img + (int64_t)(ty0 - rad + py) * pitch + (tx0 - rad);
-				for (int px = lane; px < PW; px += 32) tile[py * PW + px] = __ldg(rowp + px);
-			} else {
-				const uint8_t *rowp = img + (int64_t)reflect_index_fast(ty0 - rad + py, h) * pitch;
-				for (int px = lane; px < PW; px += 32) tile[py * PW + px] = __ldg(rowp + reflect_index_fast(tx0 - rad + px, w));
+		const bool vec = ty0 - rad >= 0 && ty0 + ST_H + rad <= h && tx0 - XO >= 0 && tx0 + TW + XO <= w &&
+			((reinterpret_cast<uintptr_t>(img) | (uintptr_t)pitch | (uintptr_t)tx0) & 15) == 0;
+		if (vec) {
+			// whole margins inside the image: 16 bytes per thread and load
+			const int CH = TPITCH >> 4;
+			const uint8_t *base = img + (int64_t)(ty0 - rad) * pitch + (tx0 - XO);
+			for (int c = tid; c < PH * CH; c += BTHREADS) {
+				const int py = c / CH, cx = (c - py * CH) << 4;
+				*reinterpret_cast<uint4 *>(tile0 + py * TPITCH + cx) = __ldg(reinterpret_cast<const uint4 *>(base + (int64_t)py * pitch + cx));
+			}
+		} else {
+			for (int py = wid; py < PH; py += BTHREADS / 32) {
+				if (interior) {
+					const uint8_t *rowp = img + (int64_t)(ty0 - rad + py) * pitch + (tx0 - rad);
+					for (int px = lane; px < PW; px += 32) tile[py * TP + px] = __ldg(rowp + px);
+				} else {
+					const uint8_t *rowp = img + (int64_t)reflect_index_fast(ty0 - rad + py, h) * pitch;
+					for (int px = lane; px < PW; px += 32) tile[py * TP + px] = __ldg(rowp + reflect_index_fast(tx0 - rad + px, w));
+				}
 			}
 		}
 	}
@@ -348,14 +367,14 @@ __device__ void sauvola_tile(const uint8_t *__restrict__ img, int h, int w, int6
 			for (int px = px0; px < PW; px += pstep) {
 				unsigned int s1 = 0, s2 = 0;
 				for (int py = ybeg; py < ybeg + win; ++py) {
-					const unsigned int v = tile[py * PW + px];
+					const unsigned int v = tile[py * TP + px];
 					s1 += v;
 					s2 += v * v;
 				}
 				v1[ybeg * PV + px] = s1;
 				v2[ybeg * PV + px] = s2;
 				for (int y = ybeg + 1; y < yend; ++y) {
-					const unsigned int a = tile[(y - 1) * PW + px], b = tile[(y + win - 1) * PW + px];
+					const unsigned int a = tile[(y - 1) * TP + px], b = tile[(y + win - 1) * TP + px];
 					s1 += b - a;
 					s2 += b * b - a * a;
 					v1[y * PV + px] = s1;
@@ -378,19 +397,22 @@ __device__ void sauvola_tile(const uint8_t *__restrict__ img, int h, int w, int6
 		}
 		const double n = (double)(win * win);
 		const unsigned int nwin = (unsigned int)(win * win);
+		const bool small_win = nwin <= 256u;
 		const float c1 = (float)((1.0 - kk) / n), c2 = (float)(kk / (n * n * rr));
 		for (int j = 0; j < SEG; ++j) {
 			if (j > 0) {
 				s1 += r1[xb + j + win - 1] - r1[xb + j - 1];
 				s2 += r2[xb + j + win - 1] - r2[xb + j - 1];
 			}
-			const int pv = tile[(row + rad) * PW + xb + j + rad];
+			const int pv = tile[(row + rad) * TP + xb + j + rad];
 			// Screening in fp32: t = (A/n)(1 - k + k sqrt(nB - A^2)/(n r)) with the variance
 			// numerator D = nB - A^2 formed exactly in 64-bit integers (no cancellation).  Its
 			// error is < 2e-4 gray levels, so a pixel further than 1e-3 from the estimate is
 			// decided by it; the few others take the float64 sequence of the reference.
-			const unsigned long long D = (unsigned long long)nwin * s2 - (unsigned long long)s1 * s1;
-			const float ta = __fmul_rn((float)s1, __fadd_rn(c1, __fmul_rn(c2, sqrtf((float)D))));
+			// (up to 15 x 15 windows n * S2 <= n^2 * 255^2 < 2^32: 32-bit arithmetic gives the same D)
+			const float fD = small_win ? (float)(nwin * s2 - s1 * s1)
+				: (float)((unsigned long long)nwin * s2 - (unsigned long long)s1 * s1);
+			const float ta = __fmul_rn((float)s1, __fadd_rn(c1, __fmul_rn(c2, sqrtf(fD))));
 			const float diff = __fsub_rn((float)pv, ta);
 			bool white;
 			if (fabsf(diff) > 1.0e-3f) {
@@ -438,7 +460,8 @@ template <int TW>
 __host__ __device__ inline size_t sauvola_smem_bytes(int win) {
 	const int rad = win / 2;
 	const int PW = TW + 2 * rad, PH = ST_H + 2 * rad;
-	return (size_t)((PH * PW + 15) & ~15) + (size_t)2 * ST_H * (PW | 1) * sizeof(unsigned int) + (size_t)ST_H * (TW + 16);
+	const int TPITCH = TW + 2 * ((rad + 15) & ~15);
+	return (size_t)((PH * TPITCH + 15) & ~15) + (size_t)2 * ST_H * (PW | 1) * sizeof(unsigned int) + (size_t)ST_H * (TW + 16);
 }
 
 __global__ void __launch_bounds__(BTHREADS) og_sauvola_page_kernel(

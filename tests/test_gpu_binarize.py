@@ -10,7 +10,8 @@ from origami_b200 import ops, synth
 pytestmark = pytest.mark.gpu
 
 
-@pytest.mark.parametrize("shape,window", [((300, 420), 15), ((97, 131), 3), ((64, 64), 31), ((40, 500), 15), ((5, 9), 7)])
+@pytest.mark.parametrize("shape,window", [((300, 420), 15), ((97, 131), 3), ((64, 64), 31), ((40, 500), 15), ((5, 9), 7),
+	((200, 700), 31), ((150, 600), 41)])
 @pytest.mark.parametrize("kind", ["noise", "text"])
 def test_sauvola_page_bit_exact(cuda, shape, window, kind):
 	img = synth.make_page(shape[1], shape[0], seed=window, kind=kind)
