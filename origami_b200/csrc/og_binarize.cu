@@ -399,12 +399,18 @@ __device__ void sauvola_tile(const uint8_t *__restrict__ img, int h, int w, int6
 		const unsigned int nwin = (unsigned int)(win * win);
 		const bool small_win = nwin <= 256u;
 		const float c1 = (float)((1.0 - kk) / n), c2 = (float)(kk / (n * n * rr));
+		// constant trip count and pointers hoisted: every access below is base + immediate
+		const unsigned int *in1 = r1 + xb + win - 1, *in2 = r2 + xb + win - 1;  // column entering the window
+		const unsigned int *out1 = r1 + xb - 1, *out2 = r2 + xb - 1;            // column leaving it
+		const uint8_t *centre = tile + (row + rad) * TP + xb + rad;
+		uint8_t *res = otile + row * (TW + 16) + xb;
+#pragma unroll
 		for (int j = 0; j < SEG; ++j) {
 			if (j > 0) {
-				s1 += r1[xb + j + win - 1] - r1[xb + j - 1];
-				s2 += r2[xb + j + win - 1] - r2[xb + j - 1];
+				s1 += in1[j] - out1[j];
+				s2 += in2[j] - out2[j];
 			}
-			const int pv = tile[(row + rad) * TP + xb + j + rad];
+			const int pv = centre[j];
 			// Screening in fp32: t = (A/n)(1 - k + k sqrt(nB - A^2)/(n r)) with the variance
 			// numerator D = nB - A^2 formed exactly in 64-bit integers (no cancellation).  Its
 			// error is < 2e-4 gray levels, so a pixel further than 1e-3 from the estimate is
@@ -426,7 +432,7 @@ __device__ void sauvola_tile(const uint8_t *__restrict__ img, int h, int w, int6
 				const double t = __dmul_rn(m, __dadd_rn(1.0, __dmul_rn(kk, __dsub_rn(__ddiv_rn(sd, rr), 1.0))));
 				white = (double)pv > t;
 			}
-			otile[row * (TW + 16) + xb + j] = white ? 255 : 0;
+			res[j] = white ? 255 : 0;
 		}
 	}
 	__syncthreads();
