@@ -12,7 +12,6 @@ extraction and optional strip binarization, with bit-identical results.
 
 import collections
 import collections.abc
-import concurrent.futures
 
 import numpy as np
 import torch
@@ -42,20 +41,7 @@ class StripList(collections.abc.Sequence):
 		return self._flat[self._offs[i]:self._offs[i + 1]].reshape(self._steps[i, 1], self._steps[i, 0])
 
 
-_COPY_POOL = concurrent.futures.ThreadPoolExecutor(max_workers=4)
-
-
-def _parallel_copy(dst, src):
-	"""dst[...] = src for large contiguous uint8 arrays, split over a few threads (NumPy
-	releases the GIL while copying; one thread reaches only a fraction of the host bandwidth)."""
-	n = src.shape[0]
-	if n < (4 << 20):
-		dst[:n] = src
-		return
-	step = (n + 3) // 4
-	futs = [_COPY_POOL.submit(np.copyto, dst[i:min(n, i + step)], src[i:min(n, i + step)]) for i in range(0, n, step)]
-	for f in futs:
-		f.result()
+_parallel_copy = ops.parallel_copy
 
 
 class _Slot:

@@ -55,14 +55,34 @@ def pinned_staging(nbytes):
 	return buf[:nbytes]
 
 
+_COPY_POOL = None
+
+
+def parallel_copy(dst, src):
+	"""dst[:n] = src for large contiguous uint8 arrays, split over a few threads (NumPy releases the
+	GIL while copying; one thread reaches only a fraction of the host memory bandwidth)."""
+	global _COPY_POOL
+	n = src.shape[0]
+	if n < (4 << 20):
+		dst[:n] = src
+		return
+	if _COPY_POOL is None:
+		import concurrent.futures
+		_COPY_POOL = concurrent.futures.ThreadPoolExecutor(max_workers=4)
+	step = (n + 3) // 4
+	futs = [_COPY_POOL.submit(np.copyto, dst[i:min(n, i + step)], src[i:min(n, i + step)]) for i in range(0, n, step)]
+	for f in futs:
+		f.result()
+
+
 def to_device_image(a, device=None):
 	"""Host uint8 (h, w) ndarray -> pitched device image (through pinned staging memory)."""
 	a = np.ascontiguousarray(a, dtype=np.uint8)
 	h, w = a.shape
 	out = alloc_image(h, w, device)
-	stage = pinned_staging(h * w).view(h, w)
-	stage.numpy()[...] = a  # host copy into page-locked memory (PIL arrays are read-only views)
-	out.copy_(stage, non_blocking=True)
+	stage = pinned_staging(h * w)
+	parallel_copy(stage.numpy(), a.reshape(-1))  # host copy into page-locked memory (PIL arrays are read-only views)
+	out.copy_(stage.view(h, w), non_blocking=True)
 	torch.cuda.current_stream().synchronize()  # the staging buffer is reused by the next call
 	return out
 
