@@ -134,3 +134,27 @@ def test_bench_reference_arm_noop_on_other_ranks():
 	res = subprocess.run([sys.executable, os.path.join(ROOT, "bench.py"), "--impl", "reference", "--steps", "1", "--warmup", "0"],
 		capture_output=True, text=True, env=env, timeout=120)
 	assert res.returncode == 0 and res.stdout.strip() == ""
+
+
+def test_pipeline_strip_width_estimate_bounds_the_device_value():
+	"""PagePipeline sizes its strip buffer from a host-side estimate of the strip widths (float64
+	bilinear of the sparse grid): never below what og_line_steps derives (the oracle's value), and
+	only a few columns above it, also for lines that leave the page."""
+	from origami_b200 import ops
+	from origami_b200.batch.core import pipeline
+	grid = synth.make_grid(900, 1200, 25, seed=5)
+	dense = exact.expand_map(grid, 25)
+	lines = synth.make_lines(dense.shape[1], dense.shape[0], 120, seed=5, dpi=300)
+	lines += [dict(p=[-40.0, 300.0], right=[400.0, 5.0], up=[1.0, -30.0]),
+		dict(p=[dense.shape[1] - 100.0, 200.0], right=[300.0, -4.0], up=[0.0, -25.0])]
+	desc = ops.pack_line_arrays([l["p"] for l in lines], [l["right"] for l in lines], [l["up"] for l in lines], ysteps=48)
+	est = pipeline._estimate_xsteps(grid, 25, desc)
+	want = np.array([exact.line_steps(dense, l["p"], l["right"], l["up"], ysteps=48)[0] for l in lines])
+	assert (est >= want).all(), (est - want).min()
+	# tight away from the page border (there the dense map is flat -- cv2.resize replicates the edge --
+	# while the estimate extrapolates the sparse cell, which errs on the safe side)
+	px = np.array([[l["p"][0], l["p"][0] + l["right"][0]] for l in lines])
+	inner = (px.min(axis=1) >= 13) & (px.max(axis=1) <= dense.shape[1] - 14)
+	assert inner.sum() > 50 and (est[inner] - want[inner] <= 4).all(), (est[inner] - want[inner]).max()
+	desc["xsteps"][:10] = 77  # fixed widths are taken as they are
+	assert (pipeline._estimate_xsteps(grid, 25, desc)[:10] == 77).all()
