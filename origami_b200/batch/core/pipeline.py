@@ -97,11 +97,13 @@ def _estimate_xsteps(grid, cell, desc):
 		gh, gw = gx.shape
 		p, right, up = desc["p"][derive], desc["right"][derive], desc["up"][derive]
 		corners = np.stack([p, p + right, up + p, up + p + right], axis=1)  # (m, 4, 2) dewarped (x, y)
-		u = (corners[..., 0] + 0.5) / cell - 0.5
-		v = (corners[..., 1] + 0.5) / cell - 0.5
+		# cv2.resize replicates the border (the dense map is flat in its outer half cell) and SciPy
+		# extrapolates that flat rim, so sparse coordinates are simply clamped
+		u = np.clip(np.nan_to_num((corners[..., 0] + 0.5) / cell - 0.5), 0, gw - 1)
+		v = np.clip(np.nan_to_num((corners[..., 1] + 0.5) / cell - 0.5), 0, gh - 1)
 		with np.errstate(invalid="ignore"):
-			j0 = np.clip(np.floor(np.nan_to_num(u)), 0, gw - 2).astype(np.int64)
-			i0 = np.clip(np.floor(np.nan_to_num(v)), 0, gh - 2).astype(np.int64)
+			j0 = np.minimum(np.floor(u), gw - 2).astype(np.int64)
+			i0 = np.minimum(np.floor(v), gh - 2).astype(np.int64)
 			fu, fv = u - j0, v - i0
 			wx = (gx[i0, j0] * (1 - fu) + gx[i0, j0 + 1] * fu) * (1 - fv) + (gx[i0 + 1, j0] * (1 - fu) + gx[i0 + 1, j0 + 1] * fu) * fv
 			ext = np.maximum(np.abs(wx[:, 0] - wx[:, 1]), np.abs(wx[:, 2] - wx[:, 3])) * desc["xres"][derive]

@@ -139,7 +139,7 @@ def test_bench_reference_arm_noop_on_other_ranks():
 def test_pipeline_strip_width_estimate_bounds_the_device_value():
 	"""PagePipeline sizes its strip buffer from a host-side estimate of the strip widths (float64
 	bilinear of the sparse grid): never below what og_line_steps derives (the oracle's value), and
-	only a few columns above it, also for lines that leave the page."""
+	at most four columns above it, also for lines at the border and lines that leave the page."""
 	from origami_b200 import ops
 	from origami_b200.batch.core import pipeline
 	grid = synth.make_grid(900, 1200, 25, seed=5)
@@ -150,11 +150,6 @@ def test_pipeline_strip_width_estimate_bounds_the_device_value():
 	desc = ops.pack_line_arrays([l["p"] for l in lines], [l["right"] for l in lines], [l["up"] for l in lines], ysteps=48)
 	est = pipeline._estimate_xsteps(grid, 25, desc)
 	want = np.array([exact.line_steps(dense, l["p"], l["right"], l["up"], ysteps=48)[0] for l in lines])
-	assert (est >= want).all(), (est - want).min()
-	# tight away from the page border (there the dense map is flat -- cv2.resize replicates the edge --
-	# while the estimate extrapolates the sparse cell, which errs on the safe side)
-	px = np.array([[l["p"][0], l["p"][0] + l["right"][0]] for l in lines])
-	inner = (px.min(axis=1) >= 13) & (px.max(axis=1) <= dense.shape[1] - 14)
-	assert inner.sum() > 50 and (est[inner] - want[inner] <= 4).all(), (est[inner] - want[inner]).max()
+	assert (est >= want).all() and (est - want <= 4).all(), ((est - want).min(), (est - want).max())
 	desc["xsteps"][:10] = 77  # fixed widths are taken as they are
 	assert (pipeline._estimate_xsteps(grid, 25, desc)[:10] == 77).all()
