@@ -20,6 +20,13 @@
 // round trip.  The bound of this kernel is the FP64 pipe + instruction issue, not HBM: the
 // float64 blend that bit-parity with SciPy requires costs ~30 DP-pipe instructions per
 // sample.
+//
+// That is the engine for callers without a dense map (og_lines_kernel).  With the map
+// (the page kernel emits it) the nodes are gathered from it: og_lines_map_kernel evaluates
+// every sample in float64 (warped grids, strips with bounding boxes); strips and label
+// counts go through og_strips_screened_kernel, which decides cv2.remap's fixed-point
+// coordinate from a float32 interval and keeps the float64 sequence for the few samples the
+// interval cannot decide -- same bits, two thirds of the time.
 #include "og_common.cuh"
 
 namespace {
