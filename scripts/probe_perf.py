@@ -21,8 +21,8 @@ def timeit(fn, iters=20, warm=3):
 	return ts[len(ts) // 2], ts[0]
 
 def main():
-	W, H, cell = (4800, 7200, 25)
-	n_lines = 2000
+	W, H, cell = (int(os.environ.get('PW', 4800)), int(os.environ.get('PH', 7200)), 25)
+	n_lines = int(os.environ.get('PLINES', 2000))
 	dev = torch.device("cuda:0")
 	page = synth.make_page(W, H, seed=0, kind="text")
 	grid = synth.make_grid(W, H, cell, seed=0)
