@@ -43,6 +43,9 @@ extern "C" {
 #define OG_BIN_NONE 0
 #define OG_BIN_OTSU 1
 #define OG_BIN_SAUVOLA 2
+/* OR-ed into og_extract_lines' `binarize`: gather every sample's four nodes from the caller's dense
+ * `map` with the map-gather engines of round 1 (same bits; slower; binarization as a second kernel). */
+#define OG_FLAG_MAP_GATHER 0x100
 
 /* One text line in DEWARPED page space.  Mirrors the fields of the reference's Line
  * (origami/core/block.py:35-55; lines.zip: docs/formats.md:223-246) plus the result of
@@ -107,10 +110,10 @@ int og_line_steps(const float *grid, int gh, int gw, int cell,
 	int32_t *steps_out, int64_t *pix_offsets_out, int32_t *chunk_offsets_out, void *stream);
 
 /* The three line entry points below take `map`: the dense map (gh*cell, gw*cell, 2) fp32 that
- * og_expand_map / og_remap_page wrote for the SAME grid, or NULL.  With a map the four nodes
- * of every sample are gathered from it (fast path: the reference, too, interpolates in its
- * cached Grid.points("full")); with NULL they are recomputed from the sparse grid on chip.
- * Both paths produce identical bits. */
+ * og_expand_map / og_remap_page wrote for the SAME grid, or NULL.  With a map the engines that
+ * evaluate every sample's float64 blend (warped grids, bounding boxes, label counts) gather the
+ * four nodes from it (the reference, too, interpolates in its cached Grid.points("full")); with
+ * NULL they are recomputed from the sparse grid on chip.  Both paths produce identical bits. */
 
 /* A8  Line.warped_grid -- origami/core/block.py:223-248.  Writes the fp32 (ysteps, xsteps, 2)
  * warped sampling grid of every line, packed at 2*pix_offsets[i] floats.  capacity is in
@@ -120,19 +123,31 @@ int og_warped_grids(const float *grid, int gh, int gw, int cell, const float *ma
 	const int32_t *steps, const int64_t *pix_offsets, const int32_t *chunk_offsets,
 	float *grids_out, int64_t capacity, void *stream);
 
-/* A9+A10+A21  Line.dewarped_image / Line.image -- origami/core/block.py:129-143, 250-259,
- * batched over all lines of a page in one launch (replaces LineExtractor's ThreadPool,
- * origami/batch/core/lines.py:148-149).  src is the WARPED page.  Strip i is written as
- * (ysteps, xsteps) u8, row 0 = top of the text (the reference's pixels[::-1]), at byte
- * offset pix_offsets[i] of strips_out.  bbox_out, if not NULL, receives per line
- * (floor min x, floor min y, ceil max x, ceil max y) of its fp32 warped grid as int32
- * (origami/core/mask.py:10-12 convention).  capacity in bytes of strips_out; strips that do not fit
- * are skipped whole (compare pix_offsets[n] with the capacity). */
+/* A9+A10+A12+A21  Line.image = Line.dewarped_image + binarizer(im) -- origami/core/block.py:129-143,
+ * 250-259, origami/core/binarize.py:11-43, batched over all lines of a page in one launch (replaces
+ * LineExtractor's ThreadPool, origami/batch/core/lines.py:148-149).  src is the WARPED page.  Strip i
+ * is written as (ysteps, xsteps) u8, row 0 = top of the text (the reference's pixels[::-1]), at byte
+ * offset pix_offsets[i] of strips_out.  capacity = bytes of strips_out (and of gray_out); strips that
+ * do not fit are skipped whole (compare pix_offsets[n] with the capacity).
+ *   binarize   OG_BIN_NONE: strips_out receives the gray strips.
+ *              OG_BIN_OTSU: strips_out receives (gray > t) * 255 with t the strip's own Otsu threshold
+ *              (thresholds_out, n int32, may be NULL); the threshold is computed by the CTA that samples
+ *              the line, from a shared-memory histogram, and applied to its bytes while they are still
+ *              in L2.  gray_out, if not NULL, additionally keeps the gray strips.
+ *              OG_BIN_SAUVOLA: as og_binarize_strips (window odd, 3..127; k = 0.2, r = 127.5); the
+ *              window needs the whole gray strip, so gray_out is required and must not alias strips_out.
+ *   bbox_out   if not NULL, receives per line (floor min x, floor min y, ceil max x, ceil max y) of its
+ *              fp32 warped grid as int32 (origami/core/mask.py:10-12 convention).
+ * The dense-map nodes under a line are recomputed on chip from the sparse grid; `map` is only read
+ * when bounding boxes are asked for or OG_FLAG_MAP_GATHER is set (identical bits either way).  Like
+ * og_sample_labels the call uses the plan's work-ticket word while it runs (one call per plan at a
+ * time). */
 int og_extract_lines(const uint8_t *src, int H, int W, int64_t src_pitch,
 	const float *grid, int gh, int gw, int cell, const float *map,
 	const og_line *lines, int n,
 	const int32_t *steps, const int64_t *pix_offsets, int32_t *chunk_offsets,
-	uint8_t *strips_out, int64_t capacity, int32_t *bbox_out, void *stream);
+	uint8_t *strips_out, int64_t capacity, int32_t *bbox_out,
+	int binarize, int window, uint8_t *gray_out, int32_t *thresholds_out, void *stream);
 
 /* A12  binarizers on packed strips -- origami/core/binarize.py:11-43 as applied per line by
  * Line.image (block.py:140-141).  gray and out hold n strips packed at pix_offsets; they

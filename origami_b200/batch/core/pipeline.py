@@ -211,15 +211,11 @@ class PagePipeline:
 			if n:
 				_lib.call("og_line_steps", base_in + o_grid, gh, gw, cell, base_in + o_desc, n,
 					base_out + o_steps, base_out + o_offs, slot.d_chunks.data_ptr(), s)
-				target = slot.d_gray.data_ptr() if self.binarize is not None else base_out + o_strips
+				mode, window = ops._binarize_args(self.binarize)
+				scratch = slot.d_gray.data_ptr() if mode == ops.OG_BIN_SAUVOLA else 0
 				_lib.call("og_extract_lines", base_in, H, W, pitch, base_in + o_grid, gh, gw, cell, p_map,
 					base_in + o_desc, n, base_out + o_steps, base_out + o_offs, slot.d_chunks.data_ptr(),
-					target, cap, 0, s)
-				if self.binarize is not None:
-					mode = ops.OG_BIN_OTSU if self.binarize[0] == "otsu" else ops.OG_BIN_SAUVOLA
-					window = self.binarize[1] if len(self.binarize) > 1 else 15
-					_lib.call("og_binarize_strips", target, base_out + o_steps, base_out + o_offs, slot.d_chunks.data_ptr(),
-						n, mode, window, base_out + o_strips, cap, 0, s)
+					base_out + o_strips, cap, 0, mode, window, scratch, 0, s)
 			slot.h_out[:n_out].copy_(slot.d_out[:n_out], non_blocking=True)
 			slot.done = torch.cuda.Event()
 			slot.done.record(st)

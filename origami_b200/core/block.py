@@ -273,11 +273,7 @@ def extract_strips(dewarper, records, binarize=None, want_bbox=False):
 	total = max(int(offs[-1]), 1)
 	gray = torch.empty((total,), dtype=torch.uint8, device=dev)
 	bbox = torch.empty((max(len(records), 1), 4), dtype=torch.int32, device=dev) if want_bbox else None
-	ops.extract_lines(dewarper.device_image, grid.device_grid, grid.resolution, plan, gray, bbox)
-	if binarize is not None:
-		mode = ops.OG_BIN_OTSU if binarize[0] == "otsu" else ops.OG_BIN_SAUVOLA
-		window = binarize[1] if len(binarize) > 1 else 15
-		gray = ops.binarize_strips(gray, plan, mode, window)
+	ops.extract_lines(dewarper.device_image, grid.device_grid, grid.resolution, plan, gray, bbox, binarize=binarize)
 	bb = ops.to_host(bbox)[:len(records)] if want_bbox else None
 	flat = ops.to_host(gray)
 	strips = [flat[offs[i]:offs[i + 1]].reshape(steps[i][1], steps[i][0]) for i in range(len(records))]

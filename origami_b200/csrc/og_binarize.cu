@@ -9,6 +9,7 @@
 #include <mutex>
 
 #include "og_common.cuh"
+#include "og_internal.cuh"
 
 namespace {
 
@@ -33,77 +34,6 @@ __device__ __forceinline__ int reflect_index_fast(int i, int n) {
 	const int j = i < 0 ? -i : 2 * (n - 1) - i;
 	if ((unsigned)j < (unsigned)n) return j;
 	return reflect_index(i, n);
-}
-
-// ---------------------------------------------------------------------------------------
-// Otsu threshold from an exact 256-bin histogram (skimage 0.16.2 threshold_otsu on uint8:
-// bins = the integers [min, max], float64 cumulative sums, first argmax of
-// w1 * w2 * (m1 - m2)^2; a single-valued image is the ValueError -> 128 case of
-// origami/core/binarize.py:20-23).  One warp; each lane owns 8 consecutive bins.
-// ---------------------------------------------------------------------------------------
-__device__ int otsu_from_hist_warp(const unsigned int *hist) {
-	const int lane = threadIdx.x & 31;
-	unsigned long long cnt = 0, sum = 0;
-	int lo = 256, hi = -1;
-	for (int k = 0; k < 8; ++k) {
-		const int b = lane * 8 + k;
-		const unsigned int h = hist[b];
-		cnt += h;
-		sum += (unsigned long long)h * b;
-		if (h) {
-			lo = min(lo, b);
-			hi = max(hi, b);
-		}
-	}
-	unsigned long long icnt = cnt, isum = sum;
-#pragma unroll
-	for (int o = 1; o < 32; o <<= 1) {
-		unsigned long long tc = __shfl_up_sync(0xffffffffu, icnt, o);
-		unsigned long long ts = __shfl_up_sync(0xffffffffu, isum, o);
-		if (lane >= o) {
-			icnt += tc;
-			isum += ts;
-		}
-	}
-	const unsigned long long total_cnt = __shfl_sync(0xffffffffu, icnt, 31);
-	const unsigned long long total_sum = __shfl_sync(0xffffffffu, isum, 31);
-#pragma unroll
-	for (int o = 16; o > 0; o >>= 1) {
-		lo = min(lo, __shfl_xor_sync(0xffffffffu, lo, o));
-		hi = max(hi, __shfl_xor_sync(0xffffffffu, hi, o));
-	}
-	if (hi <= lo) return 128;  // empty or single colour
-	// candidate thresholds i in [lo, hi - 1]: class 1 = bins <= i, class 2 = bins > i
-	unsigned long long c1 = icnt - cnt, s1 = isum - sum;  // exclusive prefix
-	double best = -1.0;
-	int best_i = 0x7fffffff;
-	for (int k = 0; k < 8; ++k) {
-		const int b = lane * 8 + k;
-		const unsigned int h = hist[b];
-		c1 += h;
-		s1 += (unsigned long long)h * b;
-		if (b >= lo && b < hi) {
-			const unsigned long long c2 = total_cnt - c1, s2 = total_sum - s1;
-			const double w1 = (double)c1, w2 = (double)c2;
-			const double m1 = __ddiv_rn((double)s1, w1), m2 = __ddiv_rn((double)s2, w2);
-			const double d = __dsub_rn(m1, m2);
-			const double v = __dmul_rn(__dmul_rn(w1, w2), __dmul_rn(d, d));
-			if (v > best) {
-				best = v;
-				best_i = b;
-			}
-		}
-	}
-#pragma unroll
-	for (int o = 16; o > 0; o >>= 1) {
-		const double ob = __shfl_xor_sync(0xffffffffu, best, o);
-		const int oi = __shfl_xor_sync(0xffffffffu, best_i, o);
-		if (ob > best || (ob == best && oi < best_i)) {
-			best = ob;
-			best_i = oi;
-		}
-	}
-	return best_i;
 }
 
 // ---------------------------------------------------------------------------------------
@@ -180,7 +110,7 @@ __global__ void __launch_bounds__(OTHREADS) og_otsu_strips_kernel(
 		}
 		__syncthreads();
 		if (threadIdx.x < 32) {
-			const int t = otsu_from_hist_warp(hist);
+			const int t = og_otsu_from_hist_warp(hist);
 			if (threadIdx.x == 0) {
 				s_t = t;
 				if (thresholds != nullptr) thresholds[li] = t;
@@ -265,7 +195,7 @@ __global__ void __launch_bounds__(BTHREADS) og_otsu_apply_kernel(
 	for (int k = threadIdx.x; k < 256; k += BTHREADS) hist[k] = hist_in[k];
 	__syncthreads();
 	if (threadIdx.x < 32) {
-		const int t = otsu_from_hist_warp(hist);
+		const int t = og_otsu_from_hist_warp(hist);
 		if (threadIdx.x == 0) {
 			s_t = t;
 			if (blockIdx.x == 0 && threshold_out != nullptr) *threshold_out = t;
@@ -516,17 +446,16 @@ int check_window(int window) {
 
 }  // namespace
 
-extern "C" int og_binarize_strips(const uint8_t *gray, const int32_t *steps, const int64_t *pix_offsets,
+int og_binarize_strips_impl(const uint8_t *gray, const int32_t *steps, const int64_t *pix_offsets,
 	const int32_t *chunk_offsets, int n, int mode, int window, uint8_t *out, int64_t capacity,
-	int32_t *thresholds_out, void *stream) {
+	int32_t *thresholds_out, cudaStream_t st) {
 	OG_REQUIRE(n >= 0, OG_E_ARG, "n < 0");
 	OG_REQUIRE(mode == OG_BIN_OTSU || mode == OG_BIN_SAUVOLA, OG_E_ARG, "mode %d unsupported", mode);
 	if (n == 0) return OG_OK;
 	OG_REQUIRE(gray != nullptr && out != nullptr && steps != nullptr && pix_offsets != nullptr && chunk_offsets != nullptr,
 		OG_E_ARG, "NULL pointer");
-	cudaStream_t st = (cudaStream_t)stream;
 	if (mode == OG_BIN_OTSU) {
-		og_otsu_strips_kernel<<<min(n, OG_NUM_SMS * OG_OTSU_STRIP_CTAS), OTHREADS, 0, st>>>(gray, steps, pix_offsets, n, out, capacity, thresholds_out);
+		og_otsu_strips_kernel<<<min(n, og_num_sms() * OG_OTSU_STRIP_CTAS), OTHREADS, 0, st>>>(gray, steps, pix_offsets, n, out, capacity, thresholds_out);
 		return og_check_launch("og_otsu_strips_kernel");
 	}
 	int rc = check_window(window);
@@ -535,9 +464,16 @@ extern "C" int og_binarize_strips(const uint8_t *gray, const int32_t *steps, con
 	const size_t smem = sauvola_smem_bytes<ST_WS>(window);
 	cudaError_t e = cudaFuncSetAttribute(og_sauvola_strips_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
 	if (e != cudaSuccess) return og_set_error((int)e, "cudaFuncSetAttribute: %s", cudaGetErrorString(e));
-	og_sauvola_strips_kernel<<<OG_NUM_SMS * 4, BTHREADS, smem, st>>>(gray, steps, pix_offsets, chunk_offsets, n, out,
+	og_sauvola_strips_kernel<<<og_num_sms() * 4, BTHREADS, smem, st>>>(gray, steps, pix_offsets, chunk_offsets, n, out,
 		capacity, window, 0.2, 127.5);
 	return og_check_launch("og_sauvola_strips_kernel");
+}
+
+extern "C" int og_binarize_strips(const uint8_t *gray, const int32_t *steps, const int64_t *pix_offsets,
+	const int32_t *chunk_offsets, int n, int mode, int window, uint8_t *out, int64_t capacity,
+	int32_t *thresholds_out, void *stream) {
+	return og_binarize_strips_impl(gray, steps, pix_offsets, chunk_offsets, n, mode, window, out, capacity,
+		thresholds_out, (cudaStream_t)stream);
 }
 
 extern "C" int og_sauvola(const uint8_t *src, int h, int w, int64_t src_pitch, int window,
@@ -551,7 +487,7 @@ extern "C" int og_sauvola(const uint8_t *src, int h, int w, int64_t src_pitch, i
 	cudaError_t e = cudaFuncSetAttribute(og_sauvola_page_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
 	if (e != cudaSuccess) return og_set_error((int)e, "cudaFuncSetAttribute: %s", cudaGetErrorString(e));
 	const int64_t tiles = (int64_t)((w + ST_W - 1) / ST_W) * ((h + ST_H - 1) / ST_H);
-	const int blocks = (int)(tiles < (int64_t)OG_NUM_SMS * 8 ? tiles : (int64_t)OG_NUM_SMS * 8);
+	const int blocks = (int)(tiles < (int64_t)og_num_sms() * 8 ? tiles : (int64_t)og_num_sms() * 8);
 	og_sauvola_page_kernel<<<blocks, BTHREADS, smem, (cudaStream_t)stream>>>(src, h, w, src_pitch, dst, dst_pitch, window, k, r);
 	return og_check_launch("og_sauvola_page_kernel");
 }
@@ -564,7 +500,7 @@ extern "C" int og_otsu(const uint8_t *src, int h, int w, int64_t src_pitch,
 	cudaStream_t st = (cudaStream_t)stream;
 	cudaError_t e = cudaMemsetAsync(hist_scratch, 0, 256 * sizeof(uint32_t), st);
 	if (e != cudaSuccess) return og_set_error((int)e, "cudaMemsetAsync: %s", cudaGetErrorString(e));
-	const int blocks = OG_NUM_SMS * 8;
+	const int blocks = og_num_sms() * 8;
 	og_hist_kernel<<<blocks, BTHREADS, 0, st>>>(src, h, w, src_pitch, hist_scratch);
 	int rc = og_check_launch("og_hist_kernel");
 	if (rc) return rc;
@@ -641,7 +577,7 @@ extern "C" int og_otsu_noalloc(const uint8_t *src, int h, int w, int64_t src_pit
 	cudaStream_t st = (cudaStream_t)stream;
 	cudaError_t e = cudaMemsetAsync(hist, 0, 256 * sizeof(uint32_t), st);  // the array keeps the last call's counts
 	if (e != cudaSuccess) return og_set_error((int)e, "cudaMemsetAsync: %s", cudaGetErrorString(e));
-	const int blocks = OG_NUM_SMS * 8;
+	const int blocks = og_num_sms() * 8;
 	og_hist_kernel<<<blocks, BTHREADS, 0, st>>>(src, h, w, src_pitch, hist);
 	rc = og_check_launch("og_hist_kernel");
 	if (rc) return rc;

@@ -10,8 +10,6 @@
 
 #include "../../include/origami_b200.h"
 
-#define OG_NUM_SMS 148
-
 int og_set_error(int code, const char *fmt, ...);
 int og_check_launch(const char *what);
 

@@ -28,6 +28,7 @@
 // coordinate from a float32 interval and keeps the float64 sequence for the few samples the
 // interval cannot decide -- same bits, two thirds of the time.
 #include "og_common.cuh"
+#include "og_internal.cuh"
 
 namespace {
 
@@ -1256,7 +1257,7 @@ int launch_lines(const LineParams &p, cudaStream_t st) {
 	cudaError_t e = cudaFuncSetAttribute(og_lines_kernel<MODE, BBOX>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_BUDGET);
 	if (e != cudaSuccess) return og_set_error((int)e, "cudaFuncSetAttribute: %s", cudaGetErrorString(e));
 	// persistent grid: two CTAs per SM fit the staging budget
-	og_lines_kernel<MODE, BBOX><<<OG_NUM_SMS * 2, LTHREADS, SMEM_BUDGET, st>>>(p);
+	og_lines_kernel<MODE, BBOX><<<og_num_sms() * 2, LTHREADS, SMEM_BUDGET, st>>>(p);
 	return og_check_launch("og_lines_kernel");
 }
 
@@ -1277,10 +1278,10 @@ int launch_lines_any(const LineParams &p, const float *map, cudaStream_t st) {
 		// make this one skip work
 		cudaError_t e = cudaMemsetAsync(q.ticket, 0, sizeof(int), st);
 		if (e != cudaSuccess) return og_set_error((int)e, "cudaMemsetAsync: %s", cudaGetErrorString(e));
-		og_strips_screened_kernel<(MODE == MODE_LABELS ? MODE_LABELS : MODE_STRIP)><<<OG_NUM_SMS * OG_SCR_BLOCKS, STHREADS, 0, st>>>(q, reinterpret_cast<const float2 *>(map));
+		og_strips_screened_kernel<(MODE == MODE_LABELS ? MODE_LABELS : MODE_STRIP)><<<og_num_sms() * OG_SCR_BLOCKS, STHREADS, 0, st>>>(q, reinterpret_cast<const float2 *>(map));
 		return og_check_launch("og_strips_screened_kernel");
 	}
-	og_lines_map_kernel<MODE, BBOX><<<OG_NUM_SMS * OG_MAP_MINBLOCKS, MTHREADS, 0, st>>>(p, reinterpret_cast<const float2 *>(map));
+	og_lines_map_kernel<MODE, BBOX><<<og_num_sms() * OG_MAP_MINBLOCKS, MTHREADS, 0, st>>>(p, reinterpret_cast<const float2 *>(map));
 	return og_check_launch("og_lines_map_kernel");
 }
 
@@ -1348,11 +1349,11 @@ extern "C" int og_warped_grids(const float *grid, int gh, int gw, int cell, cons
 	return launch_lines_any<MODE_GRID, false>(p, map, (cudaStream_t)stream);
 }
 
-extern "C" int og_extract_lines(const uint8_t *src, int H, int W, int64_t src_pitch,
+int og_extract_lines_engines(const uint8_t *src, int H, int W, int64_t src_pitch,
 	const float *grid, int gh, int gw, int cell, const float *map,
 	const og_line *lines, int n,
 	const int32_t *steps, const int64_t *pix_offsets, int32_t *chunk_offsets,
-	uint8_t *strips_out, int64_t capacity, int32_t *bbox_out, void *stream) {
+	uint8_t *strips_out, int64_t capacity, int32_t *bbox_out, cudaStream_t st) {
 	int rc = check_grid(grid, gh, gw, cell);
 	if (rc) return rc;
 	rc = check_lines(lines, n, steps, chunk_offsets);
@@ -1364,7 +1365,6 @@ extern "C" int og_extract_lines(const uint8_t *src, int H, int W, int64_t src_pi
 	OG_REQUIRE(H < 32767 && W < 32767, OG_E_RANGE, "source %d x %d exceeds OpenCV's 32767 limit", W, H);
 	OG_REQUIRE((int64_t)H * src_pitch < ((int64_t)1 << 31), OG_E_RANGE, "source image larger than 2 GiB");
 	OG_REQUIRE(pix_offsets != nullptr && strips_out != nullptr, OG_E_ARG, "pix_offsets / strips_out is NULL");
-	cudaStream_t st = (cudaStream_t)stream;
 	LineParams p{};
 	p.grid = reinterpret_cast<const float2 *>(grid);
 	p.gh = gh; p.gw = gw; p.cell = cell;

@@ -11,6 +11,7 @@ from . import _lib
 from ._lib import LINE_DTYPE, OG_BIN_NONE, OG_BIN_OTSU, OG_BIN_SAUVOLA, OG_INTER_LINEAR, OG_INTER_NEAREST
 
 OG_FLAG_STAGE_SMEM = 0x100
+OG_FLAG_MAP_GATHER = 0x100  # og_extract_lines: sample through the dense map with the map-gather engines
 
 PITCH_ALIGN = 128
 
@@ -230,14 +231,37 @@ def warped_grids(grid, cell, plan, out, dense_map=None):
 	return out
 
 
-def extract_lines(src, grid, cell, plan, out, bbox=None, dense_map=None):
-	"""Line.dewarped_image for every line into the packed uint8 buffer `out`."""
+def _binarize_args(binarize):
+	"""None | ("otsu",) | ("sauvola", window) | OG_BIN_* -> (mode, window)."""
+	if binarize is None or binarize == OG_BIN_NONE:
+		return OG_BIN_NONE, 0
+	if isinstance(binarize, int):
+		return int(binarize), 15
+	if binarize[0] == "otsu":
+		return OG_BIN_OTSU, 0
+	if binarize[0] == "sauvola":
+		return OG_BIN_SAUVOLA, int(binarize[1]) if len(binarize) > 1 else 15
+	raise ValueError("unknown binarizer %r" % (binarize,))
+
+
+def extract_lines(src, grid, cell, plan, out, bbox=None, dense_map=None, binarize=None, gray_out=None, thresholds=None,
+		map_gather=False):
+	"""Line.image(dewarped=True, binarizer=...) for every line into the packed uint8 buffer `out`
+	(reference origami/core/block.py:129-143): gray strips, or strips binarized by the kernel that
+	samples them.  binarize: None | ("otsu",) | ("sauvola", window); Sauvola needs its gray input
+	whole, so a gray scratch buffer is allocated when gray_out is not given."""
 	gh, gw = _check_grid(grid)
 	_check_u8_image(src, "src")
+	mode, window = _binarize_args(binarize)
+	if (mode == OG_BIN_SAUVOLA or (mode != OG_BIN_NONE and (map_gather or bbox is not None))) and gray_out is None:
+		gray_out = torch.empty_like(out)
+	if map_gather:
+		mode |= OG_FLAG_MAP_GATHER
+	cap = out.numel() if gray_out is None else min(out.numel(), gray_out.numel())
 	_lib.call("og_extract_lines", src.data_ptr(), int(src.shape[0]), int(src.shape[1]), src.stride(0),
 		grid.data_ptr(), gh, gw, cell, _check_map(dense_map, gh, gw, cell), plan.lines.data_ptr(), plan.n,
 		plan.steps.data_ptr(), plan.pix_offsets.data_ptr(), plan.chunk_offsets.data_ptr(),
-		out.data_ptr(), out.numel(), _ptr(bbox), _stream())
+		out.data_ptr(), cap, _ptr(bbox), mode, window, _ptr(gray_out), _ptr(thresholds), _stream())
 	return out
 
 

@@ -207,8 +207,8 @@ def test_full_size_page_against_opencv(cuda):
 	a = torch.empty((int(offs[-1]),), dtype=torch.uint8, device=cuda)
 	b = torch.empty_like(a)
 	ops.extract_lines(src, gt, s, plan, a)
-	ops.extract_lines(src, gt, s, plan, b, dense_map=dmap)
-	assert torch.equal(a, b)  # staged and map-gather engines agree on all 2000 lines
+	ops.extract_lines(src, gt, s, plan, b, dense_map=dmap, map_gather=True)
+	assert torch.equal(a, b)  # line-owning and map-gather engines agree on all 2000 lines
 	a = a.cpu().numpy()
 	for i in range(0, 2000, 10):
 		l = lines[i]

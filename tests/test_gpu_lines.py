@@ -241,7 +241,7 @@ def test_screened_strips_on_adversarial_maps(cuda, ysteps):
 	offs = plan.pix_offsets.cpu().numpy()
 	for name, m in _adversarial_maps(dense).items():
 		out = torch.zeros((int(offs[-1]),), dtype=torch.uint8, device=cuda)
-		ops.extract_lines(src, g, 25, plan, out, dense_map=torch.from_numpy(m).to(cuda))
+		ops.extract_lines(src, g, 25, plan, out, dense_map=torch.from_numpy(m).to(cuda), map_gather=True)
 		out = out.cpu().numpy()
 		for i, r in enumerate(recs):
 			wg = exact.warped_grid(m, r["p"], r["right"], r["up"], xsteps=150, ysteps=ysteps)
@@ -267,14 +267,19 @@ def test_screened_strips_equal_the_float64_path(cuda):
 	for name, m in maps.items():
 		a = torch.zeros((total,), dtype=torch.uint8, device=cuda)
 		b = torch.zeros((total,), dtype=torch.uint8, device=cuda)
-		ops.extract_lines(src, g, 25, plan, a, dense_map=m)
+		ops.extract_lines(src, g, 25, plan, a, dense_map=m, map_gather=True)
 		ops.extract_lines(src, g, 25, plan, b, bbox, dense_map=m)
 		assert torch.equal(a, b), name
 		# the work ticket behind the prefix sums is back at zero, so the plan can be used again
 		assert int(plan.chunk_offsets[len(recs) + 1].item()) == 0
 		a2 = torch.zeros_like(a)
-		ops.extract_lines(src, g, 25, plan, a2, dense_map=m)
+		ops.extract_lines(src, g, 25, plan, a2, dense_map=m, map_gather=True)
 		assert torch.equal(a, a2), name
+		if name == "grid":  # the line-owning engine recomputes the nodes from the sparse grid: same bytes
+			c = torch.zeros_like(a)
+			ops.extract_lines(src, g, 25, plan, c)
+			assert torch.equal(a, c)
+			assert int(plan.chunk_offsets[len(recs) + 1].item()) == 0
 
 
 def test_screened_strips_with_absurd_line_coordinates(cuda):
@@ -292,9 +297,12 @@ def test_screened_strips_with_absurd_line_coordinates(cuda):
 	m = ops.expand_map(g, 25)
 	a = torch.zeros((total,), dtype=torch.uint8, device=cuda)
 	b = torch.zeros((total,), dtype=torch.uint8, device=cuda)
-	ops.extract_lines(src, g, 25, plan, a, dense_map=m)
+	ops.extract_lines(src, g, 25, plan, a, dense_map=m, map_gather=True)
 	ops.extract_lines(src, g, 25, plan, b, bbox, dense_map=m)
 	assert total == 3 * 8 * 64 and torch.equal(a, b)
+	c = torch.zeros_like(a)
+	ops.extract_lines(src, g, 25, plan, c)  # the line-owning engine sends such lines through its float64 path
+	assert torch.equal(a, c)
 	want = exact.remap_linear(page, exact.warped_grid(dense, recs[2]["p"], recs[2]["right"], recs[2]["up"], xsteps=64, ysteps=8))[::-1]
 	assert np.array_equal(a.cpu().numpy()[2 * 512:].reshape(want.shape), want)
 
@@ -332,9 +340,12 @@ def test_screened_strips_with_more_lines_than_the_offset_cache(cuda):
 	a = torch.zeros((total,), dtype=torch.uint8, device=cuda)
 	b = torch.zeros((total,), dtype=torch.uint8, device=cuda)
 	bbox = torch.zeros((len(recs), 4), dtype=torch.int32, device=cuda)
-	ops.extract_lines(src, g, 25, plan, a, dense_map=m)
+	ops.extract_lines(src, g, 25, plan, a, dense_map=m, map_gather=True)
 	ops.extract_lines(src, g, 25, plan, b, bbox, dense_map=m)
 	assert len(recs) > 4096 and torch.equal(a, b)
+	c = torch.zeros_like(a)
+	ops.extract_lines(src, g, 25, plan, c)
+	assert torch.equal(a, c)
 	offs = plan.pix_offsets.cpu().numpy()
 	out = a.cpu().numpy()
 	for i in (0, 59, 60, 119, len(recs) - 1):
@@ -366,3 +377,83 @@ def test_screened_label_counts_on_adversarial_maps(cuda):
 			got = exact.remap_nearest(labels, exact.scale_map(wg, page.shape[1], page.shape[0], labels.shape[1], labels.shape[0]))
 			want = np.bincount(got.reshape(-1), minlength=10)
 			assert np.array_equal(counts[i], want[:4]) and overflow[i] == want[4:].sum(), (name, i)
+
+
+# ---------------------------------------------------------------------------------------
+# The line-owning engine (og_strips.cu): nodes recomputed from the sparse grid, float32 screening
+# with one error radius per chunk, Otsu fused
+# ---------------------------------------------------------------------------------------
+def _adversarial_grids(grid, seed=11):
+	"""Sparse grids that stress the screening: rough ones (large node differences, so a wide
+	interval and a large staged rectangle), ones that leave the page or the float32 range where
+	cv2.remap's fixed point is defined, flat ones (every sample in the same source pixel), and
+	ones whose dense nodes sit on cv2.remap's rounding ties."""
+	rng = np.random.default_rng(seed)
+	f32 = np.float32
+	mean = grid.mean(axis=(0, 1), keepdims=True)
+	return {
+		"grid": grid,
+		"noise 2 px": (grid + rng.normal(0, 2, grid.shape)).astype(f32),
+		"noise 40 px": (grid + rng.normal(0, 40, grid.shape)).astype(f32),
+		"partly outside": (grid * f32(1.7)).astype(f32),
+		"negative": (grid - f32(60)).astype(f32),
+		"constant": np.full_like(grid, 123.5),
+		"tiny": (grid * f32(1e-3)).astype(f32),
+		"integral nodes": np.round(grid).astype(f32),
+		"on the rounding ties": (np.round(grid) + f32(1 / 64)).astype(f32),
+		"far outside": (grid * f32(1e6)).astype(f32),
+		"across a float32 ulp step": (f32(256) + (grid - mean) * f32(0.01)).astype(f32),
+		"steep": ((grid - mean) * f32(20) + f32(300)).astype(f32),
+		"nearly flat": (f32(100) + grid * f32(1e-6)).astype(f32),
+		"not finite": np.where(rng.random(grid.shape) < 0.02, f32(np.inf), grid).astype(f32),
+	}
+
+
+@pytest.mark.parametrize("ysteps,binarize", [(48, None), (48, ("otsu",)), (7, None), (31, ("sauvola", 9))])
+def test_line_owning_engine_on_adversarial_grids(cuda, ysteps, binarize):
+	page, grid, _, lines = _setup(cuda, n_lines=40, seed=3, kind="text")
+	src = ops.to_device_image(page, cuda)
+	recs = _records(lines, ysteps=ysteps, xsteps=150)
+	recs.append(dict(p=[60.0, 400.0], right=[180.0, 170.0], up=[14.0, -15.0], ysteps=ysteps, xsteps=150))  # 43 degrees
+	la = ops.lines_to_device(ops.pack_lines(recs), cuda)
+	for name, gr in _adversarial_grids(grid).items():
+		g = torch.from_numpy(gr).to(cuda)
+		with np.errstate(invalid="ignore", over="ignore"):
+			dense = exact.expand_map(gr, 25)
+		plan = ops.line_steps(g, 25, la, len(recs))
+		offs = plan.pix_offsets.cpu().numpy()
+		out = torch.zeros((int(offs[-1]),), dtype=torch.uint8, device=cuda)
+		thr = torch.full((len(recs),), -1, dtype=torch.int32, device=cuda)
+		ops.extract_lines(src, g, 25, plan, out, binarize=binarize, thresholds=thr)
+		out = out.cpu().numpy()
+		with np.errstate(invalid="ignore", over="ignore"):
+			for i, r in enumerate(recs):
+				wg = exact.warped_grid(dense, r["p"], r["right"], r["up"], xsteps=150, ysteps=ysteps)
+				want = exact.binarize(exact.remap_linear(page, np.nan_to_num(wg, nan=-1e9, posinf=1e9, neginf=-1e9))[::-1], binarize)
+				assert np.array_equal(out[offs[i]:offs[i + 1]].reshape(want.shape), want), (name, i)
+		if binarize == ("otsu",):
+			t = thr.cpu().numpy()
+			assert ((t >= 0) & (t <= 255)).all()
+
+
+def test_line_owning_engine_keeps_gray_beside_otsu(cuda):
+	page, grid, dense, lines = _setup(cuda, n_lines=30, seed=9, kind="text")
+	g = torch.from_numpy(grid).to(cuda)
+	src = ops.to_device_image(page, cuda)
+	recs = _records(lines, ysteps=48)
+	plan = ops.line_steps(g, 25, ops.lines_to_device(ops.pack_lines(recs), cuda), len(recs))
+	offs = plan.pix_offsets.cpu().numpy()
+	binar = torch.zeros((int(offs[-1]) + 3,), dtype=torch.uint8, device=cuda)[3:]  # odd alignment of the packed buffer
+	gray = torch.zeros((int(offs[-1]),), dtype=torch.uint8, device=cuda)
+	thr = torch.zeros((len(recs),), dtype=torch.int32, device=cuda)
+	ops.extract_lines(src, g, 25, plan, binar, binarize=("otsu",), gray_out=gray, thresholds=thr)
+	binar, gray, thr = binar.cpu().numpy(), gray.cpu().numpy(), thr.cpu().numpy()
+	for i, ln in enumerate(lines):
+		want = exact.dewarped_line_image(page, dense, ln["p"], ln["right"], ln["up"], 48)
+		assert np.array_equal(gray[offs[i]:offs[i + 1]].reshape(want.shape), want), i
+		assert np.array_equal(binar[offs[i]:offs[i + 1]].reshape(want.shape), exact.binarize(want, ("otsu",))), i
+		try:
+			tw = exact.threshold_otsu(want)
+		except ValueError:
+			tw = 128
+		assert thr[i] == tw
