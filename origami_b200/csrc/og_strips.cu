@@ -120,22 +120,25 @@ constexpr int RF_TAPS_IN = 4;   // every tap of every sample lies inside the pag
 
 struct ChunkPlan {
 	int R0, C0, NR, NC;  // rectangle of dense-map nodes: rows R0 .. R0 + NR - 1, columns C0 .. C0 + NC - 1
+	int NCP;             // row pitch of the staged rectangle in nodes (NC rounded up to even)
 	int flags;
 	float gbound;        // bound on the difference of neighbouring nodes in the rectangle
-	int pad_[2];
+	int yo;              // R0 - first dense row of the band's y-axis table
+	int groups, band;    // staging: row groups and rows per group
+	float inv_pairs;     // 1 / (NCP / 2)
+	int pad_;
 };
 
 struct __align__(16) FusedSmem {
 	float2 nodes[NODE_CAP];
 	float4 ytab_b[NR_CAP];        // (b0, b0, b1, b1) of cv2.resize's vertical pass per dense row under the band
-	int2 ytab_r[NR_CAP];          // its two sparse rows (clamped)
-	double2 rowbase[ROW_CAP];     // (ys[r] + p0) of the band's strip rows, float64   (block.py:241)
-	int2 rowfx[ROW_CAP + 16];     // (x, y) of rowbase + xs[c0] relative to the chunk's rectangle, 9.23 fixed point
+	int2 ytab_r[NR_CAP + 1];      // its two sparse rows (clamped); one sentinel entry behind the last row
+	int2 rowfx[ROW_CAP + 16];     // (ys[r] + p0) of the band's strip rows relative to the band's origin, 9.23 fixed point
 	ChunkPlan plans[PLAN_CAP];
 	unsigned int hist[256 * FHREP];
 	unsigned int hsum[256];
 	double lin[4];                // the four np.linspace steps of the line
-	int band[4];                  // RL0, NRL, band flags
+	int band[4];                  // first dense row and number of dense rows under the band
 	int line;
 	int thr;
 };
@@ -157,8 +160,8 @@ __device__ __noinline__ int sample_exact(const FusedParams &p, const FusedSmem &
 	float2 v00, v01, v10, v11;
 	const int ri = i0 - cp.R0, ci = i1 - cp.C0;
 	if (staged && ri >= 0 && ci >= 0 && ri <= cp.NR - 2 && ci <= cp.NC - 2) {
-		const float2 *nd = s.nodes + ri * cp.NC + ci;
-		v00 = nd[0]; v01 = nd[1]; v10 = nd[cp.NC]; v11 = nd[cp.NC + 1];
+		const float2 *nd = s.nodes + ri * cp.NCP + ci;
+		v00 = nd[0]; v01 = nd[1]; v10 = nd[cp.NCP]; v11 = nd[cp.NCP + 1];
 	} else {
 		v00 = og_dense_node(p.grid, p.gh, p.gw, p.inv_cell, i0, i1);
 		v01 = og_dense_node(p.grid, p.gh, p.gw, p.inv_cell, i0, i1 + 1);
@@ -199,6 +202,41 @@ __device__ __forceinline__ void plan_rect(const FusedParams &p, const og_lin &lx
 	cp.NC = max(C1 - cp.C0 + 1, 2);
 	cp.flags = (r0u >= 0 && c0u >= 0 && r1u <= p.Hd - 1 && c1u <= p.Wd - 1) ? RF_INSIDE : 0;
 	cp.gbound = 0.f;
+	cp.NCP = (cp.NC + 1) & ~1;
+	const int pairs = cp.NCP >> 1;
+	cp.groups = max(1, min(FT / pairs, cp.NR));
+	cp.band = (cp.NR + cp.groups - 1) / cp.groups;
+	cp.inv_pairs = 1.f / (float)pairs;
+	cp.yo = 0;
+}
+
+// The batch of FNB samples again, for a warp in which some lane's sample was not decided by the
+// screening: decided samples fetch their taps, the others take the float64 path.  Returns the FNB
+// gray values packed into one word.  Kept out of line so that the common path stays small.
+__device__ __noinline__ unsigned int sample_batch_slow(const FusedParams &p, const FusedSmem &s, const ChunkPlan &cp,
+	const og_lin &lx, const og_lin &ly, double cpx, double cpy, int r, int r_last, int cc,
+	int sx0, int sy0, int sx1, int sy1, int sx2, int sy2, int sx3, int sy3, unsigned okmask) {
+	const int sx[4] = {sx0, sx1, sx2, sx3}, sy[4] = {sy0, sy1, sy2, sy3};
+	unsigned int packed = 0;
+#pragma unroll
+	for (int q = 0; q < 4; ++q) {
+		int v;
+		if (okmask & (1u << q)) {
+			const uint8_t *tp = p.src + ((sy[q] >> 5) * p.pitch + (sx[q] >> 5));
+			og_taps t;
+			t.fx = sx[q] & 31;
+			t.fy = sy[q] & 31;
+			t.p00 = __ldg(tp);
+			t.p01 = __ldg(tp + 1);
+			t.p10 = __ldg(tp + p.pitch);
+			t.p11 = __ldg(tp + p.pitch + 1);
+			v = og_blend_taps(t);
+		} else {
+			v = sample_exact(p, s, cp, true, lx, ly, cpx, cpy, min(r + q, r_last), cc);
+		}
+		packed |= (unsigned int)v << (8 * q);
+	}
+	return packed;
 }
 
 // Samples of one warp's share of a chunk: 32 columns x rows [r_beg, r_end) of the band.
@@ -206,33 +244,36 @@ __device__ __forceinline__ void plan_rect(const FusedParams &p, const og_lin &lx
 template <int BIN, bool CHECKED>
 __device__ __forceinline__ void sample_rows(const FusedParams &p, FusedSmem &s, const ChunkPlan &cp,
 	const og_lin &lx, const og_lin &ly, double cpx, double cpy,
-	int ra, int r_beg, int r_end, int cc, int cc_clamped, bool col_ok, int XCx, int XCy,
+	int ra, int r_beg, int r_end, int cc_clamped, bool col_ok, int XCx, int XCy,
 	uint8_t *outp, int xsteps, unsigned int *myhist) {
-	const u64 *nodes64 = reinterpret_cast<const u64 *>(s.nodes);
-	const int NC = cp.NC, NRm = cp.NR - 2, NCm = cp.NC - 2;
+	static_assert(FNB == 4, "sample_batch_slow takes four samples");
+	const int NCP = cp.NCP, NRm = cp.NR - 2, NCm = cp.NC - 2;
 	const float eps = __fmaf_rn(cp.gbound, 0x1p-19f, 0x1p-30f);  // 32 u G + 2^-30
 	const u64 epsp = pk(eps, eps), c32 = pk(32.f, 32.f), magic = pk(OG_RINT_MAGIC_F, OG_RINT_MAGIC_F);
 	const uint8_t *__restrict__ src = p.src;
 	const int spitch = p.pitch;
 	const int2 *rfp = s.rowfx + (r_beg - ra);
+	const unsigned char *nbase = reinterpret_cast<const unsigned char *>(s.nodes);
+	const int rowbytes = NCP * 8;
 	for (int r = r_beg; r < r_end; r += FNB, rfp += FNB) {
 		int sx[FNB], sy[FNB];
-		bool okv[FNB];
-		bool good = true;
+		unsigned okmask = 0;
 #pragma unroll
 		for (int q = 0; q < FNB; ++q) {
 			const int2 rf = rfp[q];  // the table is padded with copies of the last row
 			const int fxx = rf.x + XCx, fyy = rf.y + XCy;
 			const int i1 = fxx >> 23, i0 = fyy >> 23;
 			bool ok = true;
-			int idx = i0 * NC + i1;
+			int off = i0 * rowbytes + i1 * 8;
 			if (CHECKED) {
 				ok = (unsigned)i0 <= (unsigned)NRm && (unsigned)i1 <= (unsigned)NCm;
-				idx = ok ? idx : 0;
+				off = ok ? off : 0;
 			}
 			const float b = __fsub_rn(__int_as_float((fxx & 0x7FFFFF) | 0x3F800000), 1.f);
 			const float a = __fsub_rn(__int_as_float((fyy & 0x7FFFFF) | 0x3F800000), 1.f);
-			const u64 v00 = nodes64[idx], v01 = nodes64[idx + 1], v10 = nodes64[idx + NC], v11 = nodes64[idx + NC + 1];
+			const u64 *n0 = reinterpret_cast<const u64 *>(nbase + off);
+			const u64 *n1 = reinterpret_cast<const u64 *>(nbase + off + rowbytes);
+			const u64 v00 = n0[0], v01 = n0[1], v10 = n1[0], v11 = n1[1];
 			const u64 d01 = sub2(v01, v00), d10 = sub2(v10, v00), d11 = sub2(v11, v10);
 			const u64 ap = pk(a, a), bp = pk(b, b);
 			const u64 del = fma2(ap, fma2(bp, sub2(d11, d01), d10), mul2(bp, d01));
@@ -244,11 +285,10 @@ __device__ __forceinline__ void sample_rows(const FusedParams &p, FusedSmem &s, 
 			// which the page test (or the plan's source box) implies.
 			ok = ok && lo_f(ul) == lo_f(uh) && hi_f(ul) == hi_f(uh);
 			if (CHECKED) ok = ok && (unsigned)(sx[q] >> 5) < (unsigned)p.W1 && (unsigned)(sy[q] >> 5) < (unsigned)p.H1;
-			okv[q] = ok;
-			good = good && ok;
+			okmask |= ok ? (1u << q) : 0u;
 		}
-		int val[FNB];
-		if (good) {
+		unsigned int packed;
+		if (__all_sync(0xffffffffu, okmask == (1u << FNB) - 1)) {
 			og_taps t[FNB];
 #pragma unroll
 			for (int q = 0; q < FNB; ++q) {
@@ -260,31 +300,19 @@ __device__ __forceinline__ void sample_rows(const FusedParams &p, FusedSmem &s, 
 				t[q].p10 = __ldg(tp + spitch);
 				t[q].p11 = __ldg(tp + spitch + 1);
 			}
+			packed = 0;
 #pragma unroll
-			for (int q = 0; q < FNB; ++q) val[q] = og_blend_taps(t[q]);
+			for (int q = 0; q < FNB; ++q) packed |= (unsigned int)og_blend_taps(t[q]) << (8 * q);
 		} else {
-#pragma unroll
-			for (int q = 0; q < FNB; ++q) {
-				if (okv[q]) {
-					const uint8_t *tp = src + ((sy[q] >> 5) * spitch + (sx[q] >> 5));
-					og_taps t;
-					t.fx = sx[q] & 31;
-					t.fy = sy[q] & 31;
-					t.p00 = __ldg(tp);
-					t.p01 = __ldg(tp + 1);
-					t.p10 = __ldg(tp + spitch);
-					t.p11 = __ldg(tp + spitch + 1);
-					val[q] = og_blend_taps(t);
-				} else {
-					val[q] = sample_exact(p, s, cp, true, lx, ly, cpx, cpy, min(r + q, r_end - 1), cc_clamped);
-				}
-			}
+			packed = sample_batch_slow(p, s, cp, lx, ly, cpx, cpy, r, r_end - 1, cc_clamped,
+				sx[0], sy[0], sx[1], sy[1], sx[2], sy[2], sx[3], sy[3], okmask);
 		}
 #pragma unroll
 		for (int q = 0; q < FNB; ++q) {
+			const unsigned int v = (packed >> (8 * q)) & 255u;
 			if (col_ok && r + q < r_end) {
-				*outp = (uint8_t)val[q];
-				if (BIN == OG_BIN_OTSU) atomicAdd(myhist + val[q] * FHREP, 1u);
+				*outp = (uint8_t)v;
+				if (BIN == OG_BIN_OTSU) atomicAdd(myhist + v * FHREP, 1u);
 			}
 			outp -= xsteps;
 		}
@@ -342,20 +370,28 @@ __global__ void __launch_bounds__(FT, OG_F_MINB) og_strips_fused_kernel(const __
 			const int rb = min(ysteps, ra + ROW_CAP), nrows = rb - ra;
 			const int rpg = (nrows + ROWG - 1) / ROWG;
 			const int r_beg = ra + rg * rpg, r_end = min(rb, r_beg + rpg);
+			const int nfx = ROWG * ((rpg + FNB - 1) / FNB * FNB);
+			// origin of the band's fixed-point coordinates: the integer part of its first lattice row
+			const og_d2 y0 = og_linspace_at(ly, ra);
+			const double LX = floor(__dadd_rn(y0.x, cpx)), LY = floor(__dadd_rn(y0.y, cpy));
 			for (int kbase = 0; kbase < nchunks; kbase += PLAN_CAP) {
 				const int nplan = min(PLAN_CAP, nchunks - kbase);
-				// ---- plan: (ys + p0) of the band's rows, the rectangle of every chunk, the dense rows
-				// under the whole band
+				// ---- plan, once per band: the strip rows in fixed point, the rectangle of every chunk, the
+				// dense rows under the whole band
 				__syncthreads();
+				bool far = false;
 				if (kbase == 0)
-					for (int r = tid; r < nrows; r += FT) {
-						const og_d2 yr = og_linspace_at(ly, ra + r);
-						s.rowbase[r] = make_double2(__dadd_rn(yr.x, cpx), __dadd_rn(yr.y, cpy));
+					for (int r = tid; r < nfx; r += FT) {
+						const og_d2 yr = og_linspace_at(ly, ra + min(r, nrows - 1));  // (ys + p0), block.py:241; padded with the last row
+						const double qx = __dsub_rn(__dadd_rn(yr.x, cpx), LX), qy = __dsub_rn(__dadd_rn(yr.y, cpy), LY);
+						far = far || !(fabs(qx) < 120.0 && fabs(qy) < 120.0);
+						s.rowfx[r] = make_int2(__double2int_rn(__dmul_rn(qx, 8388608.0)), __double2int_rn(__dmul_rn(qy, 8388608.0)));
 					}
 				if (tid >= 128 && tid < 128 + nplan) {
 					const int k = tid - 128, c0 = (kbase + k) * FCW;
 					ChunkPlan cp;
-					cp.R0 = cp.C0 = 0; cp.NR = cp.NC = 2; cp.flags = 0; cp.gbound = 0.f;
+					cp.R0 = cp.C0 = 0; cp.NR = cp.NC = cp.NCP = 2; cp.flags = 0; cp.gbound = 0.f;
+					cp.groups = cp.band = 1; cp.inv_pairs = 1.f; cp.yo = 0;
 					if (sane) plan_rect(p, lx, ly, cpx, cpy, ra, rb, c0, min(FCW, xsteps - c0), cp);
 					s.plans[k] = cp;
 				}
@@ -366,11 +402,15 @@ __global__ void __launch_bounds__(FT, OG_F_MINB) og_strips_fused_kernel(const __
 					s.band[0] = cp.R0;
 					s.band[1] = cp.NR;
 				}
-				__syncthreads();
+				far = __syncthreads_or(far) != 0;
+				if (kbase == 0 && tid == 0) s.band[2] = far;
 				const int RL0 = s.band[0], NRL = s.band[1];
-				const bool band_ok = sane && NRL <= NR_CAP;
-				if (band_ok) {
-					for (int i = tid; i < NRL; i += FT) {
+				if (sane && NRL <= NR_CAP) {
+					for (int i = tid; i <= NRL; i += FT) {
+						if (i == NRL) {
+							s.ytab_r[i] = make_int2(-2, -2);  // sentinel: ends the last run of rows
+							break;
+						}
 						const og_axis ay = og_resize_axis(RL0 + i, p.inv_cell);
 						const float b1 = ay.f, b0 = __fsub_rn(1.f, ay.f);
 						s.ytab_b[i] = make_float4(b0, b0, b1, b1);
@@ -385,7 +425,7 @@ __global__ void __launch_bounds__(FT, OG_F_MINB) og_strips_fused_kernel(const __
 						const ChunkPlan cp = s.plans[k];
 						int flags = cp.flags;
 						float gbound = 0.f;
-						if (cp.NR * cp.NC <= NODE_CAP && cp.NC <= 250) {
+						if (cp.NR * cp.NCP <= NODE_CAP && cp.NC <= 130) {
 							flags |= RF_STAGED;
 							const og_axis ac0 = og_resize_axis_x(cp.C0, p.inv_cell, p.gw), ac1 = og_resize_axis_x(cp.C0 + cp.NC - 1, p.inv_cell, p.gw);
 							const og_axis ar0 = og_resize_axis(cp.R0, p.inv_cell), ar1 = og_resize_axis(cp.R0 + cp.NR - 1, p.inv_cell);
@@ -425,6 +465,7 @@ __global__ void __launch_bounds__(FT, OG_F_MINB) og_strips_fused_kernel(const __
 						if (lane == 0) {
 							s.plans[k].flags = flags;
 							s.plans[k].gbound = gbound;
+							s.plans[k].yo = cp.R0 - RL0;
 						}
 					}
 				}
@@ -432,51 +473,59 @@ __global__ void __launch_bounds__(FT, OG_F_MINB) og_strips_fused_kernel(const __
 
 				for (int k = 0; k < nplan; ++k) {
 					const int c0 = (kbase + k) * FCW, ncols = min(FCW, xsteps - c0);
-					__syncthreads();  // plans / tables written; the previous chunk's samples are done with nodes and rowfx
+					__syncthreads();  // plans / tables written; the previous chunk's samples are done with the nodes
 					const ChunkPlan cp = s.plans[k];
-					const bool staged = band_ok && (cp.flags & RF_STAGED) != 0;
-					const og_d2 xc0 = og_linspace_at(lx, c0);
+					const bool staged = sane && NRL <= NR_CAP && s.band[2] == 0 && (cp.flags & RF_STAGED) != 0;
 					if (staged) {
-						// ---- stage 1: fixed-point row table of the chunk, and its rectangle of dense-map nodes.
-						// A thread owns a column of the rectangle and a band of its rows: HResizeLinear of the
-						// two sparse rows it needs (kept in registers until the row crosses into the next sparse
-						// cell), then VResizeLinear per row.
-						const int nfx = ROWG * ((rpg + FNB - 1) / FNB * FNB);
-						for (int r = tid; r < nfx; r += FT) {
-							const double2 rbv = s.rowbase[min(r, nrows - 1)];
-							const double qx = __dsub_rn(__dadd_rn(rbv.x, xc0.x), (double)cp.C0);
-							const double qy = __dsub_rn(__dadd_rn(rbv.y, xc0.y), (double)cp.R0);
-							s.rowfx[r] = make_int2(__double2int_rn(__dmul_rn(qx, 8388608.0)), __double2int_rn(__dmul_rn(qy, 8388608.0)));
-						}
-						const int NC = cp.NC, NR = cp.NR;
-						const int groups = max(1, FT / NC);
-						const int band = (NR + groups - 1) / groups;
-						for (int t = tid; t < groups * NC; t += FT) {  // one pass unless NC > FT
-							const int g = t / NC, j = t - g * NC;
-							const int ibeg = g * band, iend = min(NR, ibeg + band);
-							if (ibeg >= iend) continue;
-							const og_axis ax = og_resize_axis_x(cp.C0 + j, p.inv_cell, p.gw);
-							const int c1 = min(ax.i + 1, p.gw - 1);
-							const float w1 = ax.f, w0 = __fsub_rn(1.f, ax.f);
-							const u64 w0p = pk(w0, w0), w1p = pk(w1, w1);
+						// ---- stage 1: the chunk's rectangle of dense-map nodes.  A thread owns a pair of
+						// columns and a band of rows: HResizeLinear of the two sparse rows above and below
+						// (kept in registers while the rows stay in the same sparse cell), then
+						// VResizeLinear per row, written as one 16-byte store.
+						const int pairs = cp.NCP >> 1;
+						const int g = __float2int_rz(__fmul_rn((float)tid + 0.5f, cp.inv_pairs));
+						const int jp = tid - g * pairs;
+						if (g < cp.groups) {
+							const int ibeg = g * cp.band, iend = min(cp.NR, ibeg + cp.band);
+							const int ja = 2 * jp, jb = min(ja + 1, cp.NC - 1);  // an odd rectangle repeats its last column
+							const og_axis axa = og_resize_axis_x(cp.C0 + ja, p.inv_cell, p.gw), axb = og_resize_axis_x(cp.C0 + jb, p.inv_cell, p.gw);
+							const int ca1 = min(axa.i + 1, p.gw - 1), cb1 = min(axb.i + 1, p.gw - 1);
+							const u64 wa0 = pk(__fsub_rn(1.f, axa.f), __fsub_rn(1.f, axa.f)), wa1 = pk(axa.f, axa.f);
+							const u64 wb0 = pk(__fsub_rn(1.f, axb.f), __fsub_rn(1.f, axb.f)), wb1 = pk(axb.f, axb.f);
 							const u64 *g64 = reinterpret_cast<const u64 *>(p.grid);
-							u64 *nd = reinterpret_cast<u64 *>(s.nodes) + ibeg * NC + j;
-							const int yo = cp.R0 - RL0;
-							int cr0 = -1, cr1 = -1;
-							u64 u = 0, v = 0;
-							for (int i = ibeg; i < iend; ++i, nd += NC) {
-								const int2 rr = s.ytab_r[yo + i];
-								const float4 bw = s.ytab_b[yo + i];
-								if (rr.x != cr0) {
-									if (rr.x == cr1) u = v;
-									else u = lerp2_cv(__ldg(g64 + rr.x * p.gw + ax.i), w0p, __ldg(g64 + rr.x * p.gw + c1), w1p);
-									cr0 = rr.x;
+							ulonglong2 *nd = reinterpret_cast<ulonglong2 *>(s.nodes + ibeg * cp.NCP + ja);
+							const int ndstep = cp.NCP >> 1;  // in 16-byte units
+							const int2 *yr = s.ytab_r + cp.yo;
+							const float4 *yb = s.ytab_b + cp.yo;
+							int i = ibeg;
+							int pr1 = -1;
+							u64 ua = 0, va = 0, ub = 0, vb = 0;
+							while (i < iend) {
+								const int2 rr = yr[i];
+								if (rr.x == pr1) {
+									ua = va; ub = vb;
+								} else {
+									const u64 *row = g64 + rr.x * p.gw;
+									ua = lerp2_cv(__ldg(row + axa.i), wa0, __ldg(row + ca1), wa1);
+									ub = lerp2_cv(__ldg(row + axb.i), wb0, __ldg(row + cb1), wb1);
 								}
-								if (rr.y != cr1) {
-									v = rr.y == cr0 ? u : lerp2_cv(__ldg(g64 + rr.y * p.gw + ax.i), w0p, __ldg(g64 + rr.y * p.gw + c1), w1p);
-									cr1 = rr.y;
+								if (rr.y == rr.x) {
+									va = ua; vb = ub;
+								} else {
+									const u64 *row = g64 + rr.y * p.gw;
+									va = lerp2_cv(__ldg(row + axa.i), wa0, __ldg(row + ca1), wa1);
+									vb = lerp2_cv(__ldg(row + axb.i), wb0, __ldg(row + cb1), wb1);
 								}
-								*nd = lerp2_cv(u, pk(bw.x, bw.y), v, pk(bw.z, bw.w));
+								pr1 = rr.y;
+								do {  // the rows of this sparse cell
+									const float4 bw = yb[i];
+									const u64 w0 = pk(bw.x, bw.y), w1 = pk(bw.z, bw.w);
+									ulonglong2 o;
+									o.x = lerp2_cv(ua, w0, va, w1);
+									o.y = lerp2_cv(ub, w0, vb, w1);
+									*nd = o;
+									nd += ndstep;
+									++i;
+								} while (i < iend && yr[i].x == rr.x);
 							}
 						}
 					}
@@ -497,13 +546,15 @@ __global__ void __launch_bounds__(FT, OG_F_MINB) og_strips_fused_kernel(const __
 									if (BIN == OG_BIN_OTSU) atomicAdd(myhist + v * FHREP, 1u);
 								}
 						} else {
+							// this lane's column relative to the rectangle, minus the band origin the row table
+							// is relative to: (row term) + (column term) = lattice point - rectangle origin
 							const og_d2 xcc = og_linspace_at(lx, ccc);
-							const int XCx = __double2int_rn(__dmul_rn(__dsub_rn(xcc.x, xc0.x), 8388608.0));
-							const int XCy = __double2int_rn(__dmul_rn(__dsub_rn(xcc.y, xc0.y), 8388608.0));
+							const int XCx = __double2int_rn(__dmul_rn(__dadd_rn(xcc.x, __dsub_rn(LX, (double)cp.C0)), 8388608.0));
+							const int XCy = __double2int_rn(__dmul_rn(__dadd_rn(xcc.y, __dsub_rn(LY, (double)cp.R0)), 8388608.0));
 							if ((cp.flags & (RF_INSIDE | RF_TAPS_IN)) == (RF_INSIDE | RF_TAPS_IN))
-								sample_rows<BIN, false>(p, s, cp, lx, ly, cpx, cpy, ra, r_beg, r_end, cc, ccc, col_ok, XCx, XCy, outp, xsteps, myhist);
+								sample_rows<BIN, false>(p, s, cp, lx, ly, cpx, cpy, ra, r_beg, r_end, ccc, col_ok, XCx, XCy, outp, xsteps, myhist);
 							else
-								sample_rows<BIN, true>(p, s, cp, lx, ly, cpx, cpy, ra, r_beg, r_end, cc, ccc, col_ok, XCx, XCy, outp, xsteps, myhist);
+								sample_rows<BIN, true>(p, s, cp, lx, ly, cpx, cpy, ra, r_beg, r_end, ccc, col_ok, XCx, XCy, outp, xsteps, myhist);
 						}
 					}
 				}
