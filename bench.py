@@ -252,7 +252,7 @@ class PageSet:
 		self.plan = ops.LinePlan(self.lines, self.n, self.steps, self.pix, self.chunks)
 
 
-KERNELS = ["og_page_kernel", "og_line_plan_kernel", "og_strips_fused_kernel"]
+KERNELS = ["og_page_kernel", "og_line_plan_kernel", "og_strips_kernels"]
 
 
 def run_step(ps, args, events=None):
@@ -277,12 +277,12 @@ def run_step(ps, args, events=None):
 	mark("og_line_plan_kernel")
 	mode = {"none": ops.OG_BIN_NONE, "otsu": ops.OG_BIN_OTSU, "sauvola": ops.OG_BIN_SAUVOLA}[args.binarize]
 	_lib.call("og_extract_lines", ps.src.data_ptr(), ps.H, ps.W, ps.src.stride(0), ps.grid.data_ptr(), ps.gh, ps.gw, CELL,
-		0, ps.lines.data_ptr(), ps.n, ps.steps.data_ptr(), ps.pix.data_ptr(), ps.chunks.data_ptr(),
+		ps.map.data_ptr(), ps.lines.data_ptr(), ps.n, ps.steps.data_ptr(), ps.pix.data_ptr(), ps.chunks.data_ptr(),
 		ps.bin.data_ptr(), ps.bin.numel(), 0, mode, 15, ps.gray.data_ptr() if mode == ops.OG_BIN_SAUVOLA else 0, 0, st)
-	mark("og_strips_fused_kernel")
-	# og_page_kernel, og_line_plan_kernel (up to 8192 lines: one launch), og_strips_fused_kernel (samples the
-	# strips and applies Otsu); Sauvola on strips is a fourth launch
-	return 4 if mode == ops.OG_BIN_SAUVOLA else 3
+	mark("og_strips_kernels")
+	# og_page_kernel, og_line_plan_kernel (up to 8192 lines: one launch), og_strips_screened_kernel, and the
+	# strip binarizer (og_otsu_strips_kernel / og_sauvola_strips_kernel)
+	return 3 if mode == ops.OG_BIN_NONE else 4
 
 
 def run_e2e(args, inputs, device, n_steps):
@@ -439,7 +439,7 @@ def run_ours(args):
 		src_rows = float(np.mean([np.ceil(np.hypot(*l["up"])) + 2 for l in inputs[0][2]]))
 		alg_bytes = {
 			"og_page_kernel": 9 * ps0.Hd * ps0.Wd + ps0.H * ps0.W,
-			"og_strips_fused_kernel": strip_px + strip_px / LINE_HEIGHT * src_rows,
+			"og_strips_kernels": strip_px + strip_px / LINE_HEIGHT * src_rows,
 			"og_line_plan_kernel": ps0.n * (112 + 8 + 8 + 4),
 		}
 		traffic = recorded_traffic()

@@ -43,8 +43,8 @@ extern "C" {
 #define OG_BIN_NONE 0
 #define OG_BIN_OTSU 1
 #define OG_BIN_SAUVOLA 2
-/* OR-ed into og_extract_lines' `binarize`: gather every sample's four nodes from the caller's dense
- * `map` with the map-gather engines of round 1 (same bits; slower; binarization as a second kernel). */
+/* OR-ed into og_extract_lines' `binarize`: use the map-gather engines even without bounding boxes
+ * (what a non-NULL `map` selects anyway; kept as an explicit switch for tests and comparisons). */
 #define OG_FLAG_MAP_GATHER 0x100
 
 /* One text line in DEWARPED page space.  Mirrors the fields of the reference's Line
@@ -131,17 +131,17 @@ int og_warped_grids(const float *grid, int gh, int gw, int cell, const float *ma
  * do not fit are skipped whole (compare pix_offsets[n] with the capacity).
  *   binarize   OG_BIN_NONE: strips_out receives the gray strips.
  *              OG_BIN_OTSU: strips_out receives (gray > t) * 255 with t the strip's own Otsu threshold
- *              (thresholds_out, n int32, may be NULL); the threshold is computed by the CTA that samples
- *              the line, from a shared-memory histogram, and applied to its bytes while they are still
- *              in L2.  gray_out, if not NULL, additionally keeps the gray strips.
+ *              (thresholds_out, n int32, may be NULL).  gray_out, if not NULL, additionally keeps the
+ *              gray strips.
  *              OG_BIN_SAUVOLA: as og_binarize_strips (window odd, 3..127; k = 0.2, r = 127.5); the
  *              window needs the whole gray strip, so gray_out is required and must not alias strips_out.
  *   bbox_out   if not NULL, receives per line (floor min x, floor min y, ceil max x, ceil max y) of its
  *              fp32 warped grid as int32 (origami/core/mask.py:10-12 convention).
- * The dense-map nodes under a line are recomputed on chip from the sparse grid; `map` is only read
- * when bounding boxes are asked for or OG_FLAG_MAP_GATHER is set (identical bits either way).  Like
- * og_sample_labels the call uses the plan's work-ticket word while it runs (one call per plan at a
- * time). */
+ * With `map` (the dense map of the SAME grid) the samples' nodes are gathered from it and the
+ * binarizer runs as a second pass over the L2-resident strips; with map == NULL the dense-map nodes
+ * under every line are recomputed on chip from the sparse grid by CTAs that own a line each, and Otsu
+ * is applied by the CTA that sampled the line.  Identical bits either way.  Like og_sample_labels the
+ * call uses the plan's work-ticket word while it runs (one call per plan at a time). */
 int og_extract_lines(const uint8_t *src, int H, int W, int64_t src_pitch,
 	const float *grid, int gh, int gw, int cell, const float *map,
 	const og_line *lines, int n,

@@ -661,12 +661,14 @@ extern "C" int og_extract_lines(const uint8_t *src, int H, int W, int64_t src_pi
 		OG_REQUIRE(gray_out != nullptr && gray_out != strips_out, OG_E_ARG, "Sauvola needs a separate gray_out buffer of `capacity` bytes");
 	}
 	cudaStream_t st = (cudaStream_t)stream;
-	if (bbox_out != nullptr || gather) {  // the engines of og_lines.cu: float64 samples, bounding boxes, nodes gathered from `map`
+	// Engine choice (measured on B200, 2000 lines of a 4800x7200 page, profiles/README.md): with the
+	// materialised map the screened map-gather engine of og_lines.cu is the fastest (0.217 ms, Otsu as
+	// a second pass over the L2-resident strips 0.042 ms); without a map the line-owning engine below
+	// recomputes the nodes on chip (0.37 ms; Otsu fused, +0.06 ms) and reads no dense map at all.
+	if (bbox_out != nullptr || gather || map != nullptr) {
 		uint8_t *target = strips_out;
-		if (binarize != OG_BIN_NONE) {
-			OG_REQUIRE(gray_out != nullptr && gray_out != strips_out, OG_E_ARG, "these engines binarize in a second pass: gray_out is required");
-			target = gray_out;
-		}
+		if (binarize == OG_BIN_OTSU && gray_out != nullptr) target = gray_out;  // else Otsu runs in place
+		if (binarize == OG_BIN_SAUVOLA) target = gray_out;
 		int rc = og_extract_lines_engines(src, H, W, src_pitch, grid, gh, gw, cell, map, lines, n, steps, pix_offsets,
 			chunk_offsets, target, capacity, bbox_out, st);
 		if (rc || n == 0 || binarize == OG_BIN_NONE) return rc;

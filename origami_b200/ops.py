@@ -247,13 +247,14 @@ def _binarize_args(binarize):
 def extract_lines(src, grid, cell, plan, out, bbox=None, dense_map=None, binarize=None, gray_out=None, thresholds=None,
 		map_gather=False):
 	"""Line.image(dewarped=True, binarizer=...) for every line into the packed uint8 buffer `out`
-	(reference origami/core/block.py:129-143): gray strips, or strips binarized by the kernel that
-	samples them.  binarize: None | ("otsu",) | ("sauvola", window); Sauvola needs its gray input
-	whole, so a gray scratch buffer is allocated when gray_out is not given."""
+	(reference origami/core/block.py:129-143): gray strips, or binarized ones.  binarize: None |
+	("otsu",) | ("sauvola", window); Sauvola needs its gray input whole, so a gray scratch buffer is
+	allocated when gray_out is not given.  With dense_map the nodes are gathered from it (fastest),
+	without it they are recomputed on chip (no dense map needed at all)."""
 	gh, gw = _check_grid(grid)
 	_check_u8_image(src, "src")
 	mode, window = _binarize_args(binarize)
-	if (mode == OG_BIN_SAUVOLA or (mode != OG_BIN_NONE and (map_gather or bbox is not None))) and gray_out is None:
+	if mode == OG_BIN_SAUVOLA and gray_out is None:
 		gray_out = torch.empty_like(out)
 	if map_gather:
 		mode |= OG_FLAG_MAP_GATHER

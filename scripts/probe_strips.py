@@ -34,13 +34,13 @@ def main():
 		row, col = divmod(int(bad[k] - offs[i]), int(steps[i, 0]))
 		print("  line %d (xsteps %d) r=%d col %d (chunk col %d): %d vs %d" % (i, steps[i, 0], 47 - row, col, col % 64, an[bad[k]], bn[bad[k]]))
 	ops.extract_lines(src, g, cell, plan, a, binarize=("otsu",))
-	ops.extract_lines(src, g, cell, plan, b, dense_map=mp, map_gather=True, binarize=("otsu",), gray_out=c)
+	ops.extract_lines(src, g, cell, plan, b, dense_map=mp, binarize=("otsu",))
 	print("otsu: equal =", torch.equal(a, b))
 	for name, fn in [
 		("line-owning none", lambda: ops.extract_lines(src, g, cell, plan, a)),
 		("line-owning otsu", lambda: ops.extract_lines(src, g, cell, plan, a, binarize=("otsu",))),
 		("screened none", lambda: ops.extract_lines(src, g, cell, plan, b, dense_map=mp, map_gather=True)),
-		("screened + otsu", lambda: ops.extract_lines(src, g, cell, plan, b, dense_map=mp, map_gather=True, binarize=("otsu",), gray_out=c)),
+		("screened + otsu", lambda: ops.extract_lines(src, g, cell, plan, b, dense_map=mp, binarize=("otsu",))),
 	]:
 		med, best = timeit(fn)
 		print("%-18s median %8.3f ms  best %8.3f ms  (%.1f MP strips)" % (name, med, best, total / 1e6))

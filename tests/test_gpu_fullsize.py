@@ -11,28 +11,30 @@ from origami_b200 import ops, synth
 pytestmark = pytest.mark.gpu
 
 
-def _strips(cuda, page, g, s, lines, height, binarize=None):
+def _strips(cuda, page, g, s, lines, height, binarize=None, use_map=False):
 	gt = torch.from_numpy(g).to(cuda)
+	dmap = ops.expand_map(gt, s) if use_map else None
 	src = ops.to_device_image(page, cuda)
 	la = ops.pack_lines([dict(p=l["p"], right=l["right"], up=l["up"], ysteps=height) for l in lines])
 	plan = ops.line_steps(gt, s, ops.lines_to_device(la, cuda), len(lines))
 	offs = plan.pix_offsets.cpu().numpy()
 	out = torch.empty((int(offs[-1]),), dtype=torch.uint8, device=cuda)
-	ops.extract_lines(src, gt, s, plan, out, binarize=binarize)
+	ops.extract_lines(src, gt, s, plan, out, binarize=binarize, dense_map=dmap)
 	return out.cpu().numpy(), offs, plan
 
 
-@pytest.mark.parametrize("kind", ["noise", "text"])
-def test_all_strips_of_the_stress_page_against_the_oracle(cuda, kind):
+@pytest.mark.parametrize("kind,use_map", [("noise", True), ("text", True), ("noise", False), ("text", False)])
+def test_all_strips_of_the_stress_page_against_the_oracle(cuda, kind, use_map):
 	"""configs[1] + configs[3]: every one of the 2000 strips of a 4800x7200 page, gray and Otsu'd,
-	through the engine the bench times, against exact.dewarped_line_image / exact.binarize."""
+	against exact.dewarped_line_image / exact.binarize -- through the engines the bench times (dense map
+	given: screened map-gather + Otsu pass) and through the line-owning engine (no map, Otsu fused)."""
 	W, H, s = 4800, 7200, 25
 	page = synth.make_page(W, H, seed=3, kind=kind)
 	g = synth.make_grid(W, H, s, seed=3)
 	dense = exact.expand_map(g, s)
 	lines = synth.make_lines(dense.shape[1], dense.shape[0], 2000, seed=3, dpi=600)
-	gray, offs, plan = _strips(cuda, page, g, s, lines, 48)
-	fused, offs2, _ = _strips(cuda, page, g, s, lines, 48, binarize=("otsu",))
+	gray, offs, plan = _strips(cuda, page, g, s, lines, 48, use_map=use_map)
+	fused, offs2, _ = _strips(cuda, page, g, s, lines, 48, binarize=("otsu",), use_map=use_map)
 	assert np.array_equal(offs, offs2)
 	two_pass = ops.binarize_strips(torch.from_numpy(gray).to(cuda), plan, ops.OG_BIN_OTSU).cpu().numpy()
 	for i, l in enumerate(lines):
@@ -55,8 +57,8 @@ def test_config0_page_2400x3600_with_1200_lines(cuda):
 	assert np.array_equal(dmap.cpu().numpy().view(np.uint32), dense.view(np.uint32))
 	assert np.array_equal(dst.cpu().numpy(), exact.remap_linear(page, dense))
 	lines = synth.make_lines(dense.shape[1], dense.shape[0], 1200, seed=5, dpi=300)
-	for height in (48, 56):
-		got, offs, _ = _strips(cuda, page, g, s, lines, height)
+	for height, use_map in ((48, True), (56, False)):
+		got, offs, _ = _strips(cuda, page, g, s, lines, height, use_map=use_map)
 		for i, l in enumerate(lines):
 			want = exact.dewarped_line_image(page, dense, l["p"], l["right"], l["up"], height)
 			assert np.array_equal(got[offs[i]:offs[i + 1]].reshape(want.shape), want), (height, i)
