@@ -44,16 +44,43 @@ def parse_args():
 	ap.add_argument("--page-sets", type=int, default=3, help="distinct resident pages rotated through")
 	ap.add_argument("--lines", type=int, default=N_LINES)
 	ap.add_argument("--binarize", default="otsu", choices=["none", "otsu", "sauvola"])
+	ap.add_argument("--config", default="page", choices=["page", "page-2400", "segpost"],
+		help="page: configs[1]+[3] (default, the metric's workload); page-2400: configs[0]; segpost: configs[4]")
+	ap.add_argument("--pages", type=int, default=256, help="page indices of the job (configs[2]); rank r takes r, r+N, ...")
+	ap.add_argument("--ref-sample", type=int, default=0,
+		help="reference arm: time only this many lines per step and scale the line time (prints extrapolated: true)")
 	ap.add_argument("--e2e-steps", type=int, default=6)
 	ap.add_argument("--no-cpu-baseline", action="store_true")
 	ap.add_argument("--no-e2e", action="store_true")
 	return ap.parse_args()
 
 
+def apply_config(args):
+	"""Sizes of the selected BASELINE configuration (module globals, read by both arms)."""
+	global PAGE_W, PAGE_H, N_LINES, DPI
+	if args.config == "page-2400":
+		PAGE_W, PAGE_H, DPI = 2400, 3600, 300
+		if args.lines == 2000:
+			args.lines = 1200
+	return args
+
+
+DPI = 600
+
+
 def workload_config(args, extra=None):
+	if args.config == "segpost":
+		cfg = {"workload": "configs[4]: segmentation post-process per page: label argmax of (5, 2400, 1280, 4) softmax tiles to "
+			"labels + 3 class masks, and Sauvola-15 binarization of the 4800x7200 page",
+			"page": [PAGE_W, PAGE_H], "label_map": [1280, 2400], "models": 5, "classes": 4, "sauvola_window": 15,
+			"cache": "inputs larger than L2: 98 MB of probabilities + 35 MB page per step, 3 resident sets rotated",
+			"sharding": "pages by index, no collective"}
+		if extra:
+			cfg.update(extra)
+		return cfg
 	cfg = {
-		"workload": "configs[1]: single 600-dpi 4800x7200 broadsheet page: dense map expansion + bilinear remap + "
-			"extraction of %d text lines to %d-px strips" % (args.lines, LINE_HEIGHT),
+		"workload": "configs[%s]: single %d-dpi %dx%d broadsheet page: dense map expansion + bilinear remap + "
+			"extraction of %d text lines to %d-px strips" % ("0" if args.config == "page-2400" else "1", DPI, PAGE_W, PAGE_H, args.lines, LINE_HEIGHT),
 		"page": [PAGE_W, PAGE_H], "cell": CELL, "lines_per_page": args.lines, "line_height": LINE_HEIGHT,
 		"binarize": args.binarize, "emit_dense_map": True,
 		"cache": "inputs larger than L2: every step writes a 281 MB dense map + 35 MB page and rotates over "
@@ -67,10 +94,10 @@ def workload_config(args, extra=None):
 
 def make_inputs(args, page_index):
 	from origami_b200 import synth
-	page = synth.make_page(PAGE_W, PAGE_H, seed=page_index, kind="text", dpi=600)
+	page = synth.make_page(PAGE_W, PAGE_H, seed=page_index, kind="text", dpi=DPI)
 	grid = synth.make_grid(PAGE_W, PAGE_H, CELL, seed=page_index)
 	gh, gw = grid.shape[:2]
-	lines = synth.make_lines(gw * CELL, gh * CELL, args.lines, seed=page_index, dpi=600)
+	lines = synth.make_lines(gw * CELL, gh * CELL, args.lines, seed=page_index, dpi=DPI)
 	return page, grid, lines
 
 
@@ -179,8 +206,9 @@ def cpu_baseline(args, page, grid, lines, n_sample=512, reps=3):
 	e, tp, tl = min(est)
 	return {
 		"value": mp / e, "unit": UNIT, "cores": max(cv2.getNumThreads(), 8), "kind": "port",
-		"sample": "1 page 4800x7200 expand+remap in full (%.3f s) + %d of %d lines through the 8-thread pool (%.3f s), "
-			"line time scaled to %d lines; best of %d; host has %d logical cores, cv2 threads %d" % (
+		"extrapolated": n_sample < len(lines),
+		"sample": "1 page %dx%d expand+remap in full (%.3f s) + %d of %d lines through the 8-thread pool (%.3f s), "
+			"line time scaled to %d lines; best of %d; host has %d logical cores, cv2 threads %d" % (PAGE_W, PAGE_H,
 			tp, n_sample, len(lines), tl, len(lines), reps, os.cpu_count(), cv2.getNumThreads()),
 	}
 
@@ -190,14 +218,14 @@ def run_reference(args):
 	if rank != 0:
 		return
 	import cv2
+	if args.config == "segpost":
+		return run_reference_segpost(args)
 	page, grid, lines = make_inputs(args, 0)
 	gh, gw = grid.shape[:2]
 	mp = gh * CELL * gw * CELL / 1e6
-	# size the line sample so that warmup + steps stay within ~150 s
-	_, t_meas, t_page, t_lines = cpu_reference_step(page, grid, lines, 16, args.binarize)
-	per_line = t_lines / 16
-	budget = 150.0 / max(args.steps + args.warmup, 1)
-	n_sample = int(max(8, min(len(lines), (budget - t_page) / max(per_line, 1e-6))))
+	# every step runs the whole configuration (all lines of the page) unless --ref-sample asks for a
+	# bounded sample, whose line time is then scaled and the line says so
+	n_sample = len(lines) if args.ref_sample <= 0 else min(args.ref_sample, len(lines))
 	for _ in range(args.warmup):
 		cpu_reference_step(page, grid, lines, n_sample, args.binarize)
 	t0 = time.perf_counter()
@@ -208,14 +236,52 @@ def run_reference(args):
 	wall = time.perf_counter() - t0
 	value = mp * args.steps / total_est
 	cores = max(cv2.getNumThreads(), 8)
-	sample = ("each step: 1 page 4800x7200 expand+remap in full + %d of %d lines through the reference's 8-thread pool, "
-		"line time scaled to %d lines (measured wall %.1f s for %d steps)" % (n_sample, len(lines), len(lines), wall, args.steps))
+	extrapolated = n_sample < len(lines)
+	sample = ("each step: 1 page %dx%d expand+remap + %d of %d lines through the reference's 8-thread pool%s "
+		"(measured wall %.1f s for %d steps; host has %d logical cores, cv2 threads %d)" % (PAGE_W, PAGE_H, n_sample, len(lines),
+		", line time scaled to all lines" if extrapolated else "", wall, args.steps, os.cpu_count(), cv2.getNumThreads()))
 	print(json.dumps({
 		"impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus,
 		"steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * total_est / max(args.steps, 1),
 		"higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "u8", "data": "synthetic",
-		"config": workload_config(args),
+		"config": workload_config(args), "extrapolated": extrapolated,
 		"cpu_baseline": {"value": value, "unit": UNIT, "cores": cores, "kind": "port", "sample": sample},
+		"e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+		"gpu_launches": 0,
+	}))
+
+
+def segpost_inputs(seed):
+	from origami_b200 import synth
+	probs = synth.make_probabilities(5, 1280, 2400, 4, seed=seed)
+	page = synth.make_page(PAGE_W, PAGE_H, seed=seed, kind="text", dpi=600)
+	return probs, page
+
+
+def cpu_segpost_step(probs, page):
+	"""predict.py:281-285 + contours.py:488 + page.py:101-104 on the host (NumPy; skimage's Sauvola restated)."""
+	from oracle import exact
+	t0 = time.perf_counter()
+	labels = np.argmax(np.sum([p[None] for p in probs], axis=0).squeeze(), axis=-1).astype(np.uint8)
+	masks = [labels == c for c in (1, 2, 3)]
+	exact.binarize(page, ("sauvola", 15))
+	return time.perf_counter() - t0, masks
+
+
+def run_reference_segpost(args):
+	probs, page = segpost_inputs(0)
+	mp = (probs.shape[1] * probs.shape[2] + page.size) / 1e6
+	for _ in range(args.warmup):
+		cpu_segpost_step(probs, page)
+	total = sum(cpu_segpost_step(probs, page)[0] for _ in range(args.steps))
+	value = mp * args.steps / total
+	sample = "each step: argmax of (5, 2400, 1280, 4) + 3 masks + Sauvola-15 of a %dx%d page in NumPy, single thread" % (PAGE_W, PAGE_H)
+	print(json.dumps({
+		"impl": "reference", "metric": "megapixels/sec segmentation post-process", "value": value, "unit": UNIT, "n_gpus": args.gpus,
+		"steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * total / max(args.steps, 1),
+		"higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "u8", "data": "synthetic",
+		"config": workload_config(args), "extrapolated": False,
+		"cpu_baseline": {"value": value, "unit": UNIT, "cores": 1, "kind": "port", "sample": sample},
 		"e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
 		"gpu_launches": 0,
 	}))
@@ -256,8 +322,8 @@ KERNELS = ["og_page_kernel", "og_line_plan_kernel", "og_strips_kernels"]
 
 
 def run_step(ps, args, events=None):
-	"""One page through the path: 4 C-ABI calls = 5 kernel launches (page, steps, scan, lines, otsu);
-	4 without binarization."""
+	"""One page through the path: 3 C-ABI calls = 4 kernel launches (page, line plan, strips, strip
+	binarizer); 3 without binarization."""
 	import torch
 	from origami_b200 import _lib, ops
 	st = torch.cuda.current_stream().cuda_stream
@@ -358,8 +424,9 @@ def run_ours(args):
 	torch.cuda.set_device(local_rank)
 	device = torch.device("cuda", local_rank)
 
-	# every rank owns the pages rank, rank+N, ... of a conceptually endless page stream
-	inputs = [make_inputs(args, rank + k * world) for k in range(args.page_sets)]
+	# configs[2]: the job is args.pages page indices; rank r owns r, r+N, ... (no collective)
+	page_ids = shard.pages_of_rank(args.pages, rank, world) or [rank]
+	inputs = [make_inputs(args, page_ids[k % len(page_ids)]) for k in range(args.page_sets)]
 	sets = [PageSet(args, p, g, l, device) for (p, g, l) in inputs]
 	ps0 = sets[0]
 	mp_page = ps0.Hd * ps0.Wd / 1e6
@@ -458,8 +525,10 @@ def run_ours(args):
 			"metric": METRIC, "value": world * mp_page * args.steps / (ms * 1e-3), "unit": UNIT, "n_gpus": world,
 			"steps": args.steps, "warmup": max(args.warmup, 3), "ms_per_step": ms / args.steps,
 			"higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "u8", "data": "synthetic",
-			"config": workload_config(args, {"strip_pixels_per_page": strip_px,
-				"strip_megapixels_per_s": world * strip_px * args.steps / (ms * 1e-3) / 1e6}),
+			"config": workload_config(args),
+			"strip_pixels_per_page": strip_px, "strip_megapixels_per_s": world * strip_px * args.steps / (ms * 1e-3) / 1e6,
+			"page_indices": {"job": args.pages, "this_rank": page_ids[:8], "note": "rank r of N takes pages r, r+N, ... (shard.pages_of_rank); "
+				"step i works on page index this_rank[i %% len]; %d distinct pages are resident per rank" % args.page_sets},
 			"clocks": clocks, "e2e": e2e, "gpu_launches": n_launch,
 			"roofline": roof, "roofline_kernels": rl_all, "cpu_baseline": cpu, "impl": "ours",
 		}
@@ -467,10 +536,137 @@ def run_ours(args):
 	shard.finalize()
 
 
+def run_ours_segpost(args):
+	"""configs[4]: label argmax + class masks + page Sauvola, device-resident inputs rotated over 3 sets."""
+	import torch
+	from origami_b200 import _lib, ops, shard
+	if not torch.cuda.is_available():
+		raise SystemExit("bench.py needs a CUDA device: the CUDA path has no CPU fallback")
+	_lib.load()
+	rank, local_rank, world = shard.init()
+	torch.cuda.set_device(local_rank)
+	device = torch.device("cuda", local_rank)
+	page_ids = shard.pages_of_rank(args.pages, rank, world) or [rank]
+	host = [segpost_inputs(page_ids[k % len(page_ids)]) for k in range(args.page_sets)]
+	sets = []
+	for probs, page in host:
+		pr = torch.from_numpy(probs).to(device)
+		src = ops.to_device_image(page, device)
+		sets.append((pr, src, torch.empty((2400, 1280), dtype=torch.uint8, device=device),
+			torch.empty((3, 2400, 1280), dtype=torch.uint8, device=device), ops.alloc_image(PAGE_H, PAGE_W, device)))
+	mv = np.array([1, 2, 3], dtype=np.uint8)
+	st = torch.cuda.current_stream().cuda_stream
+
+	def step(k, events=None):
+		pr, src, labels, masks, dst = sets[k % len(sets)]
+		if events is not None:
+			e = torch.cuda.Event(enable_timing=True); e.record(); events.append(("start", e))
+		_lib.call("og_argmax_labels", pr.data_ptr(), 5, 4, 2400, 1280, labels.data_ptr(), masks.data_ptr(), mv.ctypes.data, 3, st)
+		if events is not None:
+			e = torch.cuda.Event(enable_timing=True); e.record(); events.append(("og_argmax4_kernel", e))
+		_lib.call("og_sauvola", src.data_ptr(), PAGE_H, PAGE_W, src.stride(0), 15, 0.2, 127.5, dst.data_ptr(), dst.stride(0), st)
+		if events is not None:
+			e = torch.cuda.Event(enable_timing=True); e.record(); events.append(("og_sauvola_page_kernel", e))
+		return 2
+
+	for i in range(max(args.warmup, 3)):
+		step(i)
+	torch.cuda.synchronize()
+	sampler = ClockSampler(local_rank) if rank == 0 else None
+	events = []
+	shard.barrier()
+	torch.cuda.synchronize()
+	if sampler:
+		sampler.start()
+	start, end = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+	start.record()
+	n_launch = 0
+	for i in range(args.steps):
+		n_launch += step(i, events)
+	end.record()
+	torch.cuda.synchronize()
+	ms_timed = start.elapsed_time(end)
+	if sampler and ms_timed < 250.0:
+		t_end = time.perf_counter() + (250.0 - ms_timed) * 1e-3
+		i = 0
+		while time.perf_counter() < t_end:
+			for _ in range(8):
+				step(i)
+				i += 1
+			torch.cuda.synchronize()
+	clocks = sampler.stop() if sampler else None
+	shard.barrier()
+	ms = shard.max_over_ranks(ms_timed, device)
+	per_kernel = {}
+	for (k0, e0), (k1, e1) in zip(events[:-1], events[1:]):
+		if k1 != "start":
+			per_kernel.setdefault(k1, []).append(e0.elapsed_time(e1))
+	kernel_ms = dict((k, float(np.mean(v))) for k, v in per_kernel.items())
+	mp = (2400 * 1280 + PAGE_W * PAGE_H) / 1e6
+
+	# end to end: host arrays in (pinned), labels + masks + binarized page back on the host
+	e2e = None
+	if not args.no_e2e:
+		pin = [(torch.from_numpy(p).pin_memory(), torch.from_numpy(g).pin_memory()) for p, g in host]
+		out_l = torch.empty((2400, 1280), dtype=torch.uint8).pin_memory()
+		out_m = torch.empty((3, 2400, 1280), dtype=torch.uint8).pin_memory()
+		out_b = torch.empty((PAGE_H, PAGE_W), dtype=torch.uint8).pin_memory()
+
+		def one(k):
+			pr, src, labels, masks, dst = sets[k % len(sets)]
+			hp, hg = pin[k % len(pin)]
+			pr.copy_(hp, non_blocking=True)
+			src.copy_(hg, non_blocking=True)
+			step(k)
+			out_l.copy_(labels, non_blocking=True)
+			out_m.copy_(masks, non_blocking=True)
+			out_b.copy_(dst, non_blocking=True)
+			torch.cuda.current_stream().synchronize()
+			return int(out_l[0, 0]) + int(out_b[-1, -1])
+
+		for k in range(3):
+			one(k)
+		t0 = time.perf_counter()
+		n_e2e = 4 * args.e2e_steps
+		for k in range(n_e2e):
+			one(k)
+		s_e2e = shard.max_over_ranks((time.perf_counter() - t0) / n_e2e, device)
+		e2e = {"value": world * mp / s_e2e, "unit": UNIT, "ms_per_step": 1e3 * s_e2e,
+			"h2d_bytes_per_step": int(host[0][0].nbytes + host[0][1].nbytes), "d2h_bytes_per_step": int(4 * 2400 * 1280 + PAGE_W * PAGE_H),
+			"api": "pinned host arrays -> og_argmax_labels + og_sauvola -> pinned host arrays, one page at a time"}
+	cpu = None
+	if rank == 0 and world == 1 and not args.no_cpu_baseline:
+		t, _ = cpu_segpost_step(*host[0])
+		cpu = {"value": mp / t, "unit": UNIT, "cores": 1, "kind": "port",
+			"sample": "one page: NumPy argmax + masks + restated skimage Sauvola-15 (%.2f s)" % t}
+	if rank == 0:
+		peak, peak_src = measured_peak()
+		alg = {"og_argmax4_kernel": (4 * 5 * 4 + 1 + 3) * 2400 * 1280, "og_sauvola_page_kernel": 2 * PAGE_W * PAGE_H}
+		traffic = recorded_traffic()
+		rl_all = {}
+		for k, t in kernel_ms.items():
+			a = alg[k] / (t * 1e-3) / 1e9
+			rl_all[k] = {"ms": t, "algorithmic_bytes": int(alg[k]), "achieved": a, "frac": a / peak,
+				"share_of_step": t / max(sum(kernel_ms.values()), 1e-9), "traffic": traffic.get(k)}
+		dom = max(kernel_ms, key=kernel_ms.get)
+		roof = {"bound": "hbm", "kernel": dom, "achieved": rl_all[dom]["achieved"], "peak": peak, "unit": "GB/s",
+			"frac": rl_all[dom]["frac"], "traffic": traffic.get(dom), "peak_source": peak_src,
+			"algorithmic_bytes": rl_all[dom]["algorithmic_bytes"], "ms": rl_all[dom]["ms"], "share_of_step": rl_all[dom]["share_of_step"]}
+		print(json.dumps({
+			"metric": "megapixels/sec segmentation post-process", "value": world * mp * args.steps / (ms * 1e-3), "unit": UNIT,
+			"n_gpus": world, "steps": args.steps, "warmup": max(args.warmup, 3), "ms_per_step": ms / args.steps,
+			"higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "u8 / f32", "data": "synthetic",
+			"config": workload_config(args), "clocks": clocks, "e2e": e2e, "gpu_launches": n_launch,
+			"roofline": roof, "roofline_kernels": rl_all, "cpu_baseline": cpu, "impl": "ours"}))
+	shard.finalize()
+
+
 def main():
-	args = parse_args()
+	args = apply_config(parse_args())
 	if args.impl == "reference":
 		run_reference(args)
+	elif args.config == "segpost":
+		run_ours_segpost(args)
 	else:
 		run_ours(args)
 

@@ -214,12 +214,64 @@ def inverse_yx(dense, pts_yx):
 # A7 / A8  Line._position, Line.warped_grid     origami/core/block.py:195-248
 # --------------------------------------------------------------------------------------
 
+def _segment_intersection_dd(p1, p2, q1, q2):
+	"""Intersection point of segments p1-p2 and q1-q2, or None when they do not meet in exactly one
+	point -- the logic of GEOS's LineIntersector as shapely's `a.intersection(b)` reaches it
+	(geos/algorithm/LineIntersector.cpp computeIntersect + CGAlgorithmsDD::intersection):
+	orientation tests, an endpoint that lies on the other segment is returned with its own
+	coordinates, a proper crossing is evaluated in homogeneous (determinant) form in extended
+	precision and rounded to double.  GEOS uses double-double (~106 bits); decimal arithmetic with
+	60 digits stands in for it here."""
+	import decimal
+	ctx = decimal.Context(prec=60)
+	D = lambda v: decimal.Decimal(float(v))  # exact conversion of a double
+
+	def orient(a, b, c):
+		v = ctx.subtract(ctx.multiply(ctx.subtract(D(b[0]), D(a[0])), ctx.subtract(D(c[1]), D(a[1]))),
+			ctx.multiply(ctx.subtract(D(b[1]), D(a[1])), ctx.subtract(D(c[0]), D(a[0]))))
+		return (v > 0) - (v < 0)
+
+	def env_overlap():
+		return (max(min(p1[0], p2[0]), min(q1[0], q2[0])) <= min(max(p1[0], p2[0]), max(q1[0], q2[0]))
+			and max(min(p1[1], p2[1]), min(q1[1], q2[1])) <= min(max(p1[1], p2[1]), max(q1[1], q2[1])))
+
+	if not env_overlap():
+		return None
+	Pq1, Pq2 = orient(p1, p2, q1), orient(p1, p2, q2)
+	if (Pq1 > 0 and Pq2 > 0) or (Pq1 < 0 and Pq2 < 0):
+		return None
+	Qp1, Qp2 = orient(q1, q2, p1), orient(q1, q2, p2)
+	if (Qp1 > 0 and Qp2 > 0) or (Qp1 < 0 and Qp2 < 0):
+		return None
+	if Pq1 == 0 and Pq2 == 0 and Qp1 == 0 and Qp2 == 0:
+		return None  # collinear: a segment or nothing, not a Point (a single shared end point is not a case here)
+	if Pq1 == 0 or Pq2 == 0 or Qp1 == 0 or Qp2 == 0:
+		if Pq1 == 0:
+			return np.array(q1, dtype=F64)
+		if Pq2 == 0:
+			return np.array(q2, dtype=F64)
+		if Qp1 == 0:
+			return np.array(p1, dtype=F64)
+		return np.array(p2, dtype=F64)
+	px = ctx.subtract(D(p1[1]), D(p2[1]))
+	py = ctx.subtract(D(p2[0]), D(p1[0]))
+	pw = ctx.subtract(ctx.multiply(D(p1[0]), D(p2[1])), ctx.multiply(D(p2[0]), D(p1[1])))
+	qx = ctx.subtract(D(q1[1]), D(q2[1]))
+	qy = ctx.subtract(D(q2[0]), D(q1[0]))
+	qw = ctx.subtract(ctx.multiply(D(q1[0]), D(q2[1])), ctx.multiply(D(q2[0]), D(q1[1])))
+	x = ctx.subtract(ctx.multiply(py, qw), ctx.multiply(qy, pw))
+	y = ctx.subtract(ctx.multiply(qx, pw), ctx.multiply(px, qw))
+	w = ctx.subtract(ctx.multiply(px, qy), ctx.multiply(qx, py))
+	return np.array([float(ctx.divide(x, w)), float(ctx.divide(y, w))], dtype=F64)
+
+
 def line_position(p, right, up, xres=1, column=None):
 	"""Line._position (origami/core/block.py:195-221) without shapely.
 
-	The reference intersects the baseline with the two vertical lines x = x0, x = x1 via
-	shapely (absent here: parity of the intersection point's last bits is unpinned).
-	Restated as the parametric intersection in float64; a miss keeps the endpoint, as
+	The reference intersects the baseline with the two vertical segments x = x0, x = x1 (from
+	py0 - 1 to py1 + 1) via shapely / GEOS, absent here: parity of the intersection point's last
+	bits is unpinned.  Restated with GEOS's own formulation (_segment_intersection_dd), which is
+	independent of the parametric form the product code uses; a miss keeps the endpoint, as
 	`intersect_segments(..., default=...)` does.
 	"""
 	p0 = np.asarray(p, dtype=F64)
@@ -228,6 +280,7 @@ def line_position(p, right, up, xres=1, column=None):
 	if column is not None:
 		p1 = p0 + right
 		px0, px1 = min(p0[0], p1[0]), max(p0[0], p1[0])
+		py0, py1 = min(p0[1], p1[1]), max(p0[1], p1[1])
 		x0, x1 = column
 		if x0 is None:
 			x0 = px0
@@ -235,13 +288,8 @@ def line_position(p, right, up, xres=1, column=None):
 			x1 = px1
 
 		def hit(xv, default):
-			dx = p1[0] - p0[0]
-			if dx == 0:
-				return default
-			t = (xv - p0[0]) / dx
-			if t < 0 or t > 1:
-				return default
-			return np.array([xv, p0[1] + t * (p1[1] - p0[1])], dtype=F64)
+			c = _segment_intersection_dd(p0, p1, (xv, py0 - 1), (xv, py1 + 1))
+			return default if c is None else c
 
 		q0 = hit(x0, p0)
 		q1 = hit(x1, p1)

@@ -12,6 +12,7 @@ extraction and optional strip binarization, with bit-identical results.
 
 import collections
 import collections.abc
+import weakref
 
 import numpy as np
 import torch
@@ -81,7 +82,9 @@ def pinned_page(pixels_or_shape):
 	a = t.numpy()
 	if src is not None:
 		a[...] = src
-	_PINNED[a.ctypes.data] = t
+	key = a.ctypes.data
+	_PINNED[key] = t
+	weakref.finalize(a, _PINNED.pop, key, None)  # the registry entry (and the pinned block) goes with the array
 	return a
 
 

@@ -73,15 +73,21 @@ class Block:
 def position(p, right, up, xres, column):
 	"""Line._position (block.py:195-221): clip the baseline to a table column [x0, x1].
 
-	The reference intersects shapely LineStrings; this is the same intersection of the
-	baseline with the vertical lines x = x0 and x = x1 in float64 (a miss keeps the end
-	point, as intersect_segments' default does)."""
+	The reference intersects shapely LineStrings: the baseline with the vertical segments
+	x = x0 and x = x1 (spanning the baseline's y range +- 1); GEOS evaluates a proper
+	intersection in double-double arithmetic and returns an endpoint's own coordinates when the
+	other segment passes through it.  Here the parameter of the hit and its ordinate are computed
+	in exact rational arithmetic and rounded once, which is the correctly rounded intersection
+	point and reproduces both cases (host-side scalar work: a handful of fractions per table cell).
+	A miss keeps the end point, as intersect_segments' default does."""
+	from fractions import Fraction
 	p0 = np.asarray(p, dtype=np.float64)
 	right = np.asarray(right, dtype=np.float64)
 	up = np.asarray(up, dtype=np.float64)
 	if column is not None:
 		p1 = p0 + right
 		px0, px1 = min(p0[0], p1[0]), max(p0[0], p1[0])
+		py0, py1 = min(p0[1], p1[1]), max(p0[1], p1[1])
 		x0, x1 = column
 		if x0 is None:
 			x0 = px0
@@ -89,13 +95,20 @@ def position(p, right, up, xres, column):
 			x1 = px1
 
 		def hit(xv, default):
-			dx = p1[0] - p0[0]
-			if dx == 0:
+			xv = float(xv)
+			if not (np.isfinite(xv) and np.isfinite(p0).all() and np.isfinite(p1).all()):
 				return default
-			t = (xv - p0[0]) / dx
+			ax, ay, bx, by = (Fraction(float(v)) for v in (p0[0], p0[1], p1[0], p1[1]))
+			dx = bx - ax
+			if dx == 0:
+				return default  # parallel (or a degenerate baseline): no single intersection point
+			t = (Fraction(xv) - ax) / dx
 			if t < 0 or t > 1:
 				return default
-			return np.array([xv, p0[1] + t * (p1[1] - p0[1])], dtype=np.float64)
+			y = ay + t * (by - ay)
+			if not (Fraction(float(py0 - 1)) <= y <= Fraction(float(py1 + 1))):
+				return default
+			return np.array([xv, float(y)], dtype=np.float64)
 
 		q0 = hit(x0, p0)
 		q1 = hit(x1, p1)
@@ -218,7 +231,14 @@ class Line:
 
 
 def affine_transform(src_tri, dst_tri):
-	"""cv2.getAffineTransform: the 6x6 system solved in float64 on fp32-rounded points."""
+	"""cv2.getAffineTransform (host-side scalars): OpenCV's own routine when it is installed (same
+	LU solve, same last bits as the reference), else the 6x6 system solved in float64 on
+	fp32-rounded points (equal to 1e-9)."""
+	try:
+		import cv2
+		return cv2.getAffineTransform(np.asarray(src_tri, dtype=np.float32), np.asarray(dst_tri, dtype=np.float32))
+	except ImportError:
+		pass
 	src = np.asarray(src_tri, dtype=np.float32).astype(np.float64)
 	dst = np.asarray(dst_tri, dtype=np.float32).astype(np.float64)
 	A = np.zeros((6, 6))

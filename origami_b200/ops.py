@@ -25,6 +25,23 @@ def _stream():
 	return torch.cuda.current_stream().cuda_stream
 
 
+def _call(name, anchor, *tensors_then_args):
+	"""Runs a library call on the device that owns `anchor` (a CUDA tensor): that device is made
+	current for the duration of the call and the work goes to ITS current stream -- the kernels
+	launch on whatever device is current, so a tensor on cuda:1 with cuda:0 current would otherwise
+	be handed to the wrong device.  `tensors_then_args` is (list of other tensors that must live on
+	the same device, builder) where builder(stream) returns the argument tuple."""
+	others, build = tensors_then_args
+	dev = anchor.device
+	for t in others:
+		if t is not None and t.device != dev:
+			raise ValueError("origami_b200: arguments live on different devices (%s and %s)" % (dev, t.device))
+	if dev.index is not None and dev.index != torch.cuda.current_device():
+		with torch.cuda.device(dev):
+			return _lib.call(name, *build(torch.cuda.current_stream(dev).cuda_stream))
+	return _lib.call(name, *build(torch.cuda.current_stream(dev).cuda_stream))
+
+
 def _ptr(t):
 	return 0 if t is None else t.data_ptr()
 
@@ -84,7 +101,7 @@ def to_device_image(a, device=None):
 	stage = pinned_staging(h * w)
 	parallel_copy(stage.numpy(), a.reshape(-1))  # host copy into page-locked memory (PIL arrays are read-only views)
 	out.copy_(stage.view(h, w), non_blocking=True)
-	torch.cuda.current_stream().synchronize()  # the staging buffer is reused by the next call
+	torch.cuda.current_stream(out.device).synchronize()  # the staging buffer is reused by the next call
 	return out
 
 
@@ -93,7 +110,7 @@ def to_host(t):
 	this is one DMA at PCIe speed instead of a staged pageable copy)."""
 	host = torch.empty(t.shape, dtype=t.dtype, pin_memory=True)
 	host.copy_(t, non_blocking=True)
-	torch.cuda.current_stream().synchronize()
+	torch.cuda.current_stream(t.device).synchronize()
 	return host.numpy()
 
 
@@ -109,7 +126,7 @@ def expand_map(grid, cell, out=None):
 	gh, gw = _check_grid(grid)
 	if out is None:
 		out = torch.empty((gh * cell, gw * cell, 2), dtype=torch.float32, device=grid.device)
-	_lib.call("og_expand_map", grid.data_ptr(), gh, gw, cell, out.data_ptr(), _stream())
+	_call("og_expand_map", grid, ([out], lambda st: (grid.data_ptr(), gh, gw, cell, out.data_ptr(), st)))
 	return out
 
 
@@ -126,10 +143,11 @@ def remap_page(src, grid, cell, dst=None, map_out=None, scale=(1.0, 1.0), interp
 		if dst is None:
 			dst = alloc_image(gh * cell, gw * cell, grid.device)
 		_check_u8_image(dst, "dst")
-	_lib.call("og_remap_page", _ptr(src) if want_image else 0, H, W, src.stride(0) if want_image else 0,
+	_call("og_remap_page", grid, ([src if want_image else None, dst if want_image else None, map_out], lambda st: (
+		_ptr(src) if want_image else 0, H, W, src.stride(0) if want_image else 0,
 		grid.data_ptr(), gh, gw, cell,
 		_ptr(dst) if want_image else 0, dst.stride(0) if want_image else 0, _ptr(map_out),
-		float(np.float32(scale[0])), float(np.float32(scale[1])), int(interpolation), _stream())
+		float(np.float32(scale[0])), float(np.float32(scale[1])), int(interpolation), st)))
 	return dst, map_out
 
 
@@ -141,7 +159,7 @@ def inverse_yx(grid, cell, pts_yx):
 	if pts.dtype != torch.float64 or pts.dim() != 2 or pts.shape[1] != 2:
 		raise ValueError("pts_yx must be float64 (n, 2)")
 	out = torch.empty_like(pts)
-	_lib.call("og_inverse_yx", grid.data_ptr(), gh, gw, cell, pts.data_ptr(), pts.shape[0], out.data_ptr(), _stream())
+	_call("og_inverse_yx", grid, ([pts], lambda st: (grid.data_ptr(), gh, gw, cell, pts.data_ptr(), pts.shape[0], out.data_ptr(), st)))
 	return out
 
 
@@ -208,8 +226,8 @@ def line_steps(grid, cell, lines_dev, n):
 	steps = torch.empty((max(n, 1), 2), dtype=torch.int32, device=dev)
 	pix = torch.empty((n + 1,), dtype=torch.int64, device=dev)
 	chunks = torch.empty((n + 2,), dtype=torch.int32, device=dev)  # n + 1 prefix sums + the work ticket
-	_lib.call("og_line_steps", grid.data_ptr(), gh, gw, cell, lines_dev.data_ptr(), n,
-		steps.data_ptr(), pix.data_ptr(), chunks.data_ptr(), _stream())
+	_call("og_line_steps", grid, ([lines_dev], lambda st: (grid.data_ptr(), gh, gw, cell, lines_dev.data_ptr(), n,
+		steps.data_ptr(), pix.data_ptr(), chunks.data_ptr(), st)))
 	return LinePlan(lines_dev, n, steps, pix, chunks)
 
 
@@ -225,9 +243,10 @@ def _check_map(dense_map, gh, gw, cell):
 def warped_grids(grid, cell, plan, out, dense_map=None):
 	"""Line.warped_grid for every line; out: float32 buffer of 2*capacity elements."""
 	gh, gw = _check_grid(grid)
-	_lib.call("og_warped_grids", grid.data_ptr(), gh, gw, cell, _check_map(dense_map, gh, gw, cell), plan.lines.data_ptr(), plan.n,
+	_call("og_warped_grids", grid, ([dense_map, plan.lines, plan.steps, out], lambda st: (
+		grid.data_ptr(), gh, gw, cell, _check_map(dense_map, gh, gw, cell), plan.lines.data_ptr(), plan.n,
 		plan.steps.data_ptr(), plan.pix_offsets.data_ptr(), plan.chunk_offsets.data_ptr(),
-		out.data_ptr(), out.numel() // 2, _stream())
+		out.data_ptr(), out.numel() // 2, st)))
 	return out
 
 
@@ -259,19 +278,21 @@ def extract_lines(src, grid, cell, plan, out, bbox=None, dense_map=None, binariz
 	if map_gather:
 		mode |= OG_FLAG_MAP_GATHER
 	cap = out.numel() if gray_out is None else min(out.numel(), gray_out.numel())
-	_lib.call("og_extract_lines", src.data_ptr(), int(src.shape[0]), int(src.shape[1]), src.stride(0),
+	_call("og_extract_lines", grid, ([src, dense_map, plan.lines, plan.steps, out, bbox, gray_out, thresholds], lambda st: (
+		src.data_ptr(), int(src.shape[0]), int(src.shape[1]), src.stride(0),
 		grid.data_ptr(), gh, gw, cell, _check_map(dense_map, gh, gw, cell), plan.lines.data_ptr(), plan.n,
 		plan.steps.data_ptr(), plan.pix_offsets.data_ptr(), plan.chunk_offsets.data_ptr(),
-		out.data_ptr(), cap, _ptr(bbox), mode, window, _ptr(gray_out), _ptr(thresholds), _stream())
+		out.data_ptr(), cap, _ptr(bbox), mode, window, _ptr(gray_out), _ptr(thresholds), st)))
 	return out
 
 
 def binarize_strips(gray, plan, mode, window=15, out=None, thresholds=None):
 	if out is None:
 		out = torch.empty_like(gray)
-	_lib.call("og_binarize_strips", gray.data_ptr(), plan.steps.data_ptr(), plan.pix_offsets.data_ptr(),
+	_call("og_binarize_strips", gray, ([plan.steps, out, thresholds], lambda st: (
+		gray.data_ptr(), plan.steps.data_ptr(), plan.pix_offsets.data_ptr(),
 		plan.chunk_offsets.data_ptr(), plan.n, int(mode), int(window), out.data_ptr(), min(gray.numel(), out.numel()),
-		_ptr(thresholds), _stream())
+		_ptr(thresholds), st)))
 	return out
 
 
@@ -282,8 +303,8 @@ def sauvola(src, window=15, k=0.2, r=127.5, dst=None):
 	h, w = int(src.shape[0]), int(src.shape[1])
 	if dst is None:
 		dst = alloc_image(h, w, src.device)
-	_lib.call("og_sauvola", src.data_ptr(), h, w, src.stride(0), int(window), float(k), float(r),
-		dst.data_ptr(), dst.stride(0), _stream())
+	_call("og_sauvola", src, ([dst], lambda st: (src.data_ptr(), h, w, src.stride(0), int(window), float(k), float(r),
+		dst.data_ptr(), dst.stride(0), st)))
 	return dst
 
 
@@ -298,8 +319,8 @@ def otsu(src, dst=None, hist_scratch=None, threshold=None):
 		hist_scratch = torch.empty((256,), dtype=torch.int32, device=src.device)
 	if threshold is None:
 		threshold = torch.empty((1,), dtype=torch.int32, device=src.device)
-	_lib.call("og_otsu", src.data_ptr(), h, w, src.stride(0), dst.data_ptr(), dst.stride(0),
-		hist_scratch.data_ptr(), threshold.data_ptr(), _stream())
+	_call("og_otsu", src, ([dst, hist_scratch, threshold], lambda st: (src.data_ptr(), h, w, src.stride(0), dst.data_ptr(), dst.stride(0),
+		hist_scratch.data_ptr(), threshold.data_ptr(), st)))
 	return dst, threshold
 
 
@@ -309,10 +330,11 @@ def sample_labels(labels, page_shape, grid, cell, plan, n_classes, dense_map=Non
 	_check_u8_image(labels, "labels")
 	counts = torch.empty((max(plan.n, 1), n_classes), dtype=torch.int64, device=grid.device)
 	overflow = torch.empty((max(plan.n, 1),), dtype=torch.int64, device=grid.device)
-	_lib.call("og_sample_labels", labels.data_ptr(), int(labels.shape[0]), int(labels.shape[1]), labels.stride(0),
+	_call("og_sample_labels", grid, ([labels, dense_map, plan.lines, plan.steps], lambda st: (
+		labels.data_ptr(), int(labels.shape[0]), int(labels.shape[1]), labels.stride(0),
 		int(page_shape[0]), int(page_shape[1]), grid.data_ptr(), gh, gw, cell, _check_map(dense_map, gh, gw, cell),
 		plan.lines.data_ptr(), plan.n,
-		plan.steps.data_ptr(), plan.chunk_offsets.data_ptr(), n_classes, counts.data_ptr(), overflow.data_ptr(), _stream())
+		plan.steps.data_ptr(), plan.chunk_offsets.data_ptr(), n_classes, counts.data_ptr(), overflow.data_ptr(), st)))
 	return counts[:plan.n], overflow[:plan.n]
 
 
@@ -330,8 +352,8 @@ def argmax_labels(probs, mask_values=None):
 		mv = np.ascontiguousarray(mask_values, dtype=np.uint8)
 		n_mask = int(mv.shape[0])
 		masks = torch.empty((n_mask, h, w), dtype=torch.uint8, device=probs.device)
-	_lib.call("og_argmax_labels", probs.data_ptr(), M, C, h, w, labels.data_ptr(), _ptr(masks),
-		mv.ctypes.data if mv is not None else 0, n_mask, _stream())
+	_call("og_argmax_labels", probs, ([], lambda st: (probs.data_ptr(), M, C, h, w, labels.data_ptr(), _ptr(masks),
+		mv.ctypes.data if mv is not None else 0, n_mask, st)))
 	return labels, masks
 
 
@@ -341,8 +363,8 @@ def class_masks(labels, mask_values):
 	mv = np.ascontiguousarray(mask_values, dtype=np.uint8)
 	h, w = int(labels.shape[0]), int(labels.shape[1])
 	masks = torch.empty((int(mv.shape[0]), h, w), dtype=torch.uint8, device=labels.device)
-	_lib.call("og_class_masks", labels.data_ptr(), h, w, labels.stride(0), masks.data_ptr(), mv.ctypes.data,
-		int(mv.shape[0]), _stream())
+	_call("og_class_masks", labels, ([], lambda st: (labels.data_ptr(), h, w, labels.stride(0), masks.data_ptr(), mv.ctypes.data,
+		int(mv.shape[0]), st)))
 	return masks
 
 
@@ -352,8 +374,8 @@ def warp_affine(src, M, width, height, border_value=0):
 	_check_u8_image(src, "src")
 	Mh = np.ascontiguousarray(M, dtype=np.float64).reshape(6)
 	dst = alloc_image(height, width, src.device)
-	_lib.call("og_warp_affine", src.data_ptr(), int(src.shape[0]), int(src.shape[1]), src.stride(0),
-		Mh.ctypes.data, dst.data_ptr(), width, height, dst.stride(0), int(border_value), _stream())
+	_call("og_warp_affine", src, ([], lambda st: (src.data_ptr(), int(src.shape[0]), int(src.shape[1]), src.stride(0),
+		Mh.ctypes.data, dst.data_ptr(), width, height, dst.stride(0), int(border_value), st)))
 	return dst
 
 
@@ -363,7 +385,7 @@ def label_mask_ne(labels, background):
 	_check_u8_image(labels, "labels")
 	h, w = int(labels.shape[0]), int(labels.shape[1])
 	out = alloc_image(h, w, labels.device)
-	_lib.call("og_label_mask_ne", labels.data_ptr(), h, w, labels.stride(0), int(background), out.data_ptr(), out.stride(0), _stream())
+	_call("og_label_mask_ne", labels, ([], lambda st: (labels.data_ptr(), h, w, labels.stride(0), int(background), out.data_ptr(), out.stride(0), st)))
 	return out
 
 
@@ -377,6 +399,6 @@ def or_dilate3(binary, mask=None):
 		if tuple(mask.shape) != (h, w):
 			raise ValueError("mask shape differs from the binary image")
 	out = torch.empty((h, w), dtype=torch.float32, device=binary.device)
-	_lib.call("og_or_dilate3", binary.data_ptr(), binary.stride(0), _ptr(mask), mask.stride(0) if mask is not None else 0,
-		h, w, out.data_ptr(), _stream())
+	_call("og_or_dilate3", binary, ([mask], lambda st: (binary.data_ptr(), binary.stride(0), _ptr(mask), mask.stride(0) if mask is not None else 0,
+		h, w, out.data_ptr(), st)))
 	return out

@@ -310,3 +310,27 @@ def test_page_pipeline_without_lines_and_without_dewarped_page(small):
 		assert (res.dewarped is None) == (not dewarped)
 		if dewarped:
 			assert np.array_equal(res.dewarped, exact.remap_linear(small.page, exact.expand_map(small.g, small.s)))
+
+
+def test_objects_on_a_second_device_while_the_first_is_current():
+	"""ops.* run on the device that owns their tensors, whatever device is current (needs 2 GPUs)."""
+	if torch.cuda.device_count() < 2:
+		pytest.skip("needs two GPUs")
+	W, H, s = 400, 300, 25
+	page = synth.make_page(W, H, seed=2, kind="noise")
+	g = synth.make_grid(W, H, s, seed=2)
+	dense = exact.expand_map(g, s)
+	torch.cuda.set_device(0)
+	grid = Grid(g, s, device="cuda:1")
+	pg = Page(page, grid)
+	assert np.array_equal(np.array(pg.dewarped), exact.remap_linear(page, dense))
+	assert np.array_equal(grid.points("full").view(np.uint32), dense.view(np.uint32))
+	lines = synth.make_lines(dense.shape[1], dense.shape[0], 12, seed=2, dpi=150)
+	block = Block(pg, None, Stage.RELIABLE)
+	for ln in lines[:4]:
+		im = Line(block, ln["p"], ln["right"], ln["up"]).image(48, binarizer=binarize.otsu())
+		want = exact.binarize(exact.dewarped_line_image(page, dense, ln["p"], ln["right"], ln["up"], 48), ("otsu",))
+		assert np.array_equal(np.array(im), want)
+	assert torch.cuda.current_device() == 0
+	with pytest.raises(ValueError):
+		ops.remap_page(ops.to_device_image(page, torch.device("cuda:0")), grid.device_grid, s)

@@ -48,19 +48,37 @@ def test_binarizer_spec_strings():
 		binarize.from_string("niblack(3)")
 
 
-def test_position_matches_oracle():
+def test_position_matches_the_independent_oracle():
+	"""Line._position: the product evaluates the hit parametrically in exact rational arithmetic,
+	the oracle with GEOS's orientation tests + determinant form in 60-digit decimals; they must agree
+	to the last bit, also when a column boundary passes through an end point of the baseline, misses
+	it, or the baseline runs right to left."""
 	rng = np.random.default_rng(0)
-	for _ in range(50):
+	cases = 0
+	for k in range(120):
 		p = rng.uniform(10, 500, 2)
 		right = np.array([rng.uniform(50, 400), rng.uniform(-3, 3)])
+		if k % 7 == 0:
+			right[0] = -right[0]  # right to left
+		if k % 11 == 0:
+			right[1] = 0.0
 		up = np.array([rng.uniform(-1, 1), -rng.uniform(10, 40)])
-		x0 = p[0] + rng.uniform(0.05, 0.45) * right[0]
-		x1 = p[0] + rng.uniform(0.55, 0.95) * right[0]
-		for col in (None, (None, x0), (x0, x1), (x1, None), (p[0] - 50, x1)):
+		lo, hi = sorted((p[0], p[0] + right[0]))
+		x0 = lo + rng.uniform(0.05, 0.45) * (hi - lo)
+		x1 = lo + rng.uniform(0.55, 0.95) * (hi - lo)
+		for col in (None, (None, x0), (x0, x1), (x1, None), (lo - 50, x1), (lo, hi), (x0, hi + 3), (float(np.float32(x0)), None)):
 			a = position(p, right, up, 1, col)
 			b = exact.line_position(p, right, up, 1, col)
 			for u, v in zip(a, b):
-				assert np.array_equal(np.asarray(u), np.asarray(v))
+				assert np.array_equal(np.asarray(u), np.asarray(v)), (k, col)
+			cases += 1
+	assert cases == 960
+	# a boundary through an end point returns that end point's own coordinates
+	p, right, up = np.array([10.25, 20.1]), np.array([100.3, 0.7]), np.array([0.0, -10.0])
+	q0, r, _, _ = position(p, right, up, 1, (None, 60.0))
+	assert np.array_equal(q0, p) and r[0] == 60.0 - p[0]
+	q0, r, _, _ = position(p, right, up, 1, (50.0, None))
+	assert np.array_equal(q0 + r, p + right) or abs((q0 + r - (p + right))[1]) < 1e-13
 
 
 def test_line_rewriter_splits_table_rows():

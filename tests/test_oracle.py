@@ -255,3 +255,24 @@ def test_dilate3_is_3x3_maximum_with_zero_border():
 	m = rng.random((23, 31)) < 0.05
 	want = cv2.dilate(m.astype(np.uint8), np.ones((3, 3), np.uint8), borderType=cv2.BORDER_CONSTANT, borderValue=0) > 0
 	assert np.array_equal(exact.dilate3(m), want)
+
+
+def test_otsu_agrees_with_opencv():
+	"""cv2.threshold(THRESH_OTSU) maximises the same between-class variance over the same 256 bins
+	(another code base, float arithmetic of its own): a transcription slip in exact.threshold_otsu
+	would show up here.  The two may differ only where the criterion is tied to within rounding."""
+	for seed in range(12):
+		img = synth.make_page(320, 200, seed=seed, kind="text" if seed % 2 else "noise", dpi=300)
+		if seed % 3 == 0:
+			img = (img // 3 + 40).astype(np.uint8)  # a narrow histogram
+		t_cv, _ = cv2.threshold(img, 0, 255, cv2.THRESH_BINARY + cv2.THRESH_OTSU)
+		t = exact.threshold_otsu(img)
+		if int(t_cv) != t:
+			hist = np.bincount(img.ravel(), minlength=256).astype(np.float64)
+
+			def crit(k):
+				w1, w2 = hist[:k + 1].sum(), hist[k + 1:].sum()
+				m1 = (hist[:k + 1] * np.arange(k + 1)).sum() / w1
+				m2 = (hist[k + 1:] * np.arange(k + 1, 256)).sum() / w2
+				return w1 * w2 * (m1 - m2) ** 2
+			assert abs(crit(int(t_cv)) - crit(t)) <= 1e-9 * crit(t), (seed, t_cv, t)

@@ -10,6 +10,7 @@ import numpy as np
 import pytest
 import torch
 
+from oracle import exact
 from origami_b200 import _lib, ops, synth
 
 pytestmark = pytest.mark.gpu
@@ -33,6 +34,8 @@ def test_noalloc_matches_og_otsu_on_two_calls_in_a_row(cuda):
 		got, got_t = _otsu_noalloc(src)
 		assert torch.equal(got, want)
 		assert int(got_t.item()) == int(want_t.item())
+		# and against the oracle itself, not only against the sibling entry point
+		assert np.array_equal(got.cpu().numpy(), exact.binarize(src.cpu().numpy(), ("otsu",)))
 
 
 def test_noalloc_rejects_images_beyond_its_limit(cuda):
