@@ -22,24 +22,7 @@ from ...core import binarize as _binarize
 
 PageResult = collections.namedtuple("PageResult", ["dewarped", "strips", "steps"])
 
-class StripList(collections.abc.Sequence):
-	"""The strips of one page as a read-only sequence of (ysteps, xsteps) uint8 views into the
-	packed result buffer; a view is only made when an item is accessed."""
-
-	def __init__(self, flat, offsets, steps):
-		self._flat, self._offs, self._steps = flat, offsets, steps
-
-	def __len__(self):
-		return int(self._steps.shape[0])
-
-	def __getitem__(self, i):
-		if isinstance(i, slice):
-			return [self[k] for k in range(*i.indices(len(self)))]
-		if i < 0:
-			i += len(self)
-		if not 0 <= i < len(self):
-			raise IndexError(i)
-		return self._flat[self._offs[i]:self._offs[i + 1]].reshape(self._steps[i, 1], self._steps[i, 0])
+from ...core.block import StripList  # noqa: E402  (re-exported: results of PagePipeline use it too)
 
 
 _parallel_copy = ops.parallel_copy

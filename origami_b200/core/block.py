@@ -8,6 +8,7 @@ warped_path (block.py:129-267).  Geometry that the reference delegates to shapel
 lines of a page go through ONE kernel launch instead of a Python thread pool.
 """
 
+import collections.abc
 import enum
 import math
 from functools import cached_property
@@ -257,15 +258,38 @@ def affine_transform(src_tri, dst_tri):
 # batched forms
 # ---------------------------------------------------------------------------------------
 
+class StripList(collections.abc.Sequence):
+	"""The strips of one page as a read-only sequence of (ysteps, xsteps) uint8 views into the
+	packed result buffer; a view is only made when an item is accessed."""
+
+	def __init__(self, flat, offsets, steps):
+		self._flat, self._offs, self._steps = flat, offsets, steps
+
+	def __len__(self):
+		return int(self._steps.shape[0])
+
+	def __iter__(self):
+		flat = self._flat
+		offs = self._offs.tolist()
+		for (w, h), a, b in zip(self._steps.tolist(), offs, offs[1:]):
+			yield flat[a:b].reshape(h, w)
+
+	def __getitem__(self, i):
+		if isinstance(i, slice):
+			return [self[k] for k in range(*i.indices(len(self)))]
+		if i < 0:
+			i += len(self)
+		if not 0 <= i < len(self):
+			raise IndexError(i)
+		return self._flat[self._offs[i]:self._offs[i + 1]].reshape(self._steps[i, 1], self._steps[i, 0])
+
+
 def _plan(grid, records):
 	la = records if isinstance(records, np.ndarray) else ops.pack_lines(records)
 	dev = grid._device
 	ld = ops.lines_to_device(la, dev) if len(records) else torch.zeros((8,), dtype=torch.uint8, device=dev)
 	plan = ops.line_steps(grid.device_grid, grid.resolution, ld, len(records))
-	host = torch.empty((len(records) + 1,), dtype=torch.int64, pin_memory=True)
-	host.copy_(plan.pix_offsets, non_blocking=True)
-	steps = ops.to_host(plan.steps)[:len(records)]
-	offs = host.numpy()
+	steps, offs = ops.plan_to_host(plan)  # one download for step counts and offsets
 	if len(records) and (steps <= 0).any():
 		bad = int(np.argmax((steps <= 0).any(axis=1)))
 		raise ValueError("line %d has a degenerate or non-finite extent" % bad)
@@ -276,7 +300,7 @@ def warped_grids(grid, records):
 	"""Line.warped_grid for a list of og_line records -> ([ (ysteps, xsteps, 2) fp32 ], steps)."""
 	plan, steps, offs = _plan(grid, records)
 	out = torch.empty((max(int(offs[-1]), 1) * 2,), dtype=torch.float32, device=grid._device)
-	ops.warped_grids(grid.device_grid, grid.resolution, plan, out)
+	ops.warped_grids(grid.device_grid, grid.resolution, plan, out, dense_map=grid._device_points)
 	flat = ops.to_host(out)
 	res = [flat[2 * offs[i]:2 * offs[i + 1]].reshape(steps[i][1], steps[i][0], 2) for i in range(len(records))]
 	return res, steps
@@ -285,7 +309,9 @@ def warped_grids(grid, records):
 def extract_strips(dewarper, records, binarize=None, want_bbox=False):
 	"""Line.image(dewarped=True) for a list of records in one launch.
 
-	binarize: None | ("otsu",) | ("sauvola", window).  Returns ([ (ysteps, xsteps) uint8 ], bbox | None).
+	binarize: None | ("otsu",) | ("sauvola", window).  Returns (sequence of (ysteps, xsteps) uint8
+	arrays -- views into one result buffer --, bbox | None).  When the page's dense map is on the
+	device (Dewarper.dewarped left it there) the samples gather from it.
 	"""
 	grid = dewarper.grid
 	plan, steps, offs = _plan(grid, records)
@@ -293,8 +319,8 @@ def extract_strips(dewarper, records, binarize=None, want_bbox=False):
 	total = max(int(offs[-1]), 1)
 	gray = torch.empty((total,), dtype=torch.uint8, device=dev)
 	bbox = torch.empty((max(len(records), 1), 4), dtype=torch.int32, device=dev) if want_bbox else None
-	ops.extract_lines(dewarper.device_image, grid.device_grid, grid.resolution, plan, gray, bbox, binarize=binarize)
+	ops.extract_lines(dewarper.device_image, grid.device_grid, grid.resolution, plan, gray, bbox, binarize=binarize,
+		dense_map=grid._device_points)
 	bb = ops.to_host(bbox)[:len(records)] if want_bbox else None
 	flat = ops.to_host(gray)
-	strips = [flat[offs[i]:offs[i + 1]].reshape(steps[i][1], steps[i][0]) for i in range(len(records))]
-	return strips, bb
+	return StripList(flat, offs, steps), bb

@@ -47,6 +47,7 @@ class Grid:
 		self._grid_res = int(res)
 		self._device_arg = device
 		self._points_cache = dict()
+		self._device_points = None
 
 	@cached_property
 	def _device(self):
@@ -98,8 +99,15 @@ class Grid:
 
 	# -- A2
 	def device_points(self):
-		"""Dense map as a CUDA tensor (Hd, Wd, 2) fp32 (not cached)."""
-		return ops.expand_map(self.device_grid, self._grid_res)
+		"""Dense map as a CUDA tensor (Hd, Wd, 2) fp32.  Kept on the device once computed -- the
+		reference keeps its host copy the same way (lru_cache on Grid.points, dewarp.py:514) -- because
+		every line of the page interpolates in it; release_device_points() drops it."""
+		if self._device_points is None:
+			self._device_points = ops.expand_map(self.device_grid, self._grid_res)
+		return self._device_points
+
+	def release_device_points(self):
+		self._device_points = None
 
 	def points(self, resolution="full", interpolation=INTER_LINEAR):
 		if resolution == "sample":
@@ -140,6 +148,7 @@ class Dewarper:
 		self._im = im
 		self._grid = grid
 		self._pixels = pixels  # optional ndarray view of `im` (saves a PIL -> bytes round trip)
+		self._pending = None
 
 	@property
 	def grid(self):
@@ -152,12 +161,31 @@ class Dewarper:
 		return ops.to_device_image(pixels, self._grid._device)
 
 	def device_dewarped(self, map_out=None):
-		dst, _ = ops.remap_page(self.device_image, self._grid.device_grid, self._grid.resolution, map_out=map_out)
+		"""The dewarped page on the device.  The fused kernel also emits the grid's dense map when the
+		grid does not hold it yet (one launch for both), so that the line kernels of the same page can
+		gather from it."""
+		grid = self._grid
+		if map_out is None and grid._device_points is None:
+			gh, gw = grid.shape[:2]
+			map_out = torch.empty((gh * grid.resolution, gw * grid.resolution, 2), dtype=torch.float32, device=grid._device)
+			dst, _ = ops.remap_page(self.device_image, grid.device_grid, grid.resolution, map_out=map_out)
+			grid._device_points = map_out
+			return dst
+		dst, _ = ops.remap_page(self.device_image, grid.device_grid, grid.resolution, map_out=map_out)
 		return dst
+
+	def start_dewarped(self):
+		"""Launches the remap and the download of the dewarped page without waiting for either; the
+		`dewarped` property collects it.  Page.__init__ calls this, so the copy runs beside whatever
+		the caller does next (the line kernels of the same page, typically)."""
+		if self._pending is None and "dewarped" not in self.__dict__:
+			self._pending = ops.HostCopy(self.device_dewarped())
 
 	@cached_property
 	def dewarped(self):
-		return PIL.Image.fromarray(ops.to_host(self.device_dewarped()))
+		self.start_dewarped()
+		pending, self._pending = self._pending, None
+		return PIL.Image.fromarray(pending.result())
 
 	def dewarp_image(self, im, interpolation=INTER_LINEAR):
 		w0, h0 = self._im.size

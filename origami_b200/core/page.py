@@ -38,11 +38,12 @@ class Page:
 			self._warped = PIL.Image.open(str(_find_image_path(path))).convert("L")
 
 		if dewarping_transform is not None:
+			# the reference dewarps eagerly here (page.py:86-88); so does this, but without waiting: the
+			# kernel and the download are queued, `dewarped` collects the image when somebody asks for it
 			self._dewarper = Dewarper(self._warped, dewarping_transform, pixels=pixels)
-			self._dewarped = self._dewarper.dewarped
+			self._dewarper.start_dewarped()
 		else:
 			self._dewarper = None
-			self._dewarped = None
 
 	@property
 	def warped(self):
@@ -50,7 +51,11 @@ class Page:
 
 	@property
 	def dewarped(self):
-		return self._dewarped
+		return self._dewarper.dewarped if self._dewarper is not None else None
+
+	@property
+	def _dewarped(self):
+		return self.dewarped
 
 	@cached_property
 	def binarized(self):

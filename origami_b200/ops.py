@@ -25,13 +25,13 @@ def _stream():
 	return torch.cuda.current_stream().cuda_stream
 
 
-def _call(name, anchor, *tensors_then_args):
+def _call(name, anchor, spec):
 	"""Runs a library call on the device that owns `anchor` (a CUDA tensor): that device is made
 	current for the duration of the call and the work goes to ITS current stream -- the kernels
 	launch on whatever device is current, so a tensor on cuda:1 with cuda:0 current would otherwise
-	be handed to the wrong device.  `tensors_then_args` is (list of other tensors that must live on
-	the same device, builder) where builder(stream) returns the argument tuple."""
-	others, build = tensors_then_args
+	be handed to the wrong device.  `spec` is (list of other tensors that must live on the same
+	device, builder) where builder(stream) returns the argument tuple."""
+	others, build = spec
 	dev = anchor.device
 	for t in others:
 		if t is not None and t.device != dev:
@@ -81,7 +81,7 @@ def parallel_copy(dst, src):
 	GIL while copying; one thread reaches only a fraction of the host memory bandwidth)."""
 	global _COPY_POOL
 	n = src.shape[0]
-	if n < (4 << 20):
+	if n < (2 << 20):
 		dst[:n] = src
 		return
 	if _COPY_POOL is None:
@@ -93,16 +93,61 @@ def parallel_copy(dst, src):
 		f.result()
 
 
+_STAGE_CHUNKS = 4
+
+
 def to_device_image(a, device=None):
-	"""Host uint8 (h, w) ndarray -> pitched device image (through pinned staging memory)."""
+	"""Host uint8 (h, w) ndarray -> pitched device image through pinned staging memory.  The page is
+	cut into a few row bands: while band k travels to the device, band k+1 is copied into the pinned
+	buffer by the host threads, so the upload costs about the slower of the two instead of their sum."""
 	a = np.ascontiguousarray(a, dtype=np.uint8)
 	h, w = a.shape
 	out = alloc_image(h, w, device)
 	stage = pinned_staging(h * w)
-	parallel_copy(stage.numpy(), a.reshape(-1))  # host copy into page-locked memory (PIL arrays are read-only views)
-	out.copy_(stage.view(h, w), non_blocking=True)
-	torch.cuda.current_stream(out.device).synchronize()  # the staging buffer is reused by the next call
+	stage_np = stage.numpy()
+	flat = a.reshape(-1)
+	stream = torch.cuda.current_stream(out.device)
+	rows = max(1, (h + _STAGE_CHUNKS - 1) // _STAGE_CHUNKS) if h * w >= (8 << 20) else h
+	with torch.cuda.device(out.device):
+		for r0 in range(0, h, rows):
+			r1 = min(h, r0 + rows)
+			parallel_copy(stage_np[r0 * w:r1 * w], flat[r0 * w:r1 * w])  # PIL arrays are read-only views: copy, never pin in place
+			out[r0:r1].copy_(stage[r0 * w:r1 * w].view(r1 - r0, w), non_blocking=True)
+	stream.synchronize()  # the staging buffer is reused by the next call
 	return out
+
+
+class HostCopy:
+	"""A device->host copy in flight on a side stream: result() waits for it and returns the ndarray."""
+
+	def __init__(self, t):
+		dev = t.device
+		self._host = torch.empty(t.shape, dtype=t.dtype, pin_memory=True)
+		side = _side_stream(dev)
+		side.wait_stream(torch.cuda.current_stream(dev))
+		with torch.cuda.stream(side):
+			self._host.copy_(t, non_blocking=True)
+			self._done = torch.cuda.Event()
+			self._done.record(side)
+		t.record_stream(side)
+		self._array = None
+
+	def result(self):
+		if self._array is None:
+			self._done.synchronize()
+			self._array = self._host.numpy()
+		return self._array
+
+
+_SIDE = {}
+
+
+def _side_stream(dev):
+	key = (dev.type, dev.index if dev.index is not None else torch.cuda.current_device())
+	st = _SIDE.get(key)
+	if st is None:
+		st = _SIDE[key] = torch.cuda.Stream(device=dev)
+	return st
 
 
 def to_host(t):
@@ -219,16 +264,34 @@ class LinePlan:
 
 
 def line_steps(grid, cell, lines_dev, n):
-	"""Step counts of Line.warped_grid (reference origami/core/block.py:226-236) + offsets."""
+	"""Step counts of Line.warped_grid (reference origami/core/block.py:226-236) + offsets.  The three
+	device arrays of the plan live in one buffer ([pix offsets | steps | chunk offsets]), so that the
+	host can fetch offsets and steps with a single copy (plan_to_host)."""
 	_require_cuda()
 	gh, gw = _check_grid(grid)
 	dev = grid.device
-	steps = torch.empty((max(n, 1), 2), dtype=torch.int32, device=dev)
-	pix = torch.empty((n + 1,), dtype=torch.int64, device=dev)
-	chunks = torch.empty((n + 2,), dtype=torch.int32, device=dev)  # n + 1 prefix sums + the work ticket
+	o_steps = 8 * (n + 1)
+	o_chunks = o_steps + 8 * max(n, 1)
+	buf = torch.empty((o_chunks + 4 * (n + 2),), dtype=torch.uint8, device=dev)
+	pix = buf[:o_steps].view(torch.int64)
+	steps = buf[o_steps:o_chunks].view(torch.int32).view(max(n, 1), 2)
+	chunks = buf[o_chunks:].view(torch.int32)  # n + 1 prefix sums + the work ticket
 	_call("og_line_steps", grid, ([lines_dev], lambda st: (grid.data_ptr(), gh, gw, cell, lines_dev.data_ptr(), n,
 		steps.data_ptr(), pix.data_ptr(), chunks.data_ptr(), st)))
-	return LinePlan(lines_dev, n, steps, pix, chunks)
+	plan = LinePlan(lines_dev, n, steps, pix, chunks)
+	plan.buf = buf
+	return plan
+
+
+def plan_to_host(plan):
+	"""(steps (n, 2) int32, pix_offsets (n + 1) int64) of a plan made by line_steps: one device->host copy."""
+	n = plan.n
+	nbytes = 8 * (n + 1) + 8 * max(n, 1)
+	host = torch.empty((nbytes,), dtype=torch.uint8, pin_memory=True)
+	host.copy_(plan.buf[:nbytes], non_blocking=True)
+	torch.cuda.current_stream(plan.buf.device).synchronize()
+	a = host.numpy()
+	return a[8 * (n + 1):].view(np.int32).reshape(max(n, 1), 2)[:n], a[:8 * (n + 1)].view(np.int64)
 
 
 def _check_map(dense_map, gh, gw, cell):
