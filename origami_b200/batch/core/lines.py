@@ -31,6 +31,8 @@ class LineRewriter:
 		return predictor, label, grid, str(0)
 
 	def __call__(self, lines):
+		if not self._columns:  # a page without tables: nothing to split
+			return [(path, line, None) for path, line in lines.items()]
 		line_parts = []
 		for path, line in lines.items():
 			line_columns = self._columns.get(path[:3])
@@ -63,16 +65,16 @@ class LineExtractor:
 				(k, v) for k, v in lines.items()
 				if not ignored(tuple(k[:2])))
 
-		filtered_lines = []
+		min_confidence = self._min_confidence
+		filtered_lines = dict()
 		for path, line in lines.items():
-			if line.confidence < self._min_confidence:
+			if line._confidence < min_confidence:
 				logging.info("skipping line %s with confidence %.1f" % (
 					str(path), line.confidence))
-				continue
 			else:
-				filtered_lines.append((path, line))
+				filtered_lines[path] = line
 
-		return self._rewriter(dict(filtered_lines))
+		return self._rewriter(filtered_lines)
 
 	def extract_arrays(self, lines, ignored=None):
 		"""[(line_path, uint8 ndarray)] -- the batched fast path."""

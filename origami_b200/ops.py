@@ -4,6 +4,8 @@ Thin torch-tensor front end of the C ABI: allocates outputs with torch, passes
 device memory and streams only; every computation happens in the hand-written kernels.
 """
 
+import os
+
 import numpy as np
 import torch
 
@@ -74,6 +76,7 @@ def pinned_staging(nbytes):
 
 
 _COPY_POOL = None
+_COPY_THREADS = max(2, min(8, (os.cpu_count() or 4) // 2))
 
 
 def parallel_copy(dst, src):
@@ -86,8 +89,8 @@ def parallel_copy(dst, src):
 		return
 	if _COPY_POOL is None:
 		import concurrent.futures
-		_COPY_POOL = concurrent.futures.ThreadPoolExecutor(max_workers=4)
-	step = (n + 3) // 4
+		_COPY_POOL = concurrent.futures.ThreadPoolExecutor(max_workers=_COPY_THREADS)
+	step = (n + _COPY_THREADS - 1) // _COPY_THREADS
 	futs = [_COPY_POOL.submit(np.copyto, dst[i:min(n, i + step)], src[i:min(n, i + step)]) for i in range(0, n, step)]
 	for f in futs:
 		f.result()
