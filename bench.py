@@ -395,7 +395,7 @@ def run_e2e(args, inputs, device, n_steps):
 	return dt / n_steps, h2d, d2h
 
 
-def run_e2e_pipeline(args, inputs, device, n_steps, dewarped=True):
+def run_e2e_pipeline(args, inputs, device, n_steps, dewarped=True, hand_off="host"):
 	"""End to end through the multi-page public API (origami_b200.batch.core.pipeline.PagePipeline):
 	host arrays in, host arrays out; pinned H2D / D2H copies of every page are inside the timed
 	region and overlap with the kernels of the neighbouring pages."""
@@ -407,7 +407,19 @@ def run_e2e_pipeline(args, inputs, device, n_steps, dewarped=True):
 		jobs.append((pinned_page(page), grid_hv, CELL, arr))  # inputs wait in pinned host memory
 	depth = 3
 	pipe = PagePipeline(line_height=LINE_HEIGHT, binarize="" if args.binarize == "none" else args.binarize, depth=depth,
-		dewarped=dewarped)
+		dewarped=dewarped, hand_off=hand_off)
+	if hand_off == "device":
+		for res in pipe.run(jobs[i % len(jobs)] for i in range(depth * len(jobs))):
+			pass
+		torch.cuda.synchronize()
+		t0 = time.perf_counter()
+		total = 0
+		for res in pipe.run(jobs[i % len(jobs)] for i in range(n_steps)):
+			total += int(res.strips.widths.sum())  # widths and indices are read on the host, the batch stays on the device
+		torch.cuda.synchronize()
+		dt = time.perf_counter() - t0
+		h2d, d2h = pipe.bytes_per_page
+		return dt / n_steps, h2d, d2h
 	checksum = 0
 	for res in pipe.run(jobs[i % len(jobs)] for i in range(depth * len(jobs))):  # warm-up: every slot sees every page
 		checksum += int(res.dewarped[0, 0]) if dewarped else len(res.strips)
@@ -504,6 +516,12 @@ def run_ours(args):
 		e2e["strips_only"] = {"pages_per_s": world / s_ocr, "ms_per_step": 1e3 * s_ocr,
 			"h2d_bytes_per_step": int(h2d_o), "d2h_bytes_per_step": int(d2h_o),
 			"api": "PagePipeline(..., dewarped=False): dense map + strips, what origami.batch.detect.ocr consumes"}
+		s_dev, h2d_d, d2h_d = run_e2e_pipeline(args, inputs, device, 4 * args.e2e_steps, dewarped=False, hand_off="device")
+		s_dev = shard.max_over_ranks(s_dev, device)
+		e2e["strips_on_device"] = {"pages_per_s": world / s_dev, "ms_per_step": 1e3 * s_dev,
+			"h2d_bytes_per_step": int(h2d_d), "d2h_bytes_per_step": int(d2h_d),
+			"api": "PagePipeline(..., dewarped=False, hand_off='device'): strips filtered (>= 6x6) and padded into the recogniser's "
+				"batch by og_pack_strips, handed over as a CUDA tensor (DLPack-exportable); only step counts, widths and indices are downloaded"}
 	if rank == 0 and world == 1 and not args.no_cpu_baseline:
 		cpu = cpu_baseline(args, *inputs[0])
 

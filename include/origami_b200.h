@@ -186,6 +186,18 @@ int og_otsu(const uint8_t *src, int h, int w, int64_t src_pitch,
 int og_otsu_noalloc(const uint8_t *src, int h, int w, int64_t src_pitch,
 	uint8_t *dst, int64_t dst_pitch, int32_t *threshold_out, void *stream);
 
+/* (f)4  strip hand-off to the recogniser -- origami/batch/detect/ocr.py:238-268: the OCR stage drops
+ * strips smaller than min_w x min_h (6 x 6) and feeds the rest to its model in batches padded to the
+ * widest line.  strips / steps / pix_offsets as written by og_line_steps + og_extract_lines (capacity
+ * = bytes of strips; a strip the extraction skipped becomes an all-padding slot).  Kept strips
+ * (xsteps >= min_w, ysteps >= min_h, and fitting the batch: ysteps <= H, xsteps <= w_max), in line
+ * order, are copied into batch_out (n, H, w_max) u8 -- slot j at byte j * H * w_max, right and bottom
+ * padded with pad_value; widths_out[j] = its xsteps, kept_index_out[j] = its line index (both n
+ * int32), *n_kept_out = the number of slots used.  slot_scratch: n int32 the call may overwrite. */
+int og_pack_strips(const uint8_t *strips, const int32_t *steps, const int64_t *pix_offsets, int n, int64_t capacity,
+	int min_w, int min_h, int pad_value, int H, int w_max,
+	uint8_t *batch_out, int32_t *slot_scratch, int32_t *widths_out, int32_t *kept_index_out, int32_t *n_kept_out, void *stream);
+
 /* A15  ConfidenceSampler.__call__ -- origami/batch/detect/lines.py:34-54.  For every line:
  * warped grid at (xres, yres) from the descriptors, scaled to the label map by
  * fp32(lw/W), fp32(lh/H), NEAREST lookup (OOB -> label 0), histogram.  counts_out

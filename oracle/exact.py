@@ -602,3 +602,21 @@ def regions_binarized(page, grid, s, median_line_height, separator_labels=()):
 		mask = dewarp_image(mask, (page.shape[1], page.shape[0]), grid, s, INTER_NEAREST)
 		binary = np.logical_or(binary, dilate3(mask > 0))
 	return binary.astype(np.float32)
+
+
+# --------------------------------------------------------------------------------------
+# (f)4  OCR hand-off                origami/batch/detect/ocr.py:238-268
+# --------------------------------------------------------------------------------------
+
+def ocr_batch(strips, height, w_max, min_width=6, min_height=6, pad_value=0):
+	"""The strips the OCR stage keeps (`im.width >= min_width and im.height >= min_height`,
+	ocr.py:241-246), in order, as the padded batch its predictor's input pipeline forms: every kept
+	image in the top-left corner of a (height, w_max) slot filled with pad_value.
+	Returns (batch (n_kept, height, w_max) u8, widths, kept indices)."""
+	kept = [i for i, s in enumerate(strips) if s.shape[1] >= min_width and s.shape[0] >= min_height
+		and s.shape[0] <= height and s.shape[1] <= w_max]
+	batch = np.full((len(kept), height, w_max), pad_value, dtype=np.uint8)
+	for j, i in enumerate(kept):
+		s = strips[i]
+		batch[j, :s.shape[0], :s.shape[1]] = s
+	return batch, np.array([strips[i].shape[1] for i in kept], dtype=np.int32), np.array(kept, dtype=np.int32)

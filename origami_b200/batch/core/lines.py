@@ -101,6 +101,39 @@ class LineExtractor:
 		strips, _ = extract_strips(dewarper, records, binarize=spec)
 		return [(part[0], strip) for part, strip in zip(line_parts, strips)]
 
+	def extract_device(self, lines, ignored=None, min_width=6, min_height=6, pad_value=0):
+		"""The OCR stage's hand-off without the host round trip (reference origami/batch/detect/ocr.py:
+		238-268): returns (kept_paths, batch, widths, empty_paths) where batch is a CUDA uint8 tensor
+		(n_kept, line_height, w_max) holding the strips of at least min_width x min_height pixels in
+		line order, right-padded with pad_value, widths a CUDA int32 tensor (n_kept) and empty_paths the
+		lines the reference would write an empty transcription for.  The tensors export through
+		DLPack (torch.utils.dlpack / tensor.__dlpack__) to whatever framework runs the recogniser."""
+		import numpy as np
+		import torch
+		from ...core.block import _plan
+		line_parts = self._filtered_parts(lines, ignored)
+		if not line_parts:
+			return [], None, None, []
+		if self._options.get("do_not_dewarp"):
+			raise ValueError("extract_device covers the dewarped path")
+		dewarper = line_parts[0][1].block.page.dewarper
+		grid = dewarper.grid
+		records = [line.record(ysteps=self._line_height, column=column) for _, line, column in line_parts]
+		plan, steps, offs = _plan(grid, records)
+		dev = grid._device
+		gray = torch.empty((max(int(offs[-1]), 1),), dtype=torch.uint8, device=dev)
+		spec = self._binarizer.spec if self._binarizer is not None else None
+		ops.extract_lines(dewarper.device_image, grid.device_grid, grid.resolution, plan, gray, binarize=spec,
+			dense_map=grid._device_points)
+		keep = (steps[:, 0] >= min_width) & (steps[:, 1] >= min_height)
+		w_max = int(steps[keep, 0].max()) if keep.any() else 1
+		w_max = (w_max + 3) // 4 * 4
+		batch, widths, kept, n_kept = ops.pack_strips(gray, plan, self._line_height, w_max, min_width, min_height, pad_value)
+		nk = int(keep.sum())
+		kept_paths = [line_parts[i][0] for i in np.nonzero(keep)[0]]
+		empty_paths = [line_parts[i][0] for i in np.nonzero(~keep)[0]]
+		return kept_paths, batch[:nk], widths[:nk], empty_paths
+
 	def __call__(self, lines, ignored=None):
 		return [(path, im if isinstance(im, PIL.Image.Image) else PIL.Image.fromarray(im))
 			for path, im in self.extract_arrays(lines, ignored)]

@@ -21,6 +21,9 @@ from ... import _lib, ops
 from ...core import binarize as _binarize
 
 PageResult = collections.namedtuple("PageResult", ["dewarped", "strips", "steps"])
+# strips of a page handed over on the device: batch (n_kept, line_height, w_max) uint8 CUDA tensor (valid
+# until the slot is reused, like the host views), widths and line indices of the kept strips (NumPy)
+DeviceBatch = collections.namedtuple("DeviceBatch", ["batch", "widths", "line_index"])
 
 from ...core.block import StripList  # noqa: E402  (re-exported: results of PagePipeline use it too)
 
@@ -37,6 +40,7 @@ class _Slot:
 		self.done = None
 		self.h_in = self.h_out = None
 		self.d_in = self.d_out = self.d_gray = self.d_chunks = self.d_map = None
+		self.d_strips = self.d_batch = self.d_slots = None
 		self.meta = None
 		self.bytes = (0, 0)
 
@@ -109,7 +113,8 @@ class PagePipeline:
 	pinned buffer that is recycled when the NEXT result is requested: copy what must outlive that.
 	With dewarped=False no dewarped page is computed (PageResult.dewarped is None): strips only."""
 
-	def __init__(self, line_height=48, binarize="", depth=2, device=None, use_map=True, dewarped=True):
+	def __init__(self, line_height=48, binarize="", depth=2, device=None, use_map=True, dewarped=True, hand_off="host",
+			min_size=(6, 6), pad_value=0):
 		if not torch.cuda.is_available():
 			raise _lib.OrigamiB200Error("origami_b200 needs a CUDA device (there is no CPU fallback)")
 		self.device = torch.device(device) if device is not None else torch.device("cuda", torch.cuda.current_device())
@@ -121,10 +126,16 @@ class PagePipeline:
 		# expanded on the device, no dewarped page is produced or downloaded
 		self.want_dewarped = bool(dewarped)
 		self.use_map = use_map or not self.want_dewarped
+		# hand_off="device": the strips stay on the GPU as the recogniser's padded input batch
+		# (origami/batch/detect/ocr.py:238-268); only step counts, widths and indices travel back
+		if hand_off not in ("host", "device"):
+			raise ValueError("hand_off must be 'host' or 'device'")
+		self.hand_off = hand_off
+		self.min_size, self.pad_value = (int(min_size[0]), int(min_size[1])), int(pad_value)
 		self.slots = [_Slot(self.device) for _ in range(max(2, depth))]
 
 	# -- one page: everything is enqueued on the slot's stream, nothing waits
-	def _submit(self, slot, job, cap=None):
+	def _submit(self, slot, job, cap=None, w_cap=None):
 		page, grid, cell, lines = job
 		page = np.ascontiguousarray(page, dtype=np.uint8)
 		grid = np.ascontiguousarray(grid, dtype=np.float32)
@@ -140,8 +151,15 @@ class PagePipeline:
 			lines = np.ascontiguousarray(lines, dtype=np.float64).reshape(-1, 3, 2)
 			desc = ops.pack_line_arrays(lines[:, 0], lines[:, 1], lines[:, 2], ysteps=self.line_height)
 		n = desc.shape[0]
-		if cap is None:
-			cap = int(np.sum(self.line_height * _estimate_xsteps(grid, cell, desc))) if n else 1
+		w_max = 4
+		if cap is None or self.hand_off == "device":
+			est = _estimate_xsteps(grid, cell, desc) if n else np.zeros(0, np.int64)
+			if cap is None:
+				cap = int(np.sum(self.line_height * est)) if n else 1
+			w_max = (int(est.max()) + 3) // 4 * 4 if n else 4
+		if w_cap is not None:
+			w_max = w_cap
+		on_device = self.hand_off == "device"
 
 		pitch = W  # the source is only read with byte loads: no row padding, one contiguous copy
 		dpitch = (Wd + 127) // 128 * 128
@@ -152,9 +170,10 @@ class PagePipeline:
 		n_in = o_desc + al(max(desc.nbytes, 1))
 		# output block: dewarped page (pitched) | strips | steps | pix offsets
 		o_strips = al(Hd * dpitch) if self.want_dewarped else 0
-		o_steps = o_strips + al(cap)
+		o_steps = o_strips + (0 if on_device else al(cap))  # device hand-off: the strips are not part of the download
 		o_offs = o_steps + al(8 * max(n, 1))
-		n_out = o_offs + al(8 * (n + 1))
+		o_meta = o_offs + al(8 * (n + 1))  # widths | kept indices | n_kept (device hand-off)
+		n_out = o_meta + (al(4 * (2 * max(n, 1) + 1)) if on_device else 0)
 
 		if slot.done is not None:
 			slot.done.synchronize()  # the slot's previous results must have been consumed
@@ -163,6 +182,10 @@ class PagePipeline:
 		slot.d_in = _Slot._grow(slot.d_in, n_in, device=self.device)
 		slot.d_out = _Slot._grow(slot.d_out, n_out, device=self.device)
 		slot.d_gray = _Slot._grow(slot.d_gray, cap, device=self.device)
+		if on_device:
+			slot.d_strips = _Slot._grow(slot.d_strips, cap, device=self.device)
+			slot.d_batch = _Slot._grow(slot.d_batch, max(n, 1) * self.line_height * w_max, device=self.device)
+			slot.d_slots = _Slot._grow(slot.d_slots, 4 * max(n, 1), device=self.device)
 		slot.d_chunks = _Slot._grow(slot.d_chunks, 4 * (n + 2), device=self.device)
 		if self.use_map:
 			slot.d_map = _Slot._grow(slot.d_map, Hd * Wd * 8, device=self.device)
@@ -199,13 +222,20 @@ class PagePipeline:
 					base_out + o_steps, base_out + o_offs, slot.d_chunks.data_ptr(), s)
 				mode, window = ops._binarize_args(self.binarize)
 				scratch = slot.d_gray.data_ptr() if mode == ops.OG_BIN_SAUVOLA else 0
+				p_strips = slot.d_strips.data_ptr() if on_device else base_out + o_strips
 				_lib.call("og_extract_lines", base_in, H, W, pitch, base_in + o_grid, gh, gw, cell, p_map,
 					base_in + o_desc, n, base_out + o_steps, base_out + o_offs, slot.d_chunks.data_ptr(),
-					base_out + o_strips, cap, 0, mode, window, scratch, 0, s)
+					p_strips, cap, 0, mode, window, scratch, 0, s)
+				if on_device:
+					p_meta = base_out + o_meta
+					_lib.call("og_pack_strips", p_strips, base_out + o_steps, base_out + o_offs, n, cap,
+						self.min_size[0], self.min_size[1], self.pad_value, self.line_height, w_max,
+						slot.d_batch.data_ptr(), slot.d_slots.data_ptr(), p_meta, p_meta + 4 * max(n, 1), p_meta + 8 * max(n, 1), s)
 			slot.h_out[:n_out].copy_(slot.d_out[:n_out], non_blocking=True)
 			slot.done = torch.cuda.Event()
 			slot.done.record(st)
 		slot.meta = (Hd, Wd, dpitch, n, cap, o_strips, o_steps, o_offs)
+		slot.meta_dev = (o_meta, w_max)
 		slot.bytes = (n_in, n_out)
 
 	def _collect(self, slot):
@@ -222,6 +252,18 @@ class PagePipeline:
 			return self._collect(slot)
 		if n and (steps <= 0).any():
 			raise ValueError("line %d has a degenerate or non-finite extent" % int(np.argmax((steps <= 0).any(axis=1))))
+		if self.hand_off == "device":
+			o_meta, w_max = slot.meta_dev
+			m = max(n, 1)
+			meta = hout[o_meta:o_meta + 4 * (2 * m + 1)].view(np.int32)
+			keep = (steps[:, 0] >= self.min_size[0]) & (steps[:, 1] >= self.min_size[1]) if n else np.zeros(0, bool)
+			n_kept = int(meta[2 * m]) if n else 0
+			if n_kept != int(keep.sum()):
+				# a strip was wider than the batch sized from the host-side estimate: again, with the exact width
+				self._submit(slot, slot.job, cap=max(cap, int(offs[n])), w_cap=(int(steps[keep, 0].max()) + 3) // 4 * 4)
+				return self._collect(slot)
+			batch = slot.d_batch[:n_kept * self.line_height * w_max].view(n_kept, self.line_height, w_max)
+			return PageResult(dewarped, DeviceBatch(batch, meta[:n_kept].copy(), meta[m:m + n_kept].copy()), steps)
 		flat = hout[o_strips:o_strips + cap]
 		return PageResult(dewarped, StripList(flat, offs, steps), steps)
 

@@ -362,6 +362,25 @@ def binarize_strips(gray, plan, mode, window=15, out=None, thresholds=None):
 	return out
 
 
+def pack_strips(strips, plan, height, w_max, min_w=6, min_h=6, pad_value=0, batch=None):
+	"""The recogniser's input batch, assembled on the device (reference origami/batch/detect/ocr.py:
+	238-268): strips of at least min_w x min_h pixels, in line order, right-padded to w_max.
+	Returns (batch (n, height, w_max) uint8 -- the first n_kept slots are filled --, widths (n) int32,
+	kept_index (n) int32, n_kept (1) int32), all on the device."""
+	_require_cuda()
+	n = plan.n
+	dev = strips.device
+	if batch is None:
+		batch = torch.empty((max(n, 1), height, w_max), dtype=torch.uint8, device=dev)
+	meta = torch.empty((3 * max(n, 1) + 1,), dtype=torch.int32, device=dev)
+	slots, widths, kept, n_kept = meta[:n], meta[max(n, 1):max(n, 1) + n], meta[2 * max(n, 1):2 * max(n, 1) + n], meta[3 * max(n, 1):]
+	_call("og_pack_strips", strips, ([plan.steps, batch], lambda st: (
+		strips.data_ptr(), plan.steps.data_ptr(), plan.pix_offsets.data_ptr(), n, strips.numel(),
+		int(min_w), int(min_h), int(pad_value), int(height), int(w_max),
+		batch.data_ptr(), slots.data_ptr(), widths.data_ptr(), kept.data_ptr(), n_kept.data_ptr(), st)))
+	return batch, widths, kept, n_kept
+
+
 def sauvola(src, window=15, k=0.2, r=127.5, dst=None):
 	"""(src > threshold_sauvola(src, window)) * 255 on a device image."""
 	_require_cuda()
