@@ -198,6 +198,22 @@ int og_pack_strips(const uint8_t *strips, const int32_t *steps, const int64_t *p
 	int min_w, int min_h, int pad_value, int H, int w_max,
 	uint8_t *batch_out, int32_t *slot_scratch, int32_t *widths_out, int32_t *kept_index_out, int32_t *n_kept_out, void *stream);
 
+/* (f)2  Grid.transformer / lininterp evaluation -- origami/core/dewarp.py:143-161, 555-559 and
+ * origami/core/lingrid.py:185-206, 266-275 (scipy.interpolate.LinearNDInterpolator over the warped
+ * lattice nodes), applied to all contour vertices of a page by origami/batch/detect/dewarp.py:16-39.
+ * pts (n, 2) f64 -> out (n, 2) f64: the query is clipped to clip_box (HOST array minx, miny, maxx,
+ * maxy), located in the triangulation and blended from the three vertex values; NaN where no
+ * triangle holds it.  The triangulation comes from the host (scipy.spatial.Delaunay, the oracle's
+ * own): simplices (m, 3) int32, transform (m, 3, 2) f64 = Delaunay.transform, values (n_vertices, 2)
+ * f64, plus a bucket grid over the triangles' bounding boxes: bucket (cy, cx) of size `cell` at
+ * (ox, oy) lists cell_tris[cell_start[cy*gx+cx] .. cell_start[cy*gx+cx+1]).  eps: barycentric
+ * tolerance of the inside test.  only_nan != 0: only entries of out that hold NaN are computed (the
+ * hull-edge extrapolation pass of lingrid's Interpolator). */
+int og_tri_interp(const double *pts, int64_t n, const double *clip_box,
+	const int32_t *cell_start, const int32_t *cell_tris, int gx, int gy, double ox, double oy, double cell,
+	const double *transform, const int32_t *simplices, const double *values, double eps,
+	double *out, int only_nan, void *stream);
+
 /* A15  ConfidenceSampler.__call__ -- origami/batch/detect/lines.py:34-54.  For every line:
  * warped grid at (xres, yres) from the descriptors, scaled to the label map by
  * fp32(lw/W), fp32(lh/H), NEAREST lookup (OOB -> label 0), histogram.  counts_out

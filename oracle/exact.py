@@ -620,3 +620,125 @@ def ocr_batch(strips, height, w_max, min_width=6, min_height=6, pad_value=0):
 		s = strips[i]
 		batch[j, :s.shape[0], :s.shape[1]] = s
 	return batch, np.array([strips[i].shape[1] for i in kept], dtype=np.int32), np.array(kept, dtype=np.int32)
+
+
+# --------------------------------------------------------------------------------------
+# (f)2  Grid.transformer            origami/core/dewarp.py:143-161, core/lingrid.py:192-301
+# --------------------------------------------------------------------------------------
+
+def _ray_box_hit(p, direction, box, size):
+	"""First crossing of the ray p + t * direction * size (t in [0, 1]) with the outline of
+	box = (minx, miny, maxx, maxy) -- what `ray.intersection(LinearRing(box))` gives in
+	lingrid.py:62-78 for a point inside the box (shapely absent: restated, slab method)."""
+	d = np.asarray(direction, F64) * size
+	cands = []
+	for axis, lo, hi in ((0, box[0], box[2]), (1, box[1], box[3])):
+		for bound in (lo, hi):
+			if d[axis] != 0:
+				t = (bound - p[axis]) / d[axis]
+				if 0 <= t <= 1:
+					q = np.array(p, F64) + t * d
+					q[axis] = bound
+					o = 1 - axis
+					if box[o] <= q[o] <= box[o + 2]:
+						cands.append((t, float(q[0]), float(q[1])))
+	if not cands:
+		raise ValueError("point outside given domain")
+	return min(cands)[1:]
+
+
+def lininterp_points(points, values, bounds, margin=1):
+	"""The extrapolation point set of lingrid.InterpolatorFactory (lingrid.py:207-262): hull
+	vertices, their projections on the enlarged box along the hull-edge normals, the corners."""
+	import scipy.spatial
+	points = np.asarray(points, F64)
+	values = np.asarray(values, F64).reshape(len(points), -1)
+	minx, miny, maxx, maxy = bounds
+	box = (minx - margin, miny - margin, maxx + margin, maxy + margin)
+	size = max(maxx - minx, maxy - miny) + 2 * margin + 1
+	hull = scipy.spatial.ConvexHull(points)
+	hv = list(hull.vertices)
+	pts = [points[i] for i in hv]
+	vals = [values[i] for i in hv]
+	on = {"L": [], "R": [], "T": [], "B": []}
+	proj = []
+	for a_i, b_i in zip(hv, hv[1:] + hv[:1]):
+		a, b = points[a_i], points[b_i]
+		v = a - b
+		if np.linalg.norm(v) < 1e-2:
+			continue
+		nrm = np.array([-v[1], v[0]]) / np.linalg.norm(v)
+		for q, val in ((a, values[a_i]), (b, values[b_i])):
+			x, y = _ray_box_hit(q, nrm, box, size)
+			e = (x, y, val)
+			proj.append(e)
+			if x == box[0]:
+				on["L"].append(e)
+			elif x == box[2]:
+				on["R"].append(e)
+			if y == box[1]:
+				on["T"].append(e)
+			elif y == box[3]:
+				on["B"].append(e)
+	for x, y, val in proj:
+		pts.append(np.array([x, y]))
+		vals.append(val)
+
+	def corner(cx, cy, p1, p2):
+		if p1 is None and p2 is None:
+			return
+		if p1 is None:
+			val = p2[2]
+		elif p2 is None:
+			val = p1[2]
+		else:
+			a, b = np.array(p1[:2]), np.array(p2[:2])
+			dt = np.linalg.norm(b - a)
+			if dt == 0:
+				return
+			# foot of the perpendicular from the corner onto the line a b (sympy Line.projection, lingrid.py:115-120)
+			t = ((cx - a[0]) * (b[0] - a[0]) + (cy - a[1]) * (b[1] - a[1])) / (dt * dt)
+			foot = a + t * (b - a)
+			w = np.linalg.norm(foot - a) / dt
+			val = (1 - w) * p1[2] + w * p2[2]
+		pts.append(np.array([cx, cy]))
+		vals.append(val)
+
+	pick = lambda lst, f, k: f(lst, key=lambda e: e[k]) if lst else None  # noqa: E731
+	corner(box[0], box[1], pick(on["L"], min, 1), pick(on["T"], min, 0))
+	corner(box[2], box[1], pick(on["R"], min, 1), pick(on["T"], max, 0))
+	corner(box[2], box[3], pick(on["R"], max, 1), pick(on["B"], max, 0))
+	corner(box[0], box[3], pick(on["L"], max, 1), pick(on["B"], min, 0))
+	return np.array(pts), np.array(vals)
+
+
+def lininterp(points, values, bounds):
+	"""lingrid.lininterp (lingrid.py:173-189, 266-275, 300-301) evaluated with SciPy's own
+	LinearNDInterpolator, as the reference does: clip to the bounds, interpolate inside the hull of
+	the data, use the extrapolating interpolator where that gives NaN."""
+	import scipy.interpolate
+	points = np.asarray(points, F64)
+	values = np.asarray(values, F64).reshape(len(points), -1)
+	inter = scipy.interpolate.LinearNDInterpolator(points, values, fill_value=np.nan)
+	ep, ev = lininterp_points(points, values, bounds)
+	extra = scipy.interpolate.LinearNDInterpolator(ep, ev, fill_value=np.nan)
+
+	def f(pts):
+		pts = np.array(pts, dtype=F64).reshape(-1, 2)
+		pts[:, 0] = np.clip(pts[:, 0], bounds[0], bounds[2])
+		pts[:, 1] = np.clip(pts[:, 1], bounds[1], bounds[3])
+		ri, rx = inter(pts), extra(pts)
+		return np.where(np.isnan(ri), rx, ri), np.isnan(ri).any(axis=1)
+
+	return f
+
+
+def transformer(dense, s):
+	"""Grid.transformer (core/dewarp.py:555-559 + Transformer :143-161) -> f(pts (n, 2)) ->
+	(dewarped (n, 2), outside-the-hull flags)."""
+	nodes = np.asarray(dense)[::s, ::s]
+	h, w = nodes.shape[:2]
+	source = nodes.reshape(h * w, 2).astype(F64)
+	target = np.flip(np.dstack(np.mgrid[0:h, 0:w]), axis=-1).reshape(h * w, 2) * s
+	b = (source[:, 0].min(), source[:, 1].min(), source[:, 0].max(), source[:, 1].max())
+	return lininterp(source, target.astype(F64), b)

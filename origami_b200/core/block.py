@@ -165,6 +165,17 @@ class Line:
 	def _position(self, xres, column):
 		return position(self._p, self._right, self._up, xres, column)
 
+	def dewarped_height(self, dewarper):
+		"""reference block.py:326-333: length of the line's `up` vector after dewarping (a line of a
+		WARPED-stage block)."""
+		assert not self._block.stage.is_dewarped
+		p0, up = self._p, self._up
+		tfm = dewarper.grid.transformer
+		p1 = p0 + up
+		tx, ty = tfm(*np.array([p0, p1]).transpose())
+		q0, q1 = np.array([tx, ty]).transpose()
+		return np.linalg.norm(q1 - q0)
+
 	def record(self, xsteps=None, ysteps=None, xres=1, yres=1, column=None):
 		"""The og_line descriptor of this line for the given sampling request."""
 		p0, right, up, xres = self._position(xres, column)

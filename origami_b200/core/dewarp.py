@@ -122,6 +122,18 @@ class Grid:
 		else:
 			raise ValueError(resolution)
 
+	@cached_property
+	def transformer(self):
+		"""reference :555-559: Transformer over Grid.points("full")[::r, ::r].  Those nodes are read off
+		the device (the A5 lookup at an integral pixel returns the dense-map node itself), so the
+		281 MB map is not materialised for them."""
+		r = self._grid_res
+		gh, gw = self._grid_hv.shape[:2]
+		ii, jj = np.mgrid[0:gh, 0:gw]
+		pts_yx = np.stack([ii.ravel() * r, jj.ravel() * r], axis=1).astype(np.float64)
+		nodes = self.inverse_yx(pts_yx).astype(np.float32).reshape(gh, gw, 2)
+		return Transformer(nodes, r, device=self._device)
+
 	# -- A5
 	@cached_property
 	def inverse_yx(self):
@@ -141,6 +153,39 @@ class Grid:
 			return interp(np.flip(pts, axis=-1))
 
 		return f
+
+
+class Transformer:
+	"""Warped -> dewarped point transform (reference origami/core/dewarp.py:143-161): linear
+	interpolation of the dewarped lattice positions over the warped positions of the lattice nodes,
+	with lingrid's extrapolation outside their hull.  grid: (h, w, 2) warped (x, y) of the node at
+	dewarped (j * grid_res, i * grid_res)."""
+
+	def __init__(self, grid, grid_res, device=None):
+		from .lingrid import lininterp
+		grid = np.asarray(grid)
+		h, w = grid.shape[:2]
+		source = grid.reshape((h * w, 2))
+		target = np.flip(np.dstack(
+			np.mgrid[0:h, 0:w]), axis=-1).reshape((h * w, 2)) * grid_res
+		minx = np.min(source[:, 0])
+		miny = np.min(source[:, 1])
+		maxx = np.max(source[:, 0])
+		maxy = np.max(source[:, 1])
+		self._interp = lininterp(source, target, (minx, miny, maxx, maxy), device=device)
+
+	def transform_points(self, pts):
+		"""(n, 2) warped (x, y) -> (n, 2) dewarped (x, y), one kernel launch for all points."""
+		pts = np.asarray(pts, dtype=np.float64).reshape(-1, 2)
+		if pts.shape[0] == 0:
+			return pts.copy()
+		out = self._interp(pts)
+		assert not np.any(np.isnan(out))
+		return out
+
+	def __call__(self, x, y):
+		pts = self.transform_points(np.squeeze(np.dstack([x, y]), axis=0))
+		return pts[:, 0], pts[:, 1]
 
 
 class Dewarper:

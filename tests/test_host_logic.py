@@ -171,3 +171,21 @@ def test_pipeline_strip_width_estimate_bounds_the_device_value():
 	assert (est >= want).all() and (est - want <= 4).all(), ((est - want).min(), (est - want).max())
 	desc["xsteps"][:10] = 77  # fixed widths are taken as they are
 	assert (pipeline._estimate_xsteps(grid, 25, desc)[:10] == 77).all()
+
+
+def test_lingrid_extrapolation_points_match_the_oracle():
+	"""The hull / box / corner points of lingrid's extrapolating interpolator (host geometry):
+	product construction against the oracle's restatement, on a warped lattice and on a small cloud."""
+	from origami_b200.core.lingrid import extrapolation_points
+	g = synth.make_grid(600, 400, 25, seed=3).astype(np.float64)
+	src = g.reshape(-1, 2)
+	h, w = g.shape[:2]
+	tgt = np.flip(np.dstack(np.mgrid[0:h, 0:w]), axis=-1).reshape(-1, 2) * 25.0
+	bounds = (src[:, 0].min(), src[:, 1].min(), src[:, 0].max(), src[:, 1].max())
+	rng = np.random.default_rng(5)
+	cloud = rng.uniform(10, 90, (12, 2))
+	for pts, vals, b in ((src, tgt, bounds), (cloud, rng.uniform(-3, 3, (12, 2)), (0, 0, 100, 100))):
+		ep, ev, collinear = extrapolation_points(pts, vals, b)
+		wp, wv = exact.lininterp_points(pts, vals, b)
+		assert not collinear and ep.shape == wp.shape
+		assert np.allclose(ep, wp, rtol=0, atol=1e-9) and np.allclose(ev, wv, rtol=0, atol=1e-9)
