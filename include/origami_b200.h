@@ -236,6 +236,15 @@ int og_argmax_labels(const float *probs, int M, int C, int h, int w,
 	uint8_t *labels_out, uint8_t *masks_out, const uint8_t *mask_values, int n_mask,
 	void *stream);
 
+/* A18  per-tile label assembly -- origami/core/predict.py:43-63 (Tile.write_inner) and :275-285: the
+ * network runs on overlapping tiles; each tile's labels = argmax_c sum_m probs[m, y, x, c], and only
+ * the tile's inner rectangle is copied into the page label map.  probs (M, th, tw, C) fp32 of ONE
+ * tile; the rectangle (inner_dx, inner_dy, inner_w, inner_h) in tile coordinates is written to
+ * labels (lh, lw) u8 at (x0, y0) -- one launch, nothing else of the map is touched. */
+int og_argmax_tile(const float *probs, int M, int C, int th, int tw,
+	int inner_dx, int inner_dy, int inner_w, int inner_h,
+	uint8_t *labels, int lh, int lw, int64_t labels_pitch, int x0, int y0, void *stream);
+
 /* A19 alone: masks from an existing label map. */
 int og_class_masks(const uint8_t *labels, int h, int w, int64_t pitch,
 	uint8_t *masks_out, const uint8_t *mask_values, int n_mask, void *stream);
@@ -250,6 +259,18 @@ int og_label_mask_ne(const uint8_t *labels, int h, int w, int64_t pitch, int bac
 	uint8_t *out, int64_t out_pitch, void *stream);
 int og_or_dilate3(const uint8_t *bin, int64_t bin_pitch, const uint8_t *mask, int64_t mask_pitch,
 	int h, int w, float *out, void *stream);
+
+/* A11  polygon mask / cut-out -- origami/core/mask.py:8-74 (Mask.__init__: cairo fill of the polygon,
+ * `R > 0`; Mask._extract: pixels outside the mask become `background`), used by
+ * Line._extract_deskewed (origami/core/block.py:174-186), Line.masked_image (:143-153) and
+ * Block.image (:396-401).  verts_xy: DEVICE array of k (x, y) f64 vertices of a closed ring, relative
+ * to the mask's origin (the caller rounds them to integers as Mask.__init__ does).  A pixel belongs to
+ * the mask when the polygon covers at least 1/510 of it (cairo's 8-bit alpha rounds to non-zero); the
+ * coverage is exact polygon-area arithmetic, cairo's own rasteriser is not reproduced (unpinned).
+ * mask_out (h, w) u8 255/0 and/or img_inout (h, w) u8 whose pixels outside the polygon are set to
+ * background; either may be NULL. */
+int og_polygon_mask(const double *verts_xy, int k, int w, int h,
+	uint8_t *mask_out, int64_t mask_pitch, uint8_t *img_inout, int64_t img_pitch, int background, void *stream);
 
 /* A11  warpAffine stage of Line._extract_deskewed -- origami/core/block.py:155-172
  * (--do-not-dewarp path; the cairo polygon cut-out that follows is not reproduced).

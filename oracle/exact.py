@@ -742,3 +742,56 @@ def transformer(dense, s):
 	target = np.flip(np.dstack(np.mgrid[0:h, 0:w]), axis=-1).reshape(h * w, 2) * s
 	b = (source[:, 0].min(), source[:, 1].min(), source[:, 0].max(), source[:, 1].max())
 	return lininterp(source, target.astype(F64), b)
+
+
+# --------------------------------------------------------------------------------------
+# A11  polygon masks                 origami/core/mask.py:8-74
+# --------------------------------------------------------------------------------------
+
+def _clip_ring(ring, axis, bound, keep_greater):
+	"""Sutherland-Hodgman: the part of a closed ring (list of points) on one side of an axis-parallel line."""
+	out = []
+	n = len(ring)
+	for i in range(n):
+		a, b = ring[i], ring[(i + 1) % n]
+		ina = a[axis] >= bound if keep_greater else a[axis] <= bound
+		inb = b[axis] >= bound if keep_greater else b[axis] <= bound
+		if ina:
+			out.append(a)
+		if ina != inb:
+			t = (bound - a[axis]) / (b[axis] - a[axis])
+			out.append((a[0] + t * (b[0] - a[0]), a[1] + t * (b[1] - a[1])))
+	return out
+
+
+def polygon_coverage(ring, w, h):
+	"""Exact area of polygon /\\ pixel square for every pixel of a (h, w) raster, by clipping the
+	ring against the four sides of each pixel and the shoelace formula (pure Python: small cases).
+	ring: (k, 2) vertices, closing edge implied."""
+	pts = [(float(x), float(y)) for x, y in np.asarray(ring, F64).reshape(-1, 2)]
+	if len(pts) > 1 and pts[0] == pts[-1]:
+		pts = pts[:-1]
+	cov = np.zeros((h, w), F64)
+	xs = [p[0] for p in pts]
+	ys = [p[1] for p in pts]
+	for y in range(max(0, int(math.floor(min(ys)))), min(h, int(math.ceil(max(ys))))):
+		row = _clip_ring(_clip_ring(pts, 1, y, True), 1, y + 1, False)
+		if len(row) < 3:
+			continue
+		for x in range(max(0, int(math.floor(min(p[0] for p in row)))), min(w, int(math.ceil(max(p[0] for p in row))))):
+			cell = _clip_ring(_clip_ring(row, 0, x, True), 0, x + 1, False)
+			if len(cell) >= 3:
+				a = 0.0
+				for i in range(len(cell)):
+					p, q = cell[i], cell[(i + 1) % len(cell)]
+					a += p[0] * q[1] - q[0] * p[1]
+				cov[y, x] = abs(a) / 2
+	return cov
+
+
+def polygon_mask(ring, w, h):
+	"""Mask.__init__ (mask.py:36-43) for one polygon whose vertices are already relative to the mask
+	origin: vertices rounded to integers, a pixel is set where cairo's 8-bit coverage is non-zero
+	(coverage >= 1/510).  cairo's rasteriser is not available: exact coverage stands in (unpinned)."""
+	pts = np.round(np.asarray(ring, F64).reshape(-1, 2)).astype(np.int32)
+	return polygon_coverage(pts, w, h) >= 0.5 / 255.0

@@ -57,9 +57,12 @@ _SIGNATURES = {
 	"og_sample_labels": [c_void_p, c_int, c_int, c_int64, c_int, c_int, c_void_p, c_int, c_int, c_int, c_void_p,
 		c_void_p, c_int, c_void_p, c_void_p, c_int, c_void_p, c_void_p, c_void_p],
 	"og_argmax_labels": [c_void_p, c_int, c_int, c_int, c_int, c_void_p, c_void_p, c_void_p, c_int, c_void_p],
+	"og_argmax_tile": [c_void_p, c_int, c_int, c_int, c_int, c_int, c_int, c_int, c_int,
+		c_void_p, c_int, c_int, c_int64, c_int, c_int, c_void_p],
 	"og_class_masks": [c_void_p, c_int, c_int, c_int64, c_void_p, c_void_p, c_int, c_void_p],
 	"og_label_mask_ne": [c_void_p, c_int, c_int, c_int64, c_int, c_void_p, c_int64, c_void_p],
 	"og_or_dilate3": [c_void_p, c_int64, c_void_p, c_int64, c_int, c_int, c_void_p, c_void_p],
+	"og_polygon_mask": [c_void_p, c_int, c_int, c_int, c_void_p, c_int64, c_void_p, c_int64, c_int, c_void_p],
 	"og_warp_affine": [c_void_p, c_int, c_int, c_int64, c_void_p, c_void_p, c_int, c_int, c_int64, c_int, c_void_p],
 }
 

@@ -58,17 +58,40 @@ class Block:
 	def image_space_polygon(self):
 		return self._image_space_polygon
 
+	def _polygon_ring(self):
+		"""Exterior ring of the block polygon as an (k, 2) array: accepts a ring, a WKT string or an
+		object with .exterior.coords / .bounds (a shapely Polygon)."""
+		poly = self._image_space_polygon
+		if poly is None:
+			return None
+		if isinstance(poly, str):
+			from .wkt import parse_wkt
+			return parse_wkt(poly)[1][0]
+		if hasattr(poly, "exterior"):
+			return np.asarray(poly.exterior.coords, dtype=np.float64)
+		return np.asarray(poly, dtype=np.float64).reshape(-1, 2)
+
 	@cached_property
 	def background(self):
-		"""0.8-quantile of the block's pixels (block.py:415-420); without a polygon
-		rasteriser the block's bounding box stands in for the polygon mask."""
+		"""0.8-quantile of the block's pixels (block.py:415-420).  The reference extracts them with
+		Mask.extract_image(..., background=None), and Mask._extract applies the polygon mask only when a
+		background value is given (mask.py:69-71): the quantile runs over the polygon's integer bounding
+		box clipped to the page -- no rasteriser is involved."""
 		pixels = self.page_pixels
-		poly = self._image_space_polygon
-		if poly is not None and hasattr(poly, "bounds"):
-			x0, y0, x1, y1 = poly.bounds
-			x0, y0 = max(int(math.floor(x0)), 0), max(int(math.floor(y0)), 0)
-			pixels = pixels[y0:int(math.ceil(y1)), x0:int(math.ceil(x1))]
+		ring = self._polygon_ring()
+		if ring is not None:
+			x0, y0 = np.floor(ring.min(axis=0)).astype(np.int64)
+			x1, y1 = np.ceil(ring.max(axis=0)).astype(np.int64)
+			pixels = pixels[max(y0, 0):max(y1, 0), max(x0, 0):max(x1, 0)]
 		return np.quantile(pixels, 0.8)
+
+	def image(self, text_area, background=None):
+		"""block.py:396-401: cut-out of the page through the mask of `text_area` (a ring)."""
+		from .mask import Mask
+		mask = Mask(text_area)
+		if background is None:
+			background = self.background
+		return mask.extract_image(self.page_pixels, background=background)
 
 
 def position(p, right, up, xres, column):
@@ -133,6 +156,7 @@ class Line:
 		self._up = np.array(up, dtype=np.float64)
 
 		self._wkt = wkt
+		self._polygon = None
 		self._confidence = confidence
 
 	@property
@@ -199,17 +223,42 @@ class Line:
 		strips, _ = extract_strips(dewarper, [self.record(ysteps=target_height, column=column)])
 		return PIL.Image.fromarray(strips[0])
 
+	@property
+	def image_space_polygon(self):
+		"""Exterior ring of the line polygon, (k, 2) float64 (the reference keeps a shapely Polygon
+		parsed from the line's wkt, block.py:48-55)."""
+		if self._polygon is None and self._wkt:
+			from .wkt import parse_wkt
+			self._polygon = parse_wkt(self._wkt)[1][0]
+		return self._polygon
+
+	def masked_image(self, mode="polygon"):
+		"""block.py:143-153."""
+		if mode not in ("polygon", "bbox"):
+			raise ValueError(mode)
+		from .mask import Mask
+		mask = Mask(self.image_space_polygon)
+		bg = self._block.background if mode == "polygon" else None
+		image, pos = mask.extract_image(self._block.page_pixels, background=bg)
+		return image
+
 	def _extract_deskewed(self, pixels, target_height=48, background=255, interpolation=None):
-		"""cv2.getAffineTransform + cv2.warpAffine stage of block.py:155-172 (INTER_AREA and
-		INTER_LINEAR give identical bytes for warpAffine).  The cairo polygon cut-out that
-		follows in the reference (block.py:174-186) needs a rasteriser and is not applied."""
+		"""block.py:155-186: cv2.getAffineTransform + cv2.warpAffine (INTER_AREA and INTER_LINEAR give
+		identical bytes for warpAffine), then the cut-out through the line polygon carried along by the
+		same affine map; pixels outside the polygon become `background`.  One upload, two kernels."""
 		p, right, up = self._p, self._right, self._up
 		width = int(math.ceil(np.linalg.norm(right)))
 		M = affine_transform(
 			np.array([p, p + right, p + up]).astype(np.float32),
 			np.array([(0, target_height - 1), (width, target_height - 1), (0, 0)]).astype(np.float32))
 		src = ops.to_device_image(np.asarray(pixels, dtype=np.uint8))
-		return ops.warp_affine(src, M, width, target_height, int(background)).cpu().numpy()
+		warped = ops.warp_affine(src, M, width, target_height, int(background))
+		ring = self.image_space_polygon
+		if ring is not None and len(ring) >= 3:
+			# shapely.affinity.affine_transform(polygon, to_shapely_matrix(matrix)), then Mask(..., bounds=(0, 0, width, height))
+			moved = ring @ np.asarray(M, dtype=np.float64)[:, :2].T + np.asarray(M, dtype=np.float64)[:, 2]
+			ops.polygon_mask(np.round(moved).astype(np.int32), width, target_height, image=warped, background=int(background))
+		return warped.cpu().numpy()
 
 	def deskewed_image(self, target_height=48, interpolation=None):
 		return PIL.Image.fromarray(self._extract_deskewed(
@@ -217,7 +266,10 @@ class Line:
 
 	@property
 	def warped_image(self):
-		raise NotImplementedError("raw polygon crops need the reference's cairo Mask (out of scope)")
+		"""Line.image(dewarped=False, deskewed=False) reads `self.warped_image` (block.py:138-139), an
+		attribute the reference never defines; the cut-out of the line polygon (masked_image) is what
+		the neighbouring code suggests it should be."""
+		return self.masked_image("polygon")
 
 	def image(
 		self, target_height=48, column=None,

@@ -100,3 +100,79 @@ extern "C" int og_tri_interp(const double *pts, int64_t n, const double *clip_bo
 	og_tri_interp_kernel<<<(unsigned)((n + 255) / 256), 256, 0, (cudaStream_t)stream>>>(p);
 	return og_check_launch("og_tri_interp_kernel");
 }
+
+// ---------------------------------------------------------------------------------------
+// Polygon masks (A11): origami/core/mask.py:8-48 fills the polygon (vertices rounded to integers)
+// with cairo and keeps the pixels whose red channel is non-zero, i.e. every pixel the polygon
+// covers by at least half an 8-bit alpha step.  cairo is not available, so the coverage is
+// computed exactly instead: the area of polygon /\ pixel square by Green's theorem, edge by edge,
+// each edge's clamped abscissa integrated over the pixel's row in closed form (float64).  A thread
+// owns a pixel and walks all edges in order, so the result does not depend on scheduling.
+// ---------------------------------------------------------------------------------------
+namespace {
+
+// integral over y in [ya, yb] of clamp(x(y) - px, 0, 1), x linear with x(ya) = xa, x(yb) = xb
+__device__ __forceinline__ double clamped_strip_area(double ya, double yb, double xa, double xb, double px) {
+	const double fa = xa - px, fb = xb - px, len = yb - ya;
+	if (len <= 0.0) return 0.0;
+	if (fa <= 0.0 && fb <= 0.0) return 0.0;
+	if (fa >= 1.0 && fb >= 1.0) return len;
+	// breakpoints where the edge crosses the left (f = 0) and the right (f = 1) side of the pixel column
+	const double df = fb - fa;
+	double t0 = 0.0, t1 = 1.0;  // parameters of the crossings, sorted below
+	double area = 0.0, tprev = 0.0, fprev = fmin(fmax(fa, 0.0), 1.0);
+	double ts[2];
+	int nt = 0;
+	if (df != 0.0) {
+		t0 = (0.0 - fa) / df;
+		t1 = (1.0 - fa) / df;
+		const double lo = fmin(t0, t1), hi = fmax(t0, t1);
+		if (lo > 0.0 && lo < 1.0) ts[nt++] = lo;
+		if (hi > 0.0 && hi < 1.0) ts[nt++] = hi;
+	}
+	for (int k = 0; k <= nt; ++k) {
+		const double t = k < nt ? ts[k] : 1.0;
+		const double f = fmin(fmax(fa + df * t, 0.0), 1.0);
+		area += 0.5 * (fprev + f) * (t - tprev);
+		tprev = t;
+		fprev = f;
+	}
+	return area * len;
+}
+
+__global__ void __launch_bounds__(256) og_polygon_mask_kernel(const double *__restrict__ verts, int k, int w, int h,
+	uint8_t *__restrict__ mask, int64_t mask_pitch, uint8_t *__restrict__ img, int64_t img_pitch, int background) {
+	const int x = blockIdx.x * blockDim.x + threadIdx.x, y = blockIdx.y;
+	if (x >= w || y >= h) return;
+	const double px = (double)x, py = (double)y;
+	double acc = 0.0;
+	for (int e = 0; e < k; ++e) {
+		const int e1 = e + 1 == k ? 0 : e + 1;
+		const double x0 = verts[2 * e], y0 = verts[2 * e + 1], x1 = verts[2 * e1], y1 = verts[2 * e1 + 1];
+		if (y0 == y1) continue;
+		const double ylo = fmin(y0, y1), yhi = fmax(y0, y1);
+		const double ya = fmax(ylo, py), yb = fmin(yhi, py + 1.0);
+		if (ya >= yb) continue;
+		const double m = (x1 - x0) / (y1 - y0);
+		const double xa = x0 + (ya - y0) * m, xb = x0 + (yb - y0) * m;
+		const double a = clamped_strip_area(ya, yb, xa, xb, px);
+		acc += y1 > y0 ? a : -a;
+	}
+	const bool inside = fabs(acc) >= 0.5 / 255.0;  // alpha = round(255 * coverage) > 0
+	if (mask != nullptr) mask[(int64_t)y * mask_pitch + x] = inside ? 255 : 0;
+	if (img != nullptr && !inside) img[(int64_t)y * img_pitch + x] = (uint8_t)background;
+}
+
+}  // namespace
+
+extern "C" int og_polygon_mask(const double *verts_xy, int k, int w, int h,
+	uint8_t *mask_out, int64_t mask_pitch, uint8_t *img_inout, int64_t img_pitch, int background, void *stream) {
+	OG_REQUIRE(w > 0 && h > 0, OG_E_ARG, "mask size %d x %d invalid", w, h);
+	OG_REQUIRE(k >= 0 && (k == 0 || verts_xy != nullptr), OG_E_ARG, "vertices missing");
+	OG_REQUIRE(mask_out != nullptr || img_inout != nullptr, OG_E_ARG, "neither mask_out nor img_inout given");
+	OG_REQUIRE((mask_out == nullptr || mask_pitch >= w) && (img_inout == nullptr || img_pitch >= w), OG_E_ARG, "pitch smaller than row");
+	dim3 grid((w + 255) / 256, h);
+	OG_REQUIRE(h <= 65535, OG_E_RANGE, "mask taller than 65535 rows");
+	og_polygon_mask_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>(verts_xy, k, w, h, mask_out, mask_pitch, img_inout, img_pitch, background);
+	return og_check_launch("og_polygon_mask_kernel");
+}

@@ -156,7 +156,61 @@ int fill_masks(MaskValues &mv, const uint8_t *mask_values, int n_mask) {
 	return OG_OK;
 }
 
+// Tile.write_inner (predict.py:60-63): argmax of a tile's inner rectangle straight into the page's
+// label map.  One pixel per thread; consecutive threads walk a row of the rectangle.
+__global__ void __launch_bounds__(256) og_argmax_tile_kernel(
+	const float *__restrict__ probs, int M, int C, int th, int tw, int dx, int dy, int iw, int ih,
+	uint8_t *__restrict__ labels, int64_t pitch, int x0, int y0) {
+	const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+	if (i >= (int64_t)iw * ih) return;
+	const int r = (int)(i / iw), c = (int)(i - (int64_t)r * iw);
+	const int64_t tpix = (int64_t)th * tw, q = (int64_t)(dy + r) * tw + dx + c;
+	int bi = 0;
+	if (C == 4 && (reinterpret_cast<uintptr_t>(probs) & 15) == 0) {
+		const float4 *p4 = reinterpret_cast<const float4 *>(probs);
+		float4 acc = __ldcs(p4 + q);
+		for (int m = 1; m < M; ++m) {
+			const float4 v = __ldcs(p4 + (int64_t)m * tpix + q);
+			acc.x = __fadd_rn(acc.x, v.x);
+			acc.y = __fadd_rn(acc.y, v.y);
+			acc.z = __fadd_rn(acc.z, v.z);
+			acc.w = __fadd_rn(acc.w, v.w);
+		}
+		float best = acc.x;
+		if (acc.y > best) { best = acc.y; bi = 1; }
+		if (acc.z > best) { best = acc.z; bi = 2; }
+		if (acc.w > best) { best = acc.w; bi = 3; }
+	} else {
+		float best = 0.f;
+		for (int k = 0; k < C; ++k) {
+			float acc = probs[q * C + k];
+			for (int m = 1; m < M; ++m) acc = __fadd_rn(acc, probs[((int64_t)m * tpix + q) * C + k]);
+			if (k == 0 || acc > best) {  // first maximum wins
+				best = acc;
+				bi = k;
+			}
+		}
+	}
+	labels[(int64_t)(y0 + r) * pitch + x0 + c] = (uint8_t)bi;
+}
+
 }  // namespace
+
+extern "C" int og_argmax_tile(const float *probs, int M, int C, int th, int tw,
+	int inner_dx, int inner_dy, int inner_w, int inner_h,
+	uint8_t *labels, int lh, int lw, int64_t labels_pitch, int x0, int y0, void *stream) {
+	OG_REQUIRE(probs != nullptr && labels != nullptr, OG_E_ARG, "NULL pointer");
+	OG_REQUIRE(M >= 1 && C >= 1 && C <= 256 && th > 0 && tw > 0, OG_E_ARG, "tile shape (%d, %d, %d, %d) invalid", M, th, tw, C);
+	OG_REQUIRE(inner_w >= 0 && inner_h >= 0 && inner_dx >= 0 && inner_dy >= 0 && inner_dx + inner_w <= tw && inner_dy + inner_h <= th,
+		OG_E_ARG, "inner rectangle leaves the tile");
+	OG_REQUIRE(lh > 0 && lw > 0 && labels_pitch >= lw && x0 >= 0 && y0 >= 0 && x0 + inner_w <= lw && y0 + inner_h <= lh,
+		OG_E_ARG, "inner rectangle leaves the label map");
+	const int64_t n = (int64_t)inner_w * inner_h;
+	if (n == 0) return OG_OK;
+	og_argmax_tile_kernel<<<(unsigned)((n + 255) / 256), 256, 0, (cudaStream_t)stream>>>(probs, M, C, th, tw,
+		inner_dx, inner_dy, inner_w, inner_h, labels, labels_pitch, x0, y0);
+	return og_check_launch("og_argmax_tile_kernel");
+}
 
 extern "C" int og_argmax_labels(const float *probs, int M, int C, int h, int w,
 	uint8_t *labels_out, uint8_t *masks_out, const uint8_t *mask_values, int n_mask, void *stream) {

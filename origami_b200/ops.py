@@ -442,6 +442,22 @@ def argmax_labels(probs, mask_values=None):
 	return labels, masks
 
 
+def argmax_tile(probs, inner, outer_origin, labels):
+	"""Tile.write_inner (reference origami/core/predict.py:60-63) fused with the argmax: probs (M, th,
+	tw, C) of one tile; inner = (x0, y0, x1, y1) in page coordinates, outer_origin = (x, y) of the
+	tile's top-left corner; the inner rectangle of the tile's labels lands in `labels` (device image)."""
+	_require_cuda()
+	if probs.dtype != torch.float32 or probs.dim() != 4 or not probs.is_cuda or not probs.is_contiguous():
+		raise ValueError("probs must be a contiguous float32 CUDA tensor (M, th, tw, C)")
+	_check_u8_image(labels, "labels")
+	M, th, tw, C = (int(v) for v in probs.shape)
+	x0, y0, x1, y1 = (int(v) for v in inner)
+	dx, dy = x0 - int(outer_origin[0]), y0 - int(outer_origin[1])
+	_call("og_argmax_tile", probs, ([labels], lambda st: (probs.data_ptr(), M, C, th, tw, dx, dy, x1 - x0, y1 - y0,
+		labels.data_ptr(), int(labels.shape[0]), int(labels.shape[1]), labels.stride(0), x0, y0, st)))
+	return labels
+
+
 def class_masks(labels, mask_values):
 	_require_cuda()
 	_check_u8_image(labels, "labels")
@@ -462,6 +478,24 @@ def warp_affine(src, M, width, height, border_value=0):
 	_call("og_warp_affine", src, ([], lambda st: (src.data_ptr(), int(src.shape[0]), int(src.shape[1]), src.stride(0),
 		Mh.ctypes.data, dst.data_ptr(), width, height, dst.stride(0), int(border_value), st)))
 	return dst
+
+
+def polygon_mask(verts_xy, w, h, device=None, image=None, background=255):
+	"""Mask.__init__ / Mask._extract (reference origami/core/mask.py:8-74): verts_xy (k, 2) ring relative
+	to the mask origin.  Returns the (h, w) uint8 mask (255 inside); with `image` (a device image of
+	that size) the pixels outside the polygon are set to background in place as well."""
+	_require_cuda()
+	v = np.ascontiguousarray(verts_xy, dtype=np.float64).reshape(-1, 2)
+	if len(v) > 1 and np.array_equal(v[0], v[-1]):
+		v = v[:-1]  # closed ring: the closing edge is implied
+	dev = image.device if image is not None else torch.device(device or "cuda")
+	vd = torch.from_numpy(v).to(dev)
+	mask = alloc_image(h, w, dev)
+	if image is not None:
+		_check_u8_image(image, "image")
+	_call("og_polygon_mask", mask, ([vd, image], lambda st: (vd.data_ptr(), int(v.shape[0]), int(w), int(h),
+		mask.data_ptr(), mask.stride(0), _ptr(image), image.stride(0) if image is not None else 0, int(background), st)))
+	return mask
 
 
 def label_mask_ne(labels, background):

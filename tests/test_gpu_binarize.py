@@ -99,3 +99,25 @@ def test_warp_affine_bit_exact(cuda):
 	want = exact.warp_affine_linear(page, M, width, 48, border=200)
 	got = ops.warp_affine(ops.to_device_image(page, cuda), M, width, 48, border_value=200).cpu().numpy()
 	assert np.array_equal(got, want)
+
+
+def test_tiled_label_assembly_is_write_inner(cuda):
+	"""predict.py:275-285: per tile argmax + Tile.write_inner, against the NumPy expressions of the reference."""
+	from origami_b200.core.predict import Tiles
+	full = (1280, 2400)  # (w, h) as the reference's full_size
+	rng = np.random.default_rng(3)
+	want = np.empty((full[1], full[0]), np.uint8)
+	labels = ops.alloc_image(full[1], full[0], cuda)
+	labels.fill_(255)
+	tiles = list(Tiles((512, 768), beta0=50)(full))
+	assert len(tiles) > 6
+	for k, tile in enumerate(tiles):
+		x0, y0, x1, y1 = tile.outer
+		pr = [rng.random((1, y1 - y0, x1 - x0, 4), dtype=np.float32) for _ in range(1 + k % 3)]
+		tile.write_inner(want, np.argmax(np.sum(pr, axis=0).squeeze(), axis=-1).astype(np.uint8))
+		tile.write_inner_argmax(labels, pr)
+	assert np.array_equal(labels.cpu().numpy(), want)
+	pr6 = rng.random((2, 40, 50, 6), dtype=np.float32)  # another class count: the general path
+	small = ops.alloc_image(40, 50, cuda)
+	ops.argmax_tile(torch.from_numpy(pr6).to(cuda), (0, 0, 50, 40), (0, 0), small)
+	assert np.array_equal(small.cpu().numpy(), exact.argmax_labels(pr6))

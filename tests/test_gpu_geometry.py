@@ -71,3 +71,68 @@ def test_dewarped_contours_and_line_height(setup):
 	line = Line(Block(page, None, Stage.WARPED), [400.0, 500.0], [300.0, 2.0], [1.0, -30.0])
 	q, _ = want_f(np.array([[400.0, 500.0], [401.0, 470.0]]))
 	assert abs(line.dewarped_height(page.dewarper) - np.linalg.norm(q[1] - q[0])) < 1e-8
+
+
+def _rings():
+	rng = np.random.default_rng(7)
+	star = []
+	for k in range(14):
+		r = 28 if k % 2 else 11
+		star.append([45 + r * np.cos(k * np.pi / 7), 33 + r * np.sin(k * np.pi / 7)])
+	return {
+		"rectangle": np.array([[3, 4], [70, 4], [70, 30], [3, 30]], float),
+		"thin sliver": np.array([[0, 0], [80, 1], [80, 3]], float),
+		"1/510 sliver": np.array([[0, 10], [255, 11], [0, 11]], float),
+		"convex": np.array([[10.4, 5.2], [60.7, 2.1], [85.2, 20.9], [70.3, 44.6], [20.5, 40.1], [2.2, 22.8]]),
+		"star (concave)": np.array(star),
+		"clockwise": np.array([[10, 10], [10, 40], [50, 40], [50, 10]], float),
+		"leaves the raster": np.array([[-20, -10], [60, -15], [120, 30], [40, 80], [-30, 40]], float),
+		"random": rng.uniform(0, 60, (9, 2)),
+	}
+
+
+def test_polygon_mask_matches_exact_coverage(cuda):
+	from origami_b200 import ops
+	w, h = 90, 64
+	for name, ring in _rings().items():
+		if name == "random":
+			continue  # self-intersecting: winding rule territory, not produced by the line detector
+		pts = np.round(ring).astype(np.int32)
+		got = ops.polygon_mask(pts, w, h, device=cuda).cpu().numpy() > 0
+		cov = exact.polygon_coverage(pts, w, h)
+		want = cov >= 0.5 / 255.0
+		near = np.abs(cov - 0.5 / 255.0) < 1e-12  # exactly on cairo's rounding step: either answer is defensible
+		assert np.array_equal(got[~near], want[~near]), name
+		assert got.sum() > 0
+
+
+def test_mask_cutout_and_deskewed_line_with_polygon(cuda, setup):
+	import cv2
+	from origami_b200.core.mask import Mask
+	W, H, s, g, grid, _ = setup
+	page_px = synth.make_page(W, H, seed=4, kind="noise")
+	ring = np.array([[100.3, 200.2], [420.9, 204.7], [430.0, 230.0], [260.5, 244.4], [99.1, 236.5]])
+	mask = Mask(ring)
+	x0, y0, x1, y1 = mask.bounds
+	assert (x0, y0, x1, y1) == (99, 200, 430, 245)
+	want = exact.polygon_mask(ring - np.array([x0, y0]), x1 - x0, y1 - y0)
+	assert np.array_equal(mask.binary, want)
+	cut = mask.cutout(page_px, background=7)
+	ref = page_px[y0:y1, x0:x1].copy()
+	ref[~want] = 7
+	assert np.array_equal(cut, ref)
+	# Line._extract_deskewed: warpAffine, then the cut-out through the affinely moved polygon
+	wkt = "POLYGON ((" + ", ".join("%r %r" % (float(x), float(y)) for x, y in np.vstack([ring, ring[:1]])) + "))"
+	block = Block(Page(page_px), wkt, Stage.WARPED)
+	line = Line(block, [100.3, 236.2], [320.6, 4.5], [1.2, -30.0], wkt=wkt)
+	got = line._extract_deskewed(page_px, 48, background=200)
+	p, right, up = line._p, line._right, line._up
+	width = int(np.ceil(np.linalg.norm(right)))
+	M = cv2.getAffineTransform(np.array([p, p + right, p + up]).astype(np.float32), np.array([(0, 47), (width, 47), (0, 0)]).astype(np.float32))
+	warped = exact.warp_affine_linear(page_px, M, width, 48, border=200)
+	moved = ring @ M[:, :2].T + M[:, 2]
+	inside = exact.polygon_mask(moved, width, 48)
+	warped[~inside] = 200
+	assert np.array_equal(got, warped)
+	assert abs(block.background - np.quantile(page_px[200:245, 99:430], 0.8)) == 0  # the bounding box, as the reference
+	assert line.warped_image.size == (331, 45)
