@@ -260,6 +260,14 @@ int og_label_mask_ne(const uint8_t *labels, int h, int w, int64_t pitch, int bac
 int og_or_dilate3(const uint8_t *bin, int64_t bin_pitch, const uint8_t *mask, int64_t mask_pitch,
 	int h, int w, float *out, void *stream);
 
+/* (f)3  SplitDetector's column statistic -- origami/batch/detect/layout.py:915-931:
+ * scipy.signal.periodogram(pixels, axis=0) (mean-free columns, boxcar window, one-sided density)
+ * followed by np.quantile(dens, quantile, axis=0).  pixels (h, w): uint8 (scaled by 1/255 in float32
+ * first, as the reference does) or float32; out (w) float32.  The spectrum is evaluated in float64
+ * (the reference's is complex64 pocketfft): agreement to float32 round-off, h <= 8192. */
+int og_column_psd_quantile(const void *pixels, int is_u8, int h, int w, int64_t pitch_bytes,
+	double quantile, float *out, void *stream);
+
 /* A11  polygon mask / cut-out -- origami/core/mask.py:8-74 (Mask.__init__: cairo fill of the polygon,
  * `R > 0`; Mask._extract: pixels outside the mask become `background`), used by
  * Line._extract_deskewed (origami/core/block.py:174-186), Line.masked_image (:143-153) and

@@ -795,3 +795,25 @@ def polygon_mask(ring, w, h):
 	(coverage >= 1/510).  cairo's rasteriser is not available: exact coverage stands in (unpinned)."""
 	pts = np.round(np.asarray(ring, F64).reshape(-1, 2)).astype(np.int32)
 	return polygon_coverage(pts, w, h) >= 0.5 / 255.0
+
+
+# --------------------------------------------------------------------------------------
+# (f)3  SplitDetector               origami/batch/detect/layout.py:915-944
+# --------------------------------------------------------------------------------------
+
+def split_detector(pixels, scale, quantile=0.9, smooth=1, intensity=0.05, width=2, border=0.1):
+	"""SplitDetector.__call__ with the reference's own SciPy / NumPy calls (they are installed here).
+	Returns (peaks, info, column quantiles before smoothing)."""
+	import scipy.ndimage
+	import scipy.signal
+	if pixels.dtype == np.uint8:
+		pixels = pixels.astype(np.float32) / 255.0
+	assert pixels.dtype == np.float32
+	freq, dens = scipy.signal.periodogram(pixels, axis=0)
+	colq = np.quantile(dens, quantile, axis=0)
+	ink_h = scipy.ndimage.convolve(colq, np.ones(int(smooth * scale)) / int(smooth * scale), mode="nearest")
+	span = int(border * len(ink_h))
+	ink_h[:span] = 0
+	ink_h[-span:] = 0
+	peaks, info = scipy.signal.find_peaks(-ink_h, height=-intensity, distance=int(width * scale))
+	return peaks, info, colq

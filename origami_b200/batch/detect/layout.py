@@ -39,3 +39,56 @@ def regions_binarized(page, median_line_height, separator_labels=()):
 		mask_total = dmask if mask_total is None else (mask_total | dmask)
 	assert mask_total is None or tuple(mask_total.shape) == (hd, wd)
 	return ops.to_host(ops.or_dilate3(binary, mask_total))
+
+
+def crop(pixels, bounds):
+	"""layout.py:886-894 with the contour given by its bounds (minx, miny, maxx, maxy)."""
+	minx, miny, maxx, maxy = bounds
+	miny = int(max(0, miny))
+	minx = int(max(0, minx))
+	maxy = int(min(maxy, pixels.shape[0]))
+	maxx = int(min(maxx, pixels.shape[1]))
+	return pixels[miny:maxy, minx:maxx], (minx, miny)
+
+
+def kernel(*s):
+	"""layout.py:58-59"""
+	return np.ones(s) / np.prod(s)
+
+
+class SplitDetector:
+	"""layout.py:915-944: finds the x position of a vertical whitespace gap inside a text region from
+	the column-wise power spectra of its (binarized) pixels.  The periodogram and the quantile over
+	frequencies run on the GPU for all columns of the crop at once; the smoothing and the peak search
+	work on one number per column and stay on the host with the reference's SciPy calls."""
+
+	def __init__(self, quantile=0.9, smooth=1, intensity=0.05, width=2, border=0.1):
+		self._quantile = quantile
+		self._smooth = smooth
+		self._intensity = intensity
+		self._width = width
+		self._border = border
+
+	def column_quantiles(self, pixels, device=None):
+		import torch
+		if isinstance(pixels, torch.Tensor):
+			t = pixels
+		else:
+			if pixels.dtype != np.uint8:
+				assert pixels.dtype == np.float32
+			t = torch.from_numpy(np.ascontiguousarray(pixels)).to(device or "cuda")
+		return ops.column_psd_quantile(t, self._quantile).cpu().numpy()
+
+	def __call__(self, pixels, scale, device=None):
+		import scipy.ndimage
+		import scipy.signal
+		ink_h = scipy.ndimage.convolve(
+			self.column_quantiles(pixels, device),
+			kernel(int(self._smooth * scale)),
+			mode="nearest")
+		span = int(self._border * len(ink_h))
+		ink_h[:span] = 0
+		ink_h[-span:] = 0
+		peaks, info = scipy.signal.find_peaks(
+			-ink_h, height=-self._intensity, distance=int(self._width * scale))
+		return peaks, info

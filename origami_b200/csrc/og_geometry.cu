@@ -176,3 +176,124 @@ extern "C" int og_polygon_mask(const double *verts_xy, int k, int w, int h,
 	og_polygon_mask_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>(verts_xy, k, w, h, mask_out, mask_pitch, img_inout, img_pitch, background);
 	return og_check_launch("og_polygon_mask_kernel");
 }
+
+// ---------------------------------------------------------------------------------------
+// SplitDetector's column statistic (origami/batch/detect/layout.py:
+// 915-944): scipy.signal.periodogram(pixels, axis=0) -- per image column the one-sided power
+// spectral density of the mean-free column (boxcar window, density scaling) -- followed by
+// np.quantile(dens, q, axis=0).  One CTA per column: the column and a table of the N-th roots of
+// unity sit in shared memory, every thread evaluates a few frequencies of the DFT directly in
+// float64 (N is a region height, not a power of two; N^2 / 2 terms per column is small work for a
+// GPU and has no FFT round-off pattern to match), the densities are sorted in shared memory and
+// the quantile is read off with NumPy's linear interpolation rule.
+// ---------------------------------------------------------------------------------------
+namespace {
+
+__global__ void __launch_bounds__(256) og_column_psd_quantile_kernel(const void *__restrict__ pixels, int is_u8, int64_t pitch_elems,
+	int h, int w, double q, float *__restrict__ out, int nsort) {
+	extern __shared__ __align__(16) unsigned char smem_raw[];
+	double2 *tw = reinterpret_cast<double2 *>(smem_raw);                   // h roots of unity
+	float *col = reinterpret_cast<float *>(smem_raw + (size_t)h * 16);     // h samples
+	float *dens = col + h;                                                  // nsort (power of two) densities
+	__shared__ double s_part[8];
+	__shared__ double s_mean;
+	const int x = blockIdx.x;
+	const int nf = h / 2 + 1;
+	for (int j = threadIdx.x; j < h; j += blockDim.x) {
+		double sn, cs;
+		sincospi(-2.0 * (double)j / (double)h, &sn, &cs);
+		tw[j] = make_double2(cs, sn);
+		float v;
+		if (is_u8) v = __fdiv_rn((float)reinterpret_cast<const uint8_t *>(pixels)[(int64_t)j * pitch_elems + x], 255.0f);  // pixels.astype(float32) / 255.0
+		else v = reinterpret_cast<const float *>(pixels)[(int64_t)j * pitch_elems + x];
+		col[j] = v;
+	}
+	__syncthreads();
+	// detrend="constant": subtract the column mean
+	double part = 0.0;
+	for (int j = threadIdx.x; j < h; j += blockDim.x) part += (double)col[j];
+#pragma unroll
+	for (int o = 16; o > 0; o >>= 1) part += __shfl_xor_sync(0xffffffffu, part, o);
+	if ((threadIdx.x & 31) == 0) s_part[threadIdx.x >> 5] = part;
+	__syncthreads();
+	if (threadIdx.x == 0) {
+		double t = 0.0;
+		for (int k = 0; k < (int)(blockDim.x >> 5); ++k) t += s_part[k];
+		s_mean = t / (double)h;
+	}
+	__syncthreads();
+	const float mean = (float)s_mean;
+	for (int j = threadIdx.x; j < h; j += blockDim.x) col[j] = __fsub_rn(col[j], mean);
+	__syncthreads();
+	for (int k = threadIdx.x; k < nsort; k += blockDim.x) {
+		float d = __int_as_float(0x7f800000);  // padding sorts to the end
+		if (k < nf) {
+			double re = 0.0, im = 0.0;
+			int idx = 0;
+			for (int n = 0; n < h; ++n) {
+				const double2 t = tw[idx];
+				const double v = (double)col[n];
+				re += v * t.x;
+				im += v * t.y;
+				idx += k;
+				if (idx >= h) idx -= h;
+			}
+			double p = (re * re + im * im) / (double)h;
+			const bool doubled = k > 0 && ((h & 1) ? true : k < h / 2);
+			if (doubled) p *= 2.0;
+			d = (float)p;
+		}
+		dens[k] = d;
+	}
+	__syncthreads();
+	// bitonic sort of nsort values
+	for (int size = 2; size <= nsort; size <<= 1) {
+		for (int stride = size >> 1; stride > 0; stride >>= 1) {
+			for (int i = threadIdx.x; i < nsort; i += blockDim.x) {
+				const int j = i ^ stride;
+				if (j > i) {
+					const bool up = (i & size) == 0;
+					const float a = dens[i], b = dens[j];
+					if ((a > b) == up) {
+						dens[i] = b;
+						dens[j] = a;
+					}
+				}
+			}
+			__syncthreads();
+		}
+	}
+	if (threadIdx.x == 0) {
+		// np.quantile, method "linear": virtual index q * (n - 1), lerp with NumPy's _lerp
+		const double pos = q * (double)(nf - 1);
+		int lo = (int)floor(pos);
+		lo = min(max(lo, 0), nf - 1);
+		const int hi = min(lo + 1, nf - 1);
+		const float t = (float)(pos - (double)lo);
+		const float a = dens[lo], b = dens[hi];
+		const float diff = __fsub_rn(b, a);
+		float r = __fadd_rn(a, __fmul_rn(diff, t));
+		if (t >= 0.5f) r = __fsub_rn(b, __fmul_rn(diff, __fsub_rn(1.f, t)));
+		if (t == 1.f || !(diff == diff)) r = b;
+		out[x] = r;
+	}
+}
+
+}  // namespace
+
+extern "C" int og_column_psd_quantile(const void *pixels, int is_u8, int h, int w, int64_t pitch_bytes,
+	double quantile, float *out, void *stream) {
+	OG_REQUIRE(pixels != nullptr && out != nullptr, OG_E_ARG, "NULL pointer");
+	OG_REQUIRE(h >= 1 && w >= 1, OG_E_ARG, "crop %d x %d invalid", w, h);
+	OG_REQUIRE(h <= 8192, OG_E_RANGE, "crop of %d rows exceeds the 8192-row limit of the shared-memory DFT", h);
+	OG_REQUIRE(quantile >= 0.0 && quantile <= 1.0, OG_E_ARG, "quantile %g outside [0, 1]", quantile);
+	const int elem = is_u8 ? 1 : 4;
+	OG_REQUIRE(pitch_bytes >= (int64_t)w * elem && pitch_bytes % elem == 0, OG_E_ARG, "pitch invalid");
+	int nsort = 1;
+	while (nsort < h / 2 + 1) nsort <<= 1;
+	const size_t smem = (size_t)h * 16 + (size_t)h * 4 + (size_t)nsort * 4;
+	cudaError_t e = cudaFuncSetAttribute(og_column_psd_quantile_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024 - 1024);
+	if (e != cudaSuccess) return og_set_error((int)e, "cudaFuncSetAttribute: %s", cudaGetErrorString(e));
+	og_column_psd_quantile_kernel<<<w, 256, smem, (cudaStream_t)stream>>>(pixels, is_u8, pitch_bytes / elem, h, w, quantile, out, nsort);
+	return og_check_launch("og_column_psd_quantile_kernel");
+}

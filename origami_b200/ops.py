@@ -480,6 +480,19 @@ def warp_affine(src, M, width, height, border_value=0):
 	return dst
 
 
+def column_psd_quantile(pixels, quantile=0.9):
+	"""np.quantile(scipy.signal.periodogram(pixels, axis=0)[1], quantile, axis=0) for a 2-D uint8 or
+	float32 CUDA tensor with unit column stride (reference origami/batch/detect/layout.py:926-930)."""
+	_require_cuda()
+	if pixels.dim() != 2 or not pixels.is_cuda or pixels.stride(1) != 1 or pixels.dtype not in (torch.uint8, torch.float32):
+		raise ValueError("pixels must be a 2-D uint8 or float32 CUDA tensor with unit column stride")
+	h, w = int(pixels.shape[0]), int(pixels.shape[1])
+	out = torch.empty((w,), dtype=torch.float32, device=pixels.device)
+	_call("og_column_psd_quantile", pixels, ([], lambda st: (pixels.data_ptr(), 1 if pixels.dtype == torch.uint8 else 0, h, w,
+		pixels.stride(0) * pixels.element_size(), float(quantile), out.data_ptr(), st)))
+	return out
+
+
 def polygon_mask(verts_xy, w, h, device=None, image=None, background=255):
 	"""Mask.__init__ / Mask._extract (reference origami/core/mask.py:8-74): verts_xy (k, 2) ring relative
 	to the mask origin.  Returns the (h, w) uint8 mask (255 inside); with `image` (a device image of

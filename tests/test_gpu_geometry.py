@@ -136,3 +136,25 @@ def test_mask_cutout_and_deskewed_line_with_polygon(cuda, setup):
 	assert np.array_equal(got, warped)
 	assert abs(block.background - np.quantile(page_px[200:245, 99:430], 0.8)) == 0  # the bounding box, as the reference
 	assert line.warped_image.size == (331, 45)
+
+
+@pytest.mark.parametrize("shape,dtype", [((301, 420), "u8"), ((256, 300), "f32"), ((1033, 200), "f32"), ((2, 40), "u8")])
+def test_split_detector_matches_scipy(cuda, shape, dtype):
+	"""layout.py:915-944 on a two-column text crop: column quantiles of the periodogram within float32
+	round-off of SciPy's (complex64 pocketfft there, float64 DFT here), same peaks."""
+	from origami_b200.batch.detect.layout import SplitDetector, crop
+	h, w = shape
+	page = synth.make_page(w + 40, h + 30, seed=h, kind="text", dpi=300)
+	px, (x0, y0) = crop(page, (20.5, 10.2, 20.5 + w, 10.2 + h))
+	assert px.shape == (h, w) and (x0, y0) == (20, 10)
+	px = np.ascontiguousarray(px)
+	px[:, w // 2 - 6:w // 2 + 6] = 235  # a whitespace gutter
+	if dtype == "f32":
+		px = (exact.binarize(px, ("otsu",)) > 0).astype(np.float32)  # what Regions.binarized hands over
+	det = SplitDetector()
+	peaks, info, colq = exact.split_detector(px, scale=20)
+	got_q = det.column_quantiles(px, cuda)
+	assert np.allclose(got_q, colq, rtol=2e-4, atol=1e-6 * max(float(colq.max()), 1e-12))
+	if h > 16:
+		gp, gi = det(px, 20, cuda)
+		assert np.array_equal(gp, peaks) and np.allclose(gi["peak_heights"], info["peak_heights"], rtol=1e-3, atol=1e-6)
