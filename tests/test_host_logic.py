@@ -189,3 +189,32 @@ def test_lingrid_extrapolation_points_match_the_oracle():
 		wp, wv = exact.lininterp_points(pts, vals, b)
 		assert not collinear and ep.shape == wp.shape
 		assert np.allclose(ep, wp, rtol=0, atol=1e-9) and np.allclose(ev, wv, rtol=0, atol=1e-9)
+
+
+def test_segment_zip_roundtrip_and_line_png_export(tmp_path):
+	"""segment.zip (paletted PNG + class table, core/segment.py:45-80) and the PNG export of strips
+	(batch/export/lines.py:57-67): written and read back byte for byte."""
+	import io
+	import zipfile
+	import PIL.Image
+	from origami_b200.core.segment import Prediction, PredictorType, Segmentation, write_line_images
+	labels = synth.make_labels(128, 240, seed=1)
+	seps = (synth.make_labels(128, 240, seed=2) == 2).astype(np.uint8)
+	preds = [Prediction(PredictorType.REGION, "regions", labels, PredictorType.REGION.classes(dict(BACKGROUND=0, TEXT=1, TABULAR=2, ILLUSTRATION=3))),
+		Prediction(PredictorType.SEPARATOR, "separators", seps, PredictorType.SEPARATOR.classes(dict(BACKGROUND=0, H=1)))]
+	path = tmp_path / "segment.zip"
+	Segmentation(preds).save(path)
+	back = Segmentation.open(path)
+	assert back.size == (128, 240) and [p.name for p in back.predictions] == ["regions", "separators"]
+	for a, b in zip(preds, back.predictions):
+		assert np.array_equal(a.labels, b.labels) and b.labels.dtype == np.uint8
+		assert [(m.name, m.value) for m in a.classes] == [(m.name, m.value) for m in b.classes]
+		assert b.background_label.value == 0 and b.type == a.type
+	strips = [(("regions", "TEXT", "1", str(k)), (np.arange(48 * (20 + k)) % 251).astype(np.uint8).reshape(48, 20 + k)) for k in range(3)]
+	zpath = tmp_path / "lines.zip"
+	with zipfile.ZipFile(zpath, "w") as zf:
+		write_line_images(zf, strips)
+	with zipfile.ZipFile(zpath) as zf:
+		assert zf.namelist() == ["regions/TEXT/1/%d.png" % k for k in range(3)]
+		for (stem, arr), name in zip(strips, zf.namelist()):
+			assert np.array_equal(np.array(PIL.Image.open(io.BytesIO(zf.read(name)))), arr)
