@@ -105,6 +105,10 @@ def extract_lines(page_pil, grid, lines, target_height=48, binarize=None, thread
 	def one(ln):
 		return line_image(page_pil, grid, ln["p"], ln["right"], ln["up"], target_height, ln.get("column"), binarize)
 
+	# The dense map is built here, in the calling thread, not by whichever pool thread asks first:
+	# cv2.setUseOptimized() is per thread for the IPP dispatch, so a map built inside a worker would
+	# come from OpenCV's IPP path even when the caller pinned the generic one (they differ by <= 2 ulp).
+	grid.inverse_yx()
 	with multiprocessing.pool.ThreadPool(processes=threads) as pool:
 		return pool.map(one, lines)
 

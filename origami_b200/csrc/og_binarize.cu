@@ -6,6 +6,7 @@
 // (origami/batch/detect/layout.py:157-169).  The thresholds are scikit-image 0.16.2's
 // threshold_otsu / threshold_sauvola; both are restated with exact integer window sums /
 // histograms followed by the same float64 operations in the same order.
+#include <cstdlib>
 #include <mutex>
 
 #include "og_common.cuh"
@@ -437,6 +438,199 @@ __global__ void __launch_bounds__(BTHREADS) og_sauvola_strips_kernel(
 	}
 }
 
+// ---------------------------------------------------------------------------------------
+// Column-streaming Sauvola (round 2).  A CTA owns a stripe of SS_W output columns and a run of
+// rows and walks down the image: a thread per input column (stripe + window radius on both sides)
+// keeps the sums of p and p^2 over the window's rows in registers and updates them with one row
+// entering and one leaving, so every source byte is read twice (entering, leaving; the second
+// read hits L1) instead of once per overlapping halo tile; the column sums of SS_R consecutive rows
+// go to shared memory, then every thread slides the horizontal window over four neighbouring
+// outputs of one of those rows (16-byte shared loads) and applies the threshold test of
+// sauvola_tile (fp32 screen, the reference's float64 sequence for the few pixels within 1e-3 of
+// the threshold).  Same exact integer window sums, same results.
+// ---------------------------------------------------------------------------------------
+constexpr int SS_W = 128;    // output columns per stripe
+constexpr int SS_R = 8;      // rows per barrier interval
+constexpr int SS_T = 256;    // threads: SS_R rows x (SS_W / 4) quads in the horizontal phase
+static_assert(SS_R * (SS_W / 4) == SS_T, "one thread per (row, quad)");
+
+__host__ __device__ inline int ss_pitch(int win) { return (SS_W + win - 1 + 3 + 4) & ~3; }  // u32 entries per row of column sums
+
+template <bool QUAD_OK>
+__device__ void sauvola_stream(const uint8_t *__restrict__ img, int h, int w, int64_t pitch,
+	uint8_t *__restrict__ out, int64_t out_pitch, int tx0, int y0, int y1, int win, double kk, double rr,
+	unsigned int *v1, unsigned int *v2) {
+	const int rad = win / 2, ncol = SS_W + 2 * rad, NP = ss_pitch(win);
+	const int tid = threadIdx.x;
+	// ---- vertical state: thread t owns input column tx0 - rad + t (reflect-101 at the image border)
+	// (ncol <= 128 + 126 = 254: one column per thread)
+	// Interior stripes of 4-byte aligned images take the quad path: a thread owns four neighbouring
+	// columns, reads them as two aligned words shifted into place, and writes its sums as 16-byte stores.
+	const int xs0 = tx0 - rad;                        // image column of sum index 0
+	const int nquad = (ncol + 3) >> 2;
+	const bool quad = QUAD_OK && xs0 >= 0 && ((xs0 + 4 * nquad + 3) | 3) < (int)pitch && tx0 + SS_W + rad <= w &&
+		((reinterpret_cast<uintptr_t>(img) | (uintptr_t)pitch) & 3) == 0;
+	const bool has_col = quad ? tid < nquad : tid < ncol;
+	const int qbyte = (xs0 + 4 * tid) & ~3, qshift = 8 * ((xs0 + 4 * tid) & 3);
+	const uint8_t *colp = img + (quad ? qbyte : (has_col ? reflect_index_fast(xs0 + tid, w) : 0));
+	unsigned int c1[4] = {0, 0, 0, 0}, c2[4] = {0, 0, 0, 0};
+	auto quad_at = [&](int yy) {  // the four bytes of this thread's columns in image row yy
+		const unsigned int *wp = reinterpret_cast<const unsigned int *>(colp + (int64_t)yy * pitch);
+		return __funnelshift_r(wp[0], wp[1], qshift);
+	};
+	auto add_quad = [&](unsigned int v) {
+#pragma unroll
+		for (int j = 0; j < 4; ++j) {
+			const unsigned int b = (v >> (8 * j)) & 255u;
+			c1[j] += b;
+			c2[j] += b * b;
+		}
+	};
+	auto sub_quad = [&](unsigned int v) {
+#pragma unroll
+		for (int j = 0; j < 4; ++j) {
+			const unsigned int b = (v >> (8 * j)) & 255u;
+			c1[j] -= b;
+			c2[j] -= b * b;
+		}
+	};
+	if (has_col) {
+		for (int yy = y0 - rad; yy < y0 + rad; ++yy) {  // rows y0 - rad .. y0 + rad - 1: the window of row y0 minus its last row
+			const int ry = reflect_index_fast(yy, h);
+			if (quad) add_quad(quad_at(ry));
+			else {
+				const unsigned int v = colp[(int64_t)ry * pitch];
+				c1[0] += v;
+				c2[0] += v * v;
+			}
+		}
+	}
+	// ---- horizontal role: row `hr` of the interval, outputs 4 * hq .. 4 * hq + 3 of the stripe
+	const int hr = tid / (SS_W / 4), hq = tid % (SS_W / 4);
+	const double n = (double)(win * win);
+	const unsigned int nwin = (unsigned int)(win * win);
+	const bool small_win = nwin <= 256u;
+	const float fc1 = (float)((1.0 - kk) / n), fc2 = (float)(kk / (n * n * rr));
+	const bool vec_io = ((reinterpret_cast<uintptr_t>(img) | (uintptr_t)pitch | reinterpret_cast<uintptr_t>(out) | (uintptr_t)out_pitch) & 3) == 0 && tx0 + SS_W <= w;
+
+	for (int yb = y0; yb < y1; yb += SS_R) {
+		__syncthreads();  // the previous interval's sums have been consumed
+		if (has_col) {
+			if (quad) {
+#pragma unroll
+				for (int i = 0; i < SS_R; ++i) {
+					const int y = yb + i;
+					add_quad(quad_at(reflect_index_fast(y + rad, h)));
+					*reinterpret_cast<uint4 *>(v1 + i * NP + 4 * tid) = make_uint4(c1[0], c1[1], c1[2], c1[3]);
+					*reinterpret_cast<uint4 *>(v2 + i * NP + 4 * tid) = make_uint4(c2[0], c2[1], c2[2], c2[3]);
+					sub_quad(quad_at(reflect_index_fast(y - rad, h)));
+				}
+			} else {
+#pragma unroll
+				for (int i = 0; i < SS_R; ++i) {
+					const int y = yb + i;
+					const unsigned int vin = colp[(int64_t)reflect_index_fast(y + rad, h) * pitch];
+					c1[0] += vin;
+					c2[0] += vin * vin;
+					v1[i * NP + tid] = c1[0];
+					v2[i * NP + tid] = c2[0];
+					const unsigned int vout = colp[(int64_t)reflect_index_fast(y - rad, h) * pitch];
+					c1[0] -= vout;
+					c2[0] -= vout * vout;
+				}
+			}
+		}
+		__syncthreads();
+		const int y = yb + hr;
+		if (y < y1 && y < h && tx0 + 4 * hq < w) {
+			const unsigned int *r1 = v1 + hr * NP + 4 * hq, *r2 = v2 + hr * NP + 4 * hq;
+			// window of output j covers column sums 4 hq + j .. 4 hq + j + 2 rad
+			unsigned int s1 = 0, s2 = 0;
+			int e = 0;
+			for (; e + 4 <= win; e += 4) {
+				const uint4 a = *reinterpret_cast<const uint4 *>(r1 + e), b = *reinterpret_cast<const uint4 *>(r2 + e);
+				s1 += a.x + a.y + a.z + a.w;
+				s2 += b.x + b.y + b.z + b.w;
+			}
+			for (; e < win; ++e) {
+				s1 += r1[e];
+				s2 += r2[e];
+			}
+			const uint8_t *cen = img + (int64_t)y * pitch + tx0 + 4 * hq;
+			unsigned int pv4;
+			const int nvalid = min(4, w - (tx0 + 4 * hq));
+			if (vec_io) pv4 = *reinterpret_cast<const unsigned int *>(cen);
+			else {
+				pv4 = 0;
+				for (int j = 0; j < nvalid; ++j) pv4 |= (unsigned int)cen[j] << (8 * j);
+			}
+			unsigned int res = 0;
+#pragma unroll
+			for (int j = 0; j < 4; ++j) {
+				if (j > 0) {
+					s1 += r1[j - 1 + win] - r1[j - 1];
+					s2 += r2[j - 1 + win] - r2[j - 1];
+				}
+				const int pv = (pv4 >> (8 * j)) & 255;
+				// screening in fp32 as in sauvola_tile: D = n S2 - S1^2 exact in integers
+				const float fD = small_win ? (float)(nwin * s2 - s1 * s1)
+					: (float)((unsigned long long)nwin * s2 - (unsigned long long)s1 * s1);
+				// s1 < 2^23 and pv < 2^8: exact integer -> float through the mantissa of 2^23 (no conversion
+				// instruction); the square root of the screen may be approximate (2 ulp): its error, 6e-5 gray
+				// levels at most, stays far inside the 1e-3 margin that hands a pixel to the float64 sequence
+				const float fs1 = __fsub_rn(__int_as_float(0x4B000000 | (int)s1), 8388608.0f);
+				const float fpv = __fsub_rn(__int_as_float(0x4B000000 | pv), 8388608.0f);
+				float rt;
+				asm("sqrt.approx.f32 %0, %1;" : "=f"(rt) : "f"(fD));
+				const float ta = __fmul_rn(fs1, __fadd_rn(fc1, __fmul_rn(fc2, rt)));
+				const float diff = __fsub_rn(fpv, ta);
+				bool white;
+				if (fabsf(diff) > 1.0e-3f) {
+					white = diff > 0.f;
+				} else {
+					const double m = __ddiv_rn((double)s1, n);
+					const double g2 = __ddiv_rn((double)s2, n);
+					double var = __dsub_rn(g2, __dmul_rn(m, m));
+					var = var > 0.0 ? var : 0.0;
+					const double sd = __dsqrt_rn(var);
+					const double t = __dmul_rn(m, __dadd_rn(1.0, __dmul_rn(kk, __dsub_rn(__ddiv_rn(sd, rr), 1.0))));
+					white = (double)pv > t;
+				}
+				res |= (white ? 255u : 0u) << (8 * j);
+			}
+			uint8_t *o = out + (int64_t)y * out_pitch + tx0 + 4 * hq;
+			if (vec_io) *reinterpret_cast<unsigned int *>(o) = res;
+			else for (int j = 0; j < nvalid; ++j) o[j] = (uint8_t)(res >> (8 * j));
+		}
+	}
+}
+
+__global__ void __launch_bounds__(SS_T) og_sauvola_stream_page_kernel(
+	const uint8_t *__restrict__ src, int h, int w, int64_t src_pitch, uint8_t *__restrict__ dst, int64_t dst_pitch,
+	int win, double kk, double rr, int seg_rows) {
+	extern __shared__ __align__(16) unsigned char smem_raw[];
+	unsigned int *v1 = reinterpret_cast<unsigned int *>(smem_raw);
+	unsigned int *v2 = v1 + SS_R * ss_pitch(win);
+	const int y0 = blockIdx.y * seg_rows;
+	sauvola_stream<true>(src, h, w, src_pitch, dst, dst_pitch, blockIdx.x * SS_W, y0, min(h, y0 + seg_rows), win, kk, rr, v1, v2);
+}
+
+// strips: item = (line, stripe of SS_W columns); the strip is a (h, w) image of pitch w
+__global__ void __launch_bounds__(SS_T) og_sauvola_stream_strips_kernel(
+	const uint8_t *__restrict__ gray, const int32_t *__restrict__ steps, const int64_t *__restrict__ pix_offsets,
+	int n, uint8_t *__restrict__ out, int64_t capacity, int win, double kk, double rr) {
+	extern __shared__ __align__(16) unsigned char smem_raw[];
+	unsigned int *v1 = reinterpret_cast<unsigned int *>(smem_raw);
+	unsigned int *v2 = v1 + SS_R * ss_pitch(win);
+	for (int li = blockIdx.x; li < n; li += gridDim.x) {
+		const int w = steps[2 * li], h = steps[2 * li + 1];
+		const int64_t off = pix_offsets[li];
+		if (w <= 0 || h <= 0 || off + (int64_t)w * h > capacity) continue;  // a strip that does not fit is skipped whole
+		for (int tx0 = 0; tx0 < w; tx0 += SS_W)
+			sauvola_stream<false>(gray + off, h, w, w, out + off, w, tx0, 0, h, win, kk, rr, v1, v2);
+	}
+}
+
 int check_window(int window) {
 	OG_REQUIRE(window >= 3 && (window & 1) == 1, OG_E_WINDOW,
 		"Window size w = %d must be odd and greater than 1.", window);
@@ -461,12 +655,10 @@ int og_binarize_strips_impl(const uint8_t *gray, const int32_t *steps, const int
 	int rc = check_window(window);
 	if (rc) return rc;
 	OG_REQUIRE(gray != out, OG_E_ARG, "Sauvola cannot run in place");
-	const size_t smem = sauvola_smem_bytes<ST_WS>(window);
-	cudaError_t e = cudaFuncSetAttribute(og_sauvola_strips_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-	if (e != cudaSuccess) return og_set_error((int)e, "cudaFuncSetAttribute: %s", cudaGetErrorString(e));
-	og_sauvola_strips_kernel<<<og_num_sms() * 4, BTHREADS, smem, st>>>(gray, steps, pix_offsets, chunk_offsets, n, out,
+	const size_t smem = (size_t)2 * SS_R * ss_pitch(window) * sizeof(unsigned int);
+	og_sauvola_stream_strips_kernel<<<min(n, og_num_sms() * 6), SS_T, smem, st>>>(gray, steps, pix_offsets, n, out,
 		capacity, window, 0.2, 127.5);
-	return og_check_launch("og_sauvola_strips_kernel");
+	return og_check_launch("og_sauvola_stream_strips_kernel");
 }
 
 extern "C" int og_binarize_strips(const uint8_t *gray, const int32_t *steps, const int64_t *pix_offsets,
@@ -483,13 +675,30 @@ extern "C" int og_sauvola(const uint8_t *src, int h, int w, int64_t src_pitch, i
 	OG_REQUIRE(src != dst, OG_E_ARG, "Sauvola cannot run in place");
 	int rc = check_window(window);
 	if (rc) return rc;
-	const size_t smem = sauvola_smem_bytes<ST_W>(window);
-	cudaError_t e = cudaFuncSetAttribute(og_sauvola_page_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-	if (e != cudaSuccess) return og_set_error((int)e, "cudaFuncSetAttribute: %s", cudaGetErrorString(e));
-	const int64_t tiles = (int64_t)((w + ST_W - 1) / ST_W) * ((h + ST_H - 1) / ST_H);
-	const int blocks = (int)(tiles < (int64_t)og_num_sms() * 8 ? tiles : (int64_t)og_num_sms() * 8);
-	og_sauvola_page_kernel<<<blocks, BTHREADS, smem, (cudaStream_t)stream>>>(src, h, w, src_pitch, dst, dst_pitch, window, k, r);
-	return og_check_launch("og_sauvola_page_kernel");
+	if (getenv("OG_SAUVOLA_STREAM") == nullptr) {
+		// Pages: the tile kernel (0.160 ms for 4800x7200, window 15).  The column-streaming kernel below reads every
+		// byte twice instead of once per overlapping halo tile, but its running sums serialise a CTA's rows
+		// (0.21 - 0.25 ms measured): it is what the strips use (0.52 -> 0.37 ms) and stays selectable here.
+		const size_t smem = sauvola_smem_bytes<ST_W>(window);
+		cudaError_t e = cudaFuncSetAttribute(og_sauvola_page_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+		if (e != cudaSuccess) return og_set_error((int)e, "cudaFuncSetAttribute: %s", cudaGetErrorString(e));
+		const int64_t tiles = (int64_t)((w + ST_W - 1) / ST_W) * ((h + ST_H - 1) / ST_H);
+		const int blocks = (int)(tiles < (int64_t)og_num_sms() * 8 ? tiles : (int64_t)og_num_sms() * 8);
+		og_sauvola_page_kernel<<<blocks, BTHREADS, smem, (cudaStream_t)stream>>>(src, h, w, src_pitch, dst, dst_pitch, window, k, r);
+		return og_check_launch("og_sauvola_page_kernel");
+	}
+	// stripes of SS_W columns x runs of rows, about six CTAs per SM; a run re-reads `window - 1` rows of warm-up
+	const int stripes = (w + SS_W - 1) / SS_W;
+	int segments = (og_num_sms() * 6 + stripes - 1) / stripes;
+	segments = max(1, min(segments, (h + 4 * window - 1) / (4 * window)));  // runs of at least four window heights
+	int seg_rows = (h + segments - 1) / segments;
+	seg_rows = (seg_rows + SS_R - 1) / SS_R * SS_R;
+	segments = (h + seg_rows - 1) / seg_rows;
+	OG_REQUIRE(segments <= 65535, OG_E_RANGE, "image too tall");
+	const size_t smem = (size_t)2 * SS_R * ss_pitch(window) * sizeof(unsigned int);
+	og_sauvola_stream_page_kernel<<<dim3(stripes, segments), SS_T, smem, (cudaStream_t)stream>>>(src, h, w, src_pitch, dst, dst_pitch,
+		window, k, r, seg_rows);
+	return og_check_launch("og_sauvola_stream_page_kernel");
 }
 
 extern "C" int og_otsu(const uint8_t *src, int h, int w, int64_t src_pitch,
