@@ -198,6 +198,46 @@ int og_pack_strips(const uint8_t *strips, const int32_t *steps, const int64_t *p
 	int min_w, int min_h, int pad_value, int H, int w_max,
 	uint8_t *batch_out, int32_t *slot_scratch, int32_t *widths_out, int32_t *kept_index_out, int32_t *n_kept_out, void *stream);
 
+/* A triangulation with vertex values on the device (all pointers are DEVICE pointers): what
+ * og_tri_interp takes as separate arguments, as one struct for the entry points that need two of them. */
+typedef struct og_tri_tables {
+	const int32_t *cell_start;  /* (gy * gx + 1) offsets into cell_tris                              */
+	const int32_t *cell_tris;   /* triangle indices per bucket                                       */
+	const double *transform;    /* (m, 3, 2) scipy.spatial.Delaunay.transform                        */
+	const int32_t *simplices;   /* (m, 3) vertex indices                                             */
+	const double *values;       /* (n_vertices, 2)                                                   */
+	double ox, oy, cell, eps;   /* bucket grid origin, bucket size; barycentric tolerance            */
+	int32_t gx, gy;
+} og_tri_tables;
+
+/* A scalar angle field as origami/core/dewarp.py:108-122 builds it with lingrid.lininterp: values
+ * component 0 = phi; `inter` over the samples (has_inter = 0 when they are collinear), `extra` over the
+ * hull / box / corner points, queries clipped to bounds = (minx, miny, maxx, maxy); with fewer than three
+ * samples the field is the constant phi0 (constant = 1, the tables are ignored).  HOST struct. */
+typedef struct og_field {
+	og_tri_tables inter, extra;
+	double bounds[4];
+	double phi0;
+	int32_t has_inter, constant;
+} og_field;
+
+/* (f)1  GridFactory's Euler integration -- origami/core/dewarp.py:123-141 (Field.estimate_extent),
+ * :341-419 (extend_border_h / _v), :421-439 (grid_h): n_points float32 points advance n_steps times by
+ * `step` pixels along (cos phi, sin phi) of the field (evaluated in float32 as Field.get does).
+ * start_xy (n_points, 2) f32 -> out_xy (n_steps, n_points, 2) f32, out[k] = positions before step k. */
+int og_field_march(const og_field *field, const float *start_xy, int n_points, int n_steps, float step,
+	float *out_xy, void *stream);
+
+/* (f)1  GridFactory.grid_hv's vertical lines -- origami/core/dewarp.py:441-470 with BatchIntersections
+ * (:176-263): for columns col0 .. col0 + ncols - 1 of the lattice, starting on h-line 0, a ray of
+ * max_step_len along the vertical field is intersected with the polyline of the next h-line (rows
+ * further down are tried when it is missed) and the nearest crossing becomes the next node.  grid_h
+ * (gh, gw, 2) f32 with the end points of every h-line already pushed outwards as the reference's
+ * make_row_slice does; grid_hv_out (gh, gw, 2) f32 receives the columns; *status_out is set to
+ * 1 + column where no crossing was found (the reference raises there), left untouched otherwise. */
+int og_grid_vlines(const og_field *field_v, const float *grid_h, int gh, int gw, int col0, int ncols,
+	float max_step_len, float *grid_hv_out, int32_t *status_out, void *stream);
+
 /* (f)2  Grid.transformer / lininterp evaluation -- origami/core/dewarp.py:143-161, 555-559 and
  * origami/core/lingrid.py:185-206, 266-275 (scipy.interpolate.LinearNDInterpolator over the warped
  * lattice nodes), applied to all contour vertices of a page by origami/batch/detect/dewarp.py:16-39.

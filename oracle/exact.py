@@ -817,3 +817,120 @@ def split_detector(pixels, scale, quantile=0.9, smooth=1, intensity=0.05, width=
 	ink_h[-span:] = 0
 	peaks, info = scipy.signal.find_peaks(-ink_h, height=-intensity, distance=int(width * scale))
 	return peaks, info, colq
+
+
+# --------------------------------------------------------------------------------------
+# (f)1  GridFactory                 origami/core/dewarp.py:108-141, 176-263, 292-493
+# --------------------------------------------------------------------------------------
+
+def _field(points, values, size, phi0):
+	"""Field (dewarp.py:108-122): angles by lininterp, directions as float32 cos / sin."""
+	if len(points) <= 2:
+		angle = lambda pts: np.full(len(pts), phi0)  # noqa: E731
+	else:
+		f = lininterp(np.asarray(points, F64), np.asarray(values, F64), (0, 0, size[0], size[1]))
+		angle = lambda pts: f(np.array(pts))[0][:, 0]  # noqa: E731
+
+	def get(pts):
+		a = angle(pts)
+		return np.squeeze(np.dstack([np.cos(a, dtype=F32), np.sin(a, dtype=F32)]), axis=0)
+	return get
+
+
+def _estimate_extent(get, size, axis, limit, step_size):
+	"""Field.estimate_extent (dewarp.py:123-141)."""
+	pts = np.array([[0, y] for y in range(0, size[1 - axis], step_size)]).astype(F32)
+	if axis != 0:
+		pts = np.flip(pts, axis=-1).copy()
+	n_steps = 1
+	max_steps = 2 * (1 + size[axis] // n_steps)
+	while np.any(pts[:, axis] < limit) and n_steps < max_steps:
+		pts += get(pts) * step_size
+		n_steps += 1
+	if n_steps >= max_steps:
+		raise RuntimeError("n_steps exceeded")
+	return n_steps
+
+
+def _nearest_crossing(p0, p1, line):
+	"""Nearest point to p0 where segment p0-p1 crosses the polyline `line` (k, 2), or None:
+	ShapelyBatchIntersections.__call__ (dewarp.py:218-262) for one ray and one row."""
+	a = np.asarray(p0, F64)
+	r = np.asarray(p1, F64) - a
+	q = line[:-1].astype(F64)
+	s = line[1:].astype(F64) - q
+	den = r[0] * s[:, 1] - r[1] * s[:, 0]
+	with np.errstate(divide="ignore", invalid="ignore"):
+		t = ((q[:, 0] - a[0]) * s[:, 1] - (q[:, 1] - a[1]) * s[:, 0]) / den
+		u = ((q[:, 0] - a[0]) * r[1] - (q[:, 1] - a[1]) * r[0]) / den
+	ok = (den != 0) & (t >= 0) & (t <= 1) & (u >= 0) & (u <= 1)
+	if not ok.any():
+		return None
+	pts = a[None, :] + t[ok, None] * r[None, :]
+	return pts[np.argmin(np.linalg.norm(pts - a, axis=1))]
+
+
+def grid_factory(size, samples_h, samples_v, grid_res=25, num_threads=2):
+	"""GridFactory.grid_hv (dewarp.py:292-493) for a page of `size` = (width, height); samples_* =
+	(points (n, 2), angles (n,)).  Returns the float32 (gh, gw, 2) grid."""
+	width, height = size
+	get_h = _field(samples_h[0], samples_h[1], size, 0.0)
+	get_v = _field(samples_v[0], samples_v[1], size, math.pi / 2)
+	gw = _estimate_extent(get_h, size, 0, width, grid_res)
+	gh = _estimate_extent(get_v, size, 1, height, grid_res)
+	grid_h = np.zeros((gh, gw, 2), dtype=F32)
+	pts = np.array([[0, gy * grid_res] for gy in range(gh)], dtype=F32)
+	for gx in range(gw):
+		grid_h[:, gx, :] = pts
+		pts += get_h(pts) * grid_res
+	# make_row_slice (dewarp.py:198-216) pushes the end points of rows 1.. outwards, in place
+	large = gw * grid_res
+	for gy in range(1, gh):
+		for a, b in ((1, 0), (-2, -1)):
+			v = grid_h[gy, b] - grid_h[gy, a]
+			v /= np.linalg.norm(v)
+			grid_h[gy, b] = grid_h[gy, b] + large * v
+	grid_hv = np.zeros(grid_h.shape, dtype=F32)
+	s = math.ceil(gw / num_threads) if num_threads >= 2 else gw
+	for c0 in range(0, gw, s):
+		sel = slice(c0, c0 + s)
+		max_dy = 0
+		for gy in range(1, gh):
+			max_dy = max(max_dy, np.max(grid_h[gy, sel, 1]) - np.min(grid_h[gy - 1, sel, 1]))
+		max_step_len = max_dy / math.cos(60 * (math.pi / 180))
+		pts0 = grid_h[0][sel].copy()
+		for gy in range(gh - 1):
+			grid_hv[gy, sel, :] = pts0
+			pts1 = pts0 + get_v(pts0) * max_step_len
+			for i in range(len(pts0)):
+				hit, dy = None, 0
+				while hit is None:
+					if gy + 1 + dy >= gh:
+						raise RuntimeError("failed to find intersection")
+					hit = _nearest_crossing(pts0[i], pts1[i], grid_h[gy + 1 + dy])
+					dy += 1
+				pts1[i] = hit
+			pts0 = pts1
+		grid_hv[-1, sel, :] = pts0
+
+	def extend(grid, get, start, cond, step, stack, first):
+		borders = [start]
+		while cond(borders[-1]):
+			borders.append((borders[-1] + get(borders[-1]) * step).astype(F32))
+		new = borders[1:]
+		if not new:
+			return grid
+		return stack(new, first)
+
+	gh0 = grid_hv.shape[0]
+	new = extend(grid_hv, get_h, grid_hv[:, 0].copy(), lambda x: np.any(x[:, 0] > 0), -grid_res,
+		lambda n, g: np.hstack([b.reshape(gh0, 1, 2) for b in reversed(n)] + [g]), grid_hv)
+	grid_hv = new
+	grid_hv = extend(grid_hv, get_h, grid_hv[:, -1].copy(), lambda x: np.any(x[:, 0] < width), grid_res,
+		lambda n, g: np.hstack([g] + [b.reshape(gh0, 1, 2) for b in n]), grid_hv)
+	gw1 = grid_hv.shape[1]
+	grid_hv = extend(grid_hv, get_v, grid_hv[0, :].copy(), lambda x: np.any(x[:, 1] > 0), -grid_res,
+		lambda n, g: np.vstack([b.reshape(1, gw1, 2) for b in reversed(n)] + [g]), grid_hv)
+	grid_hv = extend(grid_hv, get_v, grid_hv[-1, :].copy(), lambda x: np.any(x[:, 1] < height), grid_res,
+		lambda n, g: np.vstack([g] + [b.reshape(1, gw1, 2) for b in n]), grid_hv)
+	return grid_hv

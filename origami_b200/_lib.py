@@ -35,6 +35,19 @@ LINE_DTYPE = np.dtype([
 	align=True)
 assert LINE_DTYPE.itemsize == 112
 
+class TriTables(ctypes.Structure):
+	"""struct og_tri_tables (include/origami_b200.h)"""
+	_fields_ = [("cell_start", c_void_p), ("cell_tris", c_void_p), ("transform", c_void_p), ("simplices", c_void_p),
+		("values", c_void_p), ("ox", c_double), ("oy", c_double), ("cell", c_double), ("eps", c_double),
+		("gx", ctypes.c_int32), ("gy", ctypes.c_int32)]
+
+
+class Field(ctypes.Structure):
+	"""struct og_field (include/origami_b200.h)"""
+	_fields_ = [("inter", TriTables), ("extra", TriTables), ("bounds", c_double * 4), ("phi0", c_double),
+		("has_inter", ctypes.c_int32), ("constant", ctypes.c_int32)]
+
+
 # name -> argtypes; every function returns int except the two string getters
 _SIGNATURES = {
 	"og_expand_map": [c_void_p, c_int, c_int, c_int, c_void_p, c_void_p],
@@ -51,6 +64,8 @@ _SIGNATURES = {
 		c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p],
 	"og_tri_interp": [c_void_p, c_int64, c_void_p, c_void_p, c_void_p, c_int, c_int, c_double, c_double, c_double,
 		c_void_p, c_void_p, c_void_p, c_double, c_void_p, c_int, c_void_p],
+	"og_field_march": [ctypes.POINTER(Field), c_void_p, c_int, c_int, c_float, c_void_p, c_void_p],
+	"og_grid_vlines": [ctypes.POINTER(Field), c_void_p, c_int, c_int, c_int, c_int, c_float, c_void_p, c_void_p, c_void_p],
 	"og_sauvola": [c_void_p, c_int, c_int, c_int64, c_int, c_double, c_double, c_void_p, c_int64, c_void_p],
 	"og_otsu": [c_void_p, c_int, c_int, c_int64, c_void_p, c_int64, c_void_p, c_void_p, c_void_p],
 	"og_otsu_noalloc": [c_void_p, c_int, c_int, c_int64, c_void_p, c_int64, c_void_p, c_void_p],

@@ -8,7 +8,6 @@ Differences that are deliberate:
   * Dewarper.dewarp_image does not scale the cached dense map in place (the reference does,
     origami/core/dewarp.py:621-623, which corrupts later Grid.points("full") users); the
     scale is folded into the kernel instead.
-  * Grid.create (GridFactory, SURVEY.md section 8(f) "next") is not part of this path.
 """
 
 import io
@@ -79,6 +78,13 @@ class Grid:
 		dy = (pts[1:, :, 0] - pts[:-1, :, 1]).flatten()
 		dx = (pts[:, 1:, 1] - pts[:, :-1, 0]).flatten()
 		return max(np.std(dx), np.std(dy))
+
+	@staticmethod
+	def create(*args, **kwargs):
+		"""reference :532-535: the grid of a page from its flow samples (GridFactory)."""
+		from .gridfactory import GridFactory
+		factory = GridFactory(*args, **kwargs)
+		return Grid(factory.grid_hv, factory.res, device=kwargs.get("device"))
 
 	@staticmethod
 	def open(path, device=None):

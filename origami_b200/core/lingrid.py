@@ -198,6 +198,15 @@ class DeviceTriangulation:
 		self.values = torch.from_numpy(values).to(device)
 		self.n_simplices = m
 
+	def tables(self, eps=1e-9):
+		"""struct og_tri_tables over this triangulation (the tensors must stay alive while it is used)."""
+		t = ops._lib.TriTables()
+		t.cell_start, t.cell_tris = self.cell_start.data_ptr(), self.cell_tris.data_ptr()
+		t.transform, t.simplices, t.values = self.transform.data_ptr(), self.simplices.data_ptr(), self.values.data_ptr()
+		t.ox, t.oy, t.cell, t.eps = self.ox, self.oy, self.cell, float(eps)
+		t.gx, t.gy = self.gx, self.gy
+		return t
+
 	def interp(self, pts_dev, clip_box, out=None, only_nan=False, eps=1e-9):
 		if out is None:
 			out = torch.empty_like(pts_dev)
@@ -215,6 +224,23 @@ class Interpolator:
 
 	def __init__(self, inter, extra, bounds, squeeze, device):
 		self._inter, self._extra, self._bounds, self._squeeze, self._device = inter, extra, bounds, squeeze, device
+
+	def field_struct(self):
+		"""struct og_field for the kernels that evaluate this (scalar) interpolant on the device."""
+		f = ops._lib.Field()
+		f.extra = self._extra.tables()
+		if self._inter is not None:
+			f.inter = self._inter.tables()
+		f.has_inter = 0 if self._inter is None else 1
+		f.constant = 0
+		f.phi0 = 0.0
+		for k in range(4):
+			f.bounds[k] = float(self._bounds[k])
+		return f
+
+	@property
+	def device(self):
+		return self._device
 
 	def device_call(self, pts_dev):
 		"""(n, 2) float64 CUDA tensor -> (n, 2) float64 CUDA tensor."""

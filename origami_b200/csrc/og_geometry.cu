@@ -15,69 +15,158 @@
 
 namespace {
 
-struct TriParams {
-	const double *pts;       // (n, 2) query points (x, y)
-	long long n;
-	double minx, miny, maxx, maxy;  // clip box applied to the queries (lingrid.py:196-197)
-	const int32_t *cell_start;      // (gy * gx + 1) offsets into cell_tris
-	const int32_t *cell_tris;       // triangle indices per bucket
-	int gx, gy;
-	double ox, oy, inv_cell;        // bucket grid origin and 1 / bucket size
-	const double *transform;        // (m, 3, 2): rows 0-1 = inverse edge matrix, row 2 = reference vertex (scipy Delaunay.transform)
-	const int32_t *simplices;       // (m, 3) vertex indices
-	const double *values;           // (n_vertices, 2)
-	double eps;                     // barycentric tolerance
-	double *out;                    // (n, 2)
-	int only_nan;                   // fill only the entries that hold NaN (second triangulation of lingrid's Interpolator)
-};
+// value of the piecewise-linear interpolant at (x, y); false (and NaN) where no triangle holds the point
+__device__ __forceinline__ bool tri_eval(const og_tri_tables &t, double x, double y, double &rx, double &ry) {
+	const double nan = __longlong_as_double(0x7ff8000000000000ll);
+	rx = ry = nan;
+	if (!(x == x && y == y)) return false;
+	const double inv_cell = 1.0 / t.cell;
+	const int cx = min(max((int)floor((x - t.ox) * inv_cell), 0), t.gx - 1);
+	const int cy = min(max((int)floor((y - t.oy) * inv_cell), 0), t.gy - 1);
+	const int beg = t.cell_start[cy * t.gx + cx], end = t.cell_start[cy * t.gx + cx + 1];
+	double best = -1.0e300;
+	int best_t = -1;
+	double bc0 = 0, bc1 = 0;
+	for (int k = beg; k < end; ++k) {
+		const int ti = t.cell_tris[k];
+		const double *T = t.transform + (size_t)ti * 6;
+		const double dx = x - T[4], dy = y - T[5];
+		const double c0 = T[0] * dx + T[1] * dy;
+		const double c1 = T[2] * dx + T[3] * dy;
+		const double c2 = 1.0 - c0 - c1;
+		const double m = fmin(c0, fmin(c1, c2));  // NaN transforms (degenerate simplices) never win
+		if (m > best) {
+			best = m;
+			best_t = ti;
+			bc0 = c0;
+			bc1 = c1;
+		}
+	}
+	if (best_t < 0 || best < -t.eps) return false;
+	const int32_t *s = t.simplices + (size_t)best_t * 3;
+	const double *v0 = t.values + 2 * (size_t)s[0], *v1 = t.values + 2 * (size_t)s[1], *v2 = t.values + 2 * (size_t)s[2];
+	const double c2 = 1.0 - bc0 - bc1;
+	rx = bc0 * v0[0] + bc1 * v1[0] + c2 * v2[0];
+	ry = bc0 * v0[1] + bc1 * v1[1] + c2 * v2[1];
+	return true;
+}
 
-__global__ void __launch_bounds__(256) og_tri_interp_kernel(const __grid_constant__ TriParams p) {
+__global__ void __launch_bounds__(256) og_tri_interp_kernel(const __grid_constant__ og_tri_tables t, const double *__restrict__ pts, long long n,
+	double minx, double miny, double maxx, double maxy, double *__restrict__ out, int only_nan) {
 	const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
-	if (i >= p.n) return;
-	if (p.only_nan) {
-		const double o = p.out[2 * i];
+	if (i >= n) return;
+	if (only_nan) {
+		const double o = out[2 * i];
 		if (o == o) return;
 	}
-	double x = p.pts[2 * i], y = p.pts[2 * i + 1];
-	x = fmin(fmax(x, p.minx), p.maxx);  // np.clip
-	y = fmin(fmax(y, p.miny), p.maxy);
-	const double nan = __longlong_as_double(0x7ff8000000000000ll);
-	double rx = nan, ry = nan;
-	if (x == x && y == y) {
-		const int cx = min(max((int)floor((x - p.ox) * p.inv_cell), 0), p.gx - 1);
-		const int cy = min(max((int)floor((y - p.oy) * p.inv_cell), 0), p.gy - 1);
-		const int beg = p.cell_start[cy * p.gx + cx], end = p.cell_start[cy * p.gx + cx + 1];
-		double best = -1.0e300;
-		int best_t = -1;
-		double bc0 = 0, bc1 = 0;
-		for (int k = beg; k < end; ++k) {
-			const int t = p.cell_tris[k];
-			const double *T = p.transform + (size_t)t * 6;
-			const double dx = x - T[4], dy = y - T[5];
-			const double c0 = T[0] * dx + T[1] * dy;
-			const double c1 = T[2] * dx + T[3] * dy;
-			const double c2 = 1.0 - c0 - c1;
-			const double m = fmin(c0, fmin(c1, c2));  // NaN transforms (degenerate simplices) never win
-			if (m > best) {
-				best = m;
-				best_t = t;
-				bc0 = c0;
-				bc1 = c1;
+	const double x = fmin(fmax(pts[2 * i], minx), maxx);  // np.clip (lingrid.py:196-197)
+	const double y = fmin(fmax(pts[2 * i + 1], miny), maxy);
+	double rx, ry;
+	tri_eval(t, x, y, rx, ry);
+	out[2 * i] = rx;
+	out[2 * i + 1] = ry;
+}
+
+// lingrid's Interpolator for a scalar field (component 0 of the values): clip, interpolate inside the
+// hull, extrapolate elsewhere; a field built from fewer than three samples is the constant phi0
+// (origami/core/dewarp.py:112-116)
+__device__ __forceinline__ double field_angle(const og_field &f, double x, double y) {
+	if (f.constant) return f.phi0;
+	x = fmin(fmax(x, f.bounds[0]), f.bounds[2]);
+	y = fmin(fmax(y, f.bounds[1]), f.bounds[3]);
+	double a, unused;
+	if (f.has_inter && tri_eval(f.inter, x, y, a, unused)) return a;
+	tri_eval(f.extra, x, y, a, unused);
+	return a;
+}
+
+// Field.get (dewarp.py:118-122): np.cos / np.sin of the angles evaluated as float32
+__device__ __forceinline__ float2 field_dir(const og_field &f, float px, float py) {
+	const float a = (float)field_angle(f, (double)px, (double)py);
+	return make_float2(cosf(a), sinf(a));
+}
+
+// Euler integration through a direction field (GridFactory.grid_h, extend_border_*, Field.estimate_extent,
+// dewarp.py:123-141, 341-439): P points advance n_steps times by `step` along the field; out[k] holds the
+// positions BEFORE step k (out[0] = the start points), all float32 as in the reference.
+__global__ void __launch_bounds__(128) og_field_march_kernel(const __grid_constant__ og_field f, const float2 *__restrict__ start, int P,
+	int n_steps, float step, float2 *__restrict__ out) {
+	const int i = blockIdx.x * blockDim.x + threadIdx.x;
+	if (i >= P) return;
+	float2 p = start[i];
+	for (int k = 0; k < n_steps; ++k) {
+		out[(size_t)k * P + i] = p;
+		const float2 d = field_dir(f, p.x, p.y);
+		p.x = __fadd_rn(p.x, __fmul_rn(d.x, step));  // pts += field(pts) * step
+		p.y = __fadd_rn(p.y, __fmul_rn(d.y, step));
+	}
+}
+
+// GridFactory.grid_hv's column marching (dewarp.py:441-470 with BatchIntersections :176-263): a thread owns
+// a column of the lattice; from its node on h-line gy it casts a ray of length max_step_len along the
+// vertical field and moves to the nearest crossing with the polyline of h-line gy + 1 (the next rows are
+// tried when that one is missed).  grid_h holds the h-lines with their end points already pushed outwards
+// (make_row_slice does that in place in the reference).
+__global__ void __launch_bounds__(64) og_grid_vlines_kernel(const __grid_constant__ og_field fv, const float2 *__restrict__ grid_h, int gh, int gw,
+	int col0, int ncols, float max_step_len, float2 *__restrict__ grid_hv, int *__restrict__ status) {
+	const int c = blockIdx.x * blockDim.x + threadIdx.x;
+	if (c >= ncols) return;
+	const int col = col0 + c;
+	float2 p0 = grid_h[col];
+	for (int gy = 0; gy < gh - 1; ++gy) {
+		grid_hv[(size_t)gy * gw + col] = p0;
+		const float2 d = field_dir(fv, p0.x, p0.y);
+		const float2 p1 = make_float2(__fadd_rn(p0.x, __fmul_rn(d.x, max_step_len)), __fadd_rn(p0.y, __fmul_rn(d.y, max_step_len)));
+		const double ax = p0.x, ay = p0.y, rx = (double)p1.x - ax, ry = (double)p1.y - ay;
+		bool found = false;
+		double bx = 0, by = 0;
+		for (int row = gy + 1; row < gh && !found; ++row) {  // `dy += 1  # retry on next row`
+			double best = 1.0e300;
+			const float2 *line = grid_h + (size_t)row * gw;
+			for (int j = 0; j + 1 < gw; ++j) {
+				const double qx = line[j].x, qy = line[j].y, sx = (double)line[j + 1].x - qx, sy = (double)line[j + 1].y - qy;
+				const double den = rx * sy - ry * sx;
+				if (den == 0.0) continue;
+				const double t = ((qx - ax) * sy - (qy - ay) * sx) / den;  // along the ray
+				const double u = ((qx - ax) * ry - (qy - ay) * rx) / den;  // along the segment
+				if (t >= 0.0 && t <= 1.0 && u >= 0.0 && u <= 1.0) {
+					const double ix = ax + t * rx, iy = ay + t * ry;
+					const double dist = (ix - ax) * (ix - ax) + (iy - ay) * (iy - ay);
+					if (dist < best) {
+						best = dist;
+						bx = ix;
+						by = iy;
+						found = true;
+					}
+				}
 			}
 		}
-		if (best_t >= 0 && best >= -p.eps) {
-			const int32_t *s = p.simplices + (size_t)best_t * 3;
-			const double *v0 = p.values + 2 * (size_t)s[0], *v1 = p.values + 2 * (size_t)s[1], *v2 = p.values + 2 * (size_t)s[2];
-			const double c2 = 1.0 - bc0 - bc1;
-			rx = bc0 * v0[0] + bc1 * v1[0] + c2 * v2[0];
-			ry = bc0 * v0[1] + bc1 * v1[1] + c2 * v2[1];
+		if (!found) {
+			atomicExch(status, 1 + col);  // "failed to find intersection" (dewarp.py:244-246)
+			bx = p1.x;
+			by = p1.y;
 		}
+		p0 = make_float2((float)bx, (float)by);
 	}
-	p.out[2 * i] = rx;
-	p.out[2 * i + 1] = ry;
+	grid_hv[(size_t)(gh - 1) * gw + col] = p0;
 }
 
 }  // namespace
+
+static int check_tables(const og_tri_tables *t, const char *what) {
+	OG_REQUIRE(t->cell_start != nullptr && t->cell_tris != nullptr && t->transform != nullptr && t->simplices != nullptr && t->values != nullptr,
+		OG_E_ARG, "%s: triangulation table is NULL", what);
+	OG_REQUIRE(t->gx > 0 && t->gy > 0 && t->cell > 0.0, OG_E_ARG, "%s: bucket grid %d x %d / size invalid", what, t->gx, t->gy);
+	return OG_OK;
+}
+
+static int check_field(const og_field *f) {
+	OG_REQUIRE(f != nullptr, OG_E_ARG, "field is NULL");
+	if (f->constant) return OG_OK;
+	int rc = check_tables(&f->extra, "field.extra");
+	if (rc) return rc;
+	return f->has_inter ? check_tables(&f->inter, "field.inter") : OG_OK;
+}
 
 extern "C" int og_tri_interp(const double *pts, int64_t n, const double *clip_box,
 	const int32_t *cell_start, const int32_t *cell_tris, int gx, int gy, double ox, double oy, double cell,
@@ -86,19 +175,40 @@ extern "C" int og_tri_interp(const double *pts, int64_t n, const double *clip_bo
 	OG_REQUIRE(n >= 0, OG_E_ARG, "n < 0");
 	if (n == 0) return OG_OK;
 	OG_REQUIRE(pts != nullptr && out != nullptr && clip_box != nullptr, OG_E_ARG, "pts / out / clip_box is NULL");
-	OG_REQUIRE(cell_start != nullptr && cell_tris != nullptr && transform != nullptr && simplices != nullptr && values != nullptr,
-		OG_E_ARG, "triangulation table is NULL");
-	OG_REQUIRE(gx > 0 && gy > 0 && cell > 0.0, OG_E_ARG, "bucket grid %d x %d / size invalid", gx, gy);
-	TriParams p{};
-	p.pts = pts; p.n = n;
-	p.minx = clip_box[0]; p.miny = clip_box[1]; p.maxx = clip_box[2]; p.maxy = clip_box[3];  // HOST array of 4 doubles
-	p.cell_start = cell_start; p.cell_tris = cell_tris;
-	p.gx = gx; p.gy = gy; p.ox = ox; p.oy = oy; p.inv_cell = 1.0 / cell;
-	p.transform = transform; p.simplices = simplices; p.values = values;
-	p.eps = eps;
-	p.out = out; p.only_nan = only_nan;
-	og_tri_interp_kernel<<<(unsigned)((n + 255) / 256), 256, 0, (cudaStream_t)stream>>>(p);
+	og_tri_tables t{};
+	t.cell_start = cell_start; t.cell_tris = cell_tris;
+	t.gx = gx; t.gy = gy; t.ox = ox; t.oy = oy; t.cell = cell;
+	t.transform = transform; t.simplices = simplices; t.values = values;
+	t.eps = eps;
+	int rc = check_tables(&t, "og_tri_interp");
+	if (rc) return rc;
+	og_tri_interp_kernel<<<(unsigned)((n + 255) / 256), 256, 0, (cudaStream_t)stream>>>(t, pts, n,
+		clip_box[0], clip_box[1], clip_box[2], clip_box[3], out, only_nan);  // clip_box: HOST array of 4 doubles
 	return og_check_launch("og_tri_interp_kernel");
+}
+
+extern "C" int og_field_march(const og_field *field, const float *start_xy, int n_points, int n_steps, float step,
+	float *out_xy, void *stream) {
+	int rc = check_field(field);
+	if (rc) return rc;
+	OG_REQUIRE(n_points >= 0 && n_steps >= 0, OG_E_ARG, "negative count");
+	if (n_points == 0 || n_steps == 0) return OG_OK;
+	OG_REQUIRE(start_xy != nullptr && out_xy != nullptr, OG_E_ARG, "NULL pointer");
+	og_field_march_kernel<<<(n_points + 127) / 128, 128, 0, (cudaStream_t)stream>>>(*field, reinterpret_cast<const float2 *>(start_xy),
+		n_points, n_steps, step, reinterpret_cast<float2 *>(out_xy));
+	return og_check_launch("og_field_march_kernel");
+}
+
+extern "C" int og_grid_vlines(const og_field *field_v, const float *grid_h, int gh, int gw, int col0, int ncols,
+	float max_step_len, float *grid_hv_out, int32_t *status_out, void *stream) {
+	int rc = check_field(field_v);
+	if (rc) return rc;
+	OG_REQUIRE(grid_h != nullptr && grid_hv_out != nullptr && status_out != nullptr, OG_E_ARG, "NULL pointer");
+	OG_REQUIRE(gh >= 2 && gw >= 2 && col0 >= 0 && ncols >= 0 && col0 + ncols <= gw, OG_E_ARG, "grid (%d, %d) / column slice invalid", gh, gw);
+	if (ncols == 0) return OG_OK;
+	og_grid_vlines_kernel<<<(ncols + 63) / 64, 64, 0, (cudaStream_t)stream>>>(*field_v, reinterpret_cast<const float2 *>(grid_h), gh, gw,
+		col0, ncols, max_step_len, reinterpret_cast<float2 *>(grid_hv_out), status_out);
+	return og_check_launch("og_grid_vlines_kernel");
 }
 
 // ---------------------------------------------------------------------------------------

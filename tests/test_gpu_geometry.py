@@ -158,3 +158,37 @@ def test_split_detector_matches_scipy(cuda, shape, dtype):
 	if h > 16:
 		gp, gi = det(px, 20, cuda)
 		assert np.array_equal(gp, peaks) and np.allclose(gi["peak_heights"], info["peak_heights"], rtol=1e-3, atol=1e-6)
+
+
+def _flow_samples(W, H, n, seed):
+	rng = np.random.default_rng(seed)
+	ph = rng.uniform(0, [W, H], (n, 2))
+	ah = 0.02 * np.sin(ph[:, 1] / 200) + 0.01 * np.cos(ph[:, 0] / 170)
+	pv = rng.uniform(0, [W, H], (n, 2))
+	av = np.pi / 2 + 0.02 * np.cos(pv[:, 0] / 150) - 0.01 * np.sin(pv[:, 1] / 230)
+	return (ph, ah), (pv, av)
+
+
+@pytest.mark.parametrize("W,H,n,threads", [(600, 800, 60, 2), (1000, 700, 150, 1), (500, 500, 2, 2)])
+def test_grid_factory_matches_the_numpy_scipy_restatement(cuda, W, H, n, threads):
+	"""flow samples -> sparse dewarping grid (origami/core/dewarp.py:292-493).
+	Floating point: float32 positions, CUDA cosf / sinf against NumPy's, float64 segment crossings
+	against GEOS-free NumPy ones -> 5e-3 px over the whole grid; the shape must be equal."""
+	from origami_b200.core.gridfactory import GridFactory, Samples
+	from origami_b200.core.math import Geometry
+	(ph, ah), (pv, av) = _flow_samples(W, H, n, seed=W + n)
+	sh, sv = Samples(Geometry(W, H)), Samples(Geometry(W, H))
+	sh.extend(list(ph), list(ah))
+	sv.extend(list(pv), list(av))
+	fac = GridFactory((W, H), sh, sv, grid_res=25, num_threads=threads)
+	got = fac.grid_hv
+	want = exact.grid_factory((W, H), (ph, ah), (pv, av), 25, num_threads=threads)
+	assert got.dtype == np.float32 and got.shape == want.shape
+	assert np.abs(got - want).max() < 5e-3
+	# the grid covers the page (border extension) and is usable as a dewarping grid
+	assert got[:, 0, 0].max() <= 2 and got[:, -1, 0].min() >= W - 2 and got[0, :, 1].max() <= 2 and got[-1, :, 1].min() >= H - 2  # (rows added last may lean back in a little)
+	grid = Grid.create((W, H), sh, sv, grid_res=25, num_threads=threads)
+	assert grid.resolution == 25 and np.array_equal(grid.points("sample"), got)
+	page = synth.make_page(W, H, seed=1, kind="noise")
+	dew = np.array(Page(page, grid).dewarped)
+	assert np.array_equal(dew, exact.remap_linear(page, exact.expand_map(got, 25)))

@@ -218,3 +218,21 @@ def test_segment_zip_roundtrip_and_line_png_export(tmp_path):
 		assert zf.namelist() == ["regions/TEXT/1/%d.png" % k for k in range(3)]
 		for (stem, arr), name in zip(strips, zf.namelist()):
 			assert np.array_equal(np.array(PIL.Image.open(io.BytesIO(zf.read(name)))), arr)
+
+
+def test_flow_samples_zip_roundtrip(tmp_path):
+	"""flow.zip samples (origami/core/dewarp.py:43-74)."""
+	import zipfile
+	from origami_b200.core.gridfactory import Samples
+	from origami_b200.core.math import Geometry
+	s = Samples(Geometry(2400, 3600))
+	s.extend([np.array([10.0, 20.0]), np.array([300.5, 40.25])], [0.01, -0.02])
+	s.append(np.array([5.0, 6.0]), 0.5)
+	path = tmp_path / "flow.zip"
+	with zipfile.ZipFile(path, "w") as zf:
+		s.save(zf, "h")
+		Samples(Geometry(2400, 3600)).save(zf, "v")
+	with zipfile.ZipFile(path) as zf:
+		h, v = Samples.open(zf, "h"), Samples.open(zf, "v")
+	assert len(h) == 3 and np.allclose(np.array(h.points), np.array(s.points)) and np.allclose(h.values, s.values)
+	assert h.geometry.size == (2400, 3600) and len(v.values) == 0 and h.std == 0
