@@ -318,7 +318,7 @@ class PageSet:
 		self.plan = ops.LinePlan(self.lines, self.n, self.steps, self.pix, self.chunks)
 
 
-KERNELS = ["og_page_kernel", "og_line_plan_kernel", "og_strips_kernels"]
+KERNELS = ["og_page_kernel", "og_line_plan_kernel", "og_strips_screened_kernel", "og_binarize"]
 
 
 def run_step(ps, args, events=None):
@@ -341,14 +341,20 @@ def run_step(ps, args, events=None):
 	_lib.call("og_line_steps", ps.grid.data_ptr(), ps.gh, ps.gw, CELL, ps.lines.data_ptr(), ps.n,
 		ps.steps.data_ptr(), ps.pix.data_ptr(), ps.chunks.data_ptr(), st)
 	mark("og_line_plan_kernel")
-	mode = {"none": ops.OG_BIN_NONE, "otsu": ops.OG_BIN_OTSU, "sauvola": ops.OG_BIN_SAUVOLA}[args.binarize]
+	# og_extract_lines(..., binarize) would run both kernels in one call; they are issued as two calls here
+	# only so that an event can sit between them (per-kernel times for the roofline)
 	_lib.call("og_extract_lines", ps.src.data_ptr(), ps.H, ps.W, ps.src.stride(0), ps.grid.data_ptr(), ps.gh, ps.gw, CELL,
 		ps.map.data_ptr(), ps.lines.data_ptr(), ps.n, ps.steps.data_ptr(), ps.pix.data_ptr(), ps.chunks.data_ptr(),
-		ps.bin.data_ptr(), ps.bin.numel(), 0, mode, 15, ps.gray.data_ptr() if mode == ops.OG_BIN_SAUVOLA else 0, 0, st)
-	mark("og_strips_kernels")
-	# og_page_kernel, og_line_plan_kernel (up to 8192 lines: one launch), og_strips_screened_kernel, and the
-	# strip binarizer (og_otsu_strips_kernel / og_sauvola_strips_kernel)
-	return 3 if mode == ops.OG_BIN_NONE else 4
+		ps.gray.data_ptr(), ps.gray.numel(), 0, ops.OG_BIN_NONE, 0, 0, 0, st)
+	mark("og_strips_screened_kernel")
+	launches = 3  # og_page_kernel, og_line_plan_kernel (up to 8192 lines: one launch), og_strips_screened_kernel
+	if args.binarize != "none":
+		mode = ops.OG_BIN_OTSU if args.binarize == "otsu" else ops.OG_BIN_SAUVOLA
+		_lib.call("og_binarize_strips", ps.gray.data_ptr(), ps.steps.data_ptr(), ps.pix.data_ptr(), ps.chunks.data_ptr(),
+			ps.n, mode, 15, ps.bin.data_ptr(), ps.bin.numel(), 0, st)
+		mark("og_binarize")
+		launches += 1
+	return launches
 
 
 def run_e2e(args, inputs, device, n_steps):
@@ -531,7 +537,8 @@ def run_ours(args):
 		src_rows = float(np.mean([np.ceil(np.hypot(*l["up"])) + 2 for l in inputs[0][2]]))
 		alg_bytes = {
 			"og_page_kernel": 9 * ps0.Hd * ps0.Wd + ps0.H * ps0.W,
-			"og_strips_kernels": strip_px + strip_px / LINE_HEIGHT * src_rows,
+			"og_strips_screened_kernel": strip_px + strip_px / LINE_HEIGHT * src_rows,
+			"og_binarize": 2 * strip_px,
 			"og_line_plan_kernel": ps0.n * (112 + 8 + 8 + 4),
 		}
 		traffic = recorded_traffic()

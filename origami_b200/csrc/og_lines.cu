@@ -626,9 +626,14 @@ __device__ __forceinline__ void og_nodes_load(og_nodes &n, double px, double py,
 	n.b = __fsub_rn(__int_as_float((txl & 0x7FFFFF) | one_bits), 1.f);
 	const float2 *m = map + (n.ok ? i0 * (unsigned)Wd + i1 : 0u);
 	n.v00 = __ldg(m);
-	n.v01 = __ldg(m + 1);
 	n.v10 = __ldg(m + Wd);
+#ifdef OG_EXP_NODES2  // experiment (wrong pixels): how much of the time is the number of node loads?
+	n.v01 = n.v00;
+	n.v11 = n.v10;
+#else
+	n.v01 = __ldg(m + 1);
 	n.v11 = __ldg(m + Wd + 1);
+#endif
 }
 
 // stage 2: float32 interval of the blend -> fixed-point coordinates; false when undecided
@@ -665,9 +670,14 @@ __device__ __forceinline__ void og_taps_interior(og_taps &t, const uint8_t *__re
 	t.fx = sx & 31;
 	t.fy = sy & 31;
 	t.p00 = __ldg(q);
-	t.p01 = __ldg(q + 1);
 	t.p10 = __ldg(q + pitch);
+#ifdef OG_EXP_TAPS2  // experiment (wrong pixels): how much of the time is the number of tap loads?
+	t.p01 = t.p00;
+	t.p11 = t.p10;
+#else
+	t.p01 = __ldg(q + 1);
 	t.p11 = __ldg(q + pitch + 1);
+#endif
 }
 
 // --- label sampling (A15) through the same screening: what the NEAREST lookup uses of a sample is

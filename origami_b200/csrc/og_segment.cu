@@ -64,6 +64,46 @@ __global__ void __launch_bounds__(256) og_argmax4_kernel(
 	}
 }
 
+// C == 4 with the model count known at compile time: every load of a thread is issued before the first
+// sum (4 pixels x MT models = up to 20 independent 16-byte loads in flight per thread -- the runtime loop
+// above waits for each model's load in turn and reaches a third of the HBM rate when its input is not in
+// L2), and a lane's four pixels are 256 apart, so that every warp-wide load is 512 contiguous bytes.
+template <int MT>
+__global__ void __launch_bounds__(256) og_argmax4_unrolled_kernel(
+	const float4 *__restrict__ probs, int64_t npix,
+	uint8_t *__restrict__ labels, uint8_t *__restrict__ masks, MaskValues mv, int n_mask) {
+	const int64_t base = (int64_t)blockIdx.x * 1024 + threadIdx.x;
+	float4 v[MT][4];
+#pragma unroll
+	for (int m = 0; m < MT; ++m)
+#pragma unroll
+		for (int k = 0; k < 4; ++k) {
+			const int64_t i = base + 256 * k;
+			v[m][k] = i < npix ? __ldcs(probs + (int64_t)m * npix + i) : make_float4(0.f, 0.f, 0.f, 0.f);
+		}
+#pragma unroll
+	for (int k = 0; k < 4; ++k) {
+		const int64_t i = base + 256 * k;
+		if (i >= npix) continue;
+		float4 acc = v[0][k];
+#pragma unroll
+		for (int m = 1; m < MT; ++m) {  // np.sum(pr_masks, axis=0): in model order
+			acc.x = __fadd_rn(acc.x, v[m][k].x);
+			acc.y = __fadd_rn(acc.y, v[m][k].y);
+			acc.z = __fadd_rn(acc.z, v[m][k].z);
+			acc.w = __fadd_rn(acc.w, v[m][k].w);
+		}
+		float best = acc.x;
+		uint32_t bi = 0;
+		if (acc.y > best) { best = acc.y; bi = 1; }
+		if (acc.z > best) { best = acc.z; bi = 2; }
+		if (acc.w > best) { best = acc.w; bi = 3; }
+		labels[i] = (uint8_t)bi;
+		if (masks != nullptr)
+			for (int j = 0; j < n_mask; ++j) masks[(int64_t)j * npix + i] = (bi == mv.v[j]);
+	}
+}
+
 // any C: one pixel per thread
 __global__ void __launch_bounds__(256) og_argmax_kernel(
 	const float *__restrict__ probs, int M, int C, int64_t npix,
@@ -221,7 +261,16 @@ extern "C" int og_argmax_labels(const float *probs, int M, int C, int h, int w,
 	if (rc) return rc;
 	const int64_t npix = (int64_t)h * w;
 	cudaStream_t st = (cudaStream_t)stream;
-	if (C == 4 && (reinterpret_cast<uintptr_t>(probs) & 15) == 0) {
+	if (C == 4 && (reinterpret_cast<uintptr_t>(probs) & 15) == 0 && M <= 8) {
+		const float4 *p4 = reinterpret_cast<const float4 *>(probs);
+		const unsigned blocks = (unsigned)((npix + 1023) / 1024);
+		switch (M) {
+#define OG_ARGMAX_CASE(MT) case MT: og_argmax4_unrolled_kernel<MT><<<blocks, 256, 0, st>>>(p4, npix, labels_out, masks_out, mv, n_mask); break;
+			OG_ARGMAX_CASE(1) OG_ARGMAX_CASE(2) OG_ARGMAX_CASE(3) OG_ARGMAX_CASE(4)
+			OG_ARGMAX_CASE(5) OG_ARGMAX_CASE(6) OG_ARGMAX_CASE(7) OG_ARGMAX_CASE(8)
+#undef OG_ARGMAX_CASE
+		}
+	} else if (C == 4 && (reinterpret_cast<uintptr_t>(probs) & 15) == 0) {
 		const int64_t quads = (npix + 3) / 4;
 		og_argmax4_kernel<<<(unsigned)((quads + 255) / 256), 256, 0, st>>>(
 			reinterpret_cast<const float4 *>(probs), M, npix, labels_out, masks_out, mv, n_mask);

@@ -1,0 +1,21 @@
+"""A few launches of the screened strip kernel on the bench page (target for ncu)."""
+import sys, os
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+import torch
+from origami_b200 import ops, synth
+W, H, cell = 4800, 7200, 25
+dev = torch.device("cuda:0")
+page = synth.make_page(W, H, seed=0, kind="text")
+grid = synth.make_grid(W, H, cell, seed=0)
+gh, gw = grid.shape[:2]
+lines = synth.make_lines(gw * cell, gh * cell, 2000, seed=0, dpi=600)
+g = torch.from_numpy(grid).to(dev)
+src = ops.to_device_image(page, dev)
+mp = ops.expand_map(g, cell)
+plan = ops.line_steps(g, cell, ops.lines_to_device(ops.pack_lines([dict(p=l["p"], right=l["right"], up=l["up"], ysteps=48) for l in lines]), dev), 2000)
+total = int(plan.pix_offsets[-1].item())
+a = torch.empty((total,), dtype=torch.uint8, device=dev)
+for _ in range(4):
+	ops.extract_lines(src, g, cell, plan, a, dense_map=mp)
+torch.cuda.synchronize()
+print("ok")
