@@ -14,7 +14,7 @@ CSRC = os.path.join(HERE, "csrc")
 LIB_DIR = os.path.join(HERE, "lib")
 LIB_PATH = os.path.join(LIB_DIR, "liborigami_b200.so")
 
-SOURCES = ["og_api.cu", "og_page.cu", "og_lines.cu", "og_strips.cu", "og_binarize.cu", "og_segment.cu", "og_handoff.cu", "og_geometry.cu"]
+SOURCES = ["og_api.cu", "og_page.cu", "og_lines.cu", "og_strips.cu", "og_binarize.cu", "og_sauvola_warp.cu", "og_segment.cu", "og_handoff.cu", "og_geometry.cu"]
 
 NVCC_FLAGS = [
 	"-gencode", "arch=compute_100a,code=sm_100a",

@@ -43,9 +43,9 @@ int og_num_sms() {
 }
 
 bool og_first_use(int slot) {
-	static unsigned char seen[OG_MAX_DEVICES][32] = {{0}};
+	static unsigned char seen[OG_MAX_DEVICES][64] = {{0}};
 	const int dev = og_device_ordinal();
-	if (dev < 0 || dev >= OG_MAX_DEVICES || slot < 0 || slot >= 32) return true;
+	if (dev < 0 || dev >= OG_MAX_DEVICES || slot < 0 || slot >= 64) return true;
 	if (seen[dev][slot]) return false;
 	seen[dev][slot] = 1;
 	return true;

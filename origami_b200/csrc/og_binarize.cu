@@ -655,6 +655,8 @@ int og_binarize_strips_impl(const uint8_t *gray, const int32_t *steps, const int
 	int rc = check_window(window);
 	if (rc) return rc;
 	OG_REQUIRE(gray != out, OG_E_ARG, "Sauvola cannot run in place");
+	if (window <= 15 && getenv("OG_SAUVOLA_STRIPS_WARP") != nullptr)
+		return og_launch_sauvola_warp_strips(gray, steps, pix_offsets, chunk_offsets, n, window, out, capacity, st);
 	const size_t smem = (size_t)2 * SS_R * ss_pitch(window) * sizeof(unsigned int);
 	og_sauvola_stream_strips_kernel<<<min(n, og_num_sms() * 6), SS_T, smem, st>>>(gray, steps, pix_offsets, n, out,
 		capacity, window, 0.2, 127.5);
@@ -675,6 +677,8 @@ extern "C" int og_sauvola(const uint8_t *src, int h, int w, int64_t src_pitch, i
 	OG_REQUIRE(src != dst, OG_E_ARG, "Sauvola cannot run in place");
 	int rc = check_window(window);
 	if (rc) return rc;
+	if (window <= 15 && getenv("OG_SAUVOLA_LEGACY") == nullptr)
+		return og_launch_sauvola_warp_page(src, h, w, src_pitch, window, k, r, dst, dst_pitch, (cudaStream_t)stream);
 	if (getenv("OG_SAUVOLA_STREAM") == nullptr) {
 		// Pages: the tile kernel (0.160 ms for 4800x7200, window 15).  The column-streaming kernel below reads every
 		// byte twice instead of once per overlapping halo tile, but its running sums serialise a CTA's rows

@@ -33,6 +33,12 @@ int og_binarize_strips_impl(const uint8_t *gray, const int32_t *steps, const int
 	const int32_t *chunk_offsets, int n, int mode, int window, uint8_t *out, int64_t capacity,
 	int32_t *thresholds_out, cudaStream_t st);
 
+// og_sauvola_warp.cu: warp-autonomous Sauvola for odd windows 3 .. 15 (pages and packed strips)
+int og_launch_sauvola_warp_page(const uint8_t *src, int h, int w, int64_t src_pitch, int window, double k, double r,
+	uint8_t *dst, int64_t dst_pitch, cudaStream_t st);
+int og_launch_sauvola_warp_strips(const uint8_t *gray, const int32_t *steps, const int64_t *pix_offsets,
+	const int32_t *chunk_offsets, int n, int window, uint8_t *out, int64_t capacity, cudaStream_t st);
+
 #ifdef __CUDACC__
 // Otsu threshold from an exact 256-bin histogram (skimage 0.16.2 threshold_otsu on uint8: bins =
 // the integers [min, max], float64 cumulative sums, first argmax of w1 * w2 * (m1 - m2)^2; a
