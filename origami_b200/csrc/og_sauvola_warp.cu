@@ -8,13 +8,15 @@
 // pixels within 1e-3 gray levels of their threshold take the reference's float64 sequence --
 // the same decision procedure as sauvola_tile in og_binarize.cu, only the sums are formed differently:
 //
-//   * a warp owns a stripe of 112 output columns and a run of rows; lane l holds the four pixels
-//     4 l .. 4 l + 3 of the stripe's 128 input columns as one 32-bit word per row (one coalesced
-//     128-byte row read per warp);
+//   * a warp owns a stripe of columns and a run of rows; lane l holds PX = 4 or 8 neighbouring pixels
+//     of each row as one or two 32-bit words (one coalesced 128- or 256-byte row read per warp); the
+//     lanes whose windows reach past the warp's columns (8 pixels on either side) produce no output,
+//     so a stripe is 112 (PX = 4) or 240 (PX = 8) output columns wide;
 //   * horizontal: the neighbouring lanes' words come by shuffle (raw pixels, four shuffles), and the
-//     window sums of p and p^2 of the lane's four outputs are dp4a dot products of those words
-//     with byte masks (p: word . 0x01010101, p^2: (word & mask) . word) -- about seven
-//     instructions per pixel for both sums;
+//     window sums of p and p^2 of the lane's outputs are dp4a dot products of those words with byte
+//     masks (p: word . 0x01010101, p^2: (word & mask) . word), the words common to all windows
+//     (and to the windows of a group of four outputs) summed once -- six to seven instructions per
+//     pixel for both sums;
 //   * vertical: the four (S1, S2) pairs of the lane run down the rows, + the row entering the window,
 //     - the row that left it.  A row's horizontal sums wait for that in a shared-memory ring of
 //     `window` rows (zero at the start of a run), packed as H2 << 12 | H1 (H1 <= 15 * 255 < 2^12, H2 <= 15 * 255^2 < 2^20:
@@ -29,25 +31,37 @@
 
 namespace {
 
-constexpr int WS_OUT = 112;  // output columns per warp (lanes 2 .. 29)
 constexpr int WS_WARPS = 4;  // warps per CTA (independent of each other)
 #ifndef OG_WS_AHEAD
 #define OG_WS_AHEAD 3
 #endif
 constexpr int WS_AHEAD = OG_WS_AHEAD;  // rows requested ahead of use
 
-__device__ __forceinline__ int ws_reflect(int i, int n) {  // numpy.pad(mode="reflect"), any distance
-	if ((unsigned)i < (unsigned)n) return i;
+template <int PX>
+struct WsGeom {
+	static constexpr int NW = PX / 4;              // words per lane and row
+	static constexpr int NK = NW + 4;              // words a lane's windows can touch: k = -2 .. NW + 1
+	static constexpr int EDGE = 8 / PX;            // lanes at either end of the warp without output
+	static constexpr int OUT = (32 - 2 * EDGE) * PX;  // output columns per warp
+};
+
+__device__ __noinline__ int ws_reflect_far(int i, int n) {  // numpy.pad(mode="reflect"), any distance
 	if (n == 1) return 0;
-	const int j = i < 0 ? -i : 2 * (n - 1) - i;
-	if ((unsigned)j < (unsigned)n) return j;
 	const int period = 2 * (n - 1);
 	i %= period;
 	if (i < 0) i += period;
 	return i >= n ? period - i : i;
 }
 
-// bytes of the word of lane l + k (k = -2 .. 2) that lie in the window of the lane's output j
+__device__ __forceinline__ int ws_reflect(int i, int n) {
+	if ((unsigned)i < (unsigned)n) return i;
+	const int j = i < 0 ? -i : 2 * (n - 1) - i;
+	if ((unsigned)j < (unsigned)n) return j;
+	return ws_reflect_far(i, n);
+}
+
+// bytes of word k (columns 4 k .. 4 k + 3 relative to the lane's first pixel, k = -2 .. NW + 1) that
+// lie in the window of the lane's output j
 template <int RAD>
 __device__ __forceinline__ constexpr unsigned ws_mask(int j, int k) {
 	unsigned m = 0;
@@ -58,36 +72,50 @@ __device__ __forceinline__ constexpr unsigned ws_mask(int j, int k) {
 	return m;
 }
 
-template <int RAD>
-__device__ __forceinline__ constexpr unsigned ws_common(int k) {
-	return ws_mask<RAD>(0, k) & ws_mask<RAD>(1, k) & ws_mask<RAD>(2, k) & ws_mask<RAD>(3, k);
+template <int RAD, int PX>
+__device__ __forceinline__ constexpr unsigned ws_all(int k) {  // ... in the windows of all outputs
+	unsigned m = 0x01010101u;
+	for (int j = 0; j < PX; ++j) m &= ws_mask<RAD>(j, k);
+	return m;
 }
 
-// window sums of p (h1) and p^2 (h2) along the row for the lane's four outputs
-template <int RAD>
-__device__ __forceinline__ void ws_hsums(const unsigned (&wd)[5], unsigned (&h1)[4], unsigned (&h2)[4]) {
+template <int RAD, int PX>
+__device__ __forceinline__ constexpr unsigned ws_group(int g, int k) {  // ... of outputs 4 g .. 4 g + 3, beyond ws_all
+	unsigned m = 0x01010101u;
+	for (int j = 4 * g; j < 4 * g + 4; ++j) m &= ws_mask<RAD>(j, k);
+	return m & ~ws_all<RAD, PX>(k);
+}
+
+__device__ __forceinline__ void ws_dot(unsigned word, unsigned mask, unsigned &s1, unsigned &s2) {
+	s1 = __dp4a(word, mask, s1);
+	s2 = __dp4a(mask == 0x01010101u ? word : (word & (mask * 255u)), word, s2);
+}
+
+// window sums of p (h1) and p^2 (h2) along the row for the lane's PX outputs; wd[k + 2] = word k
+template <int RAD, int PX>
+__device__ __forceinline__ void ws_hsums(const unsigned (&wd)[WsGeom<PX>::NK], unsigned (&h1)[PX], unsigned (&h2)[PX]) {
+	constexpr int NK = WsGeom<PX>::NK;
 	unsigned b1 = 0, b2 = 0;
 #pragma unroll
-	for (int k = 0; k < 5; ++k) {
-		const unsigned mc = ws_common<RAD>(k - 2);
-		if (mc != 0) {
-			b1 = __dp4a(wd[k], mc, b1);
-			b2 = __dp4a(mc == 0x01010101u ? wd[k] : (wd[k] & (mc * 255u)), wd[k], b2);
-		}
-	}
+	for (int k = 0; k < NK; ++k)
+		if (ws_all<RAD, PX>(k - 2) != 0) ws_dot(wd[k], ws_all<RAD, PX>(k - 2), b1, b2);
 #pragma unroll
-	for (int j = 0; j < 4; ++j) {
-		unsigned e1 = b1, e2 = b2;
+	for (int g = 0; g < PX / 4; ++g) {
+		unsigned g1 = b1, g2 = b2;
 #pragma unroll
-		for (int k = 0; k < 5; ++k) {
-			const unsigned m = ws_mask<RAD>(j, k - 2) & ~ws_common<RAD>(k - 2);
-			if (m != 0) {
-				e1 = __dp4a(wd[k], m, e1);
-				e2 = __dp4a(wd[k] & (m * 255u), wd[k], e2);
+		for (int k = 0; k < NK; ++k)
+			if (ws_group<RAD, PX>(g, k - 2) != 0) ws_dot(wd[k], ws_group<RAD, PX>(g, k - 2), g1, g2);
+#pragma unroll
+		for (int j = 4 * g; j < 4 * g + 4; ++j) {
+			unsigned e1 = g1, e2 = g2;
+#pragma unroll
+			for (int k = 0; k < NK; ++k) {
+				const unsigned m = ws_mask<RAD>(j, k - 2) & ~ws_all<RAD, PX>(k - 2) & ~ws_group<RAD, PX>(g, k - 2);
+				if (m != 0) ws_dot(wd[k], m, e1, e2);
 			}
+			h1[j] = e1;
+			h2[j] = e2;
 		}
-		h1[j] = e1;
-		h2[j] = e2;
 	}
 }
 
@@ -104,143 +132,222 @@ struct WsConst {
 	double n, kk, rr;
 };
 
-// One stripe: output columns x0 .. x0 + 111, output rows y0 .. y1 - 1 of an (h, w) image
-// (pitch and out_pitch below 2^31).
-template <int RAD, bool ALIGNED>
+// the pixels of a group of four whose float32 estimate is within 1e-3 of the pixel: the reference's
+// float64 sequence decides them
+__device__ __noinline__ unsigned ws_settle(unsigned res, unsigned cw, uint4 s1, uint4 s2, unsigned undecided, double n, double kk, double rr) {
+	const unsigned a1[4] = {s1.x, s1.y, s1.z, s1.w}, a2[4] = {s2.x, s2.y, s2.z, s2.w};
+#pragma unroll
+	for (int j = 0; j < 4; ++j) {
+		if (!(undecided >> j & 1u)) continue;
+		const double m = __ddiv_rn((double)a1[j], n);
+		const double g2 = __ddiv_rn((double)a2[j], n);
+		double var = __dsub_rn(g2, __dmul_rn(m, m));
+		var = var > 0.0 ? var : 0.0;
+		const double sd = __dsqrt_rn(var);
+		const double t = __dmul_rn(m, __dadd_rn(1.0, __dmul_rn(kk, __dsub_rn(__ddiv_rn(sd, rr), 1.0))));
+		const bool white = (double)((cw >> (8 * j)) & 255u) > t;
+		res = (res & ~(255u << (8 * j))) | (white ? 255u << (8 * j) : 0u);
+	}
+	return res;
+}
+
+// One stripe: output columns x0 .. x0 + OUT - 1, output rows y0 .. y1 - 1 of an (h, w) image
+// (pitch and out_pitch below 2^31).  ring_h: WIN x NW x 32 uint4, ring_w: (RAD + 1) x NW x 32 words.
+template <int RAD, int PX, bool ALIGNED>
 __device__ __forceinline__ void ws_stripe(const uint8_t *__restrict__ img, int h, int w, unsigned pitch,
 	uint8_t *__restrict__ out, unsigned out_pitch, int x0, int y0, int y1, const WsConst c,
 	uint4 *__restrict__ ring_h, unsigned *__restrict__ ring_w) {
-	constexpr int WIN = 2 * RAD + 1;
+	static_assert(ALIGNED || PX == 4, "unaligned rows are read one word per lane");
+	using G = WsGeom<PX>;
+	constexpr int WIN = 2 * RAD + 1, NW = G::NW, NK = G::NK, RW = RAD + 1;
 	constexpr unsigned NWIN = WIN * WIN;
+	struct Row { unsigned w[NW]; };
 	const int lane = threadIdx.x & 31;
-	const int cx = x0 - 8 + 4 * lane;
-	const bool inside = cx >= 0 && cx + 3 < w;
-	const bool writes = lane >= 2 && lane < 30 && cx < w;
-	const bool write_word = ALIGNED && writes && cx + 3 < w;
+	const int cx = x0 - 8 + PX * lane;
+	const bool inside = cx >= 0 && cx + PX - 1 < w;
+	const bool writes = lane >= G::EDGE && lane < 32 - G::EDGE && cx < w;
+	const bool write_words = ALIGNED && writes && cx + PX - 1 < w;
 	const uint8_t *img_lane = img + (inside ? cx : 0);
 	uint8_t *out_lane = out + cx;
 	uint4 *rh = ring_h + lane;
 	unsigned *rw = ring_w + lane;
 #pragma unroll
-	for (int i = 0; i < WIN; ++i) rh[i * 32] = make_uint4(0u, 0u, 0u, 0u);  // rows "before" the first leave as zeros
-	unsigned v1[4] = {0, 0, 0, 0}, v2[4] = {0, 0, 0, 0};
-	int slot = 0, cslot = WIN - RAD;  // ring slots of row r and of row r - RAD
-	auto load_row = [&](int r) -> unsigned {
+	for (int i = 0; i < WIN * NW; ++i) rh[i * 32] = make_uint4(0u, 0u, 0u, 0u);  // the rows "before" the first leave as zeros
+	// a lane of a stripe at the left or right border of the image gathers its (reflected) columns by byte
+	int rc[PX];
+#pragma unroll
+	for (int b = 0; b < PX; ++b) rc[b] = inside ? 0 : ws_reflect(cx + b, w);
+	auto load_row = [&](int r) -> Row {
 		const int ry = (unsigned)r < (unsigned)h ? r : ws_reflect(r, h);
 		const uint8_t *row = img_lane + (uint64_t)(unsigned)ry * pitch;
+		Row v;
 		if (inside) {
-			if (ALIGNED) return __ldg(reinterpret_cast<const unsigned *>(row));
-			const uintptr_t a = reinterpret_cast<uintptr_t>(row);
-			const unsigned *wp = reinterpret_cast<const unsigned *>(a & ~(uintptr_t)3);
-			const unsigned sh = (unsigned)(a & 3) * 8;
-			const unsigned lo = __ldg(wp);
-			const unsigned hi = sh ? __ldg(wp + 1) : 0u;  // an aligned word that holds a byte of the image stays inside its page
-			return __funnelshift_r(lo, hi, sh);
-		}
-		unsigned v = 0;
+			if (ALIGNED && PX == 8) {
+				const uint2 t = __ldg(reinterpret_cast<const uint2 *>(row));
+				v.w[0] = t.x;
+				v.w[NW - 1] = t.y;
+			} else if (ALIGNED) {
+				v.w[0] = __ldg(reinterpret_cast<const unsigned *>(row));
+			} else {
+				const uintptr_t a = reinterpret_cast<uintptr_t>(row);
+				const unsigned *wp = reinterpret_cast<const unsigned *>(a & ~(uintptr_t)3);
+				const unsigned sh = (unsigned)(a & 3) * 8;
+				const unsigned lo = __ldg(wp);
+				const unsigned hi = sh ? __ldg(wp + 1) : 0u;  // an aligned word that holds a byte of the image stays inside its page
+				v.w[0] = __funnelshift_r(lo, hi, sh);
+			}
+		} else {
 #pragma unroll
-		for (int b = 0; b < 4; ++b) v |= (unsigned)__ldg(row + ws_reflect(cx + b, w)) << (8 * b);
+			for (int q = 0; q < NW; ++q) {
+				const unsigned b0 = __ldg(row + rc[4 * q]), b1 = __ldg(row + rc[4 * q + 1]);
+				const unsigned b2 = __ldg(row + rc[4 * q + 2]), b3 = __ldg(row + rc[4 * q + 3]);
+				v.w[q] = __byte_perm(b0 | (b1 << 8), b2 | (b3 << 8), 0x5410);
+			}
+		}
 		return v;
 	};
-	// rows are requested WS_AHEAD iterations before they are used (a warp has one 128-byte read per row
-	// in flight otherwise, and nothing to do until it lands); a row past the end is a harmless reflection
-	unsigned ahead[WS_AHEAD];
+	unsigned v1[PX], v2[PX];
 #pragma unroll
-	for (int i = 0; i < WS_AHEAD; ++i) ahead[i] = load_row(y0 - RAD + i);
-	for (int r = y0 - RAD; r < y1 + RAD; ++r) {
-		unsigned wd[5];
-		wd[2] = ahead[0];
-#pragma unroll
-		for (int i = 0; i + 1 < WS_AHEAD; ++i) ahead[i] = ahead[i + 1];
-		ahead[WS_AHEAD - 1] = load_row(r + WS_AHEAD);
-		wd[0] = __shfl_up_sync(0xffffffffu, wd[2], 2);
-		wd[1] = __shfl_up_sync(0xffffffffu, wd[2], 1);
-		wd[3] = __shfl_down_sync(0xffffffffu, wd[2], 1);
-		wd[4] = __shfl_down_sync(0xffffffffu, wd[2], 2);
-		unsigned h1[4], h2[4];
-		ws_hsums<RAD>(wd, h1, h2);
+	for (int j = 0; j < PX; ++j) v1[j] = v2[j] = 0;
+	int slot = 0, wslot = 0;  // ring slots of row r (sums: WIN slots, pixels: RAD + 1 slots)
+	auto body = [&](int r, const Row &cur, bool screen) {
 		// the row entering the window replaces the row that left it WIN rows ago in the ring
-		const uint4 old = rh[slot * 32];
-		v1[0] += h1[0] - (old.x & 0xFFFu); v2[0] += h2[0] - (old.x >> 12);
-		v1[1] += h1[1] - (old.y & 0xFFFu); v2[1] += h2[1] - (old.y >> 12);
-		v1[2] += h1[2] - (old.z & 0xFFFu); v2[2] += h2[2] - (old.z >> 12);
-		v1[3] += h1[3] - (old.w & 0xFFFu); v2[3] += h2[3] - (old.w >> 12);
-		rh[slot * 32] = make_uint4(h2[0] * 4096u + h1[0], h2[1] * 4096u + h1[1], h2[2] * 4096u + h1[2], h2[3] * 4096u + h1[3]);
-		rw[slot * 32] = wd[2];
-		if (r >= y0 + RAD) {  // the window of output row r - RAD is complete
-			const unsigned cw = rw[cslot * 32];
+		uint4 old[NW];
+#pragma unroll
+		for (int q = 0; q < NW; ++q) old[q] = rh[(slot * NW + q) * 32];
+		unsigned wd[NK];
+		if (PX == 4) {
+			wd[2] = cur.w[0];
+			wd[0] = __shfl_up_sync(0xffffffffu, wd[2], 2);
+			wd[1] = __shfl_up_sync(0xffffffffu, wd[2], 1);
+			wd[3] = __shfl_down_sync(0xffffffffu, wd[2], 1);
+			wd[4] = __shfl_down_sync(0xffffffffu, wd[2], 2);
+		} else {
+			wd[2] = cur.w[0];
+			wd[3] = cur.w[NW - 1];
+			wd[0] = __shfl_up_sync(0xffffffffu, wd[2], 1);
+			wd[1] = __shfl_up_sync(0xffffffffu, wd[3], 1);
+			wd[NK - 2] = __shfl_down_sync(0xffffffffu, wd[2], 1);
+			wd[NK - 1] = __shfl_down_sync(0xffffffffu, wd[3], 1);
+		}
+		unsigned h1[PX], h2[PX];
+		ws_hsums<RAD, PX>(wd, h1, h2);
+#pragma unroll
+		for (int q = 0; q < NW; ++q) {
+			const unsigned o[4] = {old[q].x, old[q].y, old[q].z, old[q].w};
+#pragma unroll
+			for (int j = 0; j < 4; ++j) {
+				v1[4 * q + j] += h1[4 * q + j] - (o[j] & 0xFFFu);
+				v2[4 * q + j] += h2[4 * q + j] - (o[j] >> 12);
+			}
+			rh[(slot * NW + q) * 32] = make_uint4(h2[4 * q] * 4096u + h1[4 * q], h2[4 * q + 1] * 4096u + h1[4 * q + 1],
+				h2[4 * q + 2] * 4096u + h1[4 * q + 2], h2[4 * q + 3] * 4096u + h1[4 * q + 3]);
+			rw[(wslot * NW + q) * 32] = cur.w[q];
+		}
+		slot = slot + 1 == WIN ? 0 : slot + 1;
+		wslot = wslot + 1 == RW ? 0 : wslot + 1;  // now the slot of row r - RAD
+		if (!screen) return;
+		const int yo = r - RAD;
+		const bool live = (unsigned)(yo - y0) < (unsigned)(y1 - y0);
+		unsigned res[NW];
+#pragma unroll
+		for (int q = 0; q < NW; ++q) {
+			const unsigned cw = rw[(wslot * NW + q) * 32];
 			float diff[4];
 #pragma unroll
 			for (int j = 0; j < 4; ++j) {
 				// D = n S2 - S1^2 exactly (n^2 255^2 < 2^32 for windows <= 15); the float32 estimate of the
 				// threshold is within 2e-4 gray levels of the float64 one (see sauvola_tile), and the
 				// approximate square root adds 6e-5 at most: |pixel - estimate| > 1e-3 decides
-				const unsigned D = NWIN * v2[j] - v1[j] * v1[j];
+				const unsigned s1 = v1[4 * q + j];
+				const unsigned D = NWIN * v2[4 * q + j] - s1 * s1;
 				float rt;
 				asm("sqrt.approx.ftz.f32 %0, %1;" : "=f"(rt) : "f"((float)D));  // D is 0 or >= 1: nothing to flush
 				const float fpv = __fsub_rn(__int_as_float((int)__byte_perm(cw, 0x4B000000u, 0x7650 + j)), 8388608.0f);
-				diff[j] = __fmaf_rn(-(float)v1[j], __fmaf_rn(c.fc2, rt, c.fc1), fpv);
+				diff[j] = __fmaf_rn(-(float)s1, __fmaf_rn(c.fc2, rt, c.fc1), fpv);
 			}
-			// bytes of sign bits: 0xFF where diff < 0 (or -0, which the slow path below settles)
+			// bytes of sign bits: 0xFF where diff < 0 (or -0, which ws_settle decides)
 			const unsigned n01 = ws_prmt(__float_as_uint(diff[0]), __float_as_uint(diff[1]), 0x00FBu);
 			const unsigned n23 = ws_prmt(__float_as_uint(diff[2]), __float_as_uint(diff[3]), 0x00FBu);
-			unsigned res = ~__byte_perm(n01, n23, 0x5410);
+			res[q] = ~__byte_perm(n01, n23, 0x5410);
 			const float closest = fminf(fminf(fabsf(diff[0]), fabsf(diff[1])), fminf(fabsf(diff[2]), fabsf(diff[3])));
 			if (!(closest > 1.0e-3f)) {
-#pragma unroll
-				for (int j = 0; j < 4; ++j) {
-					if (fabsf(diff[j]) > 1.0e-3f) continue;
-					const double m = __ddiv_rn((double)v1[j], c.n);
-					const double g2 = __ddiv_rn((double)v2[j], c.n);
-					double var = __dsub_rn(g2, __dmul_rn(m, m));
-					var = var > 0.0 ? var : 0.0;
-					const double sd = __dsqrt_rn(var);
-					const double t = __dmul_rn(m, __dadd_rn(1.0, __dmul_rn(c.kk, __dsub_rn(__ddiv_rn(sd, c.rr), 1.0))));
-					const bool white = (double)((cw >> (8 * j)) & 255u) > t;
-					res = (res & ~(255u << (8 * j))) | (white ? 255u << (8 * j) : 0u);
-				}
-			}
-			uint8_t *o = out_lane + (uint64_t)(unsigned)(r - RAD) * out_pitch;
-			if (write_word) {
-				__stcs(reinterpret_cast<unsigned *>(o), res);
-			} else if (writes) {
+				unsigned undecided = 0;
 #pragma unroll
 				for (int j = 0; j < 4; ++j)
-					if (cx + j < w) o[j] = (uint8_t)(res >> (8 * j));
+					if (!(fabsf(diff[j]) > 1.0e-3f)) undecided |= 1u << j;
+				res[q] = ws_settle(res[q], cw, make_uint4(v1[4 * q], v1[4 * q + 1], v1[4 * q + 2], v1[4 * q + 3]),
+					make_uint4(v2[4 * q], v2[4 * q + 1], v2[4 * q + 2], v2[4 * q + 3]), undecided, c.n, c.kk, c.rr);
 			}
 		}
-		slot = slot + 1 == WIN ? 0 : slot + 1;
-		cslot = cslot + 1 == WIN ? 0 : cslot + 1;
+		uint8_t *o = out_lane + (uint64_t)(unsigned)yo * out_pitch;
+		if (write_words) {
+			if (live) {
+				if (PX == 8) __stcs(reinterpret_cast<uint2 *>(o), make_uint2(res[0], res[NW - 1]));
+				else __stcs(reinterpret_cast<unsigned *>(o), res[0]);
+			}
+		} else if (writes && live) {
+#pragma unroll
+			for (int j = 0; j < PX; ++j)
+				if (cx + j < w) o[j] = (uint8_t)(res[j >> 2] >> (8 * (j & 3)));
+		}
+	};
+	// Rows are requested WS_AHEAD iterations before they are used (otherwise a warp has one row read in
+	// flight and nothing to do until it lands); the loops are unrolled by that distance so that the
+	// queue lives in fixed registers.  Rows past the end are harmless reflections whose outputs are
+	// not stored; the first rows of a run only fill the window.
+	const int r0 = y0 - RAD, r_end = y1 + RAD;
+	constexpr int WARM = (2 * RAD) / WS_AHEAD * WS_AHEAD;
+	Row ahead[WS_AHEAD];
+#pragma unroll
+	for (int i = 0; i < WS_AHEAD; ++i) ahead[i] = load_row(r0 + i);
+	int r = r0;
+	for (; r < r0 + WARM; r += WS_AHEAD) {
+#pragma unroll
+		for (int u = 0; u < WS_AHEAD; ++u) {
+			const Row cur = ahead[u];
+			ahead[u] = load_row(r + u + WS_AHEAD);
+			body(r + u, cur, false);
+		}
+	}
+	for (; r < r_end; r += WS_AHEAD) {
+#pragma unroll
+		for (int u = 0; u < WS_AHEAD; ++u) {
+			const Row cur = ahead[u];
+			ahead[u] = load_row(r + u + WS_AHEAD);
+			body(r + u, cur, true);
+		}
 	}
 }
 
-template <int RAD>
-__host__ __device__ constexpr size_t ws_smem_bytes() {
-	return (size_t)WS_WARPS * (2 * RAD + 1) * 32 * (sizeof(uint4) + sizeof(unsigned));
+template <int RAD, int PX>
+__host__ __device__ constexpr size_t ws_warp_smem() {
+	return (size_t)32 * (PX / 4) * ((2 * RAD + 1) * sizeof(uint4) + (RAD + 1) * sizeof(unsigned));
 }
 
-template <int RAD>
+template <int RAD, int PX, int WARPS>
 __device__ __forceinline__ void ws_rings(unsigned char *smem, uint4 *&ring_h, unsigned *&ring_w) {
-	constexpr int WIN = 2 * RAD + 1;
+	constexpr int NW = PX / 4, WIN = 2 * RAD + 1;
 	const int wid = threadIdx.x >> 5;
-	ring_h = reinterpret_cast<uint4 *>(smem) + wid * WIN * 32;
-	ring_w = reinterpret_cast<unsigned *>(smem + (size_t)WS_WARPS * WIN * 32 * sizeof(uint4)) + wid * WIN * 32;
+	ring_h = reinterpret_cast<uint4 *>(smem) + wid * WIN * NW * 32;
+	ring_w = reinterpret_cast<unsigned *>(smem + (size_t)WARPS * WIN * NW * 32 * sizeof(uint4)) + wid * (RAD + 1) * NW * 32;
 }
 
 // pages: item = (run of rows, stripe); neighbouring warps take neighbouring stripes of one run
-template <int RAD, bool ALIGNED>
-__global__ void __launch_bounds__(WS_WARPS * 32) og_sauvola_warp_page_kernel(
+template <int RAD, int PX, bool ALIGNED, int WARPS>
+__global__ void __launch_bounds__(WARPS * 32) og_sauvola_warp_page_kernel(
 	const uint8_t *__restrict__ src, int h, int w, int64_t src_pitch, uint8_t *__restrict__ dst, int64_t dst_pitch,
-	WsConst c, int seg_rows, int stripes, int items) {
+	const WsConst c, int seg_rows, int stripes, int items) {
 	extern __shared__ __align__(16) unsigned char smem_raw[];
 	uint4 *ring_h;
 	unsigned *ring_w;
-	ws_rings<RAD>(smem_raw, ring_h, ring_w);
-	const int item = blockIdx.x * WS_WARPS + (threadIdx.x >> 5);
+	ws_rings<RAD, PX, WARPS>(smem_raw, ring_h, ring_w);
+	const int item = blockIdx.x * WARPS + (threadIdx.x >> 5);
 	if (item >= items) return;
 	const int seg = item / stripes, stripe = item - seg * stripes;
 	const int y0 = seg * seg_rows;
-	ws_stripe<RAD, ALIGNED>(src, h, w, (unsigned)src_pitch, dst, (unsigned)dst_pitch, stripe * WS_OUT, y0, min(h, y0 + seg_rows), c, ring_h, ring_w);
+	ws_stripe<RAD, PX, ALIGNED>(src, h, w, (unsigned)src_pitch, dst, (unsigned)dst_pitch, stripe * WsGeom<PX>::OUT, y0,
+		min(h, y0 + seg_rows), c, ring_h, ring_w);
 }
 
 // strips: item = a 64-column chunk of the line plan; chunk q of a line works on stripe q when the
@@ -248,11 +355,11 @@ __global__ void __launch_bounds__(WS_WARPS * 32) og_sauvola_warp_page_kernel(
 template <int RAD>
 __global__ void __launch_bounds__(WS_WARPS * 32) og_sauvola_warp_strips_kernel(
 	const uint8_t *__restrict__ gray, const int32_t *__restrict__ steps, const int64_t *__restrict__ pix_offsets,
-	const int32_t *__restrict__ chunk_offsets, int n, uint8_t *__restrict__ out, int64_t capacity, WsConst c) {
+	const int32_t *__restrict__ chunk_offsets, int n, uint8_t *__restrict__ out, int64_t capacity, const WsConst c) {
 	extern __shared__ __align__(16) unsigned char smem_raw[];
 	uint4 *ring_h;
 	unsigned *ring_w;
-	ws_rings<RAD>(smem_raw, ring_h, ring_w);
+	ws_rings<RAD, 4, WS_WARPS>(smem_raw, ring_h, ring_w);
 	const int total = __ldg(chunk_offsets + n);
 	const int nwarps = gridDim.x * WS_WARPS;
 	for (int item = blockIdx.x * WS_WARPS + (threadIdx.x >> 5); item < total; item += nwarps) {
@@ -263,11 +370,11 @@ __global__ void __launch_bounds__(WS_WARPS * 32) og_sauvola_warp_strips_kernel(
 		}
 		const int q = item - __ldg(chunk_offsets + lo);
 		const int w = __ldg(steps + 2 * lo), h = __ldg(steps + 2 * lo + 1);
-		if (q * WS_OUT >= w || h <= 0) continue;
+		if (q * WsGeom<4>::OUT >= w || h <= 0) continue;
 		const int64_t off = __ldg(pix_offsets + lo);
 		if (off + (int64_t)w * h > capacity) continue;
 		__syncwarp();
-		ws_stripe<RAD, false>(gray + off, h, w, (unsigned)w, out + off, (unsigned)w, q * WS_OUT, 0, h, c, ring_h, ring_w);
+		ws_stripe<RAD, 4, false>(gray + off, h, w, (unsigned)w, out + off, (unsigned)w, q * WsGeom<4>::OUT, 0, h, c, ring_h, ring_w);
 		__syncwarp();
 	}
 }
@@ -283,13 +390,21 @@ WsConst ws_const(int window, double k, double r) {
 	return c;
 }
 
-template <int RAD>
-int ws_launch_page(const uint8_t *src, int h, int w, int64_t src_pitch, uint8_t *dst, int64_t dst_pitch,
-	double k, double r, cudaStream_t st) {
-	const int stripes = (w + WS_OUT - 1) / WS_OUT;
-	// About `per_sm` resident warps per SM in one wave (a run re-reads 2 RAD rows of warm-up, at half the
-	// cost of an output row, so runs are kept long).
-	static const int per_sm = getenv("OG_SAUVOLA_WARPS") ? atoi(getenv("OG_SAUVOLA_WARPS")) : 20;
+int ws_env_int(const char *name, int fallback) {
+	const char *v = getenv(name);
+	return v != nullptr && atoi(v) > 0 ? atoi(v) : fallback;
+}
+
+template <int RAD, int PX, bool ALIGNED, int WARPS>
+int ws_launch_page_as(const uint8_t *src, int h, int w, int64_t src_pitch, uint8_t *dst, int64_t dst_pitch,
+	double k, double r, int slot, cudaStream_t st) {
+	constexpr size_t smem = WARPS * ws_warp_smem<RAD, PX>();
+	const int stripes = (w + WsGeom<PX>::OUT - 1) / WsGeom<PX>::OUT;
+	// One wave of runs: as many warps as fit beside each other (shared memory: the rings), each with a
+	// run as long as that allows -- a run re-reads 2 RAD rows to fill its window.
+	const int fit = (int)((size_t)220 * 1024 / (smem + 1024)) * WARPS;
+	static const int per_sm_env = ws_env_int("OG_SAUVOLA_WARPS", 0);
+	const int per_sm = per_sm_env > 0 ? per_sm_env : (fit < 48 ? fit : 48);
 	int segments = max(1, og_num_sms() * per_sm / stripes);
 	segments = max(1, min(segments, (h + 4 * (2 * RAD + 1) - 1) / (4 * (2 * RAD + 1))));
 	const int seg_rows = (h + segments - 1) / segments;
@@ -297,30 +412,33 @@ int ws_launch_page(const uint8_t *src, int h, int w, int64_t src_pitch, uint8_t 
 	const int64_t items64 = (int64_t)stripes * segments;
 	OG_REQUIRE(items64 < ((int64_t)1 << 30) && src_pitch < ((int64_t)1 << 31) && dst_pitch < ((int64_t)1 << 31), OG_E_RANGE, "image too large");
 	const int items = (int)items64;
-	const int blocks = (items + WS_WARPS - 1) / WS_WARPS;
-	const WsConst c = ws_const(2 * RAD + 1, k, r);
-	const bool aligned = ((reinterpret_cast<uintptr_t>(src) | (uintptr_t)src_pitch | reinterpret_cast<uintptr_t>(dst) | (uintptr_t)dst_pitch) & 3) == 0;
-	constexpr size_t smem = ws_smem_bytes<RAD>();
-	if (aligned) {
-		if (og_first_use(16 + 2 * RAD))
-			cudaFuncSetAttribute(og_sauvola_warp_page_kernel<RAD, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-		og_sauvola_warp_page_kernel<RAD, true><<<blocks, WS_WARPS * 32, smem, st>>>(src, h, w, src_pitch, dst, dst_pitch, c, seg_rows, stripes, items);
-	} else {
-		if (og_first_use(17 + 2 * RAD))
-			cudaFuncSetAttribute(og_sauvola_warp_page_kernel<RAD, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-		og_sauvola_warp_page_kernel<RAD, false><<<blocks, WS_WARPS * 32, smem, st>>>(src, h, w, src_pitch, dst, dst_pitch, c, seg_rows, stripes, items);
-	}
+	if (og_first_use(slot))
+		cudaFuncSetAttribute(og_sauvola_warp_page_kernel<RAD, PX, ALIGNED, WARPS>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+	og_sauvola_warp_page_kernel<RAD, PX, ALIGNED, WARPS><<<(items + WARPS - 1) / WARPS, WARPS * 32, smem, st>>>(
+		src, h, w, src_pitch, dst, dst_pitch, ws_const(2 * RAD + 1, k, r), seg_rows, stripes, items);
 	return og_check_launch("og_sauvola_warp_page_kernel");
+}
+
+template <int RAD>
+int ws_launch_page(const uint8_t *src, int h, int w, int64_t src_pitch, uint8_t *dst, int64_t dst_pitch,
+	double k, double r, cudaStream_t st) {
+	const uintptr_t bits = reinterpret_cast<uintptr_t>(src) | (uintptr_t)src_pitch | reinterpret_cast<uintptr_t>(dst) | (uintptr_t)dst_pitch;
+	static const int px_env = ws_env_int("OG_SAUVOLA_PX", 8);
+	if ((bits & 7) == 0 && px_env == 8 && w >= 256)
+		return ws_launch_page_as<RAD, 8, true, 2>(src, h, w, src_pitch, dst, dst_pitch, k, r, 3 * RAD, st);
+	if ((bits & 3) == 0)
+		return ws_launch_page_as<RAD, 4, true, WS_WARPS>(src, h, w, src_pitch, dst, dst_pitch, k, r, 3 * RAD + 1, st);
+	return ws_launch_page_as<RAD, 4, false, WS_WARPS>(src, h, w, src_pitch, dst, dst_pitch, k, r, 3 * RAD + 2, st);
 }
 
 template <int RAD>
 int ws_launch_strips(const uint8_t *gray, const int32_t *steps, const int64_t *pix_offsets,
 	const int32_t *chunk_offsets, int n, uint8_t *out, int64_t capacity, cudaStream_t st) {
-	constexpr size_t smem = ws_smem_bytes<RAD>();
+	constexpr size_t smem = WS_WARPS * ws_warp_smem<RAD, 4>();
 	if (og_first_use(32 + RAD))
 		cudaFuncSetAttribute(og_sauvola_warp_strips_kernel<RAD>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-	const WsConst c = ws_const(2 * RAD + 1, 0.2, 127.5);
-	og_sauvola_warp_strips_kernel<RAD><<<og_num_sms() * 5, WS_WARPS * 32, smem, st>>>(gray, steps, pix_offsets, chunk_offsets, n, out, capacity, c);
+	og_sauvola_warp_strips_kernel<RAD><<<og_num_sms() * 5, WS_WARPS * 32, smem, st>>>(gray, steps, pix_offsets, chunk_offsets, n, out, capacity,
+		ws_const(2 * RAD + 1, 0.2, 127.5));
 	return og_check_launch("og_sauvola_warp_strips_kernel");
 }
 
