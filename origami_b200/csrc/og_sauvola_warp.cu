@@ -161,7 +161,6 @@ __device__ __forceinline__ void ws_stripe(const uint8_t *__restrict__ img, int h
 	using G = WsGeom<PX>;
 	constexpr int WIN = 2 * RAD + 1, NW = G::NW, NK = G::NK, RW = RAD + 1;
 	constexpr unsigned NWIN = WIN * WIN;
-	struct Row { unsigned w[NW]; };
 	const int lane = threadIdx.x & 31;
 	const int cx = x0 - 8 + PX * lane;
 	const bool inside = cx >= 0 && cx + PX - 1 < w;
@@ -173,10 +172,36 @@ __device__ __forceinline__ void ws_stripe(const uint8_t *__restrict__ img, int h
 	unsigned *rw = ring_w + lane;
 #pragma unroll
 	for (int i = 0; i < WIN * NW; ++i) rh[i * 32] = make_uint4(0u, 0u, 0u, 0u);  // the rows "before" the first leave as zeros
-	// a lane of a stripe at the left or right border of the image gathers its (reflected) columns by byte
-	int rc[PX];
+	// A lane of a stripe at the left or right border of the image holds reflected columns.  Four
+	// neighbouring columns reflect to at most four neighbouring columns, so they lie in two aligned words:
+	// the lane requests those (aligned images) and permutes them into place when the row is used, so
+	// that its loads wait in the queue like everybody's.  Unaligned images: gathered byte by byte.
+	struct Row { unsigned w[NW], x[NW]; };
+	int rc[ALIGNED ? 1 : PX];
+	unsigned boff[ALIGNED ? NW : 1], bsel[ALIGNED ? NW : 1];
+	if (ALIGNED) {
 #pragma unroll
-	for (int b = 0; b < PX; ++b) rc[b] = inside ? 0 : ws_reflect(cx + b, w);
+		for (int q = 0; q < NW; ++q) {
+			boff[q] = 0;
+			bsel[q] = 0x3210u;
+			if (!inside) {
+				int col[4], lo = 0x7fffffff, hi = 0;
+#pragma unroll
+				for (int b = 0; b < 4; ++b) {
+					col[b] = ws_reflect(cx + 4 * q + b, w);
+					lo = min(lo, col[b]);
+					hi = max(hi, col[b]);
+				}
+				boff[q] = (unsigned)lo & ~3u;
+				bsel[q] = (unsigned)(col[0] - (int)boff[q]) | (unsigned)(col[1] - (int)boff[q]) << 4 |
+					(unsigned)(col[2] - (int)boff[q]) << 8 | (unsigned)(col[3] - (int)boff[q]) << 12 |
+					(hi >= (int)boff[q] + 4 ? 0x10000u : 0u);  // bit 16: the second word is needed (and holds a column of the image)
+			}
+		}
+	} else {
+#pragma unroll
+		for (int b = 0; b < PX; ++b) rc[b] = inside ? 0 : ws_reflect(cx + b, w);
+	}
 	auto load_row = [&](int r) -> Row {
 		const int ry = (unsigned)r < (unsigned)h ? r : ws_reflect(r, h);
 		const uint8_t *row = img_lane + (uint64_t)(unsigned)ry * pitch;
@@ -196,11 +221,18 @@ __device__ __forceinline__ void ws_stripe(const uint8_t *__restrict__ img, int h
 				const unsigned hi = sh ? __ldg(wp + 1) : 0u;  // an aligned word that holds a byte of the image stays inside its page
 				v.w[0] = __funnelshift_r(lo, hi, sh);
 			}
+		} else if (ALIGNED) {
+#pragma unroll
+			for (int q = 0; q < NW; ++q) {
+				const unsigned *wp = reinterpret_cast<const unsigned *>(row + boff[ALIGNED ? q : 0]);
+				v.w[q] = __ldg(wp);
+				v.x[q] = (bsel[ALIGNED ? q : 0] & 0x10000u) ? __ldg(wp + 1) : 0u;
+			}
 		} else {
 #pragma unroll
 			for (int q = 0; q < NW; ++q) {
-				const unsigned b0 = __ldg(row + rc[4 * q]), b1 = __ldg(row + rc[4 * q + 1]);
-				const unsigned b2 = __ldg(row + rc[4 * q + 2]), b3 = __ldg(row + rc[4 * q + 3]);
+				const unsigned b0 = __ldg(row + rc[ALIGNED ? 0 : 4 * q]), b1 = __ldg(row + rc[ALIGNED ? 0 : 4 * q + 1]);
+				const unsigned b2 = __ldg(row + rc[ALIGNED ? 0 : 4 * q + 2]), b3 = __ldg(row + rc[ALIGNED ? 0 : 4 * q + 3]);
 				v.w[q] = __byte_perm(b0 | (b1 << 8), b2 | (b3 << 8), 0x5410);
 			}
 		}
@@ -210,7 +242,11 @@ __device__ __forceinline__ void ws_stripe(const uint8_t *__restrict__ img, int h
 #pragma unroll
 	for (int j = 0; j < PX; ++j) v1[j] = v2[j] = 0;
 	int slot = 0, wslot = 0;  // ring slots of row r (sums: WIN slots, pixels: RAD + 1 slots)
-	auto body = [&](int r, const Row &cur, bool screen) {
+	auto body = [&](int r, Row cur, bool screen) {
+		if (ALIGNED && !inside) {
+#pragma unroll
+			for (int q = 0; q < NW; ++q) cur.w[q] = __byte_perm(cur.w[q], cur.x[q], bsel[ALIGNED ? q : 0] & 0xFFFFu);
+		}
 		// the row entering the window replaces the row that left it WIN rows ago in the ring
 		uint4 old[NW];
 #pragma unroll
@@ -412,9 +448,10 @@ int ws_launch_page_as(const uint8_t *src, int h, int w, int64_t src_pitch, uint8
 	const int64_t items64 = (int64_t)stripes * segments;
 	OG_REQUIRE(items64 < ((int64_t)1 << 30) && src_pitch < ((int64_t)1 << 31) && dst_pitch < ((int64_t)1 << 31), OG_E_RANGE, "image too large");
 	const int items = (int)items64;
+	auto kernel = og_sauvola_warp_page_kernel<RAD, PX, ALIGNED, WARPS>;
 	if (og_first_use(slot))
-		cudaFuncSetAttribute(og_sauvola_warp_page_kernel<RAD, PX, ALIGNED, WARPS>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-	og_sauvola_warp_page_kernel<RAD, PX, ALIGNED, WARPS><<<(items + WARPS - 1) / WARPS, WARPS * 32, smem, st>>>(
+		cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+	kernel<<<(items + WARPS - 1) / WARPS, WARPS * 32, smem, st>>>(
 		src, h, w, src_pitch, dst, dst_pitch, ws_const(2 * RAD + 1, k, r), seg_rows, stripes, items);
 	return og_check_launch("og_sauvola_warp_page_kernel");
 }
@@ -435,7 +472,7 @@ template <int RAD>
 int ws_launch_strips(const uint8_t *gray, const int32_t *steps, const int64_t *pix_offsets,
 	const int32_t *chunk_offsets, int n, uint8_t *out, int64_t capacity, cudaStream_t st) {
 	constexpr size_t smem = WS_WARPS * ws_warp_smem<RAD, 4>();
-	if (og_first_use(32 + RAD))
+	if (og_first_use(48 + RAD))
 		cudaFuncSetAttribute(og_sauvola_warp_strips_kernel<RAD>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
 	og_sauvola_warp_strips_kernel<RAD><<<og_num_sms() * 5, WS_WARPS * 32, smem, st>>>(gray, steps, pix_offsets, chunk_offsets, n, out, capacity,
 		ws_const(2 * RAD + 1, 0.2, 127.5));
