@@ -595,10 +595,10 @@ def run_ours_segpost(args):
 			e = torch.cuda.Event(enable_timing=True); e.record(); events.append(("start", e))
 		_lib.call("og_argmax_labels", pr.data_ptr(), 5, 4, 2400, 1280, labels.data_ptr(), masks.data_ptr(), mv.ctypes.data, 3, st)
 		if events is not None:
-			e = torch.cuda.Event(enable_timing=True); e.record(); events.append(("og_argmax4_kernel", e))
+			e = torch.cuda.Event(enable_timing=True); e.record(); events.append(("og_argmax4_unrolled_kernel", e))
 		_lib.call("og_sauvola", src.data_ptr(), PAGE_H, PAGE_W, src.stride(0), 15, 0.2, 127.5, dst.data_ptr(), dst.stride(0), st)
 		if events is not None:
-			e = torch.cuda.Event(enable_timing=True); e.record(); events.append(("og_sauvola_page_kernel", e))
+			e = torch.cuda.Event(enable_timing=True); e.record(); events.append(("og_sauvola_warp_page_kernel", e))
 		return 2
 
 	for i in range(max(args.warmup, 3)):
@@ -673,7 +673,7 @@ def run_ours_segpost(args):
 			"sample": "one page: NumPy argmax + masks + restated skimage Sauvola-15 (%.2f s)" % t}
 	if rank == 0:
 		peak, peak_src = measured_peak()
-		alg = {"og_argmax4_kernel": (4 * 5 * 4 + 1 + 3) * 2400 * 1280, "og_sauvola_page_kernel": 2 * PAGE_W * PAGE_H}
+		alg = {"og_argmax4_unrolled_kernel": (4 * 5 * 4 + 1 + 3) * 2400 * 1280, "og_sauvola_warp_page_kernel": 2 * PAGE_W * PAGE_H}
 		traffic = recorded_traffic()
 		rl_all = {}
 		for k, t in kernel_ms.items():

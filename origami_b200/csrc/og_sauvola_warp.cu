@@ -33,7 +33,7 @@ namespace {
 
 constexpr int WS_WARPS = 4;  // warps per CTA (independent of each other)
 #ifndef OG_WS_AHEAD
-#define OG_WS_AHEAD 3
+#define OG_WS_AHEAD 1
 #endif
 constexpr int WS_AHEAD = OG_WS_AHEAD;  // rows requested ahead of use
 
