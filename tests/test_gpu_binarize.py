@@ -20,6 +20,33 @@ def test_sauvola_page_bit_exact(cuda, shape, window, kind):
 	assert np.array_equal(got, want)
 
 
+# the warp kernel of windows <= 15 (csrc/og_sauvola_warp.cu): every window, 8 pixels per lane (8-byte aligned
+# rows of >= 256 columns), 4 pixels per lane (4-byte aligned), unaligned rows, several stripes and several
+# runs of rows, widths and heights below the window, views into a larger image
+@pytest.mark.parametrize("shape,window", [((130, 256), 3), ((77, 1000), 5), ((200, 264), 9), ((320, 488), 11), ((61, 744), 13),
+	((260, 960), 15), ((50, 252), 13), ((90, 116), 5), ((33, 253), 9), ((120, 301), 11), ((1, 1), 3), ((2, 3), 15), ((3, 40), 15),
+	((1, 300), 7), ((300, 1), 7), ((17, 6), 13), ((9, 257), 15)])
+def test_sauvola_warp_kernel_paths(cuda, shape, window):
+	img = synth.make_page(max(shape[1], 16), max(shape[0], 16), seed=shape[0] + window, kind="text")[:shape[0], :shape[1]]
+	img = np.ascontiguousarray(img)
+	want = exact.binarize(img, ("sauvola", window))
+	got = ops.sauvola(ops.to_device_image(img, cuda), window).cpu().numpy()
+	assert np.array_equal(got, want)
+
+
+@pytest.mark.parametrize("x0,y0,window", [(0, 0, 15), (5, 3, 15), (8, 1, 9), (4, 2, 5), (3, 0, 3)])
+def test_sauvola_on_views(cuda, x0, y0, window):
+	big = synth.make_page(1100, 300, seed=7, kind="noise")
+	h, w = 211, 1000
+	want = exact.binarize(np.ascontiguousarray(big[y0:y0 + h, x0:x0 + w]), ("sauvola", window))
+	dbig = ops.to_device_image(big, cuda)
+	dst_big = torch.zeros_like(dbig)
+	got = ops.sauvola(dbig[y0:y0 + h, x0:x0 + w], window, dst=dst_big[y0:y0 + h, x0:x0 + w])
+	assert np.array_equal(got.cpu().numpy(), want)
+	dst_big[y0:y0 + h, x0:x0 + w] = 0
+	assert int(dst_big.count_nonzero().item()) == 0  # nothing written outside the view
+
+
 def test_sauvola_rejects_even_window(cuda):
 	img = ops.to_device_image(np.zeros((32, 32), np.uint8), cuda)
 	with pytest.raises(ValueError):
