@@ -528,6 +528,14 @@ def run_ours(args):
 			"h2d_bytes_per_step": int(h2d_d), "d2h_bytes_per_step": int(d2h_d),
 			"api": "PagePipeline(..., dewarped=False, hand_off='device'): strips filtered (>= 6x6) and padded into the recogniser's "
 				"batch by og_pack_strips, handed over as a CUDA tensor (DLPack-exportable); only step counts, widths and indices are downloaded"}
+		if args.binarize != "none":
+			# binarized strips as one bit per pixel (og_pack_bits), unpacked strip by strip when accessed: the timed
+			# loop touches one strip per page, like the strips_only loop
+			s_bits, h2d_b, d2h_b = run_e2e_pipeline(args, inputs, device, 4 * args.e2e_steps, dewarped=False, hand_off="bits")
+			s_bits = shard.max_over_ranks(s_bits, device)
+			e2e["strips_as_bits"] = {"pages_per_s": world / s_bits, "ms_per_step": 1e3 * s_bits,
+				"h2d_bytes_per_step": int(h2d_b), "d2h_bytes_per_step": int(d2h_b),
+				"api": "PagePipeline(..., dewarped=False, hand_off='bits'): binarized strips travel as 1 bit per pixel and are unpacked on access"}
 	if rank == 0 and world == 1 and not args.no_cpu_baseline:
 		cpu = cpu_baseline(args, *inputs[0])
 

@@ -198,6 +198,14 @@ int og_pack_strips(const uint8_t *strips, const int32_t *steps, const int64_t *p
 	int min_w, int min_h, int pad_value, int H, int w_max,
 	uint8_t *batch_out, int32_t *slot_scratch, int32_t *widths_out, int32_t *kept_index_out, int32_t *n_kept_out, void *stream);
 
+/* (f)4  binarized strips as one bit per pixel, for callers that take the strips to the host: eight
+ * times fewer bytes over PCIe than the 0 / 255 bytes Line.image returns (origami/core/block.py:140-141,
+ * consumed by origami/batch/detect/ocr.py:238-249 and origami/batch/export/lines.py:57-67, which writes
+ * them as 1-bit images).  No counterpart in the reference: a transport format.  dst[i] bit (7 - j) =
+ * (src[8 i + j] != 0), numpy.packbits order; n pixels in, (n + 7) / 8 bytes out, the last byte padded
+ * with zero bits.  Strip i of a packed strip buffer starts at bit pix_offsets[i]. */
+int og_pack_bits(const uint8_t *src, int64_t n, uint8_t *dst, void *stream);
+
 /* A triangulation with vertex values on the device (all pointers are DEVICE pointers): what
  * og_tri_interp takes as separate arguments, as one struct for the entry points that need two of them. */
 typedef struct og_tri_tables {

@@ -62,6 +62,7 @@ _SIGNATURES = {
 	"og_binarize_strips": [c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_void_p, c_int64, c_void_p, c_void_p],
 	"og_pack_strips": [c_void_p, c_void_p, c_void_p, c_int, c_int64, c_int, c_int, c_int, c_int, c_int,
 		c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p],
+	"og_pack_bits": [c_void_p, c_int64, c_void_p, c_void_p],
 	"og_tri_interp": [c_void_p, c_int64, c_void_p, c_void_p, c_void_p, c_int, c_int, c_double, c_double, c_double,
 		c_void_p, c_void_p, c_void_p, c_double, c_void_p, c_int, c_void_p],
 	"og_field_march": [ctypes.POINTER(Field), c_void_p, c_int, c_int, c_float, c_void_p, c_void_p],

@@ -25,7 +25,7 @@ PageResult = collections.namedtuple("PageResult", ["dewarped", "strips", "steps"
 # until the slot is reused, like the host views), widths and line indices of the kept strips (NumPy)
 DeviceBatch = collections.namedtuple("DeviceBatch", ["batch", "widths", "line_index"])
 
-from ...core.block import StripList  # noqa: E402  (re-exported: results of PagePipeline use it too)
+from ...core.block import PackedStripList, StripList  # noqa: E402  (re-exported: results of PagePipeline use them too)
 
 
 _parallel_copy = ops.parallel_copy
@@ -128,8 +128,12 @@ class PagePipeline:
 		self.use_map = use_map or not self.want_dewarped
 		# hand_off="device": the strips stay on the GPU as the recogniser's padded input batch
 		# (origami/batch/detect/ocr.py:238-268); only step counts, widths and indices travel back
-		if hand_off not in ("host", "device"):
-			raise ValueError("hand_off must be 'host' or 'device'")
+		# hand_off="bits": binarized strips travel to the host as one bit per pixel (og_pack_bits) and are
+		# unpacked strip by strip when they are accessed (PackedStripList)
+		if hand_off not in ("host", "device", "bits"):
+			raise ValueError("hand_off must be 'host', 'device' or 'bits'")
+		if hand_off == "bits" and spec is None:
+			raise ValueError("hand_off='bits' needs a binarizer: gray strips have more than one bit per pixel")
 		self.hand_off = hand_off
 		self.min_size, self.pad_value = (int(min_size[0]), int(min_size[1])), int(pad_value)
 		self.slots = [_Slot(self.device) for _ in range(max(2, depth))]
@@ -160,6 +164,7 @@ class PagePipeline:
 		if w_cap is not None:
 			w_max = w_cap
 		on_device = self.hand_off == "device"
+		as_bits = self.hand_off == "bits"
 
 		pitch = W  # the source is only read with byte loads: no row padding, one contiguous copy
 		dpitch = (Wd + 127) // 128 * 128
@@ -170,7 +175,8 @@ class PagePipeline:
 		n_in = o_desc + al(max(desc.nbytes, 1))
 		# output block: dewarped page (pitched) | strips | steps | pix offsets
 		o_strips = al(Hd * dpitch) if self.want_dewarped else 0
-		o_steps = o_strips + (0 if on_device else al(cap))  # device hand-off: the strips are not part of the download
+		# device hand-off: the strips are not part of the download; bits: an eighth of them is
+		o_steps = o_strips + (0 if on_device else al((cap + 7) // 8 + 4) if as_bits else al(cap))
 		o_offs = o_steps + al(8 * max(n, 1))
 		o_meta = o_offs + al(8 * (n + 1))  # widths | kept indices | n_kept (device hand-off)
 		n_out = o_meta + (al(4 * (2 * max(n, 1) + 1)) if on_device else 0)
@@ -182,8 +188,9 @@ class PagePipeline:
 		slot.d_in = _Slot._grow(slot.d_in, n_in, device=self.device)
 		slot.d_out = _Slot._grow(slot.d_out, n_out, device=self.device)
 		slot.d_gray = _Slot._grow(slot.d_gray, cap, device=self.device)
-		if on_device:
+		if on_device or as_bits:
 			slot.d_strips = _Slot._grow(slot.d_strips, cap, device=self.device)
+		if on_device:
 			slot.d_batch = _Slot._grow(slot.d_batch, max(n, 1) * self.line_height * w_max, device=self.device)
 			slot.d_slots = _Slot._grow(slot.d_slots, 4 * max(n, 1), device=self.device)
 		slot.d_chunks = _Slot._grow(slot.d_chunks, 4 * (n + 2), device=self.device)
@@ -222,10 +229,12 @@ class PagePipeline:
 					base_out + o_steps, base_out + o_offs, slot.d_chunks.data_ptr(), s)
 				mode, window = ops._binarize_args(self.binarize)
 				scratch = slot.d_gray.data_ptr() if mode == ops.OG_BIN_SAUVOLA else 0
-				p_strips = slot.d_strips.data_ptr() if on_device else base_out + o_strips
+				p_strips = slot.d_strips.data_ptr() if (on_device or as_bits) else base_out + o_strips
 				_lib.call("og_extract_lines", base_in, H, W, pitch, base_in + o_grid, gh, gw, cell, p_map,
 					base_in + o_desc, n, base_out + o_steps, base_out + o_offs, slot.d_chunks.data_ptr(),
 					p_strips, cap, 0, mode, window, scratch, 0, s)
+				if as_bits:
+					_lib.call("og_pack_bits", p_strips, cap, base_out + o_strips, s)
 				if on_device:
 					p_meta = base_out + o_meta
 					_lib.call("og_pack_strips", p_strips, base_out + o_steps, base_out + o_offs, n, cap,
@@ -264,6 +273,8 @@ class PagePipeline:
 				return self._collect(slot)
 			batch = slot.d_batch[:n_kept * self.line_height * w_max].view(n_kept, self.line_height, w_max)
 			return PageResult(dewarped, DeviceBatch(batch, meta[:n_kept].copy(), meta[m:m + n_kept].copy()), steps)
+		if self.hand_off == "bits":
+			return PageResult(dewarped, PackedStripList(hout[o_strips:o_strips + (cap + 7) // 8], offs, steps), steps)
 		flat = hout[o_strips:o_strips + cap]
 		return PageResult(dewarped, StripList(flat, offs, steps), steps)
 

@@ -347,6 +347,38 @@ class StripList(collections.abc.Sequence):
 		return self._flat[self._offs[i]:self._offs[i + 1]].reshape(self._steps[i, 1], self._steps[i, 0])
 
 
+class PackedStripList(collections.abc.Sequence):
+	"""Binarized strips that travelled as one bit per pixel (og_pack_bits): a read-only sequence of
+	(ysteps, xsteps) uint8 arrays of 0 / 255 like StripList, each unpacked when it is accessed.
+	`bits` is the packed buffer (numpy.packbits order); strip i starts at bit offsets[i]."""
+
+	def __init__(self, bits, offsets, steps):
+		self._bits, self._offs, self._steps = bits, offsets, steps
+
+	def __len__(self):
+		return int(self._steps.shape[0])
+
+	def _strip(self, a, b, h, w):
+		first = a >> 3
+		px = np.unpackbits(self._bits[first:(b + 7) >> 3], count=(b - 8 * first))[a - 8 * first:]
+		px *= 255
+		return px.reshape(h, w)
+
+	def __iter__(self):
+		offs = self._offs.tolist()
+		for (w, h), a, b in zip(self._steps.tolist(), offs, offs[1:]):
+			yield self._strip(a, b, h, w)
+
+	def __getitem__(self, i):
+		if isinstance(i, slice):
+			return [self[k] for k in range(*i.indices(len(self)))]
+		if i < 0:
+			i += len(self)
+		if not 0 <= i < len(self):
+			raise IndexError(i)
+		return self._strip(int(self._offs[i]), int(self._offs[i + 1]), int(self._steps[i, 1]), int(self._steps[i, 0]))
+
+
 def _plan(grid, records):
 	la = records if isinstance(records, np.ndarray) else ops.pack_lines(records)
 	dev = grid._device

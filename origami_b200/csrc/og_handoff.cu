@@ -102,6 +102,41 @@ __global__ void __launch_bounds__(256) og_pack_copy_kernel(const uint8_t *__rest
 	}
 }
 
+// Binarized pixels as one bit each (numpy.packbits order: the first pixel is the top bit).  A thread
+// packs 32 pixels: the low bit of every byte's OR-fold, gathered into nibbles by a multiplication
+// whose partial products do not overlap (bytes b0..b3 at bits 0, 8, 16, 24 times
+// 2^31 + 2^22 + 2^13 + 2^4 land on bits 31, 30, 29, 28).
+__device__ __forceinline__ unsigned og_nibble(unsigned w) {
+	w |= w >> 4;
+	w |= w >> 2;
+	w |= w >> 1;
+	return ((w & 0x01010101u) * 0x80402010u) >> 28;
+}
+
+__global__ void __launch_bounds__(256) og_pack_bits_kernel(const uint8_t *__restrict__ src, int64_t n, uint8_t *__restrict__ dst) {
+	const int64_t nout = (n + 7) >> 3;  // bytes
+	const bool vec = ((reinterpret_cast<uintptr_t>(src) & 15) == 0) && ((reinterpret_cast<uintptr_t>(dst) & 3) == 0);
+	const int64_t ngroups = (nout + 3) >> 2;  // 4 output bytes = 32 pixels
+	for (int64_t g = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; g < ngroups; g += (int64_t)gridDim.x * blockDim.x) {
+		const int64_t p0 = g * 32;
+		if (vec && p0 + 32 <= n) {
+			const uint4 a = __ldg(reinterpret_cast<const uint4 *>(src + p0)), b = __ldg(reinterpret_cast<const uint4 *>(src + p0 + 16));
+			const unsigned o0 = og_nibble(a.x) << 4 | og_nibble(a.y), o1 = og_nibble(a.z) << 4 | og_nibble(a.w);
+			const unsigned o2 = og_nibble(b.x) << 4 | og_nibble(b.y), o3 = og_nibble(b.z) << 4 | og_nibble(b.w);
+			*reinterpret_cast<unsigned *>(dst + g * 4) = o0 | o1 << 8 | o2 << 16 | o3 << 24;
+		} else {
+			for (int k = 0; k < 4 && g * 4 + k < nout; ++k) {
+				unsigned o = 0;
+				for (int j = 0; j < 8; ++j) {
+					const int64_t q = p0 + 8 * k + j;
+					o |= (q < n && src[q] != 0 ? 1u : 0u) << (7 - j);
+				}
+				dst[g * 4 + k] = (uint8_t)o;
+			}
+		}
+	}
+}
+
 }  // namespace
 
 extern "C" int og_pack_strips(const uint8_t *strips, const int32_t *steps, const int64_t *pix_offsets, int n, int64_t capacity,
@@ -123,4 +158,15 @@ extern "C" int og_pack_strips(const uint8_t *strips, const int32_t *steps, const
 	if (rc) return rc;
 	og_pack_copy_kernel<<<min(n, og_num_sms() * 8), 256, 0, st>>>(strips, steps, pix_offsets, n, capacity, slot_scratch, H, w_max, pad_value, batch_out);
 	return og_check_launch("og_pack_copy_kernel");
+}
+
+extern "C" int og_pack_bits(const uint8_t *src, int64_t n, uint8_t *dst, void *stream) {
+	OG_REQUIRE(n >= 0, OG_E_ARG, "n < 0");
+	if (n == 0) return OG_OK;
+	OG_REQUIRE(src != nullptr && dst != nullptr, OG_E_ARG, "NULL pointer");
+	const int64_t groups = (n + 31) / 32;
+	const int64_t want = (groups + 255) / 256;
+	const int blocks = (int)(want < (int64_t)og_num_sms() * 16 ? want : (int64_t)og_num_sms() * 16);
+	og_pack_bits_kernel<<<blocks, 256, 0, (cudaStream_t)stream>>>(src, n, dst);
+	return og_check_launch("og_pack_bits_kernel");
 }

@@ -383,6 +383,21 @@ def pack_strips(strips, plan, height, w_max, min_w=6, min_h=6, pad_value=0, batc
 	return batch, widths, kept, n_kept
 
 
+def pack_bits(src, n=None, out=None):
+	"""Binarized bytes -> one bit per pixel on the device (numpy.packbits order): src a flat uint8 CUDA
+	tensor, n pixels (all of it by default); returns a uint8 tensor of (n + 7) // 8 bytes."""
+	_require_cuda()
+	if src.dtype != torch.uint8 or not src.is_cuda or not src.is_contiguous():
+		raise ValueError("src must be a contiguous uint8 CUDA tensor")
+	n = src.numel() if n is None else int(n)
+	if n > src.numel():
+		raise ValueError("n exceeds the tensor")
+	if out is None:
+		out = torch.empty(((n + 7) // 8,), dtype=torch.uint8, device=src.device)
+	_call("og_pack_bits", src, ([out], lambda st: (src.data_ptr(), n, out.data_ptr(), st)))
+	return out
+
+
 def sauvola(src, window=15, k=0.2, r=127.5, dst=None):
 	"""(src > threshold_sauvola(src, window)) * 255 on a device image."""
 	_require_cuda()

@@ -82,3 +82,30 @@ def test_pipeline_hands_the_strips_over_on_the_device(cuda, spec):
 		ref, ref_w, ref_k = exact.ocr_batch(strips, 48, b.shape[2])
 		assert np.array_equal(res.strips.widths, ref_w) and np.array_equal(res.strips.line_index, ref_k)
 		assert np.array_equal(b.cpu().numpy(), ref)
+
+
+@pytest.mark.parametrize("n,offset", [(0, 0), (1, 0), (7, 0), (8, 0), (31, 0), (32, 0), (33, 0), (1000, 0), (100003, 0), (4099, 3), (65536, 16)])
+def test_pack_bits_is_numpy_packbits(cuda, n, offset):
+	rng = np.random.RandomState(n + offset)
+	px = rng.randint(0, 3, size=n + offset).astype(np.uint8) * rng.randint(1, 256, size=n + offset).astype(np.uint8)  # 0 and arbitrary non-zero bytes
+	src = torch.from_numpy(px).to(cuda)[offset:]
+	got = ops.pack_bits(src.contiguous() if offset == 0 else src, n).cpu().numpy() if n else np.zeros(0, np.uint8)
+	assert np.array_equal(got, np.packbits(px[offset:] != 0))
+
+
+def test_pipeline_bits_hand_off_equals_host_strips(cuda):
+	from origami_b200.batch.core.pipeline import PagePipeline
+	page, g, dense, lines = _page(seed=9, n=80)
+	arr = np.array([[l["p"], l["right"], l["up"]] for l in lines], dtype=np.float64)
+	jobs = [(page, g, 25, arr)] * 3
+	for spec in ("otsu", "sauvola(window_size=15)"):
+		host = [[s.copy() for s in res.strips] for res in PagePipeline(48, spec, depth=2, dewarped=False).run(jobs)]
+		bits = list(PagePipeline(48, spec, depth=2, dewarped=False, hand_off="bits").run(jobs))
+		assert len(bits) == len(host) == 3
+		for res, want in zip(bits, host):
+			assert len(res.strips) == len(want) == len(lines)
+			for a, b in zip(res.strips, want):
+				assert a.dtype == np.uint8 and np.array_equal(a, b)
+			assert np.array_equal(res.strips[-1], want[-1]) and np.array_equal(res.strips[5:7][1], want[6])
+	with pytest.raises(ValueError):
+		PagePipeline(48, "", hand_off="bits")

@@ -236,3 +236,15 @@ def test_flow_samples_zip_roundtrip(tmp_path):
 		h, v = Samples.open(zf, "h"), Samples.open(zf, "v")
 	assert len(h) == 3 and np.allclose(np.array(h.points), np.array(s.points)) and np.allclose(h.values, s.values)
 	assert h.geometry.size == (2400, 3600) and len(v.values) == 0 and h.std == 0
+
+
+def test_packed_strip_list_unpacks_what_strip_list_views():
+	from origami_b200.core.block import PackedStripList, StripList
+	rng = np.random.RandomState(0)
+	steps = np.array([[5, 3], [7, 1], [1, 1], [13, 4], [8, 8], [3, 5]], np.int32)
+	offs = np.concatenate([[0], np.cumsum(steps[:, 0] * steps[:, 1])]).astype(np.int64)
+	flat = (rng.randint(0, 2, size=int(offs[-1])) * 255).astype(np.uint8)
+	a, b = StripList(flat, offs, steps), PackedStripList(np.packbits(flat != 0), offs, steps)
+	assert len(a) == len(b) == 6
+	assert all(x.shape == y.shape and np.array_equal(x, y) for x, y in zip(a, b))
+	assert np.array_equal(a[3], b[3]) and np.array_equal(a[-1], b[-1]) and np.array_equal(a[1:3][1], b[1:3][1])
