@@ -13,7 +13,11 @@
 // is uniform across the CTA.  The y-axis state of the tile's 32 rows is computed once per
 // CTA into shared memory.  Source taps are gathered through the read-only path with 32-bit
 // offsets; the smooth warp makes neighbouring threads hit the same 128-byte lines.
+#include <mutex>
+#include <stdlib.h>
+
 #include "og_common.cuh"
+#include "og_internal.cuh"
 #include <type_traits>
 
 #ifndef OG_PAGE_MINB
@@ -51,6 +55,7 @@ struct PageParams {
 	int64_t dst_pitch;
 	float *map_out;
 	float scale_x, scale_y;
+	cudaTextureObject_t tex;  // OG_PAGE_TEX experiment: the source as a point-sampled, zero-bordered 2-D texture (0: none)
 };
 
 // image bytes of a thread's two pixel pairs (16-bit stores when aligned and complete)
@@ -417,7 +422,7 @@ constexpr int P2_ROWS = OG_P2_ROWS;    // rows walked per thread
 constexpr int P2_TILE_W = 2 * P2_TBX;
 constexpr int P2_TILE_H = P2_TBY * P2_ROWS;
 
-template <bool SCALED, bool WRITE_MAP>
+template <bool SCALED, bool WRITE_MAP, bool TEX>
 __global__ void __launch_bounds__(P2_TBX *P2_TBY, OG_P2_MINB) og_page_pipelined_kernel(const __grid_constant__ PageParams p) {
 	__shared__ RowAxis s_rows[P2_TILE_H];
 	__shared__ int s_win[4];
@@ -544,7 +549,24 @@ __global__ void __launch_bounds__(P2_TBX *P2_TBY, OG_P2_MINB) og_page_pipelined_
 				mx[k] = SCALED ? __fmul_rn(d[k].x, scx) : d[k].x;
 				my[k] = SCALED ? __fmul_rn(d[k].y, scy) : d[k].y;
 			}
-			og_load_taps_batch<2>(src, H, W, spitch, mx, my, t);
+			if (TEX) {
+				// the four taps of a sample as one gather (TLD4): texels (ix .. ix + 1, iy .. iy + 1) around
+				// (ix + 1, iy + 1), zero outside the image = cv2.remap's BORDER_CONSTANT 0
+#pragma unroll
+				for (int k = 0; k < 2; ++k) {
+					const int fsx = __float2int_rn(__fmul_rn(mx[k], 32.f)), fsy = __float2int_rn(__fmul_rn(my[k], 32.f));
+					t[k].fx = fsx & 31;
+					t[k].fy = fsy & 31;
+					const float tx = __int2float_rn(og_sat_short(fsx >> 5) + 1), ty = __int2float_rn(og_sat_short(fsy >> 5) + 1);
+					const uchar4 g = tex2Dgather<uchar4>(p.tex, tx, ty, 0);
+					t[k].p00 = g.w;
+					t[k].p01 = g.z;
+					t[k].p10 = g.x;
+					t[k].p11 = g.y;
+				}
+			} else {
+				og_load_taps_batch<2>(src, H, W, spitch, mx, my, t);
+			}
 		};
 		auto finish = [&](const og_taps (&t)[2]) {
 			const int v0 = og_blend_taps(t[0]), v1 = og_blend_taps(t[1]);
@@ -582,12 +604,15 @@ void launch_variant(const PageParams &p, bool stage, dim3 grid, dim3 block, cuda
 	const int Wd = p.gw * p.cell, Hd = p.gh * p.cell;
 	const dim3 block2(P2_TBX, P2_TBY), grid2((Wd + P2_TILE_W - 1) / P2_TILE_W, (Hd + P2_TILE_H - 1) / P2_TILE_H);
 	const bool pipelined = LINEAR && !stage && OG_PAGE_PIPELINED;
-	if (p.map_out != nullptr && p.dst != nullptr) {
-		if (pipelined) og_page_pipelined_kernel<SCALED, true><<<grid2, block2, 0, st>>>(p);
+	if (pipelined && p.tex != 0 && p.dst != nullptr) {
+		if (p.map_out != nullptr) og_page_pipelined_kernel<SCALED, true, true><<<grid2, block2, 0, st>>>(p);
+		else og_page_pipelined_kernel<SCALED, false, true><<<grid2, block2, 0, st>>>(p);
+	} else if (p.map_out != nullptr && p.dst != nullptr) {
+		if (pipelined) og_page_pipelined_kernel<SCALED, true, false><<<grid2, block2, 0, st>>>(p);
 		else if (LINEAR && stage) og_page_staged_kernel<SCALED, true><<<grid, block, 0, st>>>(p);
 		else og_page_kernel<LINEAR, SCALED, true, true><<<grid, block, 0, st>>>(p);
 	} else if (p.dst != nullptr) {
-		if (pipelined) og_page_pipelined_kernel<SCALED, false><<<grid2, block2, 0, st>>>(p);
+		if (pipelined) og_page_pipelined_kernel<SCALED, false, false><<<grid2, block2, 0, st>>>(p);
 		else if (LINEAR && stage) og_page_staged_kernel<SCALED, false><<<grid, block, 0, st>>>(p);
 		else og_page_kernel<LINEAR, SCALED, false, true><<<grid, block, 0, st>>>(p);
 	} else {
@@ -609,6 +634,42 @@ int launch_page(const PageParams &p, int interp, cudaStream_t st) {
 		else launch_variant<false, false>(p, stage, grid, block, st);
 	}
 	return og_check_launch("og_page_kernel");
+}
+
+// OG_PAGE_TEX experiment: texture objects over the caller's source images, kept per (device, pointer,
+// shape, pitch) -- a descriptor only holds the address, so it stays valid when the memory is rewritten
+// or reallocated at the same place; nothing is destroyed while kernels may still use it.
+cudaTextureObject_t page_texture(const uint8_t *src, int H, int W, int64_t pitch) {
+	static const bool enabled = getenv("OG_PAGE_TEX") != nullptr;
+	if (!enabled || (reinterpret_cast<uintptr_t>(src) & 511) != 0 || (pitch & 31) != 0) return 0;
+	struct Entry { int dev; const uint8_t *src; int H, W; int64_t pitch; cudaTextureObject_t tex; };
+	static Entry cache[64];
+	static int used = 0;
+	static std::mutex mu;
+	std::lock_guard<std::mutex> lock(mu);
+	const int dev = og_device_ordinal();
+	for (int i = 0; i < used; ++i)
+		if (cache[i].dev == dev && cache[i].src == src && cache[i].H == H && cache[i].W == W && cache[i].pitch == pitch) return cache[i].tex;
+	if (used == 64) return 0;
+	cudaResourceDesc rd{};
+	rd.resType = cudaResourceTypePitch2D;
+	rd.res.pitch2D.devPtr = const_cast<uint8_t *>(src);
+	rd.res.pitch2D.desc = cudaCreateChannelDesc<unsigned char>();
+	rd.res.pitch2D.width = (size_t)W;
+	rd.res.pitch2D.height = (size_t)H;
+	rd.res.pitch2D.pitchInBytes = (size_t)pitch;
+	cudaTextureDesc td{};
+	td.addressMode[0] = td.addressMode[1] = cudaAddressModeBorder;
+	td.filterMode = cudaFilterModePoint;
+	td.readMode = cudaReadModeElementType;
+	td.normalizedCoords = 0;
+	cudaTextureObject_t tex = 0;
+	if (cudaCreateTextureObject(&tex, &rd, &td, nullptr) != cudaSuccess) {
+		cudaGetLastError();
+		return 0;
+	}
+	cache[used++] = Entry{dev, src, H, W, pitch, tex};
+	return tex;
 }
 
 int check_grid(const float *grid, int gh, int gw, int cell) {
@@ -669,5 +730,6 @@ extern "C" int og_remap_page(const uint8_t *src, int H, int W, int64_t src_pitch
 	p.map_out = map_out;
 	p.scale_x = scale_x;
 	p.scale_y = scale_y;
+	p.tex = (dst != nullptr && (interp & 0xff) == OG_INTER_LINEAR) ? page_texture(src, H, W, src_pitch) : 0;
 	return launch_page(p, interp, (cudaStream_t)stream);
 }
