@@ -97,7 +97,7 @@ __global__ void __launch_bounds__(OTHREADS) og_otsu_strips_kernel(
 #pragma unroll
 				for (int q = 0; q < 4; ++q) {
 #pragma unroll
-					for (int b = 0; b < 4; ++b) atomicAdd(&rep[((wds[q] >> (8 * b)) & 255u) * HREP + r], 1u);
+					for (int b = 0; b < 4; ++b) atomicAdd(&rep[__byte_perm(wds[q], 0, 0x4440 + b) * HREP + r], 1u);
 				}
 			}
 		}
@@ -119,6 +119,7 @@ __global__ void __launch_bounds__(OTHREADS) og_otsu_strips_kernel(
 		}
 		__syncthreads();
 		const unsigned int t = (unsigned int)s_t;
+		const og_gt4_t gt = og_gt4_consts(t);
 		for (int64_t i = threadIdx.x; i < head; i += OTHREADS) o[i] = g[i] > t ? 255 : 0;
 		const bool out_al = ((reinterpret_cast<uintptr_t>(o + head)) & 15) == 0;
 		for (int64_t i0 = threadIdx.x; i0 < nvec; i0 += OTHREADS * OU) {
@@ -129,14 +130,7 @@ __global__ void __launch_bounds__(OTHREADS) og_otsu_strips_kernel(
 			for (int u = 0; u < OU; ++u) {
 				const int64_t i = i0 + u * OTHREADS;
 				if (i >= nvec) break;
-				unsigned int wds[4] = {v[u].x, v[u].y, v[u].z, v[u].w};
-#pragma unroll
-				for (int q = 0; q < 4; ++q) {
-					unsigned int m = 0;
-#pragma unroll
-					for (int b = 0; b < 4; ++b) m |= (((wds[q] >> (8 * b)) & 255u) > t ? 255u : 0u) << (8 * b);
-					wds[q] = m;
-				}
+				const unsigned int wds[4] = {og_gt4(v[u].x, gt), og_gt4(v[u].y, gt), og_gt4(v[u].z, gt), og_gt4(v[u].w, gt)};
 				if (out_al) {
 					reinterpret_cast<uint4 *>(o + head)[i] = make_uint4(wds[0], wds[1], wds[2], wds[3]);
 				} else {
@@ -204,6 +198,7 @@ __global__ void __launch_bounds__(BTHREADS) og_otsu_apply_kernel(
 	}
 	__syncthreads();
 	const unsigned int t = (unsigned int)s_t;
+	const og_gt4_t gt = og_gt4_consts(t);
 	for (int y = blockIdx.x; y < h; y += gridDim.x) {
 		const uint8_t *g = src + (int64_t)y * src_pitch;
 		uint8_t *o = dst + (int64_t)y * dst_pitch;
@@ -214,14 +209,7 @@ __global__ void __launch_bounds__(BTHREADS) og_otsu_apply_kernel(
 		const uint4 *gv = reinterpret_cast<const uint4 *>(g + head);
 		for (int i = threadIdx.x; i < nvec; i += BTHREADS) {
 			const uint4 v = __ldg(gv + i);
-			unsigned int wds[4] = {v.x, v.y, v.z, v.w};
-#pragma unroll
-			for (int q = 0; q < 4; ++q) {
-				unsigned int m = 0;
-#pragma unroll
-				for (int b = 0; b < 4; ++b) m |= (((wds[q] >> (8 * b)) & 255u) > t ? 255u : 0u) << (8 * b);
-				wds[q] = m;
-			}
+			const unsigned int wds[4] = {og_gt4(v.x, gt), og_gt4(v.y, gt), og_gt4(v.z, gt), og_gt4(v.w, gt)};
 			if (out_al) {
 				__stcs(reinterpret_cast<uint4 *>(o + head) + i, make_uint4(wds[0], wds[1], wds[2], wds[3]));
 			} else {

@@ -40,6 +40,29 @@ int og_launch_sauvola_warp_strips(const uint8_t *gray, const int32_t *steps, con
 	const int32_t *chunk_offsets, int n, int window, uint8_t *out, int64_t capacity, cudaStream_t st);
 
 #ifdef __CUDACC__
+// Four bytes at once: 0xFF where the byte of x exceeds t (0 .. 255), else 0.  x > t is the carry out of
+// bit 7 of x + (255 - t): the low seven bits are added per byte without crossing into the neighbour,
+// the carry out is the majority of the two top bits and that carry in, and prmt's sign-replicating
+// selectors spread it over the byte.  Four instructions per word (a compare-select-insert per byte is ~6
+// per pixel).  og_gt4_consts gives the two per-threshold constants.
+struct og_gt4_t {
+	unsigned c7, c8;
+};
+__device__ __forceinline__ og_gt4_t og_gt4_consts(unsigned t) {
+	const unsigned c = 255u - t;
+	og_gt4_t k;
+	k.c7 = (c & 0x7Fu) * 0x01010101u;
+	k.c8 = (c & 0x80u) * 0x01010101u;
+	return k;
+}
+__device__ __forceinline__ unsigned og_gt4(unsigned x, og_gt4_t k) {
+	const unsigned z = (x & 0x7F7F7F7Fu) + k.c7;
+	const unsigned o = (x & k.c8) | ((x | k.c8) & z);
+	unsigned d;
+	asm("prmt.b32 %0, %1, %1, 0xBA98;" : "=r"(d) : "r"(o));
+	return d;
+}
+
 // Otsu threshold from an exact 256-bin histogram (skimage 0.16.2 threshold_otsu on uint8: bins =
 // the integers [min, max], float64 cumulative sums, first argmax of w1 * w2 * (m1 - m2)^2; a
 // single-valued image is the ValueError -> 128 case of origami/core/binarize.py:20-23).  One

@@ -591,14 +591,14 @@ __global__ void __launch_bounds__(FT, OG_F_MINB) og_strips_fused_kernel(const __
 			for (long long i = tid; i < head; i += FT) o[i] = g[i] > t ? 255 : 0;
 			const uint4 *gv = reinterpret_cast<const uint4 *>(g + head);
 			const bool out_al = ((reinterpret_cast<uintptr_t>(o + head)) & 15) == 0;
-			const unsigned int t4 = t * 0x01010101u;
+			const og_gt4_t gt = og_gt4_consts(t);
 			for (long long i = tid; i < nvec; i += FT) {
 				const uint4 v = gv[i];  // plain loads: these bytes were written by this CTA
 				uint4 m;
-				m.x = __vcmpgtu4(v.x, t4);
-				m.y = __vcmpgtu4(v.y, t4);
-				m.z = __vcmpgtu4(v.z, t4);
-				m.w = __vcmpgtu4(v.w, t4);
+				m.x = og_gt4(v.x, gt);
+				m.y = og_gt4(v.y, gt);
+				m.z = og_gt4(v.z, gt);
+				m.w = og_gt4(v.w, gt);
 				if (out_al) {
 					reinterpret_cast<uint4 *>(o + head)[i] = m;
 				} else {
