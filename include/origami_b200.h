@@ -153,7 +153,10 @@ int og_extract_lines(const uint8_t *src, int H, int W, int64_t src_pitch,
  * Line.image (block.py:140-141).  gray and out hold n strips packed at pix_offsets; they
  * must not alias for OG_BIN_SAUVOLA (window odd, 3..127; k = 0.2, r = 127.5 as in the
  * reference).  capacity = bytes of gray and of out; strips that do not fit are skipped whole, as
- * in og_extract_lines.  thresholds_out (n int32, OTSU only, may be NULL) receives each threshold. */
+ * in og_extract_lines.  thresholds_out (n int32, OTSU only, may be NULL) receives each threshold.
+ * chunk_offsets is the n + 2 entry array og_line_steps wrote: like og_extract_lines, the Sauvola pass
+ * hands its work out through the plan's work-ticket word (entry n + 1) while it runs and leaves it at
+ * zero, so a plan serves one such call at a time. */
 int og_binarize_strips(const uint8_t *gray, const int32_t *steps, const int64_t *pix_offsets,
 	const int32_t *chunk_offsets, int n, int mode, int window, uint8_t *out, int64_t capacity,
 	int32_t *thresholds_out, void *stream);

@@ -174,66 +174,59 @@ __device__ __forceinline__ void ws_stripe(const uint8_t *__restrict__ img, int h
 	for (int i = 0; i < WIN * NW; ++i) rh[i * 32] = make_uint4(0u, 0u, 0u, 0u);  // the rows "before" the first leave as zeros
 	// A lane of a stripe at the left or right border of the image holds reflected columns.  Four
 	// neighbouring columns reflect to at most four neighbouring columns, so they lie in two aligned words:
-	// the lane requests those (aligned images) and permutes them into place when the row is used, so
-	// that its loads wait in the queue like everybody's.  Unaligned images: gathered byte by byte.
-	struct Row { unsigned w[NW], x[NW]; };
-	int rc[ALIGNED ? 1 : PX];
-	unsigned boff[ALIGNED ? NW : 1], bsel[ALIGNED ? NW : 1];
-	if (ALIGNED) {
+	// the lane requests those and permutes them into place when the row is used, so that its loads
+	// wait in the queue like everybody's.  Unaligned images (strips: a row starts wherever the previous
+	// one ended) do the same in every lane: two aligned words and a selector that depends on the row.
+	struct Row { unsigned w[NW], x[NW], sel; };
+	unsigned boff[NW], bsel[NW];  // lowest column (aligned images: rounded down to a word) and byte selectors
+	unsigned umax = 3;            // unaligned: the largest selector nibble before the row's shift
 #pragma unroll
-		for (int q = 0; q < NW; ++q) {
-			boff[q] = 0;
-			bsel[q] = 0x3210u;
-			if (!inside) {
-				int col[4], lo = 0x7fffffff, hi = 0;
+	for (int q = 0; q < NW; ++q) {
+		boff[q] = inside ? (unsigned)(cx + 4 * q) : 0u;
+		bsel[q] = 0x3210u;
+		if (!inside) {
+			int col[4], lo = 0x7fffffff, hi = 0;
 #pragma unroll
-				for (int b = 0; b < 4; ++b) {
-					col[b] = ws_reflect(cx + 4 * q + b, w);
-					lo = min(lo, col[b]);
-					hi = max(hi, col[b]);
-				}
-				boff[q] = (unsigned)lo & ~3u;
-				bsel[q] = (unsigned)(col[0] - (int)boff[q]) | (unsigned)(col[1] - (int)boff[q]) << 4 |
-					(unsigned)(col[2] - (int)boff[q]) << 8 | (unsigned)(col[3] - (int)boff[q]) << 12 |
-					(hi >= (int)boff[q] + 4 ? 0x10000u : 0u);  // bit 16: the second word is needed (and holds a column of the image)
+			for (int b = 0; b < 4; ++b) {
+				col[b] = ws_reflect(cx + 4 * q + b, w);
+				lo = min(lo, col[b]);
+				hi = max(hi, col[b]);
 			}
+			boff[q] = ALIGNED ? ((unsigned)lo & ~3u) : (unsigned)lo;
+			bsel[q] = (unsigned)(col[0] - (int)boff[q]) | (unsigned)(col[1] - (int)boff[q]) << 4 |
+				(unsigned)(col[2] - (int)boff[q]) << 8 | (unsigned)(col[3] - (int)boff[q]) << 12 |
+				(hi >= (int)boff[q] + 4 ? 0x10000u : 0u);  // bit 16: the second word is needed (and holds a column of the image)
+			if (!ALIGNED) umax = (unsigned)(hi - lo);
 		}
-	} else {
-#pragma unroll
-		for (int b = 0; b < PX; ++b) rc[b] = inside ? 0 : ws_reflect(cx + b, w);
 	}
 	auto load_row = [&](int r) -> Row {
 		const int ry = (unsigned)r < (unsigned)h ? r : ws_reflect(r, h);
-		const uint8_t *row = img_lane + (uint64_t)(unsigned)ry * pitch;
 		Row v;
+		v.sel = 0;
+		if (!ALIGNED) {
+			const uintptr_t a = reinterpret_cast<uintptr_t>(img + (uint64_t)(unsigned)ry * pitch + boff[0]);
+			const unsigned *wp = reinterpret_cast<const unsigned *>(a & ~(uintptr_t)3);
+			const unsigned sh = (unsigned)(a & 3);
+			v.w[0] = __ldg(wp);
+			v.x[0] = sh + umax >= 4 ? __ldg(wp + 1) : 0u;  // an aligned word that holds a byte of the image stays inside its page
+			v.sel = (bsel[0] & 0xFFFFu) + sh * 0x1111u;
+			return v;
+		}
+		const uint8_t *row = img_lane + (uint64_t)(unsigned)ry * pitch;
 		if (inside) {
-			if (ALIGNED && PX == 8) {
+			if (PX == 8) {
 				const uint2 t = __ldg(reinterpret_cast<const uint2 *>(row));
 				v.w[0] = t.x;
 				v.w[NW - 1] = t.y;
-			} else if (ALIGNED) {
-				v.w[0] = __ldg(reinterpret_cast<const unsigned *>(row));
 			} else {
-				const uintptr_t a = reinterpret_cast<uintptr_t>(row);
-				const unsigned *wp = reinterpret_cast<const unsigned *>(a & ~(uintptr_t)3);
-				const unsigned sh = (unsigned)(a & 3) * 8;
-				const unsigned lo = __ldg(wp);
-				const unsigned hi = sh ? __ldg(wp + 1) : 0u;  // an aligned word that holds a byte of the image stays inside its page
-				v.w[0] = __funnelshift_r(lo, hi, sh);
-			}
-		} else if (ALIGNED) {
-#pragma unroll
-			for (int q = 0; q < NW; ++q) {
-				const unsigned *wp = reinterpret_cast<const unsigned *>(row + boff[ALIGNED ? q : 0]);
-				v.w[q] = __ldg(wp);
-				v.x[q] = (bsel[ALIGNED ? q : 0] & 0x10000u) ? __ldg(wp + 1) : 0u;
+				v.w[0] = __ldg(reinterpret_cast<const unsigned *>(row));
 			}
 		} else {
 #pragma unroll
 			for (int q = 0; q < NW; ++q) {
-				const unsigned b0 = __ldg(row + rc[ALIGNED ? 0 : 4 * q]), b1 = __ldg(row + rc[ALIGNED ? 0 : 4 * q + 1]);
-				const unsigned b2 = __ldg(row + rc[ALIGNED ? 0 : 4 * q + 2]), b3 = __ldg(row + rc[ALIGNED ? 0 : 4 * q + 3]);
-				v.w[q] = __byte_perm(b0 | (b1 << 8), b2 | (b3 << 8), 0x5410);
+				const unsigned *wp = reinterpret_cast<const unsigned *>(row + boff[q]);
+				v.w[q] = __ldg(wp);
+				v.x[q] = (bsel[q] & 0x10000u) ? __ldg(wp + 1) : 0u;
 			}
 		}
 		return v;
@@ -243,9 +236,11 @@ __device__ __forceinline__ void ws_stripe(const uint8_t *__restrict__ img, int h
 	for (int j = 0; j < PX; ++j) v1[j] = v2[j] = 0;
 	int slot = 0, wslot = 0;  // ring slots of row r (sums: WIN slots, pixels: RAD + 1 slots)
 	auto body = [&](int r, Row cur, bool screen) {
-		if (ALIGNED && !inside) {
+		if (!ALIGNED) {
+			cur.w[0] = __byte_perm(cur.w[0], cur.x[0], cur.sel);
+		} else if (!inside) {
 #pragma unroll
-			for (int q = 0; q < NW; ++q) cur.w[q] = __byte_perm(cur.w[q], cur.x[q], bsel[ALIGNED ? q : 0] & 0xFFFFu);
+			for (int q = 0; q < NW; ++q) cur.w[q] = __byte_perm(cur.w[q], cur.x[q], bsel[q] & 0xFFFFu);
 		}
 		// the row entering the window replaces the row that left it WIN rows ago in the ring
 		uint4 old[NW];
@@ -387,18 +382,31 @@ __global__ void __launch_bounds__(WARPS * 32) og_sauvola_warp_page_kernel(
 }
 
 // strips: item = a 64-column chunk of the line plan; chunk q of a line works on stripe q when the
-// line has that many stripes (a strip of w columns has ceil(w / 64) chunks >= ceil(w / 112) stripes)
+// line has that many stripes (a strip of w columns has ceil(w / 64) chunks >= ceil(w / 112) stripes).
+// Items are handed out through the plan's work-ticket word (as in og_strips_screened_kernel): strips
+// are short runs of unequal width, and a static deal leaves most warps idle behind the slowest
+// (13 % of the warp slots busy, measured).  Every warp draws exactly one ticket past the end; the
+// warp that draws the very last one puts the word back to zero.
 template <int RAD>
 __global__ void __launch_bounds__(WS_WARPS * 32) og_sauvola_warp_strips_kernel(
 	const uint8_t *__restrict__ gray, const int32_t *__restrict__ steps, const int64_t *__restrict__ pix_offsets,
-	const int32_t *__restrict__ chunk_offsets, int n, uint8_t *__restrict__ out, int64_t capacity, const WsConst c) {
+	const int32_t *__restrict__ chunk_offsets, int n, uint8_t *__restrict__ out, int64_t capacity, const WsConst c,
+	int *__restrict__ ticket) {
 	extern __shared__ __align__(16) unsigned char smem_raw[];
 	uint4 *ring_h;
 	unsigned *ring_w;
 	ws_rings<RAD, 4, WS_WARPS>(smem_raw, ring_h, ring_w);
 	const int total = __ldg(chunk_offsets + n);
 	const int nwarps = gridDim.x * WS_WARPS;
-	for (int item = blockIdx.x * WS_WARPS + (threadIdx.x >> 5); item < total; item += nwarps) {
+	const int lane = threadIdx.x & 31;
+	auto draw = [&]() {
+		int t = 0;
+		if (lane == 0) t = atomicAdd(ticket, 1);
+		return __shfl_sync(0xffffffffu, t, 0);
+	};
+	int item = draw();
+	while (item < total) {
+		const int next = draw();  // the atomic's latency hides behind the item
 		int lo = 0, hi = n;
 		while (hi - lo > 1) {
 			const int mid = (lo + hi) >> 1;
@@ -406,13 +414,15 @@ __global__ void __launch_bounds__(WS_WARPS * 32) og_sauvola_warp_strips_kernel(
 		}
 		const int q = item - __ldg(chunk_offsets + lo);
 		const int w = __ldg(steps + 2 * lo), h = __ldg(steps + 2 * lo + 1);
-		if (q * WsGeom<4>::OUT >= w || h <= 0) continue;
 		const int64_t off = __ldg(pix_offsets + lo);
-		if (off + (int64_t)w * h > capacity) continue;
-		__syncwarp();
-		ws_stripe<RAD, 4, false>(gray + off, h, w, (unsigned)w, out + off, (unsigned)w, q * WsGeom<4>::OUT, 0, h, c, ring_h, ring_w);
-		__syncwarp();
+		if (q * WsGeom<4>::OUT < w && h > 0 && off + (int64_t)w * h <= capacity) {
+			__syncwarp();
+			ws_stripe<RAD, 4, false>(gray + off, h, w, (unsigned)w, out + off, (unsigned)w, q * WsGeom<4>::OUT, 0, h, c, ring_h, ring_w);
+			__syncwarp();
+		}
+		item = next;
 	}
+	if (lane == 0 && item == total + nwarps - 1) *ticket = 0;
 }
 
 WsConst ws_const(int window, double k, double r) {
@@ -474,8 +484,11 @@ int ws_launch_strips(const uint8_t *gray, const int32_t *steps, const int64_t *p
 	constexpr size_t smem = WS_WARPS * ws_warp_smem<RAD, 4>();
 	if (og_first_use(48 + RAD))
 		cudaFuncSetAttribute(og_sauvola_warp_strips_kernel<RAD>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-	og_sauvola_warp_strips_kernel<RAD><<<og_num_sms() * 5, WS_WARPS * 32, smem, st>>>(gray, steps, pix_offsets, chunk_offsets, n, out, capacity,
-		ws_const(2 * RAD + 1, 0.2, 127.5));
+	// the word behind the prefix sums is the plan's work ticket (zero between calls, see og_line_steps)
+	int *ticket = const_cast<int *>(chunk_offsets) + n + 1;
+	const int fit = (int)((size_t)220 * 1024 / (smem + 1024));
+	og_sauvola_warp_strips_kernel<RAD><<<og_num_sms() * fit, WS_WARPS * 32, smem, st>>>(gray, steps, pix_offsets, chunk_offsets, n, out, capacity,
+		ws_const(2 * RAD + 1, 0.2, 127.5), ticket);
 	return og_check_launch("og_sauvola_warp_strips_kernel");
 }
 
