@@ -643,7 +643,7 @@ int og_binarize_strips_impl(const uint8_t *gray, const int32_t *steps, const int
 	int rc = check_window(window);
 	if (rc) return rc;
 	OG_REQUIRE(gray != out, OG_E_ARG, "Sauvola cannot run in place");
-	// windows <= 15: the warp kernel with ticketed items (316 us per page of strips against 363 us for the
+	// windows <= 15: the warp kernel with ticketed items (289 us per page of strips against 363 us for the
 	// column-streaming kernel below, which stays for larger windows and as OG_SAUVOLA_LEGACY)
 	if (window <= 15 && getenv("OG_SAUVOLA_LEGACY") == nullptr)
 		return og_launch_sauvola_warp_strips(gray, steps, pix_offsets, chunk_offsets, n, window, out, capacity, st);

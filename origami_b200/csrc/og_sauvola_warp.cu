@@ -35,6 +35,9 @@ constexpr int WS_WARPS = 4;  // warps per CTA (independent of each other)
 #ifndef OG_WS_AHEAD
 #define OG_WS_AHEAD 1
 #endif
+#ifndef OG_WS_AHEAD_STRIPS
+#define OG_WS_AHEAD_STRIPS 2
+#endif
 constexpr int WS_AHEAD = OG_WS_AHEAD;  // rows requested ahead of use
 
 template <int PX>
@@ -153,7 +156,7 @@ __device__ __noinline__ unsigned ws_settle(unsigned res, unsigned cw, uint4 s1, 
 
 // One stripe: output columns x0 .. x0 + OUT - 1, output rows y0 .. y1 - 1 of an (h, w) image
 // (pitch and out_pitch below 2^31).  ring_h: WIN x NW x 32 uint4, ring_w: (RAD + 1) x NW x 32 words.
-template <int RAD, int PX, bool ALIGNED>
+template <int RAD, int PX, bool ALIGNED, int AHEAD = WS_AHEAD>
 __device__ __forceinline__ void ws_stripe(const uint8_t *__restrict__ img, int h, int w, unsigned pitch,
 	uint8_t *__restrict__ out, unsigned out_pitch, int x0, int y0, int y1, const WsConst c,
 	uint4 *__restrict__ ring_h, unsigned *__restrict__ ring_w) {
@@ -328,24 +331,24 @@ __device__ __forceinline__ void ws_stripe(const uint8_t *__restrict__ img, int h
 	// queue lives in fixed registers.  Rows past the end are harmless reflections whose outputs are
 	// not stored; the first rows of a run only fill the window.
 	const int r0 = y0 - RAD, r_end = y1 + RAD;
-	constexpr int WARM = (2 * RAD) / WS_AHEAD * WS_AHEAD;
-	Row ahead[WS_AHEAD];
+	constexpr int WARM = (2 * RAD) / AHEAD * AHEAD;
+	Row ahead[AHEAD];
 #pragma unroll
-	for (int i = 0; i < WS_AHEAD; ++i) ahead[i] = load_row(r0 + i);
+	for (int i = 0; i < AHEAD; ++i) ahead[i] = load_row(r0 + i);
 	int r = r0;
-	for (; r < r0 + WARM; r += WS_AHEAD) {
+	for (; r < r0 + WARM; r += AHEAD) {
 #pragma unroll
-		for (int u = 0; u < WS_AHEAD; ++u) {
+		for (int u = 0; u < AHEAD; ++u) {
 			const Row cur = ahead[u];
-			ahead[u] = load_row(r + u + WS_AHEAD);
+			ahead[u] = load_row(r + u + AHEAD);
 			body(r + u, cur, false);
 		}
 	}
-	for (; r < r_end; r += WS_AHEAD) {
+	for (; r < r_end; r += AHEAD) {
 #pragma unroll
-		for (int u = 0; u < WS_AHEAD; ++u) {
+		for (int u = 0; u < AHEAD; ++u) {
 			const Row cur = ahead[u];
-			ahead[u] = load_row(r + u + WS_AHEAD);
+			ahead[u] = load_row(r + u + AHEAD);
 			body(r + u, cur, true);
 		}
 	}
@@ -417,7 +420,7 @@ __global__ void __launch_bounds__(WS_WARPS * 32) og_sauvola_warp_strips_kernel(
 		const int64_t off = __ldg(pix_offsets + lo);
 		if (q * WsGeom<4>::OUT < w && h > 0 && off + (int64_t)w * h <= capacity) {
 			__syncwarp();
-			ws_stripe<RAD, 4, false>(gray + off, h, w, (unsigned)w, out + off, (unsigned)w, q * WsGeom<4>::OUT, 0, h, c, ring_h, ring_w);
+			ws_stripe<RAD, 4, false, OG_WS_AHEAD_STRIPS>(gray + off, h, w, (unsigned)w, out + off, (unsigned)w, q * WsGeom<4>::OUT, 0, h, c, ring_h, ring_w);
 			__syncwarp();
 		}
 		item = next;
