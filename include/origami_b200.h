@@ -319,6 +319,16 @@ int og_or_dilate3(const uint8_t *bin, int64_t bin_pitch, const uint8_t *mask, in
 int og_column_psd_quantile(const void *pixels, int is_u8, int h, int w, int64_t pitch_bytes,
 	double quantile, float *out, void *stream);
 
+/* (f)3  the same statistic for ALL regions of a page in one launch -- FixSpillOverH / FixSpillOverV,
+ * origami/batch/detect/layout.py:947-1075, call the detector once per contour on crop(regions.binarized,
+ * contour) (:886-894) resp. its transpose.  pixels: the (H, W) page image (uint8 or float32) on the device;
+ * regions: DEVICE array of m records (x0, y0, w, h, transposed) int32, each rectangle inside the image;
+ * a record yields w series of h samples (its columns) or, transposed, h series of w samples (its rows);
+ * offsets: DEVICE array of m + 1 int32 prefix sums of the series counts, total = offsets[m], max_len = the
+ * longest series (<= 8192).  out: total float32, region r's values at offsets[r]. */
+int og_region_psd_quantile(const void *pixels, int is_u8, int H, int W, int64_t pitch_bytes,
+	const int32_t *regions, const int32_t *offsets, int m, int total, int max_len, double quantile, float *out, void *stream);
+
 /* A11  polygon mask / cut-out -- origami/core/mask.py:8-74 (Mask.__init__: cairo fill of the polygon,
  * `R > 0`; Mask._extract: pixels outside the mask become `background`), used by
  * Line._extract_deskewed (origami/core/block.py:174-186), Line.masked_image (:143-153) and

@@ -79,6 +79,7 @@ _SIGNATURES = {
 	"og_label_mask_ne": [c_void_p, c_int, c_int, c_int64, c_int, c_void_p, c_int64, c_void_p],
 	"og_or_dilate3": [c_void_p, c_int64, c_void_p, c_int64, c_int, c_int, c_void_p, c_void_p],
 	"og_column_psd_quantile": [c_void_p, c_int, c_int, c_int, c_int64, c_double, c_void_p, c_void_p],
+	"og_region_psd_quantile": [c_void_p, c_int, c_int, c_int, c_int64, c_void_p, c_void_p, c_int, c_int, c_int, c_double, c_void_p, c_void_p],
 	"og_polygon_mask": [c_void_p, c_int, c_int, c_int, c_void_p, c_int64, c_void_p, c_int64, c_int, c_void_p],
 	"og_warp_affine": [c_void_p, c_int, c_int, c_int64, c_void_p, c_void_p, c_int, c_int, c_int64, c_int, c_void_p],
 }

@@ -79,6 +79,38 @@ class SplitDetector:
 			t = torch.from_numpy(np.ascontiguousarray(pixels)).to(device or "cuda")
 		return ops.column_psd_quantile(t, self._quantile).cpu().numpy()
 
+	def _peaks(self, column_quantiles, scale):
+		import scipy.ndimage
+		import scipy.signal
+		ink_h = scipy.ndimage.convolve(column_quantiles, kernel(int(self._smooth * scale)), mode="nearest")
+		span = int(self._border * len(ink_h))
+		ink_h[:span] = 0
+		ink_h[-span:] = 0
+		return scipy.signal.find_peaks(-ink_h, height=-self._intensity, distance=int(self._width * scale))
+
+	def detect_regions(self, binarized, bounds, scales, transposed=False):
+		"""The detector on the crops of all contours of a page at once (what FixSpillOverH / FixSpillOverV,
+		layout.py:947-1075, do one contour at a time): binarized is Regions.binarized as a CUDA tensor (or a
+		NumPy array, uploaded once), bounds a list of contour bounds (minx, miny, maxx, maxy), scales the
+		line height per contour; transposed=True is FixSpillOverV's crop.transpose().  One kernel launch
+		for all periodograms; returns [(peaks, info, (minx, miny))] like crop() + __call__."""
+		import torch
+		if not isinstance(binarized, torch.Tensor):
+			binarized = torch.from_numpy(np.ascontiguousarray(binarized)).to("cuda")
+		H, W = int(binarized.shape[0]), int(binarized.shape[1])
+		boxes = []
+		for minx, miny, maxx, maxy in bounds:  # crop(): layout.py:886-894
+			y0, x0 = int(max(0, miny)), int(max(0, minx))
+			y1, x1 = int(min(maxy, H)), int(min(maxx, W))
+			boxes.append((x0, y0, max(x1, x0), max(y1, y0)))
+		cols = ops.region_psd_quantile(binarized, boxes, transposed=transposed, quantile=self._quantile)
+		scales = np.broadcast_to(np.asarray(scales, dtype=np.float64), (len(boxes),))
+		res = []
+		for box, cq, scale in zip(boxes, cols, scales):
+			peaks, info = self._peaks(np.array(cq), scale) if len(cq) else (np.zeros(0, np.int64), {"peak_heights": np.zeros(0)})
+			res.append((peaks, info, (box[0], box[1])))
+		return res
+
 	def __call__(self, pixels, scale, device=None):
 		import scipy.ndimage
 		import scipy.signal

@@ -299,23 +299,23 @@ extern "C" int og_polygon_mask(const double *verts_xy, int k, int w, int h,
 // ---------------------------------------------------------------------------------------
 namespace {
 
-__global__ void __launch_bounds__(256) og_column_psd_quantile_kernel(const void *__restrict__ pixels, int is_u8, int64_t pitch_elems,
-	int h, int w, double q, float *__restrict__ out, int nsort) {
-	extern __shared__ __align__(16) unsigned char smem_raw[];
+// One series of h samples (element j at pixels[first + j * stride]) -> *out; the CTA's dynamic shared
+// memory holds h roots of unity, h samples and nsort (power of two >= h / 2 + 1) densities.
+__device__ __forceinline__ void psd_quantile_series(const void *__restrict__ pixels, int is_u8, int64_t first, int64_t stride,
+	int h, double q, float *__restrict__ out, int nsort, unsigned char *smem_raw) {
 	double2 *tw = reinterpret_cast<double2 *>(smem_raw);                   // h roots of unity
 	float *col = reinterpret_cast<float *>(smem_raw + (size_t)h * 16);     // h samples
 	float *dens = col + h;                                                  // nsort (power of two) densities
 	__shared__ double s_part[8];
 	__shared__ double s_mean;
-	const int x = blockIdx.x;
 	const int nf = h / 2 + 1;
 	for (int j = threadIdx.x; j < h; j += blockDim.x) {
 		double sn, cs;
 		sincospi(-2.0 * (double)j / (double)h, &sn, &cs);
 		tw[j] = make_double2(cs, sn);
 		float v;
-		if (is_u8) v = __fdiv_rn((float)reinterpret_cast<const uint8_t *>(pixels)[(int64_t)j * pitch_elems + x], 255.0f);  // pixels.astype(float32) / 255.0
-		else v = reinterpret_cast<const float *>(pixels)[(int64_t)j * pitch_elems + x];
+		if (is_u8) v = __fdiv_rn((float)reinterpret_cast<const uint8_t *>(pixels)[first + (int64_t)j * stride], 255.0f);  // pixels.astype(float32) / 255.0
+		else v = reinterpret_cast<const float *>(pixels)[first + (int64_t)j * stride];
 		col[j] = v;
 	}
 	__syncthreads();
@@ -385,8 +385,37 @@ __global__ void __launch_bounds__(256) og_column_psd_quantile_kernel(const void 
 		float r = __fadd_rn(a, __fmul_rn(diff, t));
 		if (t >= 0.5f) r = __fsub_rn(b, __fmul_rn(diff, __fsub_rn(1.f, t)));
 		if (t == 1.f || !(diff == diff)) r = b;
-		out[x] = r;
+		*out = r;
 	}
+}
+
+__global__ void __launch_bounds__(256) og_column_psd_quantile_kernel(const void *__restrict__ pixels, int is_u8, int64_t pitch_elems,
+	int h, int w, double q, float *__restrict__ out, int nsort) {
+	extern __shared__ __align__(16) unsigned char smem_raw[];
+	psd_quantile_series(pixels, is_u8, blockIdx.x, pitch_elems, h, q, out + blockIdx.x, nsort, smem_raw);
+}
+
+// All regions of a page in one launch: CTA b works on series b - offsets[r] of region r (offsets = prefix
+// sums of the regions' series counts).  A region is (x0, y0, w, h, transposed): h samples down each of
+// its w columns, or -- transposed, FixSpillOverV's crop.transpose() -- w samples along each of its h rows.
+__global__ void __launch_bounds__(256) og_region_psd_quantile_kernel(const void *__restrict__ pixels, int is_u8, int64_t pitch_elems,
+	const int32_t *__restrict__ regions, const int32_t *__restrict__ offsets, int m, double q, float *__restrict__ out) {
+	extern __shared__ __align__(16) unsigned char smem_raw[];
+	const int b = blockIdx.x;
+	int lo = 0, hi = m;
+	while (hi - lo > 1) {
+		const int mid = (lo + hi) >> 1;
+		if (__ldg(offsets + mid) <= b) lo = mid; else hi = mid;
+	}
+	const int c = b - __ldg(offsets + lo);
+	const int x0 = regions[5 * lo], y0 = regions[5 * lo + 1], w = regions[5 * lo + 2], h = regions[5 * lo + 3];
+	const bool tr = regions[5 * lo + 4] != 0;
+	const int len = tr ? w : h;
+	if (c >= (tr ? h : w) || len < 1) return;
+	int nsort = 1;
+	while (nsort < len / 2 + 1) nsort <<= 1;
+	const int64_t first = tr ? (int64_t)(y0 + c) * pitch_elems + x0 : (int64_t)y0 * pitch_elems + x0 + c;
+	psd_quantile_series(pixels, is_u8, first, tr ? (int64_t)1 : pitch_elems, len, q, out + b, nsort, smem_raw);
 }
 
 }  // namespace
@@ -406,4 +435,23 @@ extern "C" int og_column_psd_quantile(const void *pixels, int is_u8, int h, int 
 	if (e != cudaSuccess) return og_set_error((int)e, "cudaFuncSetAttribute: %s", cudaGetErrorString(e));
 	og_column_psd_quantile_kernel<<<w, 256, smem, (cudaStream_t)stream>>>(pixels, is_u8, pitch_bytes / elem, h, w, quantile, out, nsort);
 	return og_check_launch("og_column_psd_quantile_kernel");
+}
+
+extern "C" int og_region_psd_quantile(const void *pixels, int is_u8, int H, int W, int64_t pitch_bytes,
+	const int32_t *regions, const int32_t *offsets, int m, int total, int max_len, double quantile, float *out, void *stream) {
+	OG_REQUIRE(m >= 0 && total >= 0, OG_E_ARG, "m or total < 0");
+	if (m == 0 || total == 0) return OG_OK;
+	OG_REQUIRE(pixels != nullptr && out != nullptr && regions != nullptr && offsets != nullptr, OG_E_ARG, "NULL pointer");
+	OG_REQUIRE(H >= 1 && W >= 1, OG_E_ARG, "image %d x %d invalid", W, H);
+	OG_REQUIRE(max_len >= 1 && max_len <= 8192, OG_E_RANGE, "series of %d samples exceed the 8192-sample limit of the shared-memory DFT", max_len);
+	OG_REQUIRE(quantile >= 0.0 && quantile <= 1.0, OG_E_ARG, "quantile %g outside [0, 1]", quantile);
+	const int elem = is_u8 ? 1 : 4;
+	OG_REQUIRE(pitch_bytes >= (int64_t)W * elem && pitch_bytes % elem == 0, OG_E_ARG, "pitch invalid");
+	int nsort = 1;
+	while (nsort < max_len / 2 + 1) nsort <<= 1;
+	const size_t smem = (size_t)max_len * 16 + (size_t)max_len * 4 + (size_t)nsort * 4;
+	cudaError_t e = cudaFuncSetAttribute(og_region_psd_quantile_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024 - 1024);
+	if (e != cudaSuccess) return og_set_error((int)e, "cudaFuncSetAttribute: %s", cudaGetErrorString(e));
+	og_region_psd_quantile_kernel<<<total, 256, smem, (cudaStream_t)stream>>>(pixels, is_u8, pitch_bytes / elem, regions, offsets, m, quantile, out);
+	return og_check_launch("og_region_psd_quantile_kernel");
 }

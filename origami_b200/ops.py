@@ -510,6 +510,42 @@ def column_psd_quantile(pixels, quantile=0.9):
 	return out
 
 
+def region_psd_quantile(pixels, boxes, transposed=False, quantile=0.9):
+	"""column_psd_quantile for many rectangles of one device image in one launch: boxes (m, 4) int
+	(x0, y0, x1, y1), already clipped to the image; transposed: a flag or one flag per box -- the series
+	run along the rows of the box (crop.transpose() in the reference).  Returns a list of m float32
+	NumPy arrays (one value per column of the box, or per row when transposed)."""
+	_require_cuda()
+	if pixels.dim() != 2 or not pixels.is_cuda or pixels.stride(1) != 1 or pixels.dtype not in (torch.uint8, torch.float32):
+		raise ValueError("pixels must be a 2-D uint8 or float32 CUDA tensor with unit column stride")
+	H, W = int(pixels.shape[0]), int(pixels.shape[1])
+	boxes = np.asarray(boxes, dtype=np.int64).reshape(-1, 4)
+	m = boxes.shape[0]
+	if m == 0:
+		return []
+	tr = np.broadcast_to(np.asarray(transposed, dtype=bool), (m,))
+	w, h = boxes[:, 2] - boxes[:, 0], boxes[:, 3] - boxes[:, 1]
+	if (boxes[:, 0] < 0).any() or (boxes[:, 1] < 0).any() or (boxes[:, 2] > W).any() or (boxes[:, 3] > H).any() or (w < 0).any() or (h < 0).any():
+		raise ValueError("boxes must lie inside the image")
+	count = np.where((w > 0) & (h > 0), np.where(tr, h, w), 0)
+	length = np.where(tr, w, h)
+	offs = np.concatenate([[0], np.cumsum(count)]).astype(np.int64)
+	total = int(offs[-1])
+	if total == 0:
+		return [np.zeros(0, np.float32) for _ in range(m)]
+	if total >= 2 ** 31:
+		raise ValueError("too many series")
+	max_len = int(length[count > 0].max())
+	rec = np.stack([boxes[:, 0], boxes[:, 1], w, h, tr.astype(np.int64)], axis=1).astype(np.int32)
+	meta = torch.from_numpy(np.concatenate([rec.reshape(-1), offs.astype(np.int32)])).to(pixels.device)
+	out = torch.empty((total,), dtype=torch.float32, device=pixels.device)
+	_call("og_region_psd_quantile", pixels, ([meta], lambda st: (pixels.data_ptr(), 1 if pixels.dtype == torch.uint8 else 0, H, W,
+		pixels.stride(0) * pixels.element_size(), meta.data_ptr(), meta.data_ptr() + 4 * 5 * m, m, total, max_len, float(quantile),
+		out.data_ptr(), st)))
+	flat = out.cpu().numpy()
+	return [flat[offs[i]:offs[i + 1]] for i in range(m)]
+
+
 def polygon_mask(verts_xy, w, h, device=None, image=None, background=255):
 	"""Mask.__init__ / Mask._extract (reference origami/core/mask.py:8-74): verts_xy (k, 2) ring relative
 	to the mask origin.  Returns the (h, w) uint8 mask (255 inside); with `image` (a device image of

@@ -8,7 +8,7 @@ import numpy as np
 import pytest
 
 from oracle import exact
-from origami_b200 import synth
+from origami_b200 import ops, synth
 from origami_b200.batch.detect import dewarp as bdewarp
 from origami_b200.core.block import Block, Line, Stage
 from origami_b200.core.dewarp import Grid
@@ -158,6 +158,36 @@ def test_split_detector_matches_scipy(cuda, shape, dtype):
 	if h > 16:
 		gp, gi = det(px, 20, cuda)
 		assert np.array_equal(gp, peaks) and np.allclose(gi["peak_heights"], info["peak_heights"], rtol=1e-3, atol=1e-6)
+
+
+@pytest.mark.parametrize("transposed", [False, True])
+def test_split_detector_on_all_regions_of_a_page(cuda, transposed):
+	"""FixSpillOverH / FixSpillOverV (layout.py:947-1075) run the detector contour by contour on
+	crop(regions.binarized, contour) (resp. its transpose); here all crops of the page go through one launch
+	and must give what the per-crop path and the SciPy oracle give."""
+	import torch
+	from origami_b200.batch.detect.layout import SplitDetector, crop
+	page = synth.make_page(900, 700, seed=3, kind="text", dpi=300)
+	binar = (exact.binarize(page, ("otsu",)) > 0).astype(np.float32)
+	bounds = [(20.5, 10.2, 420.5, 311.2), (-5.0, 300.0, 250.0, 690.0), (400.0, 350.0, 905.0, 705.0), (600.0, 20.0, 640.0, 60.0),
+		(100.0, 100.0, 100.0, 300.0), (10.0, 500.0, 890.0, 540.0)]
+	scales = [20, 18, 25, 6, 20, 12]
+	det = SplitDetector()
+	got = det.detect_regions(torch.from_numpy(binar).to(cuda), bounds, scales, transposed=transposed)
+	assert len(got) == len(bounds)
+	for (peaks, info, origin), b, sc in zip(got, bounds, scales):
+		px, org = crop(binar, b)
+		assert origin == org
+		if px.size == 0:
+			assert len(peaks) == 0
+			continue
+		px = np.ascontiguousarray(px.transpose() if transposed else px)
+		want_p, want_i, colq = exact.split_detector(px, scale=sc)
+		assert np.array_equal(peaks, want_p) and np.allclose(info["peak_heights"], want_i["peak_heights"], rtol=1e-3, atol=1e-6)
+		one = det.column_quantiles(px, cuda)
+		assert np.allclose(one, colq, rtol=2e-4, atol=1e-6 * max(float(colq.max()), 1e-12))
+	with pytest.raises(ValueError):
+		ops.region_psd_quantile(torch.from_numpy(binar).to(cuda), [(0, 0, 901, 10)])
 
 
 def _flow_samples(W, H, n, seed):
