@@ -19,10 +19,11 @@ def sauvola_window(median_line_height):
 	return max(window_size, 3)
 
 
-def regions_binarized(page, median_line_height, separator_labels=()):
+def regions_binarized(page, median_line_height, separator_labels=(), on_device=False):
 	"""page: origami_b200.core.page.Page built with a Grid; separator_labels: iterable of
 	(labels uint8 ndarray, background label value) for every SEPARATOR prediction.
-	Returns the float32 (Hd, Wd) array of Regions.binarized."""
+	Returns the float32 (Hd, Wd) array of Regions.binarized; on_device=True leaves it on the GPU as a
+	CUDA tensor (what SplitDetector.detect_regions takes, so the page-sized image never travels)."""
 	dewarper = page.dewarper
 	gray = dewarper.device_dewarped()
 	binary = ops.sauvola(gray, sauvola_window(median_line_height))
@@ -38,7 +39,8 @@ def regions_binarized(page, median_line_height, separator_labels=()):
 		# several separator predictions: OR them before the single dilation (dilation distributes over OR)
 		mask_total = dmask if mask_total is None else (mask_total | dmask)
 	assert mask_total is None or tuple(mask_total.shape) == (hd, wd)
-	return ops.to_host(ops.or_dilate3(binary, mask_total))
+	out = ops.or_dilate3(binary, mask_total)
+	return out if on_device else ops.to_host(out)
 
 
 def crop(pixels, bounds):
