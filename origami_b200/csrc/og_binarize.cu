@@ -674,8 +674,10 @@ extern "C" int og_sauvola(const uint8_t *src, int h, int w, int64_t src_pitch, i
 		// byte twice instead of once per overlapping halo tile, but its running sums serialise a CTA's rows
 		// (0.21 - 0.25 ms measured): it is what the strips use (0.52 -> 0.37 ms) and stays selectable here.
 		const size_t smem = sauvola_smem_bytes<ST_W>(window);
-		cudaError_t e = cudaFuncSetAttribute(og_sauvola_page_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-		if (e != cudaSuccess) return og_set_error((int)e, "cudaFuncSetAttribute: %s", cudaGetErrorString(e));
+		if (og_first_use(56)) {  // once per device: the largest window's footprint
+			cudaError_t e = cudaFuncSetAttribute(og_sauvola_page_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sauvola_smem_bytes<ST_W>(MAX_WINDOW));
+			if (e != cudaSuccess) return og_set_error((int)e, "cudaFuncSetAttribute: %s", cudaGetErrorString(e));
+		}
 		const int64_t tiles = (int64_t)((w + ST_W - 1) / ST_W) * ((h + ST_H - 1) / ST_H);
 		const int blocks = (int)(tiles < (int64_t)og_num_sms() * 8 ? tiles : (int64_t)og_num_sms() * 8);
 		og_sauvola_page_kernel<<<blocks, BTHREADS, smem, (cudaStream_t)stream>>>(src, h, w, src_pitch, dst, dst_pitch, window, k, r);

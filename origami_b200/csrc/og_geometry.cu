@@ -431,8 +431,10 @@ extern "C" int og_column_psd_quantile(const void *pixels, int is_u8, int h, int 
 	int nsort = 1;
 	while (nsort < h / 2 + 1) nsort <<= 1;
 	const size_t smem = (size_t)h * 16 + (size_t)h * 4 + (size_t)nsort * 4;
-	cudaError_t e = cudaFuncSetAttribute(og_column_psd_quantile_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024 - 1024);
-	if (e != cudaSuccess) return og_set_error((int)e, "cudaFuncSetAttribute: %s", cudaGetErrorString(e));
+	if (og_first_use(57)) {
+		cudaError_t e = cudaFuncSetAttribute(og_column_psd_quantile_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024 - 1024);
+		if (e != cudaSuccess) return og_set_error((int)e, "cudaFuncSetAttribute: %s", cudaGetErrorString(e));
+	}
 	og_column_psd_quantile_kernel<<<w, 256, smem, (cudaStream_t)stream>>>(pixels, is_u8, pitch_bytes / elem, h, w, quantile, out, nsort);
 	return og_check_launch("og_column_psd_quantile_kernel");
 }
@@ -450,8 +452,10 @@ extern "C" int og_region_psd_quantile(const void *pixels, int is_u8, int H, int 
 	int nsort = 1;
 	while (nsort < max_len / 2 + 1) nsort <<= 1;
 	const size_t smem = (size_t)max_len * 16 + (size_t)max_len * 4 + (size_t)nsort * 4;
-	cudaError_t e = cudaFuncSetAttribute(og_region_psd_quantile_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024 - 1024);
-	if (e != cudaSuccess) return og_set_error((int)e, "cudaFuncSetAttribute: %s", cudaGetErrorString(e));
+	if (og_first_use(58)) {
+		cudaError_t e = cudaFuncSetAttribute(og_region_psd_quantile_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024 - 1024);
+		if (e != cudaSuccess) return og_set_error((int)e, "cudaFuncSetAttribute: %s", cudaGetErrorString(e));
+	}
 	og_region_psd_quantile_kernel<<<total, 256, smem, (cudaStream_t)stream>>>(pixels, is_u8, pitch_bytes / elem, regions, offsets, m, quantile, out);
 	return og_check_launch("og_region_psd_quantile_kernel");
 }

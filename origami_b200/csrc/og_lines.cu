@@ -1264,8 +1264,10 @@ int check_lines(const og_line *lines, int n, const int32_t *steps, const int32_t
 
 template <int MODE, bool BBOX>
 int launch_lines(const LineParams &p, cudaStream_t st) {
-	cudaError_t e = cudaFuncSetAttribute(og_lines_kernel<MODE, BBOX>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_BUDGET);
-	if (e != cudaSuccess) return og_set_error((int)e, "cudaFuncSetAttribute: %s", cudaGetErrorString(e));
+	if (og_first_use(40 + 2 * MODE + (BBOX ? 1 : 0))) {  // once per device and instantiation
+		cudaError_t e = cudaFuncSetAttribute(og_lines_kernel<MODE, BBOX>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_BUDGET);
+		if (e != cudaSuccess) return og_set_error((int)e, "cudaFuncSetAttribute: %s", cudaGetErrorString(e));
+	}
 	// persistent grid: two CTAs per SM fit the staging budget
 	og_lines_kernel<MODE, BBOX><<<og_num_sms() * 2, LTHREADS, SMEM_BUDGET, st>>>(p);
 	return og_check_launch("og_lines_kernel");
