@@ -228,6 +228,8 @@ def test_regions_binarized(small):
 	want = exact.regions_binarized(small.page, small.g, small.s, 31, [(labels, 0)])
 	assert got.dtype == np.float32 and np.array_equal(got, want)
 	assert np.array_equal(regions_binarized(small.pg, 20), exact.regions_binarized(small.page, small.g, small.s, 20))
+	dev = regions_binarized(small.pg, 31, [(labels, 0)], on_device=True)  # stays on the GPU for SplitDetector.detect_regions
+	assert dev.is_cuda and dev.dtype == torch.float32 and np.array_equal(dev.cpu().numpy(), want)
 
 
 @pytest.mark.parametrize("spec", ["", "otsu"])
