@@ -49,7 +49,7 @@ def parse_args():
 	ap.add_argument("--pages", type=int, default=256, help="page indices of the job (configs[2]); rank r takes r, r+N, ...")
 	ap.add_argument("--ref-sample", type=int, default=0,
 		help="reference arm: time only this many lines per step and scale the line time (prints extrapolated: true)")
-	ap.add_argument("--e2e-steps", type=int, default=6)
+	ap.add_argument("--e2e-steps", type=int, default=12)
 	ap.add_argument("--no-cpu-baseline", action="store_true")
 	ap.add_argument("--no-e2e", action="store_true")
 	return ap.parse_args()
