@@ -29,59 +29,42 @@ from .math import Geometry
 
 
 class Samples:
-	"""reference dewarp.py:34-105: scattered (point, angle) samples of one direction, flow.zip I/O."""
+	"""Scattered (point, angle) samples of one flow direction and their flow.zip encoding (reference
+	dewarp.py:34-105): NAME.npy holds float64 rows (x, y, angle) -- an empty set is written as a (3, 0)
+	array --, NAME.json the page size and a format version."""
 
 	def __init__(self, geometry):
-		self._points = []
-		self._values = []
 		self._geometry = geometry
+		self._points, self._values = [], []
 
 	def __len__(self):
 		return len(self._points)
 
 	@staticmethod
 	def open(zf, name):
-		info = json.loads(zf.read("%s.json" % name))
-		geometry = Geometry(*info["size"])
-		data = io.BytesIO(zf.read("%s.npy" % name))
-		array = np.load(data, allow_pickle=False)
-		samples = Samples(geometry)
-		if array.size > 0:
-			samples._points = list(array[:, :2])
-			samples._values = list(array[:, 2])
-		else:
-			samples._points = np.empty((2, 0))
-			samples._values = []
-		return samples
+		meta = json.loads(zf.read(name + ".json"))
+		table = np.load(io.BytesIO(zf.read(name + ".npy")), allow_pickle=False)
+		loaded = Samples(Geometry(*meta["size"]))
+		if table.size:
+			loaded.extend(table[:, :2], table[:, 2])
+		return loaded
 
 	def save(self, zf, name):
-		points = np.array(self._points)
-		values = np.array(self._values)
-		if points.size == 0:
-			array = np.empty((3, 0))
+		if len(self):
+			table = np.column_stack([np.asarray(self._points, dtype=np.float64).reshape(-1, 2), np.asarray(self._values, dtype=np.float64)])
 		else:
-			array = np.hstack([points, values[:, np.newaxis]])
-		data = io.BytesIO()
-		np.save(data, array.astype(np.float64), allow_pickle=False)
-		info = dict(version=1, size=self._geometry.size)
-		zf.writestr("%s.npy" % name, data.getvalue())
-		zf.writestr("%s.json" % name, json.dumps(info))
+			table = np.empty((3, 0), dtype=np.float64)
+		buf = io.BytesIO()
+		np.save(buf, table, allow_pickle=False)
+		zf.writestr(name + ".npy", buf.getvalue())
+		zf.writestr(name + ".json", json.dumps({"version": 1, "size": self._geometry.size}))
 
-	@property
-	def geometry(self):
-		return self._geometry
-
-	@property
-	def points(self):
-		return self._points
-
-	@property
-	def values(self):
-		return self._values
+	geometry = property(lambda self: self._geometry)
+	points = property(lambda self: self._points)
+	values = property(lambda self: self._values)
 
 	def append(self, point, value):
-		self._points.append(point)
-		self._values.append(value)
+		self.extend([point], [value])
 
 	def extend(self, points, values):
 		self._points.extend(points)
@@ -89,10 +72,8 @@ class Samples:
 
 	@property
 	def std(self):
-		if len(self._values) > 3:
-			return np.std(self._values)
-		else:
-			return 0
+		"""spread of the angles; 0 for fewer than four samples"""
+		return np.std(self._values) if len(self._values) > 3 else 0
 
 
 class Field:
@@ -165,9 +146,10 @@ class Field:
 
 
 def extrapolate(a, b, x):
-	v = b - a
-	v /= np.linalg.norm(v)
-	return b + x * v
+	"""the point x beyond b on the ray from a through b"""
+	d = np.subtract(b, a)
+	unit = d / np.linalg.norm(d)
+	return b + x * unit
 
 
 class GridFactory:
@@ -295,6 +277,6 @@ class GridFactory:
 
 
 def make_slices(n, k):
-	s = math.ceil(n / k)
-	for i in range(0, n, s):
-		yield slice(i, i + s)
+	"""range(n) cut into k runs of equal length (the last one shorter), as slices"""
+	run = -(-n // k)
+	return (slice(lo, lo + run) for lo in range(0, n, run))

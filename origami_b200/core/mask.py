@@ -61,19 +61,17 @@ class Mask:
 		return minx, miny, minx + w, miny + h
 
 	def _extract(self, bbox, pixels, background=255):
+		"""The part of the box that lies on the page, the pixels outside the polygon replaced by
+		`background` (None: left as they are); returns it with its top-left corner on the page."""
 		x, y, w, h = bbox
-		ph, pw = pixels.shape[:2]
-		tx = max(x, 0)
-		ty = max(y, 0)
-		sx = tx - x
-		sy = ty - y
-		tw = min(w - sx, pw - tx)
-		th = min(h - sy, ph - ty)
-		cutout = pixels[ty:ty + th, tx:tx + tw].copy()
-		assert cutout.shape[:2] == (th, tw)
+		rows, cols = pixels.shape[:2]
+		x0, y0 = max(x, 0), max(y, 0)
+		x1, y1 = min(x + w, cols), min(y + h, rows)
+		region = np.array(pixels[y0:y1, x0:x1])
 		if background is not None:
-			cutout[np.logical_not(self._mask[sy:sy + th, sx:sx + tw])] = background
-		return cutout, (tx, ty)
+			inside = self._mask[y0 - y:y1 - y, x0 - x:x1 - x]
+			region[~inside] = background
+		return region, (x0, y0)
 
 	def extract(self, pixels, background=255):
 		return self._extract(self._bbox, pixels, background)
