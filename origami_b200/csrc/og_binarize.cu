@@ -16,7 +16,6 @@ namespace {
 
 constexpr int BTHREADS = 256;
 constexpr int ST_W = 128;  // Sauvola output tile on pages: 32 rows x 128 columns
-constexpr int ST_WS = 64;  // ... on strips: one 64-column line chunk
 constexpr int ST_H = 32;
 constexpr int MAX_WINDOW = 127;
 
@@ -398,31 +397,6 @@ __global__ void __launch_bounds__(BTHREADS) og_sauvola_page_kernel(
 	for (int64_t t = blockIdx.x; t < total; t += gridDim.x) {
 		const int ty = (int)(t / tiles_x), tx = (int)(t - (int64_t)ty * tiles_x);
 		sauvola_tile<ST_W>(src, h, w, src_pitch, dst, dst_pitch, ty * ST_H, tx * ST_W, win, kk, rr, smem_raw);
-	}
-}
-
-__device__ __forceinline__ int find_line_b(const int32_t *__restrict__ chunk_offsets, int n, int item) {
-	int lo = 0, hi = n;
-	while (hi - lo > 1) {
-		int mid = (lo + hi) >> 1;
-		if (__ldg(chunk_offsets + mid) <= item) lo = mid; else hi = mid;
-	}
-	return lo;
-}
-
-__global__ void __launch_bounds__(BTHREADS) og_sauvola_strips_kernel(
-	const uint8_t *__restrict__ gray, const int32_t *__restrict__ steps, const int64_t *__restrict__ pix_offsets,
-	const int32_t *__restrict__ chunk_offsets, int n, uint8_t *__restrict__ out, int64_t capacity, int win, double kk, double rr) {
-	extern __shared__ __align__(16) unsigned char smem_raw[];
-	const int total = __ldg(chunk_offsets + n);
-	for (int item = blockIdx.x; item < total; item += gridDim.x) {
-		const int li = find_line_b(chunk_offsets, n, item);
-		const int chunk = item - __ldg(chunk_offsets + li);
-		const int w = steps[2 * li], h = steps[2 * li + 1];
-		const int64_t off = pix_offsets[li];
-		if (off + (int64_t)w * h > capacity) continue;
-		for (int ty0 = 0; ty0 < h; ty0 += ST_H)
-			sauvola_tile<ST_WS>(gray + off, h, w, w, out + off, w, ty0, chunk * ST_WS, win, kk, rr, smem_raw);
 	}
 }
 
