@@ -528,7 +528,7 @@ def run_ours(args):
 			"ms_per_step": 1e3 * s_e2e, "api": "PagePipeline(line_height, binarize, depth=3).run(jobs): pinned host arrays in, host arrays out, three pages in flight",
 			"per_page_api": {"value": world * mp_page / s_page, "ms_per_step": 1e3 * s_page,
 				"h2d_bytes_per_step": int(h2d_p), "d2h_bytes_per_step": int(d2h_p),
-				"api": "Page(ndarray, Grid).dewarped + LineExtractor.extract_arrays(lines), one page at a time"}}
+				"api": "Page(ndarray, Grid).dewarped + LineExtractor.extract_arrays(lines), one page at a time (all strips in host memory; the view of a strip is made when it is read)"}}
 		# the OCR stage's configuration (strips only, no dewarped page produced): reported beside the
 		# headline, not instead of it -- the metric's work includes the page remap
 		s_ocr, h2d_o, d2h_o = run_e2e_pipeline(args, inputs, device, 4 * args.e2e_steps, dewarped=False)

@@ -4,6 +4,7 @@ origami/batch/core/lines.py:51-149.  The reference maps Line.image over a Thread
 here every line of the page goes through one batched kernel launch.
 """
 
+import collections.abc
 import logging
 
 import PIL.Image
@@ -45,6 +46,25 @@ class LineRewriter:
 		return line_parts
 
 
+class _PathStrips(collections.abc.Sequence):
+	"""[(line_path, strip)] over the packed strips of a page: the strips are already in host memory, the
+	(ysteps, xsteps) view of one is only made when that item is read."""
+
+	def __init__(self, paths, strips):
+		self._paths, self._strips = paths, strips
+
+	def __len__(self):
+		return len(self._paths)
+
+	def __getitem__(self, i):
+		if isinstance(i, slice):
+			return [self[k] for k in range(*i.indices(len(self)))]
+		return self._paths[i], self._strips[i]
+
+	def __iter__(self):
+		return zip(self._paths, self._strips)
+
+
 class LineExtractor:
 	def __init__(self, tables, line_height, options, min_confidence=0.5):
 		self._options = options
@@ -77,7 +97,8 @@ class LineExtractor:
 		return self._rewriter(filtered_lines)
 
 	def extract_arrays(self, lines, ignored=None):
-		"""[(line_path, uint8 ndarray)] -- the batched fast path."""
+		"""Sequence of (line_path, uint8 ndarray) -- the batched fast path; every strip is in host memory when
+		this returns, the ndarray view of one is made when the item is read."""
 		line_parts = self._filtered_parts(lines, ignored)
 		if not line_parts:
 			return []
@@ -99,7 +120,7 @@ class LineExtractor:
 			records = [line.record(ysteps=self._line_height, column=column) for _, line, column in line_parts]
 		spec = self._binarizer.spec if self._binarizer is not None else None
 		strips, _ = extract_strips(dewarper, records, binarize=spec)
-		return [(part[0], strip) for part, strip in zip(line_parts, strips)]
+		return _PathStrips([part[0] for part in line_parts], strips)
 
 	def extract_device(self, lines, ignored=None, min_width=6, min_height=6, pad_value=0):
 		"""The OCR stage's hand-off without the host round trip (reference origami/batch/detect/ocr.py:
