@@ -235,7 +235,11 @@ def pack_lines(records):
 
 def pack_line_arrays(p, right, up, xsteps=0, ysteps=0, xres=1.0, yres=1.0):
 	"""Vectorised pack_lines for un-clipped lines: p, right, up are (n, 2) float64 arrays."""
-	p = np.asarray(p, dtype=np.float64).reshape(-1, 2)
+	def table(v):  # a list of n (2,) arrays is converted once (np.concatenate is the cheap way through such a list)
+		if isinstance(v, np.ndarray):
+			return np.asarray(v, dtype=np.float64).reshape(-1, 2)
+		return np.concatenate(v).astype(np.float64, copy=False).reshape(-1, 2) if len(v) else np.zeros((0, 2))
+	p, right, up = table(p), table(right), table(up)
 	a = np.zeros(p.shape[0], dtype=LINE_DTYPE)
 	a["p"] = p
 	a["cp"] = p
